@@ -1,0 +1,161 @@
+/* indy7_b200.h — C ABI of the B200-native SQP-MPC solve loop (drop-in for the hot path of A2R-Lab/indy7-mpc).
+ *
+ * Boundary being replaced (reference file:line, relative to the reference checkout):
+ *   src/osqp_solver.py:7-46    OSQPSolver.__init__            -> i7_create / i7_set_weights
+ *   src/osqp_solver.py:70-101  compute_dynamics_jacobians /
+ *                              update_constraint_matrix        -> i7_dump_qp (Adata, l), i7_dynamics
+ *   src/osqp_solver.py:103-135 update_cost_matrix              -> i7_dump_qp (Pdata, g)
+ *   src/osqp_solver.py:137-143 setup_and_solve_qp (osqp.solve) -> i7_solve_qp
+ *   src/osqp_solver.py:146-155 eepos / d_eepos                 -> i7_eepos
+ *   src/osqp_sqp.py:13-47      eepos_cost / integrator_err     -> i7_merit
+ *   src/osqp_sqp.py:49-74      linesearch                      -> i7_linesearch
+ *   src/osqp_sqp.py:76-93      sqp                             -> i7_solve
+ *   src/utils.py:3-18          rk4 (plant step)                -> i7_sim_forward
+ *   bindings.batch_sqp.SQPSolverfloat_<B> (binary absent; call sites gato_controller.py:53-138,
+ *   src/gato_mpc_batch.py:14-55): solve / reset / resetRho / resetLambda / set_external_wrench_batch /
+ *   sim_forward                                                -> i7_solve / i7_reset* / i7_set_external_wrench /
+ *                                                                 i7_sim_forward
+ *   native handle precedent: indy7-sdk/src/trajopt/include/trajopt_solver.cuh:8-226 (TrajoptSolver owns the
+ *   device workspaces; caller owns inputs/outputs)            -> i7_handle
+ *
+ * Conventions
+ *   - plain C, no torch / C++ types; every function returns an i7_status (0 = OK) and never throws.
+ *   - a handle is bound to one CUDA device, one arithmetic type (dtype) and a maximum batch; it is not
+ *     re-entrant.  Distinct handles may be used from distinct threads / streams.
+ *   - every data pointer may be HOST or DEVICE memory (queried with cudaPointerGetAttributes).  Element
+ *     type = the handle's dtype (double for I7_F64, float for I7_F32), C-contiguous, row = one problem.
+ *     With device pointers a call is asynchronous on `stream`; with host pointers the library stages through
+ *     its own pinned buffers and returns after the results are in the caller's memory.
+ *   - trajectory layout (src/osqp_solver.py:22,88-91): XU = [x_0 u_0 x_1 u_1 ... x_{N-1}], x = [q(6) v(6)],
+ *     length 18N-6.  Goals: N knots of `goal_stride` numbers (3 = [x y z]; 6 = GATO format [x y z 0 0 0],
+ *     src/gato_mpc_batch.py:80-88), only the first three of each knot are read.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ */
+#ifndef INDY7_B200_H
+#define INDY7_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define I7_NJ 6            /* joints (nq = nv = nu) */
+#define I7_NX 12
+#define I7_NXU 18
+#define I7_MAX_QP 2        /* src/osqp_sqp.py:77  `for qp in range(2)` */
+#define I7_NALPHA 8        /* src/osqp_sqp.py:58  alphas 1, 1/2, ..., 1/128 */
+#define I7_STATS_LEN 8
+
+typedef enum {
+    I7_OK = 0,
+    I7_ERR_INVALID = 1,     /* bad argument / shape */
+    I7_ERR_CUDA = 2,        /* CUDA runtime error; text in i7_last_error */
+    I7_ERR_NOMEM = 3,
+    I7_ERR_UNSUPPORTED = 4
+} i7_status;
+
+typedef enum { I7_F64 = 0, I7_F32 = 1 } i7_dtype;
+
+/* Robot constants of a serial chain of I7_NJ revolute-z joints (what pin.buildModelsFromUrdf yields for
+ * description/indy7.urdf:64-245).  Always doubles, converted to the handle dtype at create time. */
+typedef struct {
+    double R[I7_NJ][9];     /* joint placement rotation, row-major, parent <- joint frame (Rz(yaw)Ry(pitch)Rx(roll)) */
+    double p[I7_NJ][3];     /* joint placement translation in the parent frame */
+    double mass[I7_NJ];
+    double com[I7_NJ][3];   /* centre of mass in the link frame */
+    double Ic[I7_NJ][9];    /* rotational inertia about the COM, link frame, row-major */
+    double gravity[3];      /* world gravity, default (0, 0, -9.81) */
+} i7_model;
+
+typedef struct {
+    int32_t N;              /* knot points (32 in the drivers, 64 in gato_controller.py:314, 128 in trajopt_node.cu:178) */
+    int32_t batch;          /* maximum number of independent problems per call */
+    int32_t dtype;          /* i7_dtype */
+    int32_t device;         /* CUDA device ordinal */
+    double dt;              /* src/osqp_solver.py:7 defaults: 0.01 */
+    double dQ_cost;         /* 0.01  */
+    double R_cost;          /* 1e-5  */
+    double QN_cost;         /* 100   */
+    double eps;             /* 1     */
+    int32_t regularize;     /* 1     */
+    int32_t max_qp;         /* outer SQP iterations, <= I7_MAX_QP (reference: 2) */
+    double mu;              /* merit penalty, src/osqp_sqp.py:50: 10 */
+    double step_tol;        /* src/osqp_sqp.py:90: 1e-3 */
+    int32_t threads;        /* CTA size: 0 = choose from batch (256 for latency, 128 for throughput) */
+    int32_t reserved;
+    i7_model model;
+} i7_config;
+
+/* Per-problem statistics record written by i7_solve: I7_STATS_LEN numbers of the handle dtype.
+ *   [0] qp_iters        what src/osqp_sqp.py:92 appends (qp+1)
+ *   [1] n_linesearch    number of line searches run (= alphas appended, src/osqp_sqp.py:73)
+ *   [2] n_steps         number of accepted steps (= stepsizes appended, src/osqp_sqp.py:88)
+ *   [3] status          0 ok, 1 = a line search failed (alpha 0, not an error: src/osqp_sqp.py:72,81-82),
+ *                       2 = non-finite value met
+ *   [4],[5] alpha of line search 0 / 1 (0 when failed or not run)
+ *   [6],[7] 2-norm of accepted step 0 / 1 (0 when absent)                                         */
+
+typedef struct i7_handle i7_handle;
+
+const char* i7_version(void);
+void i7_default_config(i7_config* cfg);         /* reference defaults, N=32, batch=1, f64, Indy7 model zeroed */
+i7_status i7_create(const i7_config* cfg, i7_handle** out);
+void i7_destroy(i7_handle* h);
+const char* i7_last_error(const i7_handle* h);  /* h may be NULL: last create error */
+
+i7_status i7_set_weights(i7_handle* h, double dQ_cost, double R_cost, double QN_cost, int32_t regularize, double eps);
+/* f_ext: batch x 6 DOUBLES on the host, Pinocchio order [fx fy fz tx ty tz], expressed in the local frame of
+ * the last joint (src/gato_mpc_batch_sample.py:97-101,158); NULL clears. */
+i7_status i7_set_external_wrench(i7_handle* h, const double* f_ext, int32_t batch);
+/* Kept for bindings.batch_sqp compatibility.  The direct QP solve carries no warm-start state, so these only
+ * clear the statistics counters. */
+i7_status i7_reset(i7_handle* h);
+i7_status i7_reset_rho(i7_handle* h);
+i7_status i7_reset_lambda(i7_handle* h);
+
+/* One SQP solve per problem (src/osqp_sqp.py:76-93): xu_out[b] = sqp(x0[b], goals[b], xu_in[b]).
+ * xu_in/xu_out: batch x (18N-6); x0: batch x 12; goals: batch x (N*goal_stride); stats: batch x I7_STATS_LEN
+ * (may be NULL).  xu_out may alias xu_in. */
+i7_status i7_solve(i7_handle* h, int32_t batch, const void* xu_in, const void* x0, const void* goals,
+                   int32_t goal_stride, void* xu_out, void* stats, void* stream);
+
+/* Device-time of the latest i7_solve kernel in microseconds (CUDA events on the launch stream; blocks). */
+i7_status i7_last_solve_time_us(i7_handle* h, double* us);
+/* Number of kernel launches issued by this handle so far. */
+int64_t i7_launch_count(const i7_handle* h);
+
+/* One rk4 plant step of length dt per lane under that lane's external wrench (src/utils.py:3-18):
+ * x, u: batch x 12 / batch x 6 (or a single row broadcast to every lane when bcast != 0); out: batch x 12. */
+i7_status i7_sim_forward(i7_handle* h, int32_t batch, const void* x, const void* u, double dt, int32_t bcast,
+                         void* x_next, void* stream);
+
+/* ---- stage-level entry points (parity tests and debugging; same device code as i7_solve) ---- */
+/* The full-step QP solution `setup_and_solve_qp(xu, x0, goals).x` (src/osqp_solver.py:137-143). */
+i7_status i7_solve_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,
+                      int32_t goal_stride, void* z_out, void* stream);
+/* The QP data in the reference's CSC value order, per problem:
+ * Adata: 360(N-1)+144, Pdata: 33N-6... (N*27 + (N-1)*6), g: 18N-6, l: 12N.  Any pointer may be NULL. */
+i7_status i7_dump_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,
+                     int32_t goal_stride, void* Adata, void* Pdata, void* g, void* l, void* stream);
+/* merit terms of one trajectory against a reference iterate: out[b] = {qcost, vcost, ucost, integrator_err,
+ * ||xu[:12]-xu_ref[:12]||, merit} (src/osqp_sqp.py:13-47,52-56). */
+i7_status i7_merit(i7_handle* h, int32_t batch, const void* xu, const void* xu_ref, const void* goals,
+                   int32_t goal_stride, void* out6, void* stream);
+/* line search (src/osqp_sqp.py:49-74): alpha[b] and merits[b] = {base, merit(alpha_1..alpha_8)} (all nine
+ * are evaluated; the accepted alpha is the first with merit <= base). */
+i7_status i7_linesearch(i7_handle* h, int32_t batch, const void* xu, const void* xu_full, const void* goals,
+                        int32_t goal_stride, void* alpha, void* merits9, void* stream);
+/* Forward dynamics and its analytic derivatives at n samples (pin.computeABADerivatives,
+ * src/osqp_solver.py:71): q, v, tau: n x 6; outputs (any may be NULL) qdd: n x 6; dqdd_dq, dqdd_dv, Minv:
+ * n x 36 row-major.  f_ext (n x 6, Pinocchio order, handle dtype) may be NULL. */
+i7_status i7_dynamics(i7_handle* h, int32_t n, const void* q, const void* v, const void* tau, const void* f_ext,
+                      void* qdd, void* dqdd_dq, void* dqdd_dv, void* Minv, void* stream);
+/* End-effector position and translational Jacobian (src/osqp_solver.py:146-155): q: n x 6 -> p: n x 3,
+ * J: n x 18 row-major (3 x 6).  J may be NULL. */
+i7_status i7_eepos(i7_handle* h, int32_t n, const void* q, void* p, void* J, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* INDY7_B200_H */

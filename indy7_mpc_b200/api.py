@@ -1,0 +1,99 @@
+"""North-star facade: ``Indy7SQP(urdf, N, weights...).solve(x0, xref) -> (x_traj, u_traj, stats)``.
+
+A thin layer over the same C-ABI call the reference-shaped classes use (``i7_solve`` = ``SQP_OSQP.sqp``,
+src/osqp_sqp.py:76-93), batched over independent problems.  Warm start = the previous solution of the same lane
+(the reference drivers pass the shifted previous trajectory, src/osqp_mpc.py:46,65-70); the QP solve itself is
+direct and carries no hidden state.
+"""
+import numpy as np
+
+from .engine import Engine, _is_torch
+from .model import RobotModel, build_model_from_urdf
+
+try:
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+class Indy7SQP:
+    def __init__(self, urdf=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
+                 dtype="fp64", device="cuda", batch=1, threads=0):
+        if isinstance(urdf, RobotModel):
+            self.model = urdf
+        else:
+            self.model = build_model_from_urdf(urdf) if urdf else build_model_from_urdf()
+        if isinstance(device, str):
+            if not device.startswith("cuda"):
+                raise ValueError("indy7_mpc_b200 runs on CUDA devices only (no CPU fallback)")
+            device = int(device.split(":")[1]) if ":" in device else 0
+        self.N, self.dt, self.batch, self.dtype = int(N), float(dt), int(batch), dtype
+        self.nz = 18 * self.N - 6
+        self.engine = Engine(self.model, N=N, dt=dt, dQ_cost=dQ_cost, R_cost=R_cost, QN_cost=QN_cost,
+                             regularize=regularize, eps=eps, batch=batch, dtype=dtype, device=device, threads=threads)
+        self._warm = None
+
+    def reset(self):
+        self._warm = None
+        self.engine.reset()
+
+    def set_external_wrench(self, f_ext):
+        self.engine.set_external_wrench(f_ext)
+
+    def _goals(self, xref, B):
+        shp = tuple(xref.shape)
+        n = int(np.prod(shp))
+        per = n // B if n % B == 0 and len(shp) > 1 and shp[0] == B and n // B in (3 * self.N, 6 * self.N) else n
+        if per in (3 * self.N, 6 * self.N) and n == per * B:
+            return xref.reshape(B, per)
+        if n in (3 * self.N, 6 * self.N):          # one reference shared by every problem
+            flat = xref.reshape(1, n)
+            return flat.expand(B, n) if _is_torch(flat) else np.broadcast_to(flat, (B, n))
+        raise ValueError(f"xref must hold N x 3 or N x 6 numbers (optionally with a leading batch dim), got {shp}")
+
+    def solve(self, x0, xref, xu_init=None):
+        """x0: (12,) or (B,12); xref: (N,3) | (3N,) | (N,6) | (6N,) optionally batched; returns
+        (x_traj (...,N,12), u_traj (...,N-1,6), stats dict).  Inputs are never modified."""
+        tens = _is_torch(x0)
+        x0a = x0 if tens else np.asarray(x0, float)
+        batched = x0a.ndim == 2
+        B = x0a.shape[0] if batched else 1
+        if x0a.shape[-1] != 12 or B > self.batch:
+            raise ValueError(f"x0 must be (12,) or (B<= {self.batch}, 12)")
+        x0a = x0a.reshape(B, 12)
+        xr = xref if _is_torch(xref) else np.asarray(xref, float)
+        goals = self._goals(xr, B)
+        if tens and not _is_torch(goals):
+            goals = torch.as_tensor(np.ascontiguousarray(goals), device=x0a.device)
+        if xu_init is not None:
+            xu = xu_init if _is_torch(xu_init) else np.asarray(xu_init, float)
+            xu = xu.reshape(B, self.nz)
+        elif self._warm is not None and self._warm.shape[0] == B and _is_torch(self._warm) == tens:
+            xu = self._warm
+        else:
+            if tens:
+                xu = torch.zeros(B, self.nz, dtype=x0a.dtype, device=x0a.device)
+            else:
+                xu = np.zeros((B, self.nz))
+            xu[:, :12] = x0a
+        if tens and goals.is_cuda != x0a.is_cuda:
+            goals = goals.to(x0a.device)
+        if tens:
+            goals = goals.contiguous()
+        out, st = self.engine.solve(xu, x0a, goals)
+        self._warm = out
+        if tens:
+            pad = torch.cat([out, out.new_zeros(B, 6)], dim=1).reshape(B, self.N, 18)
+        else:
+            pad = np.concatenate([out, np.zeros((B, 6), out.dtype)], axis=1).reshape(B, self.N, 18)
+        x_traj, u_traj = pad[:, :, :12], pad[:, :-1, 12:]
+        stn = st.cpu().numpy() if _is_torch(st) else st
+        stats = {
+            'qp_iters': stn[:, 0].astype(int), 'n_linesearch': stn[:, 1].astype(int), 'n_steps': stn[:, 2].astype(int),
+            'status': stn[:, 3].astype(int), 'linesearch_alphas': stn[:, 4:6].copy(), 'sqp_stepsizes': stn[:, 6:8].copy(),
+            'xu': out if batched else out[0],
+        }
+        if not batched:
+            x_traj, u_traj = x_traj[0], u_traj[0]
+            stats = {k: (v[0] if k != 'xu' else v) for k, v in stats.items()}
+        return x_traj, u_traj, stats

@@ -1,0 +1,489 @@
+// i7_api.cu — C ABI of the B200-native SQP-MPC solve loop (see include/indy7_b200.h for the boundary).
+#include "../../include/indy7_b200.h"
+#undef I7_NJ
+#include "i7_sqp.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct Arena {           // a device buffer with a pinned host mirror
+    void* dev = nullptr;
+    void* host = nullptr;
+    size_t bytes = 0;
+};
+
+}  // namespace
+
+struct i7_handle {
+    i7_config cfg;
+    int esize = 8;
+    size_t nz = 0;
+    i7::Robot<double> rob64;
+    i7::Robot<float> rob32;
+    Arena in, out;               // packed inputs / outputs for host-pointer calls
+    void* d_fext = nullptr;      // batch x 6, Featherstone order, handle dtype
+    bool has_fext = false;
+    void* d_spill = nullptr;     // gains/z region when it does not fit shared memory
+    bool spill = false;
+    int smem_bytes = 0;
+    int threads = 0;
+    int max_smem_optin = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    int64_t launches = 0;
+    std::string err;
+};
+
+namespace {
+
+#define I7_CUDA(h, call)                                                                         \
+    do {                                                                                         \
+        cudaError_t e_ = (call);                                                                 \
+        if (e_ != cudaSuccess) {                                                                 \
+            (h)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                       \
+            return I7_ERR_CUDA;                                                                  \
+        }                                                                                        \
+    } while (0)
+
+template <typename T>
+void fill_robot(const i7_model& m, i7::Robot<T>& r) {
+    for (int i = 0; i < 6; ++i) {
+        for (int a = 0; a < 9; ++a) r.R[i][a] = T(m.R[i][a]);
+        for (int a = 0; a < 3; ++a) { r.p[i][a] = T(m.p[i][a]); r.h[i][a] = T(m.mass[i] * m.com[i][a]); }
+        r.m[i] = T(m.mass[i]);
+        // Ib = Ic + m (c.c I - c c')
+        const double* c = m.com[i];
+        const double cc = c[0] * c[0] + c[1] * c[1] + c[2] * c[2];
+        double Ib[3][3];
+        for (int a = 0; a < 3; ++a)
+            for (int b = 0; b < 3; ++b)
+                Ib[a][b] = m.Ic[i][3 * a + b] + m.mass[i] * ((a == b ? cc : 0.0) - c[a] * c[b]);
+        r.Ib[i][0] = T(Ib[0][0]); r.Ib[i][1] = T(Ib[0][1]); r.Ib[i][2] = T(Ib[0][2]);
+        r.Ib[i][3] = T(Ib[1][1]); r.Ib[i][4] = T(Ib[1][2]); r.Ib[i][5] = T(Ib[2][2]);
+    }
+    for (int a = 0; a < 3; ++a) r.g[a] = T(m.gravity[a]);
+}
+
+bool is_device_ptr(const void* p) {
+    if (!p) return false;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+i7_status arena_reserve(i7_handle* h, Arena& a, size_t bytes) {
+    if (bytes <= a.bytes) return I7_OK;
+    if (a.dev) cudaFree(a.dev);
+    if (a.host) cudaFreeHost(a.host);
+    a.dev = a.host = nullptr; a.bytes = 0;
+    I7_CUDA(h, cudaMalloc(&a.dev, bytes));
+    I7_CUDA(h, cudaMallocHost(&a.host, bytes));
+    a.bytes = bytes;
+    return I7_OK;
+}
+
+// One staged input: either the caller's device pointer, or a slice of the input arena filled from host memory.
+struct Stage {
+    size_t in_off = 0, out_off = 0;
+    i7_handle* h;
+    explicit Stage(i7_handle* h_) : h(h_) {}
+    // returns the device pointer to use; host data is packed into the pinned arena (copied to the device by flush_in)
+    const void* in(const void* p, size_t bytes) {
+        if (!p) return nullptr;
+        if (is_device_ptr(p)) return p;
+        std::memcpy((char*)h->in.host + in_off, p, bytes);
+        const void* d = (char*)h->in.dev + in_off;
+        in_off += (bytes + 15) & ~size_t(15);
+        return d;
+    }
+    struct Out { void* user; size_t off; size_t bytes; };
+    Out outs[8];
+    int nout = 0;
+    void* out(void* p, size_t bytes) {
+        if (!p) return nullptr;
+        if (is_device_ptr(p)) return p;
+        outs[nout++] = Out{p, out_off, bytes};
+        void* d = (char*)h->out.dev + out_off;
+        out_off += (bytes + 15) & ~size_t(15);
+        return d;
+    }
+    i7_status flush_in(cudaStream_t s) {
+        if (in_off) I7_CUDA(h, cudaMemcpyAsync(h->in.dev, h->in.host, in_off, cudaMemcpyHostToDevice, s));
+        return I7_OK;
+    }
+    i7_status flush_out(cudaStream_t s) {
+        if (!nout) return I7_OK;
+        I7_CUDA(h, cudaMemcpyAsync(h->out.host, h->out.dev, out_off, cudaMemcpyDeviceToHost, s));
+        I7_CUDA(h, cudaStreamSynchronize(s));
+        for (int i = 0; i < nout; ++i) std::memcpy(outs[i].user, (char*)h->out.host + outs[i].off, outs[i].bytes);
+        return I7_OK;
+    }
+};
+
+template <typename T> const i7::Robot<T>& get_rob(const i7_handle* h);
+template <> const i7::Robot<double>& get_rob<double>(const i7_handle* h) { return h->rob64; }
+template <> const i7::Robot<float>& get_rob<float>(const i7_handle* h) { return h->rob32; }
+
+template <typename T, int NT>
+i7_status launch_sqp_nt(i7_handle* h, const i7::Robot<T>& rob, const i7::SolveParams<T>& P, cudaStream_t s) {
+    i7::sqp_kernel<T, NT><<<P.batch, NT, h->smem_bytes, s>>>(rob, P);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return I7_OK;
+}
+
+template <typename T, int NT>
+cudaError_t allow_big_smem(int bytes) {
+    return cudaFuncSetAttribute(i7::sqp_kernel<T, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+template <typename T>
+i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& P, cudaStream_t s) {
+    P.spill_ws = h->spill ? (T*)h->d_spill : nullptr;
+    if (h->threads == 256) return launch_sqp_nt<T, 256>(h, rob, P, s);
+    return launch_sqp_nt<T, 128>(h, rob, P, s);
+}
+
+template <typename T>
+void base_params(const i7_handle* h, i7::SolveParams<T>& P, int batch, int goal_stride, int mode) {
+    std::memset(&P, 0, sizeof(P));
+    const i7_config& c = h->cfg;
+    P.N = c.N; P.batch = batch; P.goal_stride = goal_stride; P.mode = mode;
+    P.max_qp = c.max_qp; P.regularize = c.regularize;
+    P.dt = T(c.dt); P.dQ = T(c.dQ_cost); P.R = T(c.R_cost); P.QN = T(c.QN_cost); P.eps = T(c.eps);
+    P.mu = T(c.mu); P.step_tol = T(c.step_tol);
+    P.fext = h->has_fext ? (const T*)h->d_fext : nullptr;
+}
+
+i7_status check_batch(i7_handle* h, int batch, int goal_stride) {
+    if (!h) return I7_ERR_INVALID;
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    if (goal_stride != 3 && goal_stride != 6) { h->err = "goal_stride must be 3 or 6"; return I7_ERR_INVALID; }
+    return I7_OK;
+}
+
+// generic driver for every mode of the fused kernel
+struct SqpCall {
+    int mode, batch, goal_stride;
+    const void *xu, *x0, *goals, *xu_full;
+    void *xu_out, *stats, *z_out, *Adata, *Pdata, *g, *l, *alpha, *merits;
+};
+
+template <typename T>
+i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s) {
+    const int N = h->cfg.N;
+    const size_t nz = h->nz, B = c.batch, es = sizeof(T);
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    Stage st(h);
+    i7::SolveParams<T> P;
+    base_params<T>(h, P, c.batch, c.goal_stride, c.mode);
+    P.xu_in = (const T*)st.in(c.xu, B * nz * es);
+    P.x0 = (const T*)st.in(c.x0, B * 12 * es);
+    P.goals = (const T*)st.in(c.goals, B * N * c.goal_stride * es);
+    P.xu_full = (const T*)st.in(c.xu_full, B * nz * es);
+    P.xu_out = (T*)st.out(c.xu_out, B * nz * es);
+    P.stats = (T*)st.out(c.stats, B * I7_STATS_LEN * es);
+    P.z_out = (T*)st.out(c.z_out, B * nz * es);
+    P.Adata = (T*)st.out(c.Adata, B * (360 * (N - 1) + 144) * es);
+    P.Pdata = (T*)st.out(c.Pdata, B * (27 * N + 6 * (N - 1)) * es);
+    P.g = (T*)st.out(c.g, B * nz * es);
+    P.l = (T*)st.out(c.l, B * 12 * N * es);
+    P.alpha_out = (T*)st.out(c.alpha, B * es);
+    P.merits_out = (T*)st.out(c.merits, B * (c.mode == i7::MODE_MERIT ? 6 : 9) * es);
+    i7_status rc = st.flush_in(s);
+    if (rc) return rc;
+    if (c.mode == i7::MODE_SOLVE) I7_CUDA(h, cudaEventRecord(h->ev0, s));
+    rc = launch_sqp<T>(h, get_rob<T>(h), P, s);
+    if (rc) return rc;
+    if (c.mode == i7::MODE_SOLVE) { I7_CUDA(h, cudaEventRecord(h->ev1, s)); h->timed = true; }
+    return st.flush_out(s);
+}
+
+i7_status run_sqp(i7_handle* h, const SqpCall& c, void* stream) {
+    i7_status rc = check_batch(h, c.batch, c.goal_stride);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64 ? run_sqp_t<double>(h, c, s) : run_sqp_t<float>(h, c, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* i7_version(void) { return "indy7_b200 0.1.0 (sm_100a)"; }
+
+void i7_default_config(i7_config* cfg) {
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->N = 32; cfg->batch = 1; cfg->dtype = I7_F64; cfg->device = 0;
+    cfg->dt = 0.01; cfg->dQ_cost = 0.01; cfg->R_cost = 1e-5; cfg->QN_cost = 100.0; cfg->eps = 1.0;
+    cfg->regularize = 1; cfg->max_qp = 2; cfg->mu = 10.0; cfg->step_tol = 1e-3; cfg->threads = 0;
+    cfg->model.gravity[2] = -9.81;
+}
+
+const char* i7_last_error(const i7_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+void i7_destroy(i7_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    if (h->in.dev) cudaFree(h->in.dev);
+    if (h->in.host) cudaFreeHost(h->in.host);
+    if (h->out.dev) cudaFree(h->out.dev);
+    if (h->out.host) cudaFreeHost(h->out.host);
+    if (h->d_fext) cudaFree(h->d_fext);
+    if (h->d_spill) cudaFree(h->d_spill);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    delete h;
+}
+
+i7_status i7_create(const i7_config* cfg, i7_handle** out) {
+    if (!cfg || !out) { g_create_error = "null argument"; return I7_ERR_INVALID; }
+    *out = nullptr;
+    if (cfg->N < 2 || cfg->N > 512 || cfg->batch < 1 || (cfg->dtype != I7_F64 && cfg->dtype != I7_F32) ||
+        cfg->max_qp < 1 || cfg->max_qp > I7_MAX_QP || !(cfg->dt > 0)) {
+        g_create_error = "invalid configuration (N in [2,512], batch >= 1, dtype f64|f32, max_qp in [1,2], dt > 0)";
+        return I7_ERR_INVALID;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                         " (indy7_b200 has no CPU fallback)";
+        cudaGetLastError();
+        return I7_ERR_CUDA;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "device ordinal out of range"; return I7_ERR_INVALID; }
+    i7_handle* h = new i7_handle();
+    h->cfg = *cfg;
+    h->esize = cfg->dtype == I7_F64 ? 8 : 4;
+    h->nz = 18 * (size_t)cfg->N - 6;
+    fill_robot<double>(cfg->model, h->rob64);
+    fill_robot<float>(cfg->model, h->rob32);
+    auto fail = [&](i7_status rc) { g_create_error = h->err; i7_destroy(h); return rc; };
+#define I7_TRY(call) do { i7_status rc_ = (call); if (rc_) return fail(rc_); } while (0)
+#define I7_CUDA_C(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(I7_ERR_CUDA); } } while (0)
+    I7_CUDA_C(cudaSetDevice(cfg->device));
+    I7_CUDA_C(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
+    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 296 ? 256 : 128);
+    if (h->threads != 128 && h->threads != 256) { h->err = "threads must be 0, 128 or 256"; return fail(I7_ERR_INVALID); }
+    i7::Layout L = i7::make_layout(cfg->N, false);
+    h->spill = false;
+    if ((size_t)L.total * h->esize > (size_t)h->max_smem_optin) {
+        L = i7::make_layout(cfg->N, true);
+        h->spill = true;
+        if ((size_t)L.total * h->esize > (size_t)h->max_smem_optin) {
+            h->err = "horizon too long for the shared-memory layout of this dtype";
+            return fail(I7_ERR_UNSUPPORTED);
+        }
+        I7_CUDA_C(cudaMalloc(&h->d_spill, (size_t)cfg->batch * L.reg_size * h->esize));
+    }
+    h->smem_bytes = L.total * h->esize;
+    {
+        cudaError_t ea;
+        if (cfg->dtype == I7_F64) ea = h->threads == 256 ? allow_big_smem<double, 256>(h->max_smem_optin) : allow_big_smem<double, 128>(h->max_smem_optin);
+        else ea = h->threads == 256 ? allow_big_smem<float, 256>(h->max_smem_optin) : allow_big_smem<float, 128>(h->max_smem_optin);
+        if (ea != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea); return fail(I7_ERR_CUDA); }
+    }
+    const size_t B = cfg->batch, N = cfg->N, es = h->esize;
+    // worst case over all entry points: inputs xu, x0, goals(6), xu_full; outputs of the dump mode
+    const size_t in_bytes = B * (2 * h->nz + 12 + 6 * N) * es + 256;
+    const size_t out_bytes = B * ((360 * (N - 1) + 144) + (33 * N) + h->nz + 12 * N + h->nz + 64) * es + 256;
+    I7_TRY(arena_reserve(h, h->in, in_bytes));
+    I7_TRY(arena_reserve(h, h->out, out_bytes));
+    I7_CUDA_C(cudaMalloc(&h->d_fext, B * 6 * es));
+    I7_CUDA_C(cudaMemset(h->d_fext, 0, B * 6 * es));
+    I7_CUDA_C(cudaEventCreate(&h->ev0));
+    I7_CUDA_C(cudaEventCreate(&h->ev1));
+#undef I7_TRY
+#undef I7_CUDA_C
+    *out = h;
+    return I7_OK;
+}
+
+i7_status i7_set_weights(i7_handle* h, double dQ_cost, double R_cost, double QN_cost, int32_t regularize, double eps) {
+    if (!h) return I7_ERR_INVALID;
+    h->cfg.dQ_cost = dQ_cost; h->cfg.R_cost = R_cost; h->cfg.QN_cost = QN_cost;
+    h->cfg.regularize = regularize; h->cfg.eps = eps;
+    return I7_OK;
+}
+
+i7_status i7_set_external_wrench(i7_handle* h, const double* f_ext, int32_t batch) {
+    if (!h) return I7_ERR_INVALID;
+    if (!f_ext) { h->has_fext = false; return I7_OK; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    // Pinocchio [linear; angular] -> Featherstone [angular; linear], converted to the handle dtype
+    const size_t n = (size_t)batch * 6;
+    std::string buf(n * h->esize, '\0');
+    for (int b = 0; b < batch; ++b)
+        for (int a = 0; a < 6; ++a) {
+            const double v = f_ext[6 * b + (a < 3 ? a + 3 : a - 3)];
+            if (h->esize == 8) ((double*)buf.data())[6 * b + a] = v; else ((float*)buf.data())[6 * b + a] = (float)v;
+        }
+    I7_CUDA(h, cudaMemcpy(h->d_fext, buf.data(), buf.size(), cudaMemcpyHostToDevice));
+    h->has_fext = true;
+    return I7_OK;
+}
+
+i7_status i7_reset(i7_handle* h) { if (!h) return I7_ERR_INVALID; h->timed = false; return I7_OK; }
+i7_status i7_reset_rho(i7_handle* h) { return h ? I7_OK : I7_ERR_INVALID; }
+i7_status i7_reset_lambda(i7_handle* h) { return h ? I7_OK : I7_ERR_INVALID; }
+
+i7_status i7_solve(i7_handle* h, int32_t batch, const void* xu_in, const void* x0, const void* goals,
+                   int32_t goal_stride, void* xu_out, void* stats, void* stream) {
+    if (!h || !xu_in || !x0 || !goals || !xu_out) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    SqpCall c{};
+    c.mode = i7::MODE_SOLVE; c.batch = batch; c.goal_stride = goal_stride;
+    c.xu = xu_in; c.x0 = x0; c.goals = goals; c.xu_out = xu_out; c.stats = stats;
+    return run_sqp(h, c, stream);
+}
+
+i7_status i7_last_solve_time_us(i7_handle* h, double* us) {
+    if (!h || !us) return I7_ERR_INVALID;
+    if (!h->timed) { h->err = "no solve has been timed yet"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaEventSynchronize(h->ev1));
+    float ms = 0.f;
+    I7_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    *us = 1e3 * ms;
+    return I7_OK;
+}
+
+int64_t i7_launch_count(const i7_handle* h) { return h ? h->launches : 0; }
+
+i7_status i7_solve_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,
+                      int32_t goal_stride, void* z_out, void* stream) {
+    if (!h || !xu || !x0 || !goals || !z_out) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    SqpCall c{};
+    c.mode = i7::MODE_QP; c.batch = batch; c.goal_stride = goal_stride;
+    c.xu = xu; c.x0 = x0; c.goals = goals; c.z_out = z_out;
+    return run_sqp(h, c, stream);
+}
+
+i7_status i7_dump_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,
+                     int32_t goal_stride, void* Adata, void* Pdata, void* g, void* l, void* stream) {
+    if (!h || !xu || !x0 || !goals) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    SqpCall c{};
+    c.mode = i7::MODE_DUMP; c.batch = batch; c.goal_stride = goal_stride;
+    c.xu = xu; c.x0 = x0; c.goals = goals; c.Adata = Adata; c.Pdata = Pdata; c.g = g; c.l = l;
+    return run_sqp(h, c, stream);
+}
+
+i7_status i7_merit(i7_handle* h, int32_t batch, const void* xu, const void* xu_ref, const void* goals,
+                   int32_t goal_stride, void* out6, void* stream) {
+    if (!h || !xu || !xu_ref || !goals || !out6) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    SqpCall c{};
+    c.mode = i7::MODE_MERIT; c.batch = batch; c.goal_stride = goal_stride;
+    c.xu = xu; c.xu_full = xu_ref; c.goals = goals; c.merits = out6;
+    return run_sqp(h, c, stream);
+}
+
+i7_status i7_linesearch(i7_handle* h, int32_t batch, const void* xu, const void* xu_full, const void* goals,
+                        int32_t goal_stride, void* alpha, void* merits9, void* stream) {
+    if (!h || !xu || !xu_full || !goals || !alpha || !merits9) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    SqpCall c{};
+    c.mode = i7::MODE_LINESEARCH; c.batch = batch; c.goal_stride = goal_stride;
+    c.xu = xu; c.xu_full = xu_full; c.goals = goals; c.alpha = alpha; c.merits = merits9;
+    return run_sqp(h, c, stream);
+}
+
+}  // extern "C"
+
+namespace {
+template <typename T>
+i7_status dynamics_t(i7_handle* h, int n, const void* q, const void* v, const void* tau, const void* f_ext, void* qdd,
+                     void* dq, void* dv, void* minv, cudaStream_t s) {
+    const size_t es = sizeof(T);
+    const size_t need_in = (size_t)n * 24 * es + 256, need_out = (size_t)n * (6 + 108) * es + 256;
+    i7_status rc;
+    if ((rc = arena_reserve(h, h->in, need_in))) return rc;
+    if ((rc = arena_reserve(h, h->out, need_out))) return rc;
+    Stage st(h);
+    const T* dq_ = (const T*)st.in(q, n * 6 * es);
+    const T* dv_ = (const T*)st.in(v, n * 6 * es);
+    const T* dt_ = (const T*)st.in(tau, n * 6 * es);
+    const T* df_ = (const T*)st.in(f_ext, n * 6 * es);
+    T* o_qdd = (T*)st.out(qdd, n * 6 * es);
+    T* o_dq = (T*)st.out(dq, n * 36 * es);
+    T* o_dv = (T*)st.out(dv, n * 36 * es);
+    T* o_mi = (T*)st.out(minv, n * 36 * es);
+    if ((rc = st.flush_in(s))) return rc;
+    const auto& rob = get_rob<T>(h);
+    i7::dynamics_kernel<T><<<(n + 63) / 64, 64, 0, s>>>(rob, n, dq_, dv_, dt_, df_, o_qdd, o_dq, o_dv, o_mi);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
+
+template <typename T>
+i7_status eepos_t(i7_handle* h, int n, const void* q, void* p, void* J, cudaStream_t s) {
+    const size_t es = sizeof(T);
+    i7_status rc;
+    if ((rc = arena_reserve(h, h->in, (size_t)n * 6 * es + 256))) return rc;
+    if ((rc = arena_reserve(h, h->out, (size_t)n * 21 * es + 256))) return rc;
+    Stage st(h);
+    const T* dq_ = (const T*)st.in(q, n * 6 * es);
+    T* o_p = (T*)st.out(p, n * 3 * es);
+    T* o_J = (T*)st.out(J, n * 18 * es);
+    if ((rc = st.flush_in(s))) return rc;
+    const auto& rob = get_rob<T>(h);
+    i7::eepos_kernel<T><<<(n + 127) / 128, 128, 0, s>>>(rob, n, dq_, o_p, o_J);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
+
+template <typename T>
+i7_status sim_forward_t(i7_handle* h, int batch, const void* x, const void* u, double dt, int bcast, void* x_next,
+                        cudaStream_t s) {
+    const size_t es = sizeof(T);
+    Stage st(h);
+    const size_t rows = bcast ? 1 : batch;
+    const T* dx = (const T*)st.in(x, rows * 12 * es);
+    const T* du = (const T*)st.in(u, rows * 6 * es);
+    T* o = (T*)st.out(x_next, (size_t)batch * 12 * es);
+    i7_status rc;
+    if ((rc = st.flush_in(s))) return rc;
+    const auto& rob = get_rob<T>(h);
+    i7::sim_forward_kernel<T><<<(batch + 63) / 64, 64, 0, s>>>(rob, batch, dx, du, bcast,
+                                                               h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
+}  // namespace
+
+extern "C" {
+
+i7_status i7_dynamics(i7_handle* h, int32_t n, const void* q, const void* v, const void* tau, const void* f_ext,
+                      void* qdd, void* dqdd_dq, void* dqdd_dv, void* Minv, void* stream) {
+    if (!h || n < 1 || !q || !v || !tau) { if (h) h->err = "bad argument"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64 ? dynamics_t<double>(h, n, q, v, tau, f_ext, qdd, dqdd_dq, dqdd_dv, Minv, s)
+                                  : dynamics_t<float>(h, n, q, v, tau, f_ext, qdd, dqdd_dq, dqdd_dv, Minv, s);
+}
+
+i7_status i7_eepos(i7_handle* h, int32_t n, const void* q, void* p, void* J, void* stream) {
+    if (!h || n < 1 || !q || !p) { if (h) h->err = "bad argument"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64 ? eepos_t<double>(h, n, q, p, J, s) : eepos_t<float>(h, n, q, p, J, s);
+}
+
+i7_status i7_sim_forward(i7_handle* h, int32_t batch, const void* x, const void* u, double dt, int32_t bcast,
+                         void* x_next, void* stream) {
+    if (!h || !x || !u || !x_next) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64 ? sim_forward_t<double>(h, batch, x, u, dt, bcast, x_next, s)
+                                  : sim_forward_t<float>(h, batch, x, u, dt, bcast, x_next, s);
+}
+
+}  // extern "C"

@@ -1,0 +1,801 @@
+// i7_sqp.cuh — the fused SQP-MPC solve kernel: one CTA per independent problem, everything between the
+// input trajectory and the output trajectory stays in shared memory / registers.
+//
+// Phases per SQP iteration (reference call stack: src/osqp_sqp.py:76-93):
+//   setup     per-knot FK + cost terms, ABA, M^-1 columns, analytic dID columns, -M^-1 dID  (src/osqp_solver.py:70-135)
+//   riccati   exact solve of the equality-constrained QP  min 1/2 z'Pz + g'z  s.t.  Az = l  by a backward
+//             block recursion over the knots (block LDL' of the block-tridiagonal KKT system in stage order,
+//             12x12 / 6x6 blocks) and a forward roll-out                                   (src/osqp_solver.py:137-143)
+//   merit     all nine line-search candidates (base + 8 alphas) x N knots in parallel     (src/osqp_sqp.py:13-74)
+//   update    first-accept alpha selection, XU += alpha (z - XU), statistics              (src/osqp_sqp.py:80-92)
+#pragma once
+#include "i7_rbd.cuh"
+
+namespace i7 {
+
+enum Mode : int {
+    MODE_SOLVE = 0,       // full sqp()
+    MODE_QP = 1,          // z = setup_and_solve_qp(xu).x
+    MODE_DUMP = 2,        // reference-ordered Adata / Pdata / g / l
+    MODE_LINESEARCH = 3,  // alpha + nine merits for given (xu, xu_full)
+    MODE_MERIT = 4        // merit terms of xu against xu_ref (passed as xu_full)
+};
+
+template <typename T>
+struct SolveParams {
+    const T* xu_in;       // batch x (18N-6)
+    const T* x0;          // batch x 12
+    const T* goals;       // batch x (N * goal_stride)
+    const T* fext;        // batch x 6, Featherstone order [n; f], or nullptr
+    const T* xu_full;     // MODE_LINESEARCH: full step; MODE_MERIT: reference iterate
+    T* xu_out;            // batch x (18N-6)
+    T* stats;             // batch x 8 or nullptr
+    T* z_out;             // MODE_QP
+    T* Adata; T* Pdata; T* g; T* l;   // MODE_DUMP (each may be nullptr)
+    T* alpha_out; T* merits_out;      // MODE_LINESEARCH (9 per problem) / MODE_MERIT (6 per problem)
+    T* spill_ws;          // gridDim.x x Layout::reg_size workspace when the gains/z region lives in global memory
+    int N, batch, goal_stride, mode, max_qp, regularize;
+    T dt, dQ, R, QN, eps, mu, step_tol;
+};
+
+// shared-memory record strides (odd => conflict-free when consecutive threads own consecutive knots)
+constexpr int LIN_GQ = 0, LIN_GV = 36, LIN_H = 72, LIN_CV = 108, LIN_STRIDE = 115;
+constexpr int COST_STRIDE = 9;                       // j[6], Q, dQ, R
+constexpr int GAIN_K = 0, GAIN_KFF = 72, GAIN_STRIDE = 79;
+constexpr int SCR_CS = 0, SCR_QDD = 12, SCR_U = 18, SCR_D = 54, SCR_F = 60, SCR_STRIDE = 97;
+// Riccati work area
+constexpr int WK_P = 0, WK_PV = 144, WK_W = 156, WK_PT = 300, WK_T = 312, WK_F = 348, WK_QUX = 492,
+              WK_QUU = 564, WK_QX = 600, WK_QU = 612, WK_X = 618, WK_SIZE = 618 + 78;
+
+// Shared-memory layout.  The region `reg` holds the Riccati gains and the QP solution z; the setup-phase
+// scratch aliases it (scratch is dead before the first gain is written).  When the whole layout does not fit
+// the 227 KB of one SM (N = 128 in fp64) `reg` is placed in a per-problem global workspace (L2-resident).
+struct Layout {
+    int xu, goals, x0, lin, cost, work, ls, reg, reg_size, total;
+};
+__host__ __device__ inline Layout make_layout(int N, bool spill) {
+    Layout L;
+    int o = 0;
+    L.xu = o; o += 18 * N;
+    L.goals = o; o += 3 * N;
+    L.x0 = o; o += 12;
+    L.lin = o; o += LIN_STRIDE * (N - 1);
+    L.cost = o; o += COST_STRIDE * N;
+    L.work = o; o += WK_SIZE;
+    L.ls = o; o += (9 * N + 16 > 272 ? 9 * N + 16 : 272);
+    L.reg = o;
+    const int a = GAIN_STRIDE * (N - 1) + 18 * N, b = SCR_STRIDE * (N - 1);
+    L.reg_size = a > b ? a : b;
+    if (!spill) o += L.reg_size;
+    L.total = o;
+    return L;
+}
+
+template <typename T>
+struct Ptrs {
+    T *xu, *goals, *x0, *lin, *cost, *work, *ls, *gains, *z, *scr;
+};
+
+__device__ __constant__ double c_alphas[9] = {0.0, 1.0, 0.5, 0.25, 0.125, 0.0625, 0.03125, 0.015625, 0.0078125};
+
+// -----------------------------------------------------------------------------------------------------------
+// setup: linearised dynamics and cost terms at the current iterate
+template <typename T, int NT>
+__device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* fext) {
+    const int tid = threadIdx.x;
+    const int N = P.N;
+    T* xu = M.xu;
+    // --- per knot: sincos, FK, cost terms, ABA ---
+    for (int k = tid; k < N; k += NT) {
+        const T* xk = xu + 18 * k;
+        T cs[12];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) sincos_t<T>(xk[i], &cs[6 + i], &cs[i]);
+        T pee[3], zs[18], ps[18];
+        fk_ee<T>(rob, cs, pee, zs, ps);
+        const T* gk = M.goals + 3 * k;
+        const T e[3] = {pee[0] - gk[0], pee[1] - gk[1], pee[2] - gk[2]};
+        T* ck = M.cost + COST_STRIDE * k;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const T d[3] = {pee[0] - ps[3 * i], pee[1] - ps[3 * i + 1], pee[2] - ps[3 * i + 2]};
+            T c[3];
+            cross3(zs + 3 * i, d, c);
+            ck[i] = e[0] * c[0] + e[1] * c[1] + e[2] * c[2];
+        }
+        const T nrm = sqrt_t<T>(e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+        const T sc = P.regularize ? T(1) / (nrm + P.eps) : T(1);
+        ck[6] = (k == N - 1) ? P.QN : T(1);
+        ck[7] = P.dQ * sc;
+        ck[8] = P.R * sc;
+        if (k < N - 1) {
+            T* sk = M.scr + SCR_STRIDE * k;
+#pragma unroll
+            for (int i = 0; i < 12; ++i) sk[SCR_CS + i] = cs[i];
+            T qdd[6];
+            aba<T, true>(rob, cs, xk + 6, xk + 12, fext, qdd, sk + SCR_U, sk + SCR_D, sk + SCR_F);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) sk[SCR_QDD + i] = qdd[i];
+        }
+    }
+    __syncthreads();
+    // --- 18 column tasks per knot: 6 columns of M^-1, 6 of dID/dq, 6 of dID/dqd (column-major task order keeps
+    //     warps uniform) ---
+    const int nk = N - 1;
+    for (int t = tid; t < 18 * nk; t += NT) {
+        const int col = t / nk, k = t - col * nk;
+        const T* sk = M.scr + SCR_STRIDE * k;
+        T* lk = M.lin + LIN_STRIDE * k;
+        const T* xk = xu + 18 * k;
+        T cs[12], out[6];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) cs[i] = sk[SCR_CS + i];
+        if (col < 6) {
+            T U[36], D[6];
+#pragma unroll
+            for (int i = 0; i < 36; ++i) U[i] = sk[SCR_U + i];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) D[i] = sk[SCR_D + i];
+            minv_column<T>(rob, cs, U, D, col, out);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) lk[LIN_H + 6 * r + col] = P.dt * out[r];
+        } else {
+            T qd[6], qdd[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) { qd[i] = xk[6 + i]; qdd[i] = sk[SCR_QDD + i]; }
+            if (col < 12) {
+                T F[36];
+#pragma unroll
+                for (int i = 0; i < 36; ++i) F[i] = sk[SCR_F + i];
+                rnea_dcolumn<T, true>(rob, cs, qd, qdd, F, col - 6, out);
+#pragma unroll
+                for (int r = 0; r < 6; ++r) lk[LIN_GQ + 6 * r + (col - 6)] = out[r];
+            } else {
+                rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, col - 12, out);
+#pragma unroll
+                for (int r = 0; r < 6; ++r) lk[LIN_GV + 6 * r + (col - 12)] = out[r];
+            }
+        }
+    }
+    __syncthreads();
+    // --- G = -dt Minv dID (+ I on the velocity block), in place, one column per task ---
+    for (int t = tid; t < 12 * nk; t += NT) {
+        const int col = t / nk, k = t - col * nk;
+        T* lk = M.lin + LIN_STRIDE * k;
+        T* G = lk + (col < 6 ? LIN_GQ : LIN_GV);
+        const int c = col < 6 ? col : col - 6;
+        T raw[6], y[6];
+#pragma unroll
+        for (int s = 0; s < 6; ++s) raw[s] = G[6 * s + c];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            T acc = T(0);
+#pragma unroll
+            for (int s = 0; s < 6; ++s) acc -= lk[LIN_H + 6 * r + s] * raw[s];
+            y[r] = acc;
+        }
+        if (col >= 6) y[c] += T(1);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) G[6 * r + c] = y[r];
+    }
+    __syncthreads();
+    // --- affine term: cv = v + dt qdd - Gq q - Gv v - H u   (top half of c_k is identically zero) ---
+    for (int t = tid; t < 6 * nk; t += NT) {
+        const int r = t / nk, k = t - r * nk;
+        T* lk = M.lin + LIN_STRIDE * k;
+        const T* sk = M.scr + SCR_STRIDE * k;
+        const T* xk = xu + 18 * k;
+        T acc = xk[6 + r] + P.dt * sk[SCR_QDD + r];
+#pragma unroll
+        for (int s = 0; s < 6; ++s)
+            acc -= lk[LIN_GQ + 6 * r + s] * xk[s] + lk[LIN_GV + 6 * r + s] * xk[6 + s] + lk[LIN_H + 6 * r + s] * xk[12 + s];
+        lk[LIN_CV + r] = acc;
+    }
+    __syncthreads();
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// In-register LDL' solve of the 6x6 SPD system  Quu x = b
+template <typename T> I7_DEV void spd6_solve(const T* A /*36, row-major*/, T* b /*6, in/out*/) {
+    T Lm[6][6], d[6], dinv[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        T dj = A[6 * j + j];
+#pragma unroll
+        for (int k = 0; k < j; ++k) dj -= Lm[j][k] * Lm[j][k] * d[k];
+        d[j] = dj;
+        dinv[j] = T(1) / dj;
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) {
+            T s = A[6 * i + j];
+#pragma unroll
+            for (int k = 0; k < j; ++k) s -= Lm[i][k] * Lm[j][k] * d[k];
+            Lm[i][j] = s * dinv[j];
+        }
+    }
+#pragma unroll
+    for (int i = 1; i < 6; ++i)
+#pragma unroll
+        for (int k = 0; k < i; ++k) b[i] -= Lm[i][k] * b[k];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) b[i] *= dinv[i];
+#pragma unroll
+    for (int i = 4; i >= 0; --i)
+#pragma unroll
+        for (int k = i + 1; k < 6; ++k) b[i] -= Lm[k][i] * b[k];
+}
+
+// riccati: backward recursion for the gains, forward roll-out for z.  x0 = measured state (l[:12] = -xs).
+template <typename T, int NT>
+__device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M) {
+    const int tid = threadIdx.x;
+    const int N = P.N;
+    const T dt = P.dt;
+    T* wk = M.work;
+    const T* xu = M.xu;
+    // terminal value function: P_N = blkdiag(QN j j', dQ_N I), p_N = [QN j; dQ_N v]
+    {
+        const T* cN = M.cost + COST_STRIDE * (N - 1);
+        const T* xN = xu + 18 * (N - 1);
+        for (int t = tid; t < 156; t += NT) {
+            if (t < 144) {
+                const int r = t / 12, c = t - 12 * r;
+                T v = T(0);
+                if (r < 6 && c < 6) v = cN[6] * cN[r] * cN[c];
+                else if (r == c) v = cN[7];
+                wk[WK_P + t] = v;
+            } else {
+                const int r = t - 144;
+                wk[WK_PV + r] = r < 6 ? cN[6] * cN[r] : cN[7] * xN[r];
+            }
+        }
+    }
+    __syncthreads();
+    for (int k = N - 2; k >= 0; --k) {
+        const T* lk = M.lin + LIN_STRIDE * k;
+        const T* Gq = lk + LIN_GQ; const T* Gv = lk + LIN_GV; const T* H = lk + LIN_H; const T* cv = lk + LIN_CV;
+        const T* ck = M.cost + COST_STRIDE * k;
+        const T* xk = xu + 18 * k;
+        T* gk = M.gains + GAIN_STRIDE * k;
+        const T* Pm = wk + WK_P;
+        // step A: W = P A, ptil = p + P[:,6:] cv, Tm = Pvv H
+        for (int t = tid; t < 192; t += NT) {
+            if (t < 144) {
+                const int r = t / 12, c = t - 12 * r;
+                T acc;
+                if (c < 6) {
+                    acc = Pm[12 * r + c];
+#pragma unroll
+                    for (int s = 0; s < 6; ++s) acc += Pm[12 * r + 6 + s] * Gq[6 * s + c];
+                } else {
+                    acc = dt * Pm[12 * r + c - 6];
+#pragma unroll
+                    for (int s = 0; s < 6; ++s) acc += Pm[12 * r + 6 + s] * Gv[6 * s + c - 6];
+                }
+                wk[WK_W + t] = acc;
+            } else if (t < 156) {
+                const int r = t - 144;
+                T acc = wk[WK_PV + r];
+#pragma unroll
+                for (int s = 0; s < 6; ++s) acc += Pm[12 * r + 6 + s] * cv[s];
+                wk[WK_PT + r] = acc;
+            } else {
+                const int e = t - 156, r = e / 6, c = e - 6 * r;
+                T acc = T(0);
+#pragma unroll
+                for (int s = 0; s < 6; ++s) acc += Pm[12 * (6 + r) + 6 + s] * H[6 * s + c];
+                wk[WK_T + e] = acc;
+            }
+        }
+        __syncthreads();
+        // step B: Qxx = Q + A'W, Qux = H W[6:,:], Quu = R I + H Tm, qx = gx + A' ptil, qu = gu + H ptil[6:]
+        {
+            const T* W = wk + WK_W; const T* pt = wk + WK_PT;
+            for (int t = tid; t < 270; t += NT) {
+                if (t < 144) {
+                    const int r = t / 12, c = t - 12 * r;
+                    T acc;
+                    if (r < 6) {
+                        acc = W[12 * r + c];
+#pragma unroll
+                        for (int s = 0; s < 6; ++s) acc += Gq[6 * s + r] * W[12 * (6 + s) + c];
+                        if (c < 6) acc += ck[6] * ck[r] * ck[c];
+                    } else {
+                        acc = dt * W[12 * (r - 6) + c];
+#pragma unroll
+                        for (int s = 0; s < 6; ++s) acc += Gv[6 * s + r - 6] * W[12 * (6 + s) + c];
+                        if (r == c) acc += ck[7];
+                    }
+                    wk[WK_F + t] = acc;
+                } else if (t < 216) {
+                    const int e = t - 144, r = e / 12, c = e - 12 * r;
+                    T acc = T(0);
+#pragma unroll
+                    for (int s = 0; s < 6; ++s) acc += H[6 * r + s] * W[12 * (6 + s) + c];
+                    wk[WK_QUX + e] = acc;
+                } else if (t < 252) {
+                    const int e = t - 216, r = e / 6, c = e - 6 * r;
+                    T acc = (r == c) ? ck[8] : T(0);
+#pragma unroll
+                    for (int s = 0; s < 6; ++s) acc += H[6 * r + s] * wk[WK_T + 6 * s + c];
+                    wk[WK_QUU + e] = acc;
+                } else if (t < 264) {
+                    const int r = t - 252;
+                    T acc;
+                    if (r < 6) {
+                        acc = ck[6] * ck[r] + pt[r];
+#pragma unroll
+                        for (int s = 0; s < 6; ++s) acc += Gq[6 * s + r] * pt[6 + s];
+                    } else {
+                        acc = ck[7] * xk[r] + dt * pt[r - 6];
+#pragma unroll
+                        for (int s = 0; s < 6; ++s) acc += Gv[6 * s + r - 6] * pt[6 + s];
+                    }
+                    wk[WK_QX + r] = acc;
+                } else {
+                    const int r = t - 264;
+                    T acc = ck[8] * xk[12 + r];
+#pragma unroll
+                    for (int s = 0; s < 6; ++s) acc += H[6 * r + s] * pt[6 + s];
+                    wk[WK_QU + r] = acc;
+                }
+            }
+        }
+        __syncthreads();
+        // step C: X = Quu^-1 [Qux | qu]  (13 independent right-hand sides, one thread each, LDL' in registers)
+        for (int t = tid; t < 13; t += NT) {
+            T A[36], b[6];
+#pragma unroll
+            for (int i = 0; i < 36; ++i) A[i] = wk[WK_QUU + i];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) b[r] = (t < 12) ? wk[WK_QUX + 12 * r + t] : wk[WK_QU + r];
+            spd6_solve<T>(A, b);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) {
+                wk[WK_X + 13 * r + t] = b[r];
+                if (t < 12) gk[GAIN_K + 12 * r + t] = -b[r]; else gk[GAIN_KFF + r] = -b[r];
+            }
+        }
+        __syncthreads();
+        // step D: P = Qxx - Qux' X[:, :12] (symmetrised), p = qx - Qux' X[:, 12]
+        {
+            const T* X = wk + WK_X; const T* Qux = wk + WK_QUX;
+            for (int t = tid; t < 90; t += NT) {
+                if (t < 78) {
+                    // upper triangle (r <= c), mirrored
+                    int r = 0, e = t;
+                    while (e >= 12 - r) { e -= 12 - r; ++r; }
+                    const int c = r + e;
+                    T acc = T(0.5) * (wk[WK_F + 12 * r + c] + wk[WK_F + 12 * c + r]);
+#pragma unroll
+                    for (int s = 0; s < 6; ++s) acc -= Qux[12 * s + r] * X[13 * s + c];
+                    wk[WK_P + 12 * r + c] = acc;
+                    wk[WK_P + 12 * c + r] = acc;
+                } else {
+                    const int r = t - 78;
+                    T acc = wk[WK_QX + r];
+#pragma unroll
+                    for (int s = 0; s < 6; ++s) acc -= Qux[12 * s + r] * X[13 * s + 12];
+                    wk[WK_PV + r] = acc;
+                }
+            }
+        }
+        __syncthreads();
+    }
+    // forward roll-out by warp 0: x_0 = xs, u_k = K_k x_k + k_k, x_{k+1} = A_k x_k + B_k u_k + c_k
+    if (tid < 32) {
+        T* z = M.z;
+        if (tid < 12) z[tid] = M.x0[tid];
+        __syncwarp();
+        for (int k = 0; k < N - 1; ++k) {
+            const T* lk = M.lin + LIN_STRIDE * k;
+            const T* gk = M.gains + GAIN_STRIDE * k;
+            T* zk = z + 18 * k;
+            if (tid < 6) {
+                T a0 = gk[GAIN_KFF + tid], a1 = T(0);
+#pragma unroll
+                for (int c = 0; c < 6; ++c) {
+                    a0 += gk[GAIN_K + 12 * tid + c] * zk[c];
+                    a1 += gk[GAIN_K + 12 * tid + 6 + c] * zk[6 + c];
+                }
+                zk[12 + tid] = a0 + a1;
+            }
+            __syncwarp();
+            if (tid < 6) {
+                T a0 = lk[LIN_CV + tid], a1 = T(0), a2 = T(0);
+#pragma unroll
+                for (int s = 0; s < 6; ++s) {
+                    a0 += lk[LIN_GQ + 6 * tid + s] * zk[s];
+                    a1 += lk[LIN_GV + 6 * tid + s] * zk[6 + s];
+                    a2 += lk[LIN_H + 6 * tid + s] * zk[12 + s];
+                }
+                zk[18 + 6 + tid] = a0 + a1 + a2;
+            } else if (tid < 12) {
+                const int r = tid - 6;
+                zk[18 + r] = zk[r] + dt * zk[6 + r];
+            }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// merit terms of knot k of the trajectory  x = xa + alpha (xb - xa):  comps = {qcost, vcost, ucost, integ_err}
+template <typename T>
+I7_DEV void merit_knot(const Robot<T>& rob, const SolveParams<T>& P, const T* xa, const T* xb, T alpha, int k,
+                       const T* goal, const T* fext, T* comps) {
+    const int N = P.N;
+    T x[18], xn[12];
+    const int nloc = (k < N - 1) ? 18 : 12;
+#pragma unroll
+    for (int i = 0; i < 18; ++i) x[i] = (i < nloc) ? xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]) : T(0);
+    T cs[12];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) sincos_t<T>(x[i], &cs[6 + i], &cs[i]);
+    T pee[3];
+    fk_ee_only<T>(rob, cs, pee);
+    const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
+    const T Qk = (k == N - 1) ? P.QN : T(1);
+    comps[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+    T vv = T(0), uu = T(0);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) { vv += x[6 + i] * x[6 + i]; uu += x[12 + i] * x[12 + i]; }
+    comps[1] = P.dQ * vv;
+    comps[2] = P.R * uu;
+    comps[3] = T(0);
+    if (k < N - 1) {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) xn[i] = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
+        T qdd[6];
+        aba<T, false>(rob, cs, x + 6, x + 12, fext, qdd, nullptr, nullptr, nullptr);
+        T qe = T(0), ve = T(0);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const T dq = x[i] + x[6 + i] * P.dt - xn[i];
+            const T dv = x[6 + i] + qdd[i] * P.dt - xn[6 + i];
+            qe += dq * dq; ve += dv * dv;
+        }
+        comps[3] = sqrt_t<T>(qe) + sqrt_t<T>(ve);
+    }
+}
+
+// fixed-order block reduction helper: sum of vals[0..n) by one warp (lane-strided partial sums + xor tree)
+template <typename T> I7_DEV T warp_sum_strided(const T* vals, int n, int lane) {
+    T s = T(0);
+    for (int i = lane; i < n; i += 32) s += vals[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    return s;
+}
+
+// merits of the nine candidates (index 0 = base) between xa (current iterate) and xb (full step)
+template <typename T, int NT>
+__device__ void phase_merits(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* xa,
+                             const T* xb, const T* fext, T* merits /*9, shared*/) {
+    const int tid = threadIdx.x, N = P.N;
+    T* part = M.ls;
+    for (int t = tid; t < 9 * N; t += NT) {
+        const int c = t / N, k = t - c * N;
+        const T alpha = T(c_alphas[c]);
+        T comps[4];
+        merit_knot<T>(rob, P, xa, xb, alpha, k, M.goals + 3 * k, fext, comps);
+        part[t] = comps[0] + comps[1] + comps[2] + P.mu * comps[3];
+    }
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int c = warp; c < 9; c += NT / 32) {
+        T s = warp_sum_strided<T>(part + c * N, N, lane);
+        if (lane == 0) {
+            // initial-state violation || x_new[:12] - x[:12] ||  (src/osqp_sqp.py:54,64)
+            const T alpha = T(c_alphas[c]);
+            T d2 = T(0);
+            for (int i = 0; i < 12; ++i) { const T d = alpha * (xb[i] - xa[i]); d2 += d * d; }
+            merits[c] = s + P.mu * sqrt_t<T>(d2);
+        }
+    }
+    __syncthreads();
+}
+
+// -----------------------------------------------------------------------------------------------------------
+template <typename T> __device__ void dump_qp(const SolveParams<T>& P, const Ptrs<T>& M, int b) {
+    const int N = P.N, tid = threadIdx.x, NT = blockDim.x;
+    const T* xu = M.xu;
+    const int nA = 360 * (N - 1) + 144, nP = 27 * N + 6 * (N - 1), nz = 18 * N - 6, nl = 12 * N;
+    if (P.Adata) {
+        T* A = P.Adata + (size_t)b * nA;
+        for (int t = tid; t < nA; t += NT) {
+            T v;
+            const int k = t / 360, e = t - 360 * k;
+            if (k >= N - 1) {
+                const int e2 = t - 360 * (N - 1);
+                v = (e2 / 12 == e2 % 12) ? T(-1) : T(0);
+            } else if (e < 288) {
+                const int c = e / 24, r = e - 24 * c;
+                const T* lk = M.lin + LIN_STRIDE * k;
+                if (r < 12) v = (r == c) ? T(-1) : T(0);
+                else {
+                    const int rr = r - 12;
+                    if (rr < 6) v = (c < 6) ? (rr == c ? T(1) : T(0)) : (rr == c - 6 ? P.dt : T(0));
+                    else v = (c < 6) ? lk[LIN_GQ + 6 * (rr - 6) + c] : lk[LIN_GV + 6 * (rr - 6) + c - 6];
+                }
+            } else {
+                const int e2 = e - 288, c = e2 / 12, r = e2 - 12 * c;
+                const T* lk = M.lin + LIN_STRIDE * k;
+                v = (r < 6) ? T(0) : lk[LIN_H + 6 * (r - 6) + c];
+            }
+            A[t] = v;
+        }
+    }
+    if (P.l) {
+        T* l = P.l + (size_t)b * nl;
+        for (int t = tid; t < nl; t += NT) {
+            const int k = t / 12, r = t - 12 * k;
+            T v;
+            if (k == 0) v = -M.x0[r];
+            else v = (r < 6) ? T(0) : -M.lin[LIN_STRIDE * (k - 1) + LIN_CV + r - 6];
+            l[t] = v;
+        }
+    }
+    if (P.Pdata) {
+        T* Pd = P.Pdata + (size_t)b * nP;
+        for (int t = tid; t < nP; t += NT) {
+            int k = t / 33, e = t - 33 * k;        // 33 values per knot except the last (27)
+            const T* ck = M.cost + COST_STRIDE * k;
+            T v;
+            if (e < 21) {
+                int r = 0, ee = e;
+                while (ee > r) { ee -= r + 1; ++r; }
+                v = ck[6] * ck[r] * ck[ee];
+            } else if (e < 27) v = ck[7];
+            else v = ck[8];
+            Pd[t] = v;
+        }
+    }
+    if (P.g) {
+        T* g = P.g + (size_t)b * nz;
+        for (int t = tid; t < nz; t += NT) {
+            const int k = t / 18, e = t - 18 * k;
+            const T* ck = M.cost + COST_STRIDE * k;
+            T v;
+            if (e < 6) v = ck[6] * ck[e];
+            else if (e < 12) v = ck[7] * xu[t];
+            else v = ck[8] * xu[t];
+            g[t] = v;
+        }
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------------
+template <typename T, int NT>
+__global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__ SolveParams<T> P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* sm = reinterpret_cast<T*>(smem_raw);
+    const int tid = threadIdx.x, N = P.N;
+    const int nz = 18 * N - 6;
+    const bool spill = P.spill_ws != nullptr;
+    const Layout L = make_layout(N, spill);
+    Ptrs<T> M;
+    M.xu = sm + L.xu; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.lin = sm + L.lin; M.cost = sm + L.cost;
+    M.work = sm + L.work; M.ls = sm + L.ls;
+    T* reg = spill ? P.spill_ws + (size_t)blockIdx.x * L.reg_size : sm + L.reg;
+    M.gains = reg; M.z = reg + GAIN_STRIDE * (N - 1); M.scr = reg;
+    __shared__ T s_merits[9];
+    __shared__ T s_alpha;
+    __shared__ T s_fext[6];
+    __shared__ int s_flag;
+
+    for (int b = blockIdx.x; b < P.batch; b += gridDim.x) {
+        // ---- load inputs ----
+        for (int t = tid; t < nz; t += NT) M.xu[t] = P.xu_in[(size_t)b * nz + t];
+        if (tid < 6) M.xu[nz + tid] = T(0);                          // padded u_{N-1}
+        for (int t = tid; t < 3 * N; t += NT) {
+            const int k = t / 3, a = t - 3 * k;
+            M.goals[t] = P.goals[(size_t)b * N * P.goal_stride + k * P.goal_stride + a];
+        }
+        if (tid < 12) M.x0[tid] = P.x0 ? P.x0[(size_t)b * 12 + tid] : T(0);
+        if (tid < 6) s_fext[tid] = P.fext ? P.fext[(size_t)b * 6 + tid] : T(0);
+        __syncthreads();
+        const T* fext = P.fext ? s_fext : nullptr;
+
+        if (P.mode == MODE_LINESEARCH || P.mode == MODE_MERIT) {
+            for (int t = tid; t < nz; t += NT) M.z[t] = P.xu_full[(size_t)b * nz + t];
+            if (tid < 6) M.z[nz + tid] = T(0);
+            __syncthreads();
+            if (P.mode == MODE_MERIT) {
+                // xu against the reference iterate z: comps summed per term
+                T* part = M.ls;   // reuse: 4 sums need 4N entries -> use lin area instead
+                T* buf = M.lin;
+                for (int k = tid; k < N; k += NT) {
+                    T comps[4];
+                    merit_knot<T>(rob, P, M.xu, M.xu, T(0), k, M.goals + 3 * k, fext, comps);
+                    buf[k] = comps[0]; buf[N + k] = comps[1]; buf[2 * N + k] = comps[2]; buf[3 * N + k] = comps[3];
+                }
+                __syncthreads();
+                const int warp = tid >> 5, lane = tid & 31;
+                for (int c = warp; c < 4; c += NT / 32) {
+                    T s = warp_sum_strided<T>(buf + c * N, N, lane);
+                    if (lane == 0) part[c] = s;
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    T d2 = T(0);
+                    for (int i = 0; i < 12; ++i) { const T d = M.xu[i] - M.z[i]; d2 += d * d; }
+                    T* o = P.merits_out + (size_t)b * 6;
+                    o[0] = part[0]; o[1] = part[1]; o[2] = part[2]; o[3] = part[3]; o[4] = sqrt_t<T>(d2);
+                    o[5] = part[0] + part[1] + part[2] + P.mu * (part[3] + o[4]);
+                }
+                __syncthreads();
+                continue;
+            }
+        }
+
+        int qp_iters = 0, n_ls = 0, n_steps = 0, status = 0;
+        T alphas[2] = {T(0), T(0)}, steps[2] = {T(0), T(0)};
+        for (int qp = 0; qp < P.max_qp; ++qp) {
+            qp_iters = qp + 1;
+            if (P.mode != MODE_LINESEARCH) {
+                phase_setup<T, NT>(rob, P, M, fext);
+                if (P.mode == MODE_DUMP) { dump_qp<T>(P, M, b); break; }
+                phase_riccati<T, NT>(P, M);
+                if (P.mode == MODE_QP) {
+                    for (int t = tid; t < nz; t += NT) P.z_out[(size_t)b * nz + t] = M.z[t];
+                    break;
+                }
+            }
+            phase_merits<T, NT>(rob, P, M, M.xu, M.z, fext, s_merits);
+            if (tid == 0) {
+                // first alpha (in decreasing order) with merit <= base, else 0   (src/osqp_sqp.py:59-72)
+                T a = T(0);
+                int bad = !(s_merits[0] == s_merits[0]);
+                for (int c = 1; c <= 8; ++c) {
+                    if (s_merits[c] <= s_merits[0]) { a = T(c_alphas[c]); break; }
+                }
+                s_alpha = a;
+                s_flag = bad;
+            }
+            __syncthreads();
+            const T alpha = s_alpha;
+            if (s_flag) status = 2;
+            if (qp < 2) alphas[qp] = alpha;
+            ++n_ls;
+            if (P.mode == MODE_LINESEARCH) {
+                if (tid == 0) P.alpha_out[b] = alpha;
+                if (tid < 9) P.merits_out[(size_t)b * 9 + tid] = s_merits[tid];
+                break;
+            }
+            if (alpha == T(0)) {
+                // src/osqp_sqp.py:81-82 `continue`: the next pass would re-solve the identical QP and, with an
+                // exact QP solve, reach the same alpha = 0; the remaining passes are skipped but still counted.
+                if (status == 0) status = 1;
+                for (int q2 = qp + 1; q2 < P.max_qp; ++q2) { if (q2 < 2) alphas[q2] = T(0); ++n_ls; qp_iters = q2 + 1; }
+                break;
+            }
+            // XU += alpha (z - XU); step norm
+            T* part = M.ls;
+            T loc = T(0);
+            for (int t = tid; t < nz; t += NT) {
+                const T st = alpha * (M.z[t] - M.xu[t]);
+                M.xu[t] += st;
+                loc += st * st;
+            }
+            part[tid] = loc;   // NT <= 9N+16 is guaranteed by the launcher
+            __syncthreads();
+            if (tid < 32) {
+                T s = warp_sum_strided<T>(part, NT, tid);
+                if (tid == 0) s_merits[0] = sqrt_t<T>(s);
+            }
+            __syncthreads();
+            const T stepsize = s_merits[0];
+            if (n_steps < 2) steps[n_steps] = stepsize;
+            ++n_steps;
+            __syncthreads();
+            if (stepsize < P.step_tol) break;
+        }
+        if (P.mode == MODE_SOLVE) {
+            for (int t = tid; t < nz; t += NT) P.xu_out[(size_t)b * nz + t] = M.xu[t];
+            if (P.stats && tid == 0) {
+                T* st = P.stats + (size_t)b * 8;
+                st[0] = T(qp_iters); st[1] = T(n_ls); st[2] = T(n_steps); st[3] = T(status);
+                st[4] = alphas[0]; st[5] = alphas[1]; st[6] = steps[0]; st[7] = steps[1];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// sample-level kernels (one thread per sample): forward dynamics + derivatives, end-effector, rk4 plant step
+template <typename T>
+__global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, const T* q, const T* v, const T* tau,
+                                const T* fext_pin, T* qdd_out, T* dq_out, T* dv_out, T* minv_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    T cs[12], qd[6], u[6], fx[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { sincos_t<T>(q[6 * i + a], &cs[6 + a], &cs[a]); qd[a] = v[6 * i + a]; u[a] = tau[6 * i + a]; }
+    if (fext_pin) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { fx[a] = fext_pin[6 * i + 3 + a]; fx[3 + a] = fext_pin[6 * i + a]; }
+    }
+    T qdd[6], U[36], D[6], F[36];
+    aba<T, true>(rob, cs, qd, u, fext_pin ? fx : nullptr, qdd, U, D, F);
+    T Mi[36];
+    for (int c = 0; c < 6; ++c) {
+        T out[6];
+        minv_column<T>(rob, cs, U, D, c, out);
+        for (int r = 0; r < 6; ++r) Mi[6 * r + c] = out[r];
+    }
+    if (qdd_out) for (int a = 0; a < 6; ++a) qdd_out[6 * i + a] = qdd[a];
+    if (minv_out) for (int a = 0; a < 36; ++a) minv_out[36 * i + a] = Mi[a];
+    for (int j = 0; j < 6; ++j) {
+        T cq[6], cv[6];
+        rnea_dcolumn<T, true>(rob, cs, qd, qdd, F, j, cq);
+        rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, j, cv);
+        for (int r = 0; r < 6; ++r) {
+            T aq = T(0), av = T(0);
+            for (int s = 0; s < 6; ++s) { aq -= Mi[6 * r + s] * cq[s]; av -= Mi[6 * r + s] * cv[s]; }
+            if (dq_out) dq_out[36 * i + 6 * r + j] = aq;
+            if (dv_out) dv_out[36 * i + 6 * r + j] = av;
+        }
+    }
+}
+
+template <typename T>
+__global__ void eepos_kernel(const __grid_constant__ Robot<T> rob, int n, const T* q, T* p_out, T* J_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    T cs[12];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) sincos_t<T>(q[6 * i + a], &cs[6 + a], &cs[a]);
+    T pee[3], zs[18], ps[18];
+    fk_ee<T>(rob, cs, pee, zs, ps);
+    for (int a = 0; a < 3; ++a) p_out[3 * i + a] = pee[a];
+    if (J_out) {
+        T J[18];
+        ee_jacobian<T>(pee, zs, ps, J);
+        for (int a = 0; a < 18; ++a) J_out[18 * i + a] = J[a];
+    }
+}
+
+template <typename T>
+I7_DEV void aba_at(const Robot<T>& rob, const T* q, const T* qd, const T* u, const T* fx, T* qdd) {
+    T cs[12];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) sincos_t<T>(q[a], &cs[6 + a], &cs[a]);
+    aba<T, false>(rob, cs, qd, u, fx, qdd, nullptr, nullptr, nullptr);
+}
+
+// rk4 plant step, literal stage order of src/utils.py:3-18 (pin.integrate == q + dq for revolute joints)
+template <typename T>
+__global__ void sim_forward_kernel(const __grid_constant__ Robot<T> rob, int n, const T* x, const T* u, int bcast,
+                                   const T* fext /*Featherstone order or nullptr*/, T dt, T* x_next) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const T* xi = x + (bcast ? 0 : 12 * i);
+    const T* ui = u + (bcast ? 0 : 6 * i);
+    T q[6], v[6], uu[6], fx[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { q[a] = xi[a]; v[a] = xi[6 + a]; uu[a] = ui[a]; fx[a] = fext ? fext[6 * i + a] : T(0); }
+    const T* f = fext ? fx : nullptr;
+    T k1v[6], k2v[6], k3v[6], k4v[6], k2q[6], k3q[6], k4q[6], qt[6];
+    aba_at<T>(rob, q, v, uu, f, k1v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + v[a] * dt / T(2); k2q[a] = v[a] + k1v[a] * dt / T(2); }
+    aba_at<T>(rob, qt, k2q, uu, f, k2v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + k2q[a] * dt / T(2); k3q[a] = v[a] + k2v[a] * dt / T(2); }
+    aba_at<T>(rob, qt, k3q, uu, f, k3v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + k3q[a] * dt; k4q[a] = v[a] + k3v[a] * dt; }
+    aba_at<T>(rob, qt, k4q, uu, f, k4v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+        const T vn = v[a] + (dt / T(6)) * (k1v[a] + T(2) * k2v[a] + T(2) * k3v[a] + k4v[a]);
+        const T av = (v[a] + T(2) * k2q[a] + T(2) * k3q[a] + k4q[a]) / T(6);
+        x_next[12 * i + a] = q[a] + av * dt;
+        x_next[12 * i + 6 + a] = vn;
+    }
+}
+
+}  // namespace i7

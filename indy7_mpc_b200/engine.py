@@ -1,0 +1,233 @@
+"""Thin Python owner of one ``i7_handle`` (C ABI in include/indy7_b200.h).
+
+Accepts numpy arrays (host) or torch tensors (host or CUDA) and hands raw pointers to the library; the library
+detects where a pointer lives.  Outputs follow the inputs: torch CUDA in -> torch CUDA out (no host round trip),
+otherwise numpy.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .model import RobotModel, build_model_from_urdf
+
+try:  # torch is plumbing (device memory, streams, torch.distributed), never a compute fallback
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+def _is_torch(x):
+    return torch is not None and isinstance(x, torch.Tensor)
+
+
+class Engine:
+    def __init__(self, model=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
+                 batch=1, dtype="fp64", device=0, max_qp=2, mu=10.0, step_tol=1e-3, threads=0):
+        self.lib = _lib.load()
+        if model is None:
+            model = build_model_from_urdf()
+        if not isinstance(model, RobotModel):
+            raise TypeError("model must be an indy7_mpc_b200.model.RobotModel (use load_robot_model)")
+        if dtype not in ("fp64", "fp32"):
+            raise ValueError("dtype must be 'fp64' or 'fp32'")
+        self.model = model
+        self.N, self.batch, self.dtype = int(N), int(batch), dtype
+        self.np_dtype = np.float64 if dtype == "fp64" else np.float32
+        self.nz = 18 * self.N - 6
+        if isinstance(device, str):
+            device = int(device.split(":")[1]) if ":" in device else 0
+        self.device = int(device)
+        cfg = _lib.I7Config()
+        self.lib.i7_default_config(C.byref(cfg))
+        cfg.N, cfg.batch, cfg.dtype, cfg.device = self.N, self.batch, (_lib.I7_F64 if dtype == "fp64" else _lib.I7_F32), self.device
+        cfg.dt, cfg.dQ_cost, cfg.R_cost, cfg.QN_cost, cfg.eps = float(dt), float(dQ_cost), float(R_cost), float(QN_cost), float(eps)
+        cfg.regularize, cfg.max_qp, cfg.mu, cfg.step_tol, cfg.threads = int(bool(regularize)), int(max_qp), float(mu), float(step_tol), int(threads)
+        cfg.model = model.to_c()
+        self._h = C.c_void_p()
+        rc = self.lib.i7_create(C.byref(cfg), C.byref(self._h))
+        if rc != 0:
+            msg = self.lib.i7_last_error(None).decode()
+            self._h = None
+            if rc == 1:
+                raise ValueError(f"i7_create: {msg}")
+            raise RuntimeError(f"i7_create failed (status {rc}): {msg}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.i7_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- helpers ----------------------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.i7_last_error(self._h).decode()
+            if rc == 1:
+                raise ValueError(msg)
+            raise RuntimeError(f"indy7_b200 status {rc}: {msg}")
+
+    def _torch_dtype(self):
+        return torch.float64 if self.dtype == "fp64" else torch.float32
+
+    def _in(self, x, shape, keep):
+        """-> (pointer, object kept alive).  `shape` is the required 2-D shape."""
+        if x is None:
+            return None
+        if _is_torch(x):
+            t = x.detach().to(self._torch_dtype()).reshape(shape).contiguous()
+            if t.is_cuda and t.device.index != self.device:
+                raise ValueError(f"tensor on {t.device}, engine on cuda:{self.device}")
+            keep.append(t)
+            return C.c_void_p(t.data_ptr())
+        a = np.ascontiguousarray(np.asarray(x, dtype=self.np_dtype).reshape(shape))
+        keep.append(a)
+        return C.c_void_p(a.ctypes.data)
+
+    def _out(self, shape, like, keep):
+        if _is_torch(like) and like.is_cuda:
+            t = torch.empty(shape, dtype=self._torch_dtype(), device=like.device)
+            keep.append(t)
+            return t, C.c_void_p(t.data_ptr())
+        a = np.empty(shape, dtype=self.np_dtype)
+        keep.append(a)
+        return a, C.c_void_p(a.ctypes.data)
+
+    @staticmethod
+    def _stream(like):
+        if _is_torch(like) and like.is_cuda:
+            return C.c_void_p(torch.cuda.current_stream(like.device).cuda_stream)
+        return None
+
+    def _goal_stride(self, goals, B):
+        n = int(np.prod(goals.shape)) // B
+        if n == 3 * self.N:
+            return 3
+        if n == 6 * self.N:
+            return 6
+        raise ValueError(f"goals must hold N*3 or N*6 numbers per problem, got {n} for N={self.N}")
+
+    def _batch_of(self, xu):
+        n = int(np.prod(xu.shape))
+        if n % self.nz:
+            raise ValueError(f"trajectory length must be a multiple of 18N-6={self.nz}, got {n}")
+        B = n // self.nz
+        if B > self.batch:
+            raise ValueError(f"batch {B} exceeds the engine's maximum batch {self.batch}")
+        return B
+
+    # ---- C-ABI calls ------------------------------------------------------------------------------------
+    def solve(self, xu, x0, goals, want_stats=True):
+        B = self._batch_of(xu)
+        gs = self._goal_stride(goals, B)
+        keep = []
+        p_xu, p_x0, p_g = self._in(xu, (B, self.nz), keep), self._in(x0, (B, 12), keep), self._in(goals, (B, gs * self.N), keep)
+        out, p_out = self._out((B, self.nz), xu, keep)
+        stats, p_st = self._out((B, _lib.I7_STATS_LEN), xu, keep) if want_stats else (None, None)
+        self._check(self.lib.i7_solve(self._h, B, p_xu, p_x0, p_g, gs, p_out, p_st, self._stream(xu)))
+        return out, stats
+
+    def solve_qp(self, xu, x0, goals):
+        B = self._batch_of(xu)
+        gs = self._goal_stride(goals, B)
+        keep = []
+        p_xu, p_x0, p_g = self._in(xu, (B, self.nz), keep), self._in(x0, (B, 12), keep), self._in(goals, (B, gs * self.N), keep)
+        out, p_out = self._out((B, self.nz), xu, keep)
+        self._check(self.lib.i7_solve_qp(self._h, B, p_xu, p_x0, p_g, gs, p_out, self._stream(xu)))
+        return out
+
+    def dump_qp(self, xu, x0, goals):
+        B = self._batch_of(xu)
+        gs = self._goal_stride(goals, B)
+        N = self.N
+        keep = []
+        p_xu, p_x0, p_g = self._in(xu, (B, self.nz), keep), self._in(x0, (B, 12), keep), self._in(goals, (B, gs * N), keep)
+        A, pA = self._out((B, 360 * (N - 1) + 144), None, keep)
+        Pd, pP = self._out((B, 27 * N + 6 * (N - 1)), None, keep)
+        g, pg = self._out((B, self.nz), None, keep)
+        l, pl = self._out((B, 12 * N), None, keep)
+        self._check(self.lib.i7_dump_qp(self._h, B, p_xu, p_x0, p_g, gs, pA, pP, pg, pl, None))
+        return A, Pd, g, l
+
+    def merit(self, xu, xu_ref, goals):
+        B = self._batch_of(xu)
+        gs = self._goal_stride(goals, B)
+        keep = []
+        p_xu, p_ref, p_g = self._in(xu, (B, self.nz), keep), self._in(xu_ref, (B, self.nz), keep), self._in(goals, (B, gs * self.N), keep)
+        out, p_out = self._out((B, 6), None, keep)
+        self._check(self.lib.i7_merit(self._h, B, p_xu, p_ref, p_g, gs, p_out, None))
+        return out
+
+    def linesearch(self, xu, xu_full, goals):
+        B = self._batch_of(xu)
+        gs = self._goal_stride(goals, B)
+        keep = []
+        p_xu, p_f, p_g = self._in(xu, (B, self.nz), keep), self._in(xu_full, (B, self.nz), keep), self._in(goals, (B, gs * self.N), keep)
+        alpha, p_a = self._out((B,), None, keep)
+        merits, p_m = self._out((B, 9), None, keep)
+        self._check(self.lib.i7_linesearch(self._h, B, p_xu, p_f, p_g, gs, p_a, p_m, None))
+        return alpha, merits
+
+    def dynamics(self, q, v, tau, f_ext=None):
+        n = int(np.prod(np.shape(q))) // 6
+        keep = []
+        pq, pv, pt = self._in(q, (n, 6), keep), self._in(v, (n, 6), keep), self._in(tau, (n, 6), keep)
+        pf = self._in(f_ext, (n, 6), keep)
+        qdd, p1 = self._out((n, 6), None, keep)
+        dq, p2 = self._out((n, 6, 6), None, keep)
+        dv, p3 = self._out((n, 6, 6), None, keep)
+        mi, p4 = self._out((n, 6, 6), None, keep)
+        self._check(self.lib.i7_dynamics(self._h, n, pq, pv, pt, pf, p1, p2, p3, p4, None))
+        return qdd, dq, dv, mi
+
+    def eepos(self, q, jacobian=False):
+        n = int(np.prod(np.shape(q))) // 6
+        keep = []
+        pq = self._in(q, (n, 6), keep)
+        p, pp = self._out((n, 3), None, keep)
+        J, pJ = self._out((n, 3, 6), None, keep) if jacobian else (None, None)
+        self._check(self.lib.i7_eepos(self._h, n, pq, pp, pJ, None))
+        return (p, J) if jacobian else p
+
+    def sim_forward(self, x, u, dt, batch=None):
+        x_arr = x if _is_torch(x) else np.asarray(x)
+        rows = int(np.prod(x_arr.shape)) // 12
+        bcast = 1 if (rows == 1 and batch not in (None, 1)) else 0
+        B = int(batch) if batch is not None else rows
+        keep = []
+        px, pu = self._in(x, (rows, 12), keep), self._in(u, (rows, 6), keep)
+        out, po = self._out((B, 12), x, keep)
+        self._check(self.lib.i7_sim_forward(self._h, B, px, pu, float(dt), bcast, po, self._stream(x)))
+        return out
+
+    def set_external_wrench(self, f_ext):
+        if f_ext is None:
+            self._check(self.lib.i7_set_external_wrench(self._h, None, 0))
+            return
+        f = np.ascontiguousarray(np.asarray(f_ext, dtype=np.float64).reshape(-1, 6))
+        self._check(self.lib.i7_set_external_wrench(self._h, f.ctypes.data_as(C.POINTER(C.c_double)), f.shape[0]))
+
+    def set_weights(self, dQ_cost, R_cost, QN_cost, regularize, eps):
+        self._check(self.lib.i7_set_weights(self._h, float(dQ_cost), float(R_cost), float(QN_cost), int(bool(regularize)), float(eps)))
+
+    def reset(self):
+        self._check(self.lib.i7_reset(self._h))
+
+    def reset_rho(self):
+        self._check(self.lib.i7_reset_rho(self._h))
+
+    def reset_lambda(self):
+        self._check(self.lib.i7_reset_lambda(self._h))
+
+    def last_solve_time_us(self):
+        us = C.c_double()
+        self._check(self.lib.i7_last_solve_time_us(self._h, C.byref(us)))
+        return us.value
+
+    def launch_count(self):
+        return int(self.lib.i7_launch_count(self._h))

@@ -1,0 +1,266 @@
+"""Parity of the CUDA path (called through the C ABI) against the CPU oracle on identical seeded inputs.
+Tolerances: fp64 trajectories 1e-6 relative (BASELINE.json north_star); kernel-level quantities much tighter."""
+import numpy as np
+import pytest
+
+from oracle import rbd
+from oracle.osqp_solver import OSQPSolver as OracleSolver
+from oracle.osqp_sqp import SQP_OSQP as OracleSQP, ALPHAS
+from tests.cases import make_cases
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import indy7_mpc_b200 as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def engine(pkg):
+    return pkg.Engine(N=32, batch=64, dtype="fp64")
+
+
+def test_fk_known_answers_gpu(golden, engine):
+    q = np.array([e["q"] for e in golden["fk_known_answers"]])
+    p = engine.eepos(q)
+    ref = np.array([e["eepos"] for e in golden["fk_known_answers"]])
+    assert np.abs(p - ref).max() <= 6e-9
+
+
+def test_eepos_and_jacobian(engine, oracle_model):
+    rng = np.random.default_rng(0)
+    q = rng.uniform(-3, 3, (200, 6))
+    p, J = engine.eepos(q, jacobian=True)
+    pr, Jr = rbd.d_eepos(oracle_model, q)
+    assert np.abs(p - pr).max() < 1e-14 and np.abs(J - Jr).max() < 1e-14
+
+
+@pytest.mark.parametrize("with_fext", [False, True])
+def test_dynamics_and_derivatives(engine, oracle_model, with_fext):
+    rng = np.random.default_rng(1)
+    n = 300
+    q, v, u = rng.uniform(-3, 3, (n, 6)), rng.uniform(-2.6, 2.6, (n, 6)), rng.uniform(-100, 100, (n, 6))
+    f = rng.uniform(-30, 30, (n, 6)) if with_fext else None
+    qdd, dq, dv, mi = engine.dynamics(q, v, u, f)
+    rq, rv, rm, ra = rbd.aba_derivatives(oracle_model, q, v, u, f)
+    assert rel(qdd, ra) < 1e-11
+    assert rel(mi, rm) < 1e-11
+    assert rel(dq, rq) < 1e-10
+    assert rel(dv, rv) < 1e-10
+
+
+def test_qp_data_reference_order(engine, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 6, seed=2)
+    A, Pd, g, l = engine.dump_qp(xu, x0, goals)
+    for b in range(6):
+        o = OracleSolver(oracle_model)
+        o.update_constraint_matrix(xu[b], x0[b])
+        o.update_cost_matrix(xu[b], goals[b])
+        assert rel(A[b], o.Adata) < 1e-10
+        assert rel(l[b], o.l) < 1e-10
+        assert rel(Pd[b], o.Pdata) < 1e-11
+        assert rel(g[b], o.g) < 1e-11
+
+
+def test_qp_solution_matches_exact_kkt(engine, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 8, seed=3)
+    z = engine.solve_qp(xu, x0, goals)
+    for b in range(8):
+        ref = OracleSolver(oracle_model, qp_backend="kkt").setup_and_solve_qp(xu[b], x0[b], goals[b]).x
+        assert rel(z[b], ref) < 1e-6, (b, rel(z[b], ref))
+        # residuals of the equality constraints and stationarity far below the reference eps_abs = 1e-3
+        o = OracleSolver(oracle_model)
+        o.update_constraint_matrix(xu[b], x0[b]); o.update_cost_matrix(xu[b], goals[b])
+        P, A = o.matrices()
+        assert np.abs(A @ z[b] - o.l).max() < 1e-8
+
+
+def test_merit_terms(engine, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 6, seed=4)
+    m = engine.merit(xu, xu, goals)
+    for b in range(6):
+        sq = OracleSQP(OracleSolver(oracle_model))
+        qc, vc, uc = sq.eepos_cost(goals[b], xu[b])
+        ie = sq.integrator_err(xu[b])
+        assert rel(m[b, :4], [qc, vc, uc, ie]) < 1e-12
+        assert abs(m[b, 5] - sq.merit(xu[b], xu[b], goals[b])) < 1e-10 * abs(m[b, 5])
+
+
+def test_linesearch(engine, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 8, seed=5)
+    for b in range(8):
+        o = OracleSolver(oracle_model, qp_backend="kkt")
+        z = o.setup_and_solve_qp(xu[b], x0[b], goals[b]).x
+        sq = OracleSQP(o)
+        a_ref = sq.linesearch(xu[b], z, goals[b])
+        alpha, merits = engine.linesearch(xu[b], z, goals[b])
+        base, tried = sq.last_merits
+        assert abs(merits[0, 0] - base) < 1e-11 * abs(base)
+        for i, m in enumerate(tried):
+            assert abs(merits[0, 1 + i] - m) < 1e-11 * abs(m)
+        assert alpha[0] == a_ref
+
+
+def _oracle_sqp(model, xu, x0, goals, **kw):
+    sq = OracleSQP(OracleSolver(model, qp_backend="kkt", **kw))
+    out = sq.sqp(x0, goals, xu)
+    return out, sq.stats
+
+
+def test_sqp_solve_matches_oracle(engine, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 12, seed=6)
+    out, st = engine.solve(xu, x0, goals)
+    for b in range(12):
+        ref, stats = _oracle_sqp(oracle_model, xu[b], x0[b], goals[b])
+        assert int(st[b, 0]) == stats["qp_iters"]["values"][0]
+        n_ls = int(st[b, 1])
+        assert list(st[b, 4:4 + n_ls]) == stats["linesearch_alphas"]["values"], b
+        assert rel(out[b], ref) < 1e-6, (b, rel(out[b], ref))
+        n_st = int(st[b, 2])
+        assert n_st == len(stats["sqp_stepsizes"]["values"])
+        assert rel(st[b, 6:6 + n_st], stats["sqp_stepsizes"]["values"]) < 1e-6 if n_st else True
+
+
+def test_reference_shaped_classes(pkg, oracle_model):
+    """OSQPSolver / SQP_OSQP used exactly as notebooks/pin_mpc_indy7.ipynb cell 0-1 does."""
+    model, _, _ = pkg.load_robot_model(pkg.DEFAULT_URDF, None)
+    solver = pkg.OSQPSolver(model)
+    sqp = pkg.SQP_OSQP(solver)
+    assert (solver.nq, solver.nv, solver.nx, solver.nu, solver.traj_len) == (6, 6, 12, 6, 570)
+    xs = np.ones(12)
+    goal = np.tile(solver.eepos(0.3 * np.ones(6)), 32)
+    XU0 = np.zeros(570)
+    XU = sqp.sqp(xs, goal, XU0)
+    assert np.all(XU0 == 0)                         # inputs are never modified
+    ref, stats = _oracle_sqp(oracle_model, XU0, xs, goal)
+    assert rel(XU, ref) < 1e-6
+    assert sqp.get_stats()["qp_iters"]["values"] == stats["qp_iters"]["values"]
+    assert sqp.get_stats()["linesearch_alphas"]["values"] == stats["linesearch_alphas"]["values"]
+    sol = solver.setup_and_solve_qp(XU0, xs, goal)
+    assert sol.x.shape == (570,)
+    with pytest.raises(ValueError):
+        sqp.sqp(xs, goal[:-3], XU0)
+
+
+def test_closed_loop_golden_prefix(pkg, golden):
+    """The reference's stored 500-step series (notebooks/pin_mpc_indy7.ipynb cell 2): first 21 values."""
+    g = golden["closed_loop"]
+    model, _, _ = pkg.load_robot_model()
+    solver = pkg.OSQPSolver(model)
+    mpc = pkg.MPC_OSQP(model, pkg.SQP_OSQP(solver), solver)
+    endpoints = np.array([solver.eepos(np.array(q)) for q in g["endpoint_qs"]])
+    mpc.run_mpc(np.array(g["xstart"]), endpoints, num_steps=21)
+    got, ref = np.array(mpc.goal_distances), np.array(g["goal_distances"][:21])
+    assert np.abs(got - ref).max() / 1.0 < 5e-6 and (np.abs(got - ref) / ref).max() < 5e-6
+
+
+def test_batch_determinism_and_independence(engine, oracle_model):
+    """Identical lanes -> identical outputs (src/gato_mpc_batch.py:124-134), and a lane's result does not depend
+    on what else is in the batch."""
+    xu, x0, goals = make_cases(oracle_model, 5, seed=7)
+    rep = lambda a: np.repeat(a[:1], 64, axis=0)
+    out, st = engine.solve(rep(xu), rep(x0), rep(goals))
+    assert np.all(out == out[0]) and np.all(st == st[0])
+    mixed, _ = engine.solve(xu, x0, goals)
+    for b in range(5):
+        single, _ = engine.solve(xu[b], x0[b], goals[b])
+        assert np.array_equal(single[0], mixed[b])
+
+
+def test_external_wrench(pkg, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 3, seed=8)
+    f = np.array([[5.0, 0, 15, 0, 0, 0], [-6, 2, -4, 0.5, 0, -0.3], [0, 0, 0, 0, 0, 0]])
+    eng = pkg.Engine(N=32, batch=3)
+    eng.set_external_wrench(f)
+    out, st = eng.solve(xu, x0, goals)
+    for b in range(3):
+        ref, _ = _oracle_sqp(oracle_model, xu[b], x0[b], goals[b], f_ext=f[b])
+        assert rel(out[b], ref) < 1e-6
+    # plant step under the same wrenches (src/utils.py:3-18)
+    xn = eng.sim_forward(x0, xu[:, 12:18], 0.01)
+    for b in range(3):
+        qn, vn = rbd.rk4(oracle_model, x0[b, :6], x0[b, 6:], xu[b, 12:18], 0.01, f[b])
+        assert rel(xn[b], np.concatenate([qn, vn])) < 1e-12
+
+
+def test_goal_stride_six_and_facade(pkg, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 4, seed=9)
+    g6 = np.zeros((4, 32, 6)); g6[:, :, :3] = goals.reshape(4, 32, 3)
+    s = pkg.Indy7SQP(N=32, batch=4)
+    x_traj, u_traj, stats = s.solve(x0, g6.reshape(4, -1), xu_init=xu)
+    assert x_traj.shape == (4, 32, 12) and u_traj.shape == (4, 31, 6)
+    eng = pkg.Engine(N=32, batch=4)
+    ref, _ = eng.solve(xu, x0, goals)
+    assert np.array_equal(stats["xu"], ref)
+    x1, u1, st1 = s.solve(x0[0], goals[0].reshape(32, 3), xu_init=xu[0])
+    assert x1.shape == (32, 12) and u1.shape == (31, 6) and np.array_equal(st1["xu"], ref[0])
+
+
+def test_batch_sqp_shim(oracle_model):
+    import bindings.batch_sqp as batch_sqp
+    solver = batch_sqp.SQPSolverfloat_4()
+    xu, x0, goals = make_cases(oracle_model, 4, seed=10)
+    g6 = np.zeros((4, 32, 6)); g6[:, :, :3] = goals.reshape(4, 32, 3)
+    f = np.zeros((4, 6)); f[1:, :3] = np.random.default_rng(0).normal(0, 5, (3, 3))
+    solver.set_external_wrench_batch(f)
+    solver.reset(); solver.resetRho(); solver.resetLambda()
+    res = solver.solve(xu, 0.01, x0, g6.reshape(4, -1))
+    assert res["xu_trajectory"].shape == (4, 570) and res["xu_trajectory"].dtype == np.float32
+    assert res["sqp_iterations"].shape == (4,) and res["solve_time_us"] > 0
+    assert len(res["line_search_stats"]) == len(res["pcg_stats"]) and len(res["line_search_stats"][0]["step_size"]) == 4
+    for b in range(4):
+        ref, _ = _oracle_sqp(oracle_model, xu[b], x0[b], goals[b], f_ext=f[b])
+        assert rel(res["xu_trajectory"][b], ref) < 1e-5      # float32 output of the fp64 computation
+    xn = solver.sim_forward(x0[0], xu[0, 12:18], 0.01)
+    assert xn.shape == (4, 12)
+    with pytest.raises(ValueError):
+        solver.solve(xu[:2], 0.01, x0[:2], g6[:2].reshape(2, -1))
+
+
+def test_fp32_mode(pkg, oracle_model):
+    """fp32 arithmetic mode: trajectories within 1e-4 relative of the fp64 oracle (north_star tolerance)."""
+    xu, x0, goals = make_cases(oracle_model, 8, seed=11)
+    eng = pkg.Engine(N=32, batch=8, dtype="fp32")
+    z = eng.solve_qp(xu, x0, goals)
+    errs = []
+    for b in range(8):
+        ref = OracleSolver(oracle_model, qp_backend="kkt").setup_and_solve_qp(xu[b], x0[b], goals[b]).x
+        errs.append(rel(z[b], ref))
+    assert max(errs) < 1e-4, errs
+
+
+def test_torch_cuda_tensors(pkg, oracle_model):
+    import torch
+    xu, x0, goals = make_cases(oracle_model, 4, seed=12)
+    eng = pkg.Engine(N=32, batch=4)
+    ref, _ = eng.solve(xu, x0, goals)
+    dev = torch.device("cuda:0")
+    out, st = eng.solve(torch.tensor(xu, device=dev), torch.tensor(x0, device=dev), torch.tensor(goals, device=dev))
+    assert out.is_cuda and np.array_equal(out.cpu().numpy(), ref)
+
+
+def test_long_horizon(pkg, oracle_model):
+    """N = 128 (the horizon of the reference's C++ node, trajopt_node.cu:178); fp64 spills gains to global memory."""
+    xu, x0, goals = make_cases(oracle_model, 2, N=128, seed=13)
+    eng = pkg.Engine(N=128, batch=2)
+    z = eng.solve_qp(xu, x0, goals)
+    for b in range(2):
+        ref = OracleSolver(oracle_model, N=128, qp_backend="kkt").setup_and_solve_qp(xu[b], x0[b], goals[b]).x
+        assert rel(z[b], ref) < 1e-6
+
+
+def test_error_behaviour(pkg):
+    with pytest.raises(ValueError):
+        pkg.Engine(N=1)
+    eng = pkg.Engine(N=32, batch=2)
+    with pytest.raises(ValueError):
+        eng.solve(np.zeros((3, 570)), np.zeros((3, 12)), np.zeros((3, 96)))
+    with pytest.raises(ValueError):
+        eng.solve(np.zeros((1, 570)), np.zeros((1, 12)), np.zeros((1, 100)))

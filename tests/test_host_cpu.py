@@ -1,0 +1,78 @@
+"""CPU-side checks of the host layer: the C ABI library loads and exports every declared symbol, the URDF loader
+agrees with the oracle's independent loader, and the product refuses to run without a GPU (no CPU fallback)."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _build():
+    from indy7_mpc_b200 import build
+    return build.build()
+
+
+def test_library_exports_every_declared_symbol():
+    _build()
+    from indy7_mpc_b200 import _lib
+    lib = _lib.load()
+    header = open(os.path.join(ROOT, "include", "indy7_b200.h")).read()
+    declared = set(re.findall(r"\b(i7_[a-z0-9_]+)\s*\(", header)) - {"i7_status"}
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    for name in declared:
+        assert hasattr(lib, name)
+    assert b"sm_100a" in lib.i7_version()
+
+
+def test_config_struct_layout_matches_header():
+    import ctypes as C
+    from indy7_mpc_b200 import _lib
+    lib = _lib.load()
+    cfg = _lib.I7Config()
+    lib.i7_default_config(C.byref(cfg))
+    assert (cfg.N, cfg.batch, cfg.dtype, cfg.max_qp, cfg.regularize) == (32, 1, 0, 2, 1)
+    assert (cfg.dt, cfg.dQ_cost, cfg.R_cost, cfg.QN_cost, cfg.eps, cfg.mu, cfg.step_tol) == (0.01, 0.01, 1e-5, 100.0, 1.0, 10.0, 1e-3)
+    assert cfg.model.gravity[2] == -9.81
+
+
+def test_product_urdf_loader_agrees_with_oracle_loader(oracle_model):
+    from indy7_mpc_b200.model import build_model_from_urdf
+    m = build_model_from_urdf()
+    assert (m.nq, m.nv, m.njoints, len(m.joints)) == (6, 6, 7, 7)
+    assert np.abs(m.R - oracle_model.R).max() < 1e-15
+    assert np.array_equal(m.p, oracle_model.p) and np.array_equal(m.mass, oracle_model.mass)
+    assert np.array_equal(m.com, oracle_model.com) and np.array_equal(m.Ic, oracle_model.Ic)
+    c = m.to_c()
+    assert c.mass[5] == m.mass[5] and c.gravity[2] == -9.81
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import indy7_mpc_b200 as pkg
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        pkg.Engine()
+    with pytest.raises(ValueError):
+        pkg.Indy7SQP(device="cpu")
+
+
+def test_product_never_imports_oracle():
+    pkg_dir = os.path.join(ROOT, "indy7_mpc_b200")
+    for dp, _, files in os.walk(pkg_dir):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+                assert "oracle/" not in src, f
+
+
+def test_batch_sqp_surface():
+    import bindings.batch_sqp as b
+    for B in (1, 2, 4, 8, 16, 32, 64, 128, 256):
+        cls = getattr(b, f"SQPSolverfloat_{B}")
+        for meth in ("solve", "reset", "resetRho", "resetLambda", "set_external_wrench_batch", "sim_forward"):
+            assert callable(getattr(cls, meth))
+    assert not hasattr(b, "SQPSolverfloat_3")
