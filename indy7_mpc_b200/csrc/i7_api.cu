@@ -138,9 +138,15 @@ i7_status launch_sqp_nt(i7_handle* h, const i7::Robot<T>& rob, const i7::SolvePa
     return I7_OK;
 }
 
+// raise the dynamic shared-memory cap of the kernel to everything the SM offers beyond its static usage;
+// returns that cap in *cap
 template <typename T, int NT>
-cudaError_t allow_big_smem(int bytes) {
-    return cudaFuncSetAttribute(i7::sqp_kernel<T, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+cudaError_t allow_big_smem(int optin_bytes, int* cap) {
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, i7::sqp_kernel<T, NT>);
+    if (e != cudaSuccess) return e;
+    *cap = optin_bytes - (int)fa.sharedSizeBytes;
+    return cudaFuncSetAttribute(i7::sqp_kernel<T, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, *cap);
 }
 
 template <typename T>
@@ -272,24 +278,25 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
     I7_CUDA_C(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
     h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 296 ? 256 : 128);
     if (h->threads != 128 && h->threads != 256) { h->err = "threads must be 0, 128 or 256"; return fail(I7_ERR_INVALID); }
+    int cap = 0;
+    {
+        cudaError_t ea;
+        if (cfg->dtype == I7_F64) ea = h->threads == 256 ? allow_big_smem<double, 256>(h->max_smem_optin, &cap) : allow_big_smem<double, 128>(h->max_smem_optin, &cap);
+        else ea = h->threads == 256 ? allow_big_smem<float, 256>(h->max_smem_optin, &cap) : allow_big_smem<float, 128>(h->max_smem_optin, &cap);
+        if (ea != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea); return fail(I7_ERR_CUDA); }
+    }
     i7::Layout L = i7::make_layout(cfg->N, false);
     h->spill = false;
-    if ((size_t)L.total * h->esize > (size_t)h->max_smem_optin) {
+    if ((size_t)L.total * h->esize > (size_t)cap) {
         L = i7::make_layout(cfg->N, true);
         h->spill = true;
-        if ((size_t)L.total * h->esize > (size_t)h->max_smem_optin) {
+        if ((size_t)L.total * h->esize > (size_t)cap) {
             h->err = "horizon too long for the shared-memory layout of this dtype";
             return fail(I7_ERR_UNSUPPORTED);
         }
         I7_CUDA_C(cudaMalloc(&h->d_spill, (size_t)cfg->batch * L.reg_size * h->esize));
     }
     h->smem_bytes = L.total * h->esize;
-    {
-        cudaError_t ea;
-        if (cfg->dtype == I7_F64) ea = h->threads == 256 ? allow_big_smem<double, 256>(h->max_smem_optin) : allow_big_smem<double, 128>(h->max_smem_optin);
-        else ea = h->threads == 256 ? allow_big_smem<float, 256>(h->max_smem_optin) : allow_big_smem<float, 128>(h->max_smem_optin);
-        if (ea != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea); return fail(I7_ERR_CUDA); }
-    }
     const size_t B = cfg->batch, N = cfg->N, es = h->esize;
     // worst case over all entry points: inputs xu, x0, goals(6), xu_full; outputs of the dump mode
     const size_t in_bytes = B * (2 * h->nz + 12 + 6 * N) * es + 256;
