@@ -45,7 +45,7 @@ extern "C" {
 #define I7_NXU 18
 #define I7_MAX_QP 2        /* src/osqp_sqp.py:77  `for qp in range(2)` */
 #define I7_NALPHA 8        /* src/osqp_sqp.py:58  alphas 1, 1/2, ..., 1/128 */
-#define I7_STATS_LEN 8
+#define I7_STATS_LEN 12
 
 typedef enum {
     I7_OK = 0,
@@ -94,7 +94,11 @@ typedef struct {
  *   [3] status          0 ok, 1 = a line search failed (alpha 0, not an error: src/osqp_sqp.py:72,81-82),
  *                       2 = non-finite value met
  *   [4],[5] alpha of line search 0 / 1 (0 when failed or not run)
- *   [6],[7] 2-norm of accepted step 0 / 1 (0 when absent)                                         */
+ *   [6],[7] 2-norm of accepted step 0 / 1 (0 when absent)
+ *   [8] merit of the returned trajectory as evaluated by the last line search (the accepted candidate, or the
+ *       base merit when that line search failed) — the per-problem cost used for best-trajectory selection
+ *   [9] base merit of the first line search (merit of the input trajectory)
+ *   [10],[11] reserved (0)                                                                            */
 
 typedef struct i7_handle i7_handle;
 
@@ -129,6 +133,21 @@ int64_t i7_launch_count(const i7_handle* h);
  * x, u: batch x 12 / batch x 6 (or a single row broadcast to every lane when bcast != 0); out: batch x 12. */
 i7_status i7_sim_forward(i7_handle* h, int32_t batch, const void* x, const void* u, double dt, int32_t bcast,
                          void* x_next, void* stream);
+
+/* Best-trajectory selection over a batch (north_star: "a single NCCL gather of per-problem costs and best
+ * trajectory"; reference analogue gato_controller.py:105-118 argmin over hypotheses).  Writes, on the device,
+ * packed = [cost_0 .. cost_{batch-1} | best_cost, best_index (as a number), XU_best (18N-6)] where cost_b =
+ * stats[b][8]; `index_offset` is added to best_index (rank * shard size).  Ties -> lowest index.  All pointers
+ * host or device; packed has batch + 2 + 18N-6 elements of the handle dtype. */
+i7_status i7_pack_best(i7_handle* h, int32_t batch, const void* stats, const void* xu, int32_t index_offset,
+                       void* packed, void* stream);
+/* Final reduction after the gather: `gathered` holds `nranks` records of `stride` elements, each ending with
+ * [best_cost, best_index, XU_best]; writes out = [best_cost, best_index, XU_best] of the winning rank. */
+i7_status i7_reduce_best(i7_handle* h, int32_t nranks, int32_t stride, const void* gathered, void* out, void* stream);
+
+/* Measurement utility for roofline denominators: sustained FMA throughput of the CUDA-core pipe of the
+ * handle's dtype (dependent-chain-free FMA loop on every SM), in TFLOP/s. */
+i7_status i7_measure_fma_peak(i7_handle* h, double* tflops);
 
 /* ---- stage-level entry points (parity tests and debugging; same device code as i7_solve) ---- */
 /* The full-step QP solution `setup_and_solve_qp(xu, x0, goals).x` (src/osqp_solver.py:137-143). */

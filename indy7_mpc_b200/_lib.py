@@ -9,7 +9,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libindy7_b200.so")
 
-I7_NJ, I7_STATS_LEN = 6, 8
+I7_NJ, I7_STATS_LEN = 6, 12
 I7_F64, I7_F32 = 0, 1
 
 
@@ -41,6 +41,9 @@ SYMBOLS = {
     "i7_solve": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "i7_last_solve_time_us": (_i32, [_vp, C.POINTER(_dbl)]),
     "i7_launch_count": (C.c_int64, [_vp]),
+    "i7_pack_best": (_i32, [_vp, _i32, _vp, _vp, _i32, _vp, _vp]),
+    "i7_reduce_best": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp]),
+    "i7_measure_fma_peak": (_i32, [_vp, C.POINTER(_dbl)]),
     "i7_sim_forward": (_i32, [_vp, _i32, _vp, _vp, _dbl, _i32, _vp, _vp]),
     "i7_solve_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp]),
     "i7_dump_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),

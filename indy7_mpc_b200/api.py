@@ -91,6 +91,7 @@ class Indy7SQP:
         stats = {
             'qp_iters': stn[:, 0].astype(int), 'n_linesearch': stn[:, 1].astype(int), 'n_steps': stn[:, 2].astype(int),
             'status': stn[:, 3].astype(int), 'linesearch_alphas': stn[:, 4:6].copy(), 'sqp_stepsizes': stn[:, 6:8].copy(),
+            'cost': stn[:, 8].copy(), 'cost_in': stn[:, 9].copy(),
             'xu': out if batched else out[0],
         }
         if not batched:

@@ -363,6 +363,73 @@ i7_status i7_last_solve_time_us(i7_handle* h, double* us) {
 
 int64_t i7_launch_count(const i7_handle* h) { return h ? h->launches : 0; }
 
+i7_status i7_pack_best(i7_handle* h, int32_t batch, const void* stats, const void* xu, int32_t index_offset,
+                       void* packed, void* stream) {
+    if (!h || !stats || !xu || !packed || batch < 1 || batch > h->cfg.batch) { if (h) h->err = "bad argument"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t es = h->esize, nz = h->nz;
+    Stage st(h);
+    const void* d_st = st.in(stats, (size_t)batch * I7_STATS_LEN * es);
+    const void* d_xu = st.in(xu, (size_t)batch * nz * es);
+    void* d_out = st.out(packed, ((size_t)batch + 2 + nz) * es);
+    i7_status rc = st.flush_in(s);
+    if (rc) return rc;
+    if (h->esize == 8) i7::pack_best_kernel<double><<<1, 256, 0, s>>>(batch, (int)nz, (const double*)d_st, I7_STATS_LEN, 8, (const double*)d_xu, index_offset, (double*)d_out);
+    else i7::pack_best_kernel<float><<<1, 256, 0, s>>>(batch, (int)nz, (const float*)d_st, I7_STATS_LEN, 8, (const float*)d_xu, index_offset, (float*)d_out);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
+
+i7_status i7_reduce_best(i7_handle* h, int32_t nranks, int32_t stride, const void* gathered, void* out, void* stream) {
+    if (!h || !gathered || !out || nranks < 1 || stride < (int)h->nz + 2) { if (h) h->err = "bad argument"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t es = h->esize, nz = h->nz;
+    i7_status rc;
+    if ((rc = arena_reserve(h, h->in, (size_t)nranks * stride * es + 256))) return rc;
+    Stage st(h);
+    const void* d_in = st.in(gathered, (size_t)nranks * stride * es);
+    void* d_out = st.out(out, (2 + nz) * es);
+    if ((rc = st.flush_in(s))) return rc;
+    if (h->esize == 8) i7::reduce_best_kernel<double><<<1, 256, 0, s>>>(nranks, stride, (int)nz, (const double*)d_in, (double*)d_out);
+    else i7::reduce_best_kernel<float><<<1, 256, 0, s>>>(nranks, stride, (int)nz, (const float*)d_in, (float*)d_out);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
+
+i7_status i7_measure_fma_peak(i7_handle* h, double* tflops) {
+    if (!h || !tflops) return I7_ERR_INVALID;
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    int sms = 0;
+    I7_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->cfg.device));
+    const int iters = 1 << 15, threads = 256, blocks = sms * 8;
+    void* sink = nullptr;
+    I7_CUDA(h, cudaMalloc(&sink, 64));
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    double best = 0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(a, 0);
+        if (h->esize == 8) i7::fma_peak_kernel<double><<<blocks, threads>>>(iters, 1.0 + rep, (double*)sink);
+        else i7::fma_peak_kernel<float><<<blocks, threads>>>(iters, 1.0f + rep, (float*)sink);
+        cudaEventRecord(b, 0);
+        cudaEventSynchronize(b);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        const double tf = 2.0 * 8.0 * iters * (double)threads * blocks / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    h->launches += 5;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    cudaFree(sink);
+    I7_CUDA(h, cudaGetLastError());
+    *tflops = best;
+    return I7_OK;
+}
+
 i7_status i7_solve_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,
                       int32_t goal_stride, void* z_out, void* stream) {
     if (!h || !xu || !x0 || !goals || !z_out) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }

@@ -205,6 +205,29 @@ class Engine:
         self._check(self.lib.i7_sim_forward(self._h, B, px, pu, float(dt), bcast, po, self._stream(x)))
         return out
 
+    def pack_best(self, stats, xu, index_offset=0):
+        """[costs | best_cost, best_index, XU_best] on the device the inputs live on (i7_pack_best)."""
+        B = self._batch_of(xu)
+        keep = []
+        p_st, p_xu = self._in(stats, (B, _lib.I7_STATS_LEN), keep), self._in(xu, (B, self.nz), keep)
+        out, p_out = self._out((B + 2 + self.nz,), xu, keep)
+        self._check(self.lib.i7_pack_best(self._h, B, p_st, p_xu, int(index_offset), p_out, self._stream(xu)))
+        return out
+
+    def reduce_best(self, gathered, nranks):
+        n = int(np.prod(gathered.shape))
+        stride = n // nranks
+        keep = []
+        p_in = self._in(gathered, (nranks, stride), keep)
+        out, p_out = self._out((2 + self.nz,), gathered, keep)
+        self._check(self.lib.i7_reduce_best(self._h, nranks, stride, p_in, p_out, self._stream(gathered)))
+        return out
+
+    def measure_fma_peak(self):
+        tf = C.c_double()
+        self._check(self.lib.i7_measure_fma_peak(self._h, C.byref(tf)))
+        return tf.value
+
     def set_external_wrench(self, f_ext):
         if f_ext is None:
             self._check(self.lib.i7_set_external_wrench(self._h, None, 0))

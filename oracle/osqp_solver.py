@@ -57,7 +57,7 @@ class OSQPSolver:
         blk = np.eye(self.nxu)
         blk[:self.nq, :self.nq] = 1.0
         bd = np.kron(np.eye(self.N), blk)[:-self.nu, :-self.nu]
-        return csc_matrix(triu(bd), shape=(self.traj_len, self.traj_len))
+        return csc_matrix(triu(csc_matrix(bd)), shape=(self.traj_len, self.traj_len))
 
     def initialize_A(self):
         nx, nu, N = self.nx, self.nu, self.N

@@ -264,3 +264,25 @@ def test_error_behaviour(pkg):
         eng.solve(np.zeros((3, 570)), np.zeros((3, 12)), np.zeros((3, 96)))
     with pytest.raises(ValueError):
         eng.solve(np.zeros((1, 570)), np.zeros((1, 12)), np.zeros((1, 100)))
+
+
+def test_best_selection_kernels(engine, oracle_model):
+    """i7_pack_best / i7_reduce_best against numpy argmin (costs = stats[:, 8])."""
+    xu, x0, goals = make_cases(oracle_model, 16, seed=14)
+    out, st = engine.solve(xu, x0, goals)
+    packed = engine.pack_best(st, out, index_offset=100)
+    bi = int(np.argmin(st[:, 8]))
+    assert np.array_equal(packed[:16], st[:, 8])
+    assert packed[16] == st[bi, 8] and packed[17] == 100 + bi and np.array_equal(packed[18:], out[bi])
+    # the cost is the merit the last line search computed for the returned trajectory
+    for b in range(4):
+        sq = OracleSQP(OracleSolver(oracle_model, qp_backend="kkt"))
+        sq.sqp(x0[b], goals[b], xu[b])
+        base, tried = sq.last_merits
+        want = tried[-1] if st[b, 5] > 0 or (st[b, 1] == 1 and st[b, 4] > 0) else base
+        assert abs(st[b, 8] - want) < 1e-9 * abs(want)
+    two = np.stack([packed, packed.copy()])
+    two[1, 16] = packed[16] - 1.0; two[1, 17] = 7.0
+    red = engine.reduce_best(two, 2)
+    assert red[0] == packed[16] - 1.0 and red[1] == 7.0
+

@@ -76,3 +76,10 @@ def test_batch_sqp_surface():
         for meth in ("solve", "reset", "resetRho", "resetLambda", "set_external_wrench_batch", "sim_forward"):
             assert callable(getattr(cls, meth))
     assert not hasattr(b, "SQPSolverfloat_3")
+
+
+def test_figure8_generator():
+    from indy7_mpc_b200.reference_traj import figure8
+    ref = np.load(os.path.join(ROOT, "tests", "golden", "figure8_first_cycle.npy"))
+    got = figure8(0.5, 0.55, (0.0, 0.4, 0.45), 10.0, 0.01, cycles=2)
+    assert got.shape == (12000,) and np.abs(got[:6000] - ref).max() < 1e-15
