@@ -399,7 +399,7 @@ def run_b200(args):
 
 
 def eng_threads(eng, B, args):
-    return args.threads if args.threads else (256 if B <= 296 else 128)
+    return args.threads if args.threads else (384 if B <= 148 else (256 if B <= 296 else 128))
 
 
 def single_problem_latency(args, local):
@@ -410,7 +410,7 @@ def single_problem_latency(args, local):
     from indy7_mpc_b200.reference_traj import figure8
     N = args.horizon
     n_ticks = args.latency_ticks
-    eng = Engine(N=N, batch=1, dtype=args.dtype, device=local, threads=256)
+    eng = Engine(N=N, batch=1, dtype=args.dtype, device=local)
     fig = figure8(0.5, 0.55, (0.0, 0.4, 0.45), 10.0, 0.01, cycles=3, stride=3).reshape(-1, 3)
     x = np.concatenate([HOME, np.zeros(6)])
     xu = np.zeros((1, 18 * N - 6)); xu[0, :12] = x

@@ -82,7 +82,7 @@ typedef struct {
     int32_t max_qp;         /* outer SQP iterations, <= I7_MAX_QP (reference: 2) */
     double mu;              /* merit penalty, src/osqp_sqp.py:50: 10 */
     double step_tol;        /* src/osqp_sqp.py:90: 1e-3 */
-    int32_t threads;        /* CTA size: 0 = choose from batch (256 for latency, 128 for throughput) */
+    int32_t threads;        /* CTA size: 0 = choose from batch (384/256 for latency, 128 for throughput) */
     int32_t reserved;
     i7_model model;
 } i7_config;
@@ -148,6 +148,13 @@ i7_status i7_reduce_best(i7_handle* h, int32_t nranks, int32_t stride, const voi
 /* Measurement utility for roofline denominators: sustained FMA throughput of the CUDA-core pipe of the
  * handle's dtype (dependent-chain-free FMA loop on every SM), in TFLOP/s. */
 i7_status i7_measure_fma_peak(i7_handle* h, double* tflops);
+
+/* Debugging aid: with enable != 0 every later i7_solve records clock64() at its phase boundaries; clocks16
+ * (batch x 32, may be NULL) receives the stamps of the latest solve: per SQP iteration i (0,1) entries
+ * 5i+0 start, +1 after setup, +2 after the QP solve, +3 after the merit evaluation, +4 after the update;
+ * [10..13] cycles of the first QP solve spent in the 6x6 solves / value updates / roll-out / control recovery;
+ * [16..24] stamps at the sub-phase boundaries of the first setup. */
+i7_status i7_profile_phases(i7_handle* h, int32_t enable, int64_t* clocks32, int32_t batch);
 
 /* ---- stage-level entry points (parity tests and debugging; same device code as i7_solve) ---- */
 /* The full-step QP solution `setup_and_solve_qp(xu, x0, goals).x` (src/osqp_solver.py:137-143). */

@@ -29,6 +29,7 @@ struct i7_handle {
     Arena in, out;               // packed inputs / outputs for host-pointer calls
     void* d_fext = nullptr;      // batch x 6, Featherstone order, handle dtype
     bool has_fext = false;
+    long long* d_prof = nullptr; // optional phase-clock buffer (i7_enable_profile)
     void* d_spill = nullptr;     // gains/z region when it does not fit shared memory
     bool spill = false;
     int smem_bytes = 0;
@@ -152,6 +153,7 @@ cudaError_t allow_big_smem(int optin_bytes, int* cap) {
 template <typename T>
 i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& P, cudaStream_t s) {
     P.spill_ws = h->spill ? (T*)h->d_spill : nullptr;
+    if (h->threads == 384) return launch_sqp_nt<T, 384>(h, rob, P, s);
     if (h->threads == 256) return launch_sqp_nt<T, 256>(h, rob, P, s);
     return launch_sqp_nt<T, 128>(h, rob, P, s);
 }
@@ -165,6 +167,7 @@ void base_params(const i7_handle* h, i7::SolveParams<T>& P, int batch, int goal_
     P.dt = T(c.dt); P.dQ = T(c.dQ_cost); P.R = T(c.R_cost); P.QN = T(c.QN_cost); P.eps = T(c.eps);
     P.mu = T(c.mu); P.step_tol = T(c.step_tol);
     P.fext = h->has_fext ? (const T*)h->d_fext : nullptr;
+    P.prof = (mode == i7::MODE_SOLVE) ? h->d_prof : nullptr;
 }
 
 i7_status check_batch(i7_handle* h, int batch, int goal_stride) {
@@ -243,6 +246,7 @@ void i7_destroy(i7_handle* h) {
     if (h->out.host) cudaFreeHost(h->out.host);
     if (h->d_fext) cudaFree(h->d_fext);
     if (h->d_spill) cudaFree(h->d_spill);
+    if (h->d_prof) cudaFree(h->d_prof);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     delete h;
@@ -276,13 +280,16 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
 #define I7_CUDA_C(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(I7_ERR_CUDA); } } while (0)
     I7_CUDA_C(cudaSetDevice(cfg->device));
     I7_CUDA_C(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
-    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 296 ? 256 : 128);
-    if (h->threads != 128 && h->threads != 256) { h->err = "threads must be 0, 128 or 256"; return fail(I7_ERR_INVALID); }
+    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 148 ? 384 : (cfg->batch <= 296 ? 256 : 128));
+    if (h->threads != 128 && h->threads != 256 && h->threads != 384) { h->err = "threads must be 0, 128, 256 or 384"; return fail(I7_ERR_INVALID); }
     int cap = 0;
     {
         cudaError_t ea;
-        if (cfg->dtype == I7_F64) ea = h->threads == 256 ? allow_big_smem<double, 256>(h->max_smem_optin, &cap) : allow_big_smem<double, 128>(h->max_smem_optin, &cap);
-        else ea = h->threads == 256 ? allow_big_smem<float, 256>(h->max_smem_optin, &cap) : allow_big_smem<float, 128>(h->max_smem_optin, &cap);
+        const int o = h->max_smem_optin;
+        if (cfg->dtype == I7_F64)
+            ea = h->threads == 384 ? allow_big_smem<double, 384>(o, &cap) : h->threads == 256 ? allow_big_smem<double, 256>(o, &cap) : allow_big_smem<double, 128>(o, &cap);
+        else
+            ea = h->threads == 384 ? allow_big_smem<float, 384>(o, &cap) : h->threads == 256 ? allow_big_smem<float, 256>(o, &cap) : allow_big_smem<float, 128>(o, &cap);
         if (ea != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea); return fail(I7_ERR_CUDA); }
     }
     i7::Layout L = i7::make_layout(cfg->N, false);
@@ -398,6 +405,21 @@ i7_status i7_reduce_best(i7_handle* h, int32_t nranks, int32_t stride, const voi
     ++h->launches;
     I7_CUDA(h, cudaGetLastError());
     return st.flush_out(s);
+}
+
+i7_status i7_profile_phases(i7_handle* h, int32_t enable, int64_t* clocks16, int32_t batch) {
+    if (!h) return I7_ERR_INVALID;
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    if (enable && !h->d_prof) {
+        I7_CUDA(h, cudaMalloc((void**)&h->d_prof, (size_t)h->cfg.batch * 32 * sizeof(long long)));
+        I7_CUDA(h, cudaMemset(h->d_prof, 0, (size_t)h->cfg.batch * 32 * sizeof(long long)));
+    }
+    if (clocks16 && h->d_prof && batch > 0 && batch <= h->cfg.batch) {
+        I7_CUDA(h, cudaDeviceSynchronize());
+        I7_CUDA(h, cudaMemcpy(clocks16, h->d_prof, (size_t)batch * 32 * sizeof(long long), cudaMemcpyDeviceToHost));
+    }
+    if (!enable && h->d_prof) { cudaFree(h->d_prof); h->d_prof = nullptr; }
+    return I7_OK;
 }
 
 i7_status i7_measure_fma_peak(i7_handle* h, double* tflops) {

@@ -356,24 +356,138 @@ I7_DEV void minv_column(const Robot<T>& rob, const T* cs, const T* U, const T* D
     }
 }
 
-// Column j of d tau/d q (WRT_Q) or d tau/d qd of inverse dynamics evaluated at (q, qd, qdd): forward-mode
-// chain rule in link coordinates.  F = total joint forces from aba<.., true> (only used for WRT_Q).
-// out[i] = d tau_i / d (q|qd)_j.
-template <typename T, bool WRT_Q>
-I7_DEV void rnea_dcolumn(const Robot<T>& rob, const T* cs, const T* qd, const T* qdd, const T* F, int j, T* out) {
+// Column j of the joint-space inertia matrix: M[:, j] = ID(q, qd = 0, qdd = e_j) without gravity (one RNEA pass
+// with unit acceleration on joint j; links below j stay at rest).  out[i] = M[i][j].
+template <typename T>
+I7_DEV void crba_column(const Robot<T>& rob, const T* cs, int j, T* out) {
+    T a[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    T f[I7_NJ][6];
+#pragma unroll
+    for (int i = 0; i < I7_NJ; ++i) {
+        if (i == j) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) a[k] = T(0);
+            a[2] = T(1);
+        } else if (i > j) {
+            T E[9], t[6];
+            joint_E(rob, i, cs[i], cs[6 + i], E);
+            xmot(E, rob.p[i], a, t);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) a[k] = t[k];
+        }
+        if (i >= j) inertia_mul(rob, i, a, f[i]);
+    }
+    T F[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+    for (int i = I7_NJ - 1; i >= 0; --i) {
+        if (i >= j) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) F[k] += f[i][k];
+        }
+        out[i] = F[2];
+        if (i > 0) {
+            T E[9], o[6];
+            joint_E(rob, i, cs[i], cs[6 + i], E);
+            xfrc_t(E, rob.p[i], F, o);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) F[k] = o[k];
+        }
+    }
+}
+
+// Bias torques b = ID(q, qd, qdd = 0) with gravity and the optional local wrench on the last link.
+template <typename T>
+I7_DEV void rnea_bias(const Robot<T>& rob, const T* cs, const T* qd, const T* fext, T* out) {
     T v[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
     T a[6] = {T(0), T(0), T(0), -rob.g[0], -rob.g[1], -rob.g[2]};
-    T dv[6], da[6];
-    T df[I7_NJ][6];
+    T f[I7_NJ][6];
 #pragma unroll
     for (int i = 0; i < I7_NJ; ++i) {
         T E[9], t[6];
         joint_E(rob, i, cs[i], cs[6 + i], E);
-        // nominal velocity / acceleration of link i
-        xmot(E, rob.p[i], a, t);                 // t = X a_parent
-        T xa[6];
+        xmot(E, rob.p[i], a, t);
 #pragma unroll
-        for (int k = 0; k < 6; ++k) xa[k] = t[k];
+        for (int k = 0; k < 6; ++k) a[k] = t[k];
+        if (i == 0) {
+            v[2] = qd[0];
+        } else {
+            xmot(E, rob.p[i], v, t);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) v[k] = t[k];
+            v[2] += qd[i];
+        }
+        crm_S_acc(v, qd[i], a);
+        T Iv[6];
+        inertia_mul(rob, i, a, f[i]);
+        inertia_mul(rob, i, v, Iv);
+        crf<T, true>(v, Iv, f[i]);
+    }
+    if (fext) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) f[I7_NJ - 1][k] -= fext[k];
+    }
+    T F[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+    for (int i = I7_NJ - 1; i >= 0; --i) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) F[k] += f[i][k];
+        out[i] = F[2];
+        if (i > 0) {
+            T E[9], o[6];
+            joint_E(rob, i, cs[i], cs[6 + i], E);
+            xfrc_t(E, rob.p[i], F, o);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) F[k] = o[k];
+        }
+    }
+}
+
+// Right-looking LDL' of a 6x6 SPD matrix held in registers (A is destroyed: unit-lower L below the diagonal),
+// dinv[j] = 1 / D_j.  Dependency depth per pivot: one reciprocal, one multiply, one FMA.
+template <typename T> I7_DEV void spd6_factor(T (&A)[6][6], T (&dinv)[6]) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        dinv[j] = T(1) / A[j][j];
+        T col[6];
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) col[i] = A[i][j];
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) {
+            const T l = col[i] * dinv[j];
+#pragma unroll
+            for (int k = j + 1; k <= i; ++k) A[i][k] -= l * col[k];
+            A[i][j] = l;
+        }
+    }
+}
+template <typename T> I7_DEV void spd6_solve_factored(const T (&A)[6][6], const T (&dinv)[6], T* b) {
+#pragma unroll
+    for (int j = 0; j < 5; ++j)
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) b[i] -= A[i][j] * b[j];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) b[i] *= dinv[i];
+#pragma unroll
+    for (int j = 5; j > 0; --j)
+#pragma unroll
+        for (int i = 0; i < j; ++i) b[i] -= A[j][i] * b[j];
+}
+
+// Column j of d tau/d q (WRT_Q) or d tau/d qd of inverse dynamics evaluated at (q, qd, qdd): forward-mode
+// chain rule in link coordinates (the recursion of Carpentier & Mansard 2018 in local frames).  fext: local wrench
+// on the last link (enters the total joint force of the WRT_Q seed) or nullptr.  out[i] = d tau_i / d (q|qd)_j.
+template <typename T, bool WRT_Q>
+I7_DEV void rnea_dcolumn(const Robot<T>& rob, const T* cs, const T* qd, const T* qdd, const T* fext, int j, T* out) {
+    T v[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    T a[6] = {T(0), T(0), T(0), -rob.g[0], -rob.g[1], -rob.g[2]};
+    T dv[6], da[6];
+    T df[I7_NJ][6];
+    T fn[I7_NJ][6];          // nominal link forces (WRT_Q only): needed for S x* F_j
+#pragma unroll
+    for (int i = 0; i < I7_NJ; ++i) {
+        T E[9], xa[6];
+        joint_E(rob, i, cs[i], cs[6 + i], E);
+        xmot(E, rob.p[i], a, xa);                 // X a_parent
         if (i == 0) {
             v[2] = qd[0];
         } else {
@@ -414,28 +528,45 @@ I7_DEV void rnea_dcolumn(const Robot<T>& rob, const T* cs, const T* qd, const T*
             inertia_mul(rob, i, dv, Idv);
             crf<T, true>(dv, Iv, df[i]);
             crf<T, true>(v, Idv, df[i]);
+            if (WRT_Q) {
+                inertia_mul(rob, i, a, fn[i]);
+                crf<T, true>(v, Iv, fn[i]);
+                if (i == I7_NJ - 1 && fext) {
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) fn[i][k] -= fext[k];
+                }
+            }
         }
     }
     T dF[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    T F[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
 #pragma unroll
     for (int i = I7_NJ - 1; i >= 0; --i) {
         if (i >= j) {
 #pragma unroll
             for (int k = 0; k < 6; ++k) dF[k] += df[i][k];
+            if (WRT_Q) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) F[k] += fn[i][k];
+            }
         }
         out[i] = dF[2];
         if (WRT_Q && i == j) {
             // d(X_j^T F_j)/dq_j = X_j^T (dF_j + S x* F_j),  S x* F = [-n_y, n_x, 0, -f_y, f_x, 0]
-            dF[0] -= F[6 * i + 1]; dF[1] += F[6 * i + 0];
-            dF[3] -= F[6 * i + 4]; dF[4] += F[6 * i + 3];
+            dF[0] -= F[1]; dF[1] += F[0];
+            dF[3] -= F[4]; dF[4] += F[3];
         }
-        if (i > 0 && i <= I7_NJ - 1) {
-            // nothing to propagate while dF is still identically zero (i > j never happens here: dF != 0 only once i <= 5)
+        if (i > 0) {
             T E[9], o[6];
             joint_E(rob, i, cs[i], cs[6 + i], E);
             xfrc_t(E, rob.p[i], dF, o);
 #pragma unroll
             for (int k = 0; k < 6; ++k) dF[k] = o[k];
+            if (WRT_Q && i > j) {
+                xfrc_t(E, rob.p[i], F, o);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) F[k] = o[k];
+            }
         }
     }
 }

@@ -2,11 +2,17 @@
 // input trajectory and the output trajectory stays in shared memory / registers.
 //
 // Phases per SQP iteration (reference call stack: src/osqp_sqp.py:76-93):
-//   setup     per-knot FK + cost terms, ABA, M^-1 columns, analytic dID columns, -M^-1 dID  (src/osqp_solver.py:70-135)
+//   setup     per-knot FK + cost terms, mass-matrix columns (CRBA by unit-acceleration RNEA), bias torques,
+//             M^-1 / forward dynamics by a 6x6 LDL', analytic dID columns, -M^-1 dID, and every stage-local
+//             product the QP recursion needs — all parallel over (knot, column) tasks    (src/osqp_solver.py:70-135)
 //   riccati   exact solve of the equality-constrained QP  min 1/2 z'Pz + g'z  s.t.  Az = l  by a backward
-//             block recursion over the knots (block LDL' of the block-tridiagonal KKT system in stage order,
-//             12x12 / 6x6 blocks) and a forward roll-out                                   (src/osqp_solver.py:137-143)
-//   merit     all nine line-search candidates (base + 8 alphas) x N knots in parallel     (src/osqp_sqp.py:13-74)
+//             block recursion over the knots — a block LDL' of the block-tridiagonal KKT system in stage
+//             order.  B_k = [0; H_k] with H_k = dt M^-1 invertible, so the free variable of stage k is taken to
+//             be w = v_{k+1} (u_k = H_k^-1 (w - G_k x_k - c_k)): the sequential part of a stage is ONE 6x6
+//             SPD solve with 13 right-hand sides plus a rank-6 update of the 12x12 value matrix; everything
+//             else is precomputed per knot in parallel.  Forward roll-out, then u_k for all knots in parallel.
+//                                                                                        (src/osqp_solver.py:137-143)
+//   merit     line-search candidates x knots in parallel, evaluated lazily in two waves  (src/osqp_sqp.py:13-74)
 //   update    first-accept alpha selection, XU += alpha (z - XU), statistics              (src/osqp_sqp.py:80-92)
 #pragma once
 #include "i7_rbd.cuh"
@@ -33,39 +39,53 @@ struct SolveParams {
     T* z_out;             // MODE_QP
     T* Adata; T* Pdata; T* g; T* l;   // MODE_DUMP (each may be nullptr)
     T* alpha_out; T* merits_out;      // MODE_LINESEARCH (9 per problem) / MODE_MERIT (6 per problem)
-    T* spill_ws;          // gridDim.x x Layout::reg_size workspace when the gains/z region lives in global memory
+    long long* prof;      // optional: per problem 32 clock64() stamps (phase boundaries), debugging aid
+    T* spill_ws;          // gridDim.x x Layout::reg_size workspace when the knot records live in global memory
     int N, batch, goal_stride, mode, max_qp, regularize;
     T dt, dQ, R, QN, eps, mu, step_tol;
 };
 
-// shared-memory record strides (odd => conflict-free when consecutive threads own consecutive knots)
-constexpr int LIN_GQ = 0, LIN_GV = 36, LIN_H = 72, LIN_CV = 108, LIN_STRIDE = 115;
+// ---- per-knot record (stride odd => conflict-free when consecutive threads own consecutive knots) ----
+constexpr int KR_GQ = 0;      // 36  dt dqdd/dq                        (A_k lower-left)
+constexpr int KR_GV = 36;     // 36  I + dt dqdd/dv                    (A_k lower-right)
+constexpr int KR_CV = 72;     // 6   affine term of the velocity rows  (c_k = [0; cv])
+constexpr int KR_Y = 78;      // 36  M during setup, then Y = H^-1 = M / dt
+constexpr int KR_S = 114;     // 36  S = R_k Y'Y   (MODE_DUMP: H = dt M^-1)
+constexpr int KR_L = 150;     // 78  upper triangle of L = G'SG; setup scratch before that:
+constexpr int KR_CS = 150;    //     12 cos/sin of q_k
+constexpr int KR_MINV = 162;  //     36 M^-1
+constexpr int KR_QDD = 198;   //     6  forward dynamics
+constexpr int KR_BIAS = 204;  //     6  ID(q, qd, 0)
+constexpr int KR_SG = 228;    // 72  S G ; after the stage is eliminated: feedback gain Kw (6x12)
+constexpr int KR_D = 300;     // 6   d = S cv - R Y u ; after elimination: feed-forward kw
+constexpr int KR_HX = 306;    // 12  gx + G'd
+constexpr int KR_STRIDE = 319;
 constexpr int COST_STRIDE = 9;                       // j[6], Q, dQ, R
-constexpr int GAIN_K = 0, GAIN_KFF = 72, GAIN_STRIDE = 79;
-constexpr int SCR_CS = 0, SCR_QDD = 12, SCR_U = 18, SCR_D = 54, SCR_F = 60, SCR_STRIDE = 97;
+// merit scratch per evaluated point (aliases the knot records, dead after the QP solve)
+constexpr int MP_CS = 0, MP_M = 12, MP_B = 48, MP_STRIDE = 55;
 // Riccati work area
-constexpr int WK_P = 0, WK_PV = 144, WK_W = 156, WK_PT = 300, WK_T = 312, WK_F = 348, WK_QUX = 492,
-              WK_QUU = 564, WK_QX = 600, WK_QU = 612, WK_X = 618, WK_SIZE = 618 + 78;
+constexpr int WK_P = 0;        // 2 x 144 value matrices (double buffered)
+constexpr int WK_PV = 288;     // 2 x 12
+constexpr int WK_AUG = 312;    // 2 x (6 x 19): [Hww | Hwx | hw]
+constexpr int WK_X = 540;      // 6 x 13
+constexpr int WK_SIZE = 620;
+constexpr int AUGW = 19;
 
-// Shared-memory layout.  The region `reg` holds the Riccati gains and the QP solution z; the setup-phase
-// scratch aliases it (scratch is dead before the first gain is written).  When the whole layout does not fit
-// the 227 KB of one SM (N = 128 in fp64) `reg` is placed in a per-problem global workspace (L2-resident).
 struct Layout {
-    int xu, goals, x0, lin, cost, work, ls, reg, reg_size, total;
+    int xu, z, goals, x0, cost, work, ls, reg, reg_size, total;
 };
 __host__ __device__ inline Layout make_layout(int N, bool spill) {
     Layout L;
     int o = 0;
     L.xu = o; o += 18 * N;
+    L.z = o; o += 18 * N;
     L.goals = o; o += 3 * N;
     L.x0 = o; o += 12;
-    L.lin = o; o += LIN_STRIDE * (N - 1);
     L.cost = o; o += COST_STRIDE * N;
     L.work = o; o += WK_SIZE;
-    L.ls = o; o += (9 * N + 16 > 272 ? 9 * N + 16 : 272);
+    L.ls = o; o += (4 * 5 * N > 400 ? 4 * 5 * N : 400) + 16;
     L.reg = o;
-    const int a = GAIN_STRIDE * (N - 1) + 18 * N, b = SCR_STRIDE * (N - 1);
-    L.reg_size = a > b ? a : b;
+    L.reg_size = KR_STRIDE * N;
     if (!spill) o += L.reg_size;
     L.total = o;
     return L;
@@ -73,96 +93,137 @@ __host__ __device__ inline Layout make_layout(int N, bool spill) {
 
 template <typename T>
 struct Ptrs {
-    T *xu, *goals, *x0, *lin, *cost, *work, *ls, *gains, *z, *scr;
+    T *xu, *z, *goals, *x0, *cost, *work, *ls, *kr;
+    int merit_cap;      // candidates per merit wave that fit the scratch region
 };
 
 __device__ __constant__ double c_alphas[9] = {0.0, 1.0, 0.5, 0.25, 0.125, 0.0625, 0.03125, 0.015625, 0.0078125};
+// upper triangle of a 12x12 matrix, row-major enumeration
+__device__ __constant__ unsigned char c_tri_r[78] = {
+    0,0,0,0,0,0,0,0,0,0,0,0, 1,1,1,1,1,1,1,1,1,1,1, 2,2,2,2,2,2,2,2,2,2, 3,3,3,3,3,3,3,3,3, 4,4,4,4,4,4,4,4,
+    5,5,5,5,5,5,5, 6,6,6,6,6,6, 7,7,7,7,7, 8,8,8,8, 9,9,9, 10,10, 11};
+__device__ __constant__ unsigned char c_tri_c[78] = {
+    0,1,2,3,4,5,6,7,8,9,10,11, 1,2,3,4,5,6,7,8,9,10,11, 2,3,4,5,6,7,8,9,10,11, 3,4,5,6,7,8,9,10,11, 4,5,6,7,8,9,10,11,
+    5,6,7,8,9,10,11, 6,7,8,9,10,11, 7,8,9,10,11, 8,9,10,11, 9,10,11, 10,11, 11};
 
 // -----------------------------------------------------------------------------------------------------------
-// setup: linearised dynamics and cost terms at the current iterate
+// setup: linearised dynamics, cost terms and all stage-local QP products at the current iterate
 template <typename T, int NT>
-__device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* fext) {
+__device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* fext, bool for_dump,
+                            long long* prof) {
     const int tid = threadIdx.x;
-    const int N = P.N;
-    T* xu = M.xu;
-    // --- per knot: sincos, FK, cost terms, ABA ---
-    for (int k = tid; k < N; k += NT) {
-        const T* xk = xu + 18 * k;
+    int pi = 16;
+#define I7_STAMP() do { if (prof && tid == 0) prof[pi++] = clock64(); } while (0)
+    I7_STAMP();
+    const int N = P.N, nk = N - 1;
+    const T* xu = M.xu;
+    const T dt = P.dt;
+    // S0: cos / sin of every joint angle
+    for (int t = tid; t < 6 * N; t += NT) {
+        const int i = t / N, k = t - i * N;
+        T s, c;
+        sincos_t<T>(xu[18 * k + i], &s, &c);
+        T* kr = M.kr + KR_STRIDE * k;
+        kr[KR_CS + i] = c; kr[KR_CS + 6 + i] = s;
+    }
+    __syncthreads();
+    I7_STAMP();
+    // S1: 6 mass-matrix columns + bias torques per knot (k < N-1), FK / cost terms per knot (k < N)
+    for (int t = tid; t < 7 * nk + N; t += NT) {
+        const int type = t < 7 * nk ? t / nk : 7;
+        const int k = t < 7 * nk ? t - type * nk : t - 7 * nk;
+        T* kr = M.kr + KR_STRIDE * k;
         T cs[12];
 #pragma unroll
-        for (int i = 0; i < 6; ++i) sincos_t<T>(xk[i], &cs[6 + i], &cs[i]);
-        T pee[3], zs[18], ps[18];
-        fk_ee<T>(rob, cs, pee, zs, ps);
-        const T* gk = M.goals + 3 * k;
-        const T e[3] = {pee[0] - gk[0], pee[1] - gk[1], pee[2] - gk[2]};
-        T* ck = M.cost + COST_STRIDE * k;
+        for (int i = 0; i < 12; ++i) cs[i] = kr[KR_CS + i];
+        if (type < 6) {
+            T out[6];
+            crba_column<T>(rob, cs, type, out);
 #pragma unroll
-        for (int i = 0; i < 6; ++i) {
-            const T d[3] = {pee[0] - ps[3 * i], pee[1] - ps[3 * i + 1], pee[2] - ps[3 * i + 2]};
-            T c[3];
-            cross3(zs + 3 * i, d, c);
-            ck[i] = e[0] * c[0] + e[1] * c[1] + e[2] * c[2];
-        }
-        const T nrm = sqrt_t<T>(e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
-        const T sc = P.regularize ? T(1) / (nrm + P.eps) : T(1);
-        ck[6] = (k == N - 1) ? P.QN : T(1);
-        ck[7] = P.dQ * sc;
-        ck[8] = P.R * sc;
-        if (k < N - 1) {
-            T* sk = M.scr + SCR_STRIDE * k;
+            for (int r = 0; r < 6; ++r) kr[KR_Y + 6 * r + type] = out[r];
+        } else if (type == 6) {
+            T qd[6], out[6];
 #pragma unroll
-            for (int i = 0; i < 12; ++i) sk[SCR_CS + i] = cs[i];
-            T qdd[6];
-            aba<T, true>(rob, cs, xk + 6, xk + 12, fext, qdd, sk + SCR_U, sk + SCR_D, sk + SCR_F);
+            for (int i = 0; i < 6; ++i) qd[i] = xu[18 * k + 6 + i];
+            rnea_bias<T>(rob, cs, qd, fext, out);
 #pragma unroll
-            for (int i = 0; i < 6; ++i) sk[SCR_QDD + i] = qdd[i];
-        }
-    }
-    __syncthreads();
-    // --- 18 column tasks per knot: 6 columns of M^-1, 6 of dID/dq, 6 of dID/dqd (column-major task order keeps
-    //     warps uniform) ---
-    const int nk = N - 1;
-    for (int t = tid; t < 18 * nk; t += NT) {
-        const int col = t / nk, k = t - col * nk;
-        const T* sk = M.scr + SCR_STRIDE * k;
-        T* lk = M.lin + LIN_STRIDE * k;
-        const T* xk = xu + 18 * k;
-        T cs[12], out[6];
-#pragma unroll
-        for (int i = 0; i < 12; ++i) cs[i] = sk[SCR_CS + i];
-        if (col < 6) {
-            T U[36], D[6];
-#pragma unroll
-            for (int i = 0; i < 36; ++i) U[i] = sk[SCR_U + i];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) D[i] = sk[SCR_D + i];
-            minv_column<T>(rob, cs, U, D, col, out);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) lk[LIN_H + 6 * r + col] = P.dt * out[r];
+            for (int r = 0; r < 6; ++r) kr[KR_BIAS + r] = out[r];
         } else {
-            T qd[6], qdd[6];
+            T pee[3], zs[18], ps[18];
+            fk_ee<T>(rob, cs, pee, zs, ps);
+            const T* gk = M.goals + 3 * k;
+            const T e[3] = {pee[0] - gk[0], pee[1] - gk[1], pee[2] - gk[2]};
+            T* ck = M.cost + COST_STRIDE * k;
 #pragma unroll
-            for (int i = 0; i < 6; ++i) { qd[i] = xk[6 + i]; qdd[i] = sk[SCR_QDD + i]; }
-            if (col < 12) {
-                T F[36];
-#pragma unroll
-                for (int i = 0; i < 36; ++i) F[i] = sk[SCR_F + i];
-                rnea_dcolumn<T, true>(rob, cs, qd, qdd, F, col - 6, out);
-#pragma unroll
-                for (int r = 0; r < 6; ++r) lk[LIN_GQ + 6 * r + (col - 6)] = out[r];
-            } else {
-                rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, col - 12, out);
-#pragma unroll
-                for (int r = 0; r < 6; ++r) lk[LIN_GV + 6 * r + (col - 12)] = out[r];
+            for (int i = 0; i < 6; ++i) {
+                const T d[3] = {pee[0] - ps[3 * i], pee[1] - ps[3 * i + 1], pee[2] - ps[3 * i + 2]};
+                T c[3];
+                cross3(zs + 3 * i, d, c);
+                ck[i] = e[0] * c[0] + e[1] * c[1] + e[2] * c[2];
             }
+            const T nrm = sqrt_t<T>(e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+            const T sc = P.regularize ? T(1) / (nrm + P.eps) : T(1);
+            ck[6] = (k == N - 1) ? P.QN : T(1);
+            ck[7] = P.dQ * sc;
+            ck[8] = P.R * sc;
         }
     }
     __syncthreads();
-    // --- G = -dt Minv dID (+ I on the velocity block), in place, one column per task ---
+    I7_STAMP();
+    // S2: M^-1 columns and qdd = M^-1 (tau - bias): every task factors M in registers (LDL') and solves one rhs
+    for (int t = tid; t < 7 * nk; t += NT) {
+        const int c = t / nk, k = t - c * nk;
+        T* kr = M.kr + KR_STRIDE * k;
+        T A[6][6], dinv[6], b[6];
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int q = 0; q <= r; ++q) A[r][q] = kr[KR_Y + 6 * r + q];
+        if (c < 6) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) b[r] = (r == c) ? T(1) : T(0);
+        } else {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) b[r] = xu[18 * k + 12 + r] - kr[KR_BIAS + r];
+        }
+        spd6_factor<T>(A, dinv);
+        spd6_solve_factored<T>(A, dinv, b);
+        if (c < 6) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) kr[KR_MINV + 6 * r + c] = b[r];
+        } else {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) kr[KR_QDD + r] = b[r];
+        }
+    }
+    __syncthreads();
+    I7_STAMP();
+    // S3: 12 analytic inverse-dynamics derivative columns per knot (raw d tau/dq, d tau/dqd into the G slots)
     for (int t = tid; t < 12 * nk; t += NT) {
         const int col = t / nk, k = t - col * nk;
-        T* lk = M.lin + LIN_STRIDE * k;
-        T* G = lk + (col < 6 ? LIN_GQ : LIN_GV);
+        T* kr = M.kr + KR_STRIDE * k;
+        T cs[12], qd[6], qdd[6], out[6];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) cs[i] = kr[KR_CS + i];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { qd[i] = xu[18 * k + 6 + i]; qdd[i] = kr[KR_QDD + i]; }
+        if (col < 6) {
+            rnea_dcolumn<T, true>(rob, cs, qd, qdd, fext, col, out);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) kr[KR_GQ + 6 * r + col] = out[r];
+        } else {
+            rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, col - 6, out);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) kr[KR_GV + 6 * r + (col - 6)] = out[r];
+        }
+    }
+    __syncthreads();
+    I7_STAMP();
+    // S4: G = -dt Minv dID (+ I on the velocity block), in place, one column per task
+    for (int t = tid; t < 12 * nk; t += NT) {
+        const int col = t / nk, k = t - col * nk;
+        T* kr = M.kr + KR_STRIDE * k;
+        T* G = kr + (col < 6 ? KR_GQ : KR_GV);
         const int c = col < 6 ? col : col - 6;
         T raw[6], y[6];
 #pragma unroll
@@ -171,245 +232,227 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
         for (int r = 0; r < 6; ++r) {
             T acc = T(0);
 #pragma unroll
-            for (int s = 0; s < 6; ++s) acc -= lk[LIN_H + 6 * r + s] * raw[s];
-            y[r] = acc;
+            for (int s = 0; s < 6; ++s) acc -= kr[KR_MINV + 6 * r + s] * raw[s];
+            y[r] = dt * acc;
         }
         if (col >= 6) y[c] += T(1);
 #pragma unroll
         for (int r = 0; r < 6; ++r) G[6 * r + c] = y[r];
     }
     __syncthreads();
-    // --- affine term: cv = v + dt qdd - Gq q - Gv v - H u   (top half of c_k is identically zero) ---
-    for (int t = tid; t < 6 * nk; t += NT) {
-        const int r = t / nk, k = t - r * nk;
-        T* lk = M.lin + LIN_STRIDE * k;
-        const T* sk = M.scr + SCR_STRIDE * k;
+    I7_STAMP();
+    // S5: cv = v + dt qdd - Gq q - Gv v - dt Minv u ;  S = R Y'Y with Y = M / dt  (dump mode: H = dt Minv instead)
+    for (int t = tid; t < 42 * nk; t += NT) {
+        const int e = t / nk, k = t - e * nk;
+        T* kr = M.kr + KR_STRIDE * k;
         const T* xk = xu + 18 * k;
-        T acc = xk[6 + r] + P.dt * sk[SCR_QDD + r];
+        if (e < 6) {
+            const int r = e;
+            T a0 = xk[6 + r] + dt * kr[KR_QDD + r], a1 = T(0), a2 = T(0);
 #pragma unroll
-        for (int s = 0; s < 6; ++s)
-            acc -= lk[LIN_GQ + 6 * r + s] * xk[s] + lk[LIN_GV + 6 * r + s] * xk[6 + s] + lk[LIN_H + 6 * r + s] * xk[12 + s];
-        lk[LIN_CV + r] = acc;
+            for (int s = 0; s < 6; ++s) {
+                a0 -= kr[KR_GQ + 6 * r + s] * xk[s];
+                a1 -= kr[KR_GV + 6 * r + s] * xk[6 + s];
+                a2 -= kr[KR_MINV + 6 * r + s] * xk[12 + s];
+            }
+            kr[KR_CV + r] = a0 + a1 + dt * a2;
+        } else {
+            const int e2 = e - 6, r = e2 / 6, c = e2 - 6 * r;
+            if (for_dump) {
+                kr[KR_S + e2] = dt * kr[KR_MINV + e2];
+            } else {
+                T acc = T(0);
+#pragma unroll
+                for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * s + r] * kr[KR_Y + 6 * s + c];
+                kr[KR_S + e2] = (M.cost[COST_STRIDE * k + 8] / (dt * dt)) * acc;
+            }
+        }
     }
     __syncthreads();
+    I7_STAMP();
+    if (for_dump) return;
+    // S6: SG = S G (6x12),  d = S cv - (R/dt) M u
+    for (int t = tid; t < 78 * nk; t += NT) {
+        const int e = t / nk, k = t - e * nk;
+        T* kr = M.kr + KR_STRIDE * k;
+        if (e < 72) {
+            const int r = e / 12, c = e - 12 * r;
+            const T* G = kr + (c < 6 ? KR_GQ + c : KR_GV + c - 6);
+            T acc = T(0);
+#pragma unroll
+            for (int s = 0; s < 6; ++s) acc += kr[KR_S + 6 * r + s] * G[6 * s];
+            kr[KR_SG + e] = acc;
+        } else {
+            const int r = e - 72;
+            const T* xk = xu + 18 * k;
+            T a0 = T(0), a1 = T(0);
+#pragma unroll
+            for (int s = 0; s < 6; ++s) {
+                a0 += kr[KR_S + 6 * r + s] * kr[KR_CV + s];
+                a1 += kr[KR_Y + 6 * r + s] * xk[12 + s];
+            }
+            kr[KR_D + r] = a0 - (M.cost[COST_STRIDE * k + 8] / dt) * a1;
+        }
+    }
+    __syncthreads();
+    I7_STAMP();
+    // S7: L = G'(SG) (upper triangle, overwrites the setup scratch), hx = gx + G'd, Y = M / dt in place
+    for (int t = tid; t < 126 * nk; t += NT) {
+        const int e = t / nk, k = t - e * nk;
+        T* kr = M.kr + KR_STRIDE * k;
+        if (e < 78) {
+            const int r = c_tri_r[e], c = c_tri_c[e];
+            const T* Gr = kr + (r < 6 ? KR_GQ + r : KR_GV + r - 6);
+            T acc = T(0);
+#pragma unroll
+            for (int s = 0; s < 6; ++s) acc += Gr[6 * s] * kr[KR_SG + 12 * s + c];
+            kr[KR_L + e] = acc;
+        } else if (e < 90) {
+            const int r = e - 78;
+            const T* ck = M.cost + COST_STRIDE * k;
+            const T* Gr = kr + (r < 6 ? KR_GQ + r : KR_GV + r - 6);
+            T acc = r < 6 ? ck[6] * ck[r] : ck[7] * xu[18 * k + r];
+#pragma unroll
+            for (int s = 0; s < 6; ++s) acc += Gr[6 * s] * kr[KR_D + s];
+            kr[KR_HX + r] = acc;
+        } else {
+            const int e2 = e - 90;
+            kr[KR_Y + e2] = kr[KR_Y + e2] / dt;
+        }
+    }
+    __syncthreads();
+    I7_STAMP();
+#undef I7_STAMP
 }
 
 // -----------------------------------------------------------------------------------------------------------
-// In-register LDL' solve of the 6x6 SPD system  Quu x = b
-template <typename T> I7_DEV void spd6_solve(const T* A /*36, row-major*/, T* b /*6, in/out*/) {
-    T Lm[6][6], d[6], dinv[6];
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-        T dj = A[6 * j + j];
-#pragma unroll
-        for (int k = 0; k < j; ++k) dj -= Lm[j][k] * Lm[j][k] * d[k];
-        d[j] = dj;
-        dinv[j] = T(1) / dj;
-#pragma unroll
-        for (int i = j + 1; i < 6; ++i) {
-            T s = A[6 * i + j];
-#pragma unroll
-            for (int k = 0; k < j; ++k) s -= Lm[i][k] * Lm[j][k] * d[k];
-            Lm[i][j] = s * dinv[j];
-        }
+// Hww / Hwx / hw of stage k from the value function (Pm, pv) of stage k+1:
+//   Hww = P_vv + S,  Hwx = [P_qv' - SG_q, dt P_qv' - SG_v],  hw = p_v - d
+template <typename T>
+I7_DEV void aug_from_P_entry(T* aug, const T* kr, int r, int c, T val, T dt) {
+    // called by the thread that owns P[r][c], r <= c
+    if (r < 6 && c >= 6) {
+        const int i = c - 6;   // Hwx[i][r] = P[r][6+i] - SG[i][r] ;  Hwx[i][6+r] = dt P[r][6+i] - SG[i][6+r]
+        aug[AUGW * i + 6 + r] = val - kr[KR_SG + 12 * i + r];
+        aug[AUGW * i + 12 + r] = dt * val - kr[KR_SG + 12 * i + 6 + r];
+    } else if (r >= 6) {
+        const int i = r - 6, j = c - 6;
+        aug[AUGW * i + j] = val + kr[KR_S + 6 * i + j];
+        if (i != j) aug[AUGW * j + i] = val + kr[KR_S + 6 * j + i];
     }
-#pragma unroll
-    for (int i = 1; i < 6; ++i)
-#pragma unroll
-        for (int k = 0; k < i; ++k) b[i] -= Lm[i][k] * b[k];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) b[i] *= dinv[i];
-#pragma unroll
-    for (int i = 4; i >= 0; --i)
-#pragma unroll
-        for (int k = i + 1; k < 6; ++k) b[i] -= Lm[k][i] * b[k];
 }
 
 // riccati: backward recursion for the gains, forward roll-out for z.  x0 = measured state (l[:12] = -xs).
 template <typename T, int NT>
-__device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M) {
+__device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long long* prof) {
     const int tid = threadIdx.x;
+    long long acc_r2 = 0, acc_r3 = 0, tt = 0;
     const int N = P.N;
     const T dt = P.dt;
     T* wk = M.work;
     const T* xu = M.xu;
-    // terminal value function: P_N = blkdiag(QN j j', dQ_N I), p_N = [QN j; dQ_N v]
+    int cur = 0;
+    // terminal value function: P_N = blkdiag(QN j j', dQ_N I), p_N = [QN j; dQ_N v]; aug for stage N-2
     {
         const T* cN = M.cost + COST_STRIDE * (N - 1);
         const T* xN = xu + 18 * (N - 1);
-        for (int t = tid; t < 156; t += NT) {
-            if (t < 144) {
-                const int r = t / 12, c = t - 12 * r;
+        const T* kr = M.kr + KR_STRIDE * (N - 2);
+        for (int t = tid; t < 90; t += NT) {
+            if (t < 78) {
+                const int r = c_tri_r[t], c = c_tri_c[t];
                 T v = T(0);
-                if (r < 6 && c < 6) v = cN[6] * cN[r] * cN[c];
+                if (c < 6) v = cN[6] * cN[r] * cN[c];
                 else if (r == c) v = cN[7];
-                wk[WK_P + t] = v;
+                wk[WK_P + 12 * r + c] = v;
+                wk[WK_P + 12 * c + r] = v;
+                aug_from_P_entry<T>(wk + WK_AUG, kr, r, c, v, dt);
             } else {
-                const int r = t - 144;
-                wk[WK_PV + r] = r < 6 ? cN[6] * cN[r] : cN[7] * xN[r];
+                const int r = t - 78;
+                const T v = r < 6 ? cN[6] * cN[r] : cN[7] * xN[r];
+                wk[WK_PV + r] = v;
+                if (r >= 6) wk[WK_AUG + AUGW * (r - 6) + 18] = v - kr[KR_D + r - 6];
             }
         }
     }
     __syncthreads();
     for (int k = N - 2; k >= 0; --k) {
-        const T* lk = M.lin + LIN_STRIDE * k;
-        const T* Gq = lk + LIN_GQ; const T* Gv = lk + LIN_GV; const T* H = lk + LIN_H; const T* cv = lk + LIN_CV;
-        const T* ck = M.cost + COST_STRIDE * k;
-        const T* xk = xu + 18 * k;
-        T* gk = M.gains + GAIN_STRIDE * k;
-        const T* Pm = wk + WK_P;
-        // step A: W = P A, ptil = p + P[:,6:] cv, Tm = Pvv H
-        for (int t = tid; t < 192; t += NT) {
-            if (t < 144) {
-                const int r = t / 12, c = t - 12 * r;
-                T acc;
-                if (c < 6) {
-                    acc = Pm[12 * r + c];
-#pragma unroll
-                    for (int s = 0; s < 6; ++s) acc += Pm[12 * r + 6 + s] * Gq[6 * s + c];
-                } else {
-                    acc = dt * Pm[12 * r + c - 6];
-#pragma unroll
-                    for (int s = 0; s < 6; ++s) acc += Pm[12 * r + 6 + s] * Gv[6 * s + c - 6];
-                }
-                wk[WK_W + t] = acc;
-            } else if (t < 156) {
-                const int r = t - 144;
-                T acc = wk[WK_PV + r];
-#pragma unroll
-                for (int s = 0; s < 6; ++s) acc += Pm[12 * r + 6 + s] * cv[s];
-                wk[WK_PT + r] = acc;
-            } else {
-                const int e = t - 156, r = e / 6, c = e - 6 * r;
-                T acc = T(0);
-#pragma unroll
-                for (int s = 0; s < 6; ++s) acc += Pm[12 * (6 + r) + 6 + s] * H[6 * s + c];
-                wk[WK_T + e] = acc;
-            }
-        }
-        __syncthreads();
-        // step B: Qxx = Q + A'W, Qux = H W[6:,:], Quu = R I + H Tm, qx = gx + A' ptil, qu = gu + H ptil[6:]
-        {
-            const T* W = wk + WK_W; const T* pt = wk + WK_PT;
-            for (int t = tid; t < 270; t += NT) {
-                if (t < 144) {
-                    const int r = t / 12, c = t - 12 * r;
-                    T acc;
-                    if (r < 6) {
-                        acc = W[12 * r + c];
-#pragma unroll
-                        for (int s = 0; s < 6; ++s) acc += Gq[6 * s + r] * W[12 * (6 + s) + c];
-                        if (c < 6) acc += ck[6] * ck[r] * ck[c];
-                    } else {
-                        acc = dt * W[12 * (r - 6) + c];
-#pragma unroll
-                        for (int s = 0; s < 6; ++s) acc += Gv[6 * s + r - 6] * W[12 * (6 + s) + c];
-                        if (r == c) acc += ck[7];
-                    }
-                    wk[WK_F + t] = acc;
-                } else if (t < 216) {
-                    const int e = t - 144, r = e / 12, c = e - 12 * r;
-                    T acc = T(0);
-#pragma unroll
-                    for (int s = 0; s < 6; ++s) acc += H[6 * r + s] * W[12 * (6 + s) + c];
-                    wk[WK_QUX + e] = acc;
-                } else if (t < 252) {
-                    const int e = t - 216, r = e / 6, c = e - 6 * r;
-                    T acc = (r == c) ? ck[8] : T(0);
-#pragma unroll
-                    for (int s = 0; s < 6; ++s) acc += H[6 * r + s] * wk[WK_T + 6 * s + c];
-                    wk[WK_QUU + e] = acc;
-                } else if (t < 264) {
-                    const int r = t - 252;
-                    T acc;
-                    if (r < 6) {
-                        acc = ck[6] * ck[r] + pt[r];
-#pragma unroll
-                        for (int s = 0; s < 6; ++s) acc += Gq[6 * s + r] * pt[6 + s];
-                    } else {
-                        acc = ck[7] * xk[r] + dt * pt[r - 6];
-#pragma unroll
-                        for (int s = 0; s < 6; ++s) acc += Gv[6 * s + r - 6] * pt[6 + s];
-                    }
-                    wk[WK_QX + r] = acc;
-                } else {
-                    const int r = t - 264;
-                    T acc = ck[8] * xk[12 + r];
-#pragma unroll
-                    for (int s = 0; s < 6; ++s) acc += H[6 * r + s] * pt[6 + s];
-                    wk[WK_QU + r] = acc;
-                }
-            }
-        }
-        __syncthreads();
-        // step C: X = Quu^-1 [Qux | qu]  (13 independent right-hand sides, one thread each, LDL' in registers)
+        T* kr = M.kr + KR_STRIDE * k;
+        T* aug = wk + WK_AUG + 114 * cur;
+        // R2: X = Hww^-1 [Hwx | hw]: 13 independent right-hand sides, LDL' in registers
+        if (prof && tid == 0) tt = clock64();
         for (int t = tid; t < 13; t += NT) {
-            T A[36], b[6];
+            T A[6][6], dinv[6], b[6];
 #pragma unroll
-            for (int i = 0; i < 36; ++i) A[i] = wk[WK_QUU + i];
+            for (int r = 0; r < 6; ++r)
 #pragma unroll
-            for (int r = 0; r < 6; ++r) b[r] = (t < 12) ? wk[WK_QUX + 12 * r + t] : wk[WK_QU + r];
-            spd6_solve<T>(A, b);
+                for (int q = 0; q <= r; ++q) A[r][q] = aug[AUGW * r + q];
 #pragma unroll
-            for (int r = 0; r < 6; ++r) {
-                wk[WK_X + 13 * r + t] = b[r];
-                if (t < 12) gk[GAIN_K + 12 * r + t] = -b[r]; else gk[GAIN_KFF + r] = -b[r];
-            }
+            for (int r = 0; r < 6; ++r) b[r] = aug[AUGW * r + 6 + t];
+            spd6_factor<T>(A, dinv);
+            spd6_solve_factored<T>(A, dinv, b);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) wk[WK_X + 13 * r + t] = b[r];
         }
         __syncthreads();
-        // step D: P = Qxx - Qux' X[:, :12] (symmetrised), p = qx - Qux' X[:, 12]
+        if (prof && tid == 0) { const long long n = clock64(); acc_r2 += n - tt; tt = n; }
+        // R3: P = Qx + L + T'aT - Hwx'X, p = hx + [pq; dt pq] - Hwx' x13; gains into the record; aug of stage k-1
         {
-            const T* X = wk + WK_X; const T* Qux = wk + WK_QUX;
-            for (int t = tid; t < 90; t += NT) {
+            const T* Pm = wk + WK_P + 144 * cur;
+            const T* pv = wk + WK_PV + 12 * cur;
+            T* Pn = wk + WK_P + 144 * (cur ^ 1);
+            T* pn = wk + WK_PV + 12 * (cur ^ 1);
+            T* augn = wk + WK_AUG + 114 * (cur ^ 1);
+            const T* X = wk + WK_X;
+            const T* ck = M.cost + COST_STRIDE * k;
+            const T* krn = M.kr + KR_STRIDE * (k > 0 ? k - 1 : 0);
+            for (int t = tid; t < 168; t += NT) {
                 if (t < 78) {
-                    // upper triangle (r <= c), mirrored
-                    int r = 0, e = t;
-                    while (e >= 12 - r) { e -= 12 - r; ++r; }
-                    const int c = r + e;
-                    T acc = T(0.5) * (wk[WK_F + 12 * r + c] + wk[WK_F + 12 * c + r]);
+                    const int r = c_tri_r[t], c = c_tri_c[t];
+                    const int ra = r < 6 ? r : r - 6, ca = c < 6 ? c : c - 6;
+                    T acc = kr[KR_L + t] + Pm[12 * ra + ca] * ((r < 6 ? T(1) : dt) * (c < 6 ? T(1) : dt));
+                    if (c < 6) acc += ck[6] * ck[r] * ck[c];
+                    else if (r == c) acc += ck[7];
 #pragma unroll
-                    for (int s = 0; s < 6; ++s) acc -= Qux[12 * s + r] * X[13 * s + c];
-                    wk[WK_P + 12 * r + c] = acc;
-                    wk[WK_P + 12 * c + r] = acc;
-                } else {
+                    for (int s = 0; s < 6; ++s) acc -= aug[AUGW * s + 6 + r] * X[13 * s + c];
+                    Pn[12 * r + c] = acc;
+                    Pn[12 * c + r] = acc;
+                    if (k > 0) aug_from_P_entry<T>(augn, krn, r, c, acc, dt);
+                } else if (t < 90) {
                     const int r = t - 78;
-                    T acc = wk[WK_QX + r];
+                    T acc = kr[KR_HX + r] + (r < 6 ? pv[r] : dt * pv[r - 6]);
 #pragma unroll
-                    for (int s = 0; s < 6; ++s) acc -= Qux[12 * s + r] * X[13 * s + 12];
-                    wk[WK_PV + r] = acc;
+                    for (int s = 0; s < 6; ++s) acc -= aug[AUGW * s + 6 + r] * X[13 * s + 12];
+                    pn[r] = acc;
+                    if (k > 0 && r >= 6) augn[AUGW * (r - 6) + 18] = acc - krn[KR_D + r - 6];
+                } else {
+                    // feedback / feed-forward of w = v_{k+1}: Kw = -X[:, :12], kw = -X[:, 12] (overwrites SG, d)
+                    const int e = t - 90, r = e / 13, c = e - 13 * r;
+                    const T v = -X[13 * r + c];
+                    if (c < 12) kr[KR_SG + 12 * r + c] = v; else kr[KR_D + r] = v;
                 }
             }
         }
         __syncthreads();
+        if (prof && tid == 0) acc_r3 += clock64() - tt;
+        cur ^= 1;
     }
-    // forward roll-out by warp 0: x_0 = xs, u_k = K_k x_k + k_k, x_{k+1} = A_k x_k + B_k u_k + c_k
+    if (prof && tid == 0) { prof[10] = acc_r2; prof[11] = acc_r3; tt = clock64(); }
+    // forward roll-out by warp 0: x_0 = xs, v_{k+1} = Kw_k x_k + kw_k, q_{k+1} = q_k + dt v_k
     if (tid < 32) {
         T* z = M.z;
         if (tid < 12) z[tid] = M.x0[tid];
         __syncwarp();
         for (int k = 0; k < N - 1; ++k) {
-            const T* lk = M.lin + LIN_STRIDE * k;
-            const T* gk = M.gains + GAIN_STRIDE * k;
+            const T* kr = M.kr + KR_STRIDE * k;
             T* zk = z + 18 * k;
             if (tid < 6) {
-                T a0 = gk[GAIN_KFF + tid], a1 = T(0);
+                T a0 = kr[KR_D + tid], a1 = T(0);
 #pragma unroll
                 for (int c = 0; c < 6; ++c) {
-                    a0 += gk[GAIN_K + 12 * tid + c] * zk[c];
-                    a1 += gk[GAIN_K + 12 * tid + 6 + c] * zk[6 + c];
+                    a0 += kr[KR_SG + 12 * tid + c] * zk[c];
+                    a1 += kr[KR_SG + 12 * tid + 6 + c] * zk[6 + c];
                 }
-                zk[12 + tid] = a0 + a1;
-            }
-            __syncwarp();
-            if (tid < 6) {
-                T a0 = lk[LIN_CV + tid], a1 = T(0), a2 = T(0);
-#pragma unroll
-                for (int s = 0; s < 6; ++s) {
-                    a0 += lk[LIN_GQ + 6 * tid + s] * zk[s];
-                    a1 += lk[LIN_GV + 6 * tid + s] * zk[6 + s];
-                    a2 += lk[LIN_H + 6 * tid + s] * zk[12 + s];
-                }
-                zk[18 + 6 + tid] = a0 + a1 + a2;
+                zk[18 + 6 + tid] = a0 + a1;
             } else if (tid < 12) {
                 const int r = tid - 6;
                 zk[18 + r] = zk[r] + dt * zk[6 + r];
@@ -418,49 +461,40 @@ __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M) {
         }
     }
     __syncthreads();
+    if (prof && tid == 0) { prof[12] = clock64() - tt; tt = clock64(); }
+    // controls for all knots in parallel: u_k = Y_k (v_{k+1} - Gq q_k - Gv v_k - cv_k)
+    {
+        const int nk = N - 1;
+        T* z = M.z;
+        T* tmp = M.ls;
+        for (int t = tid; t < 6 * nk; t += NT) {
+            const int r = t / nk, k = t - r * nk;
+            const T* kr = M.kr + KR_STRIDE * k;
+            const T* zk = z + 18 * k;
+            T a0 = zk[18 + 6 + r] - kr[KR_CV + r], a1 = T(0);
+#pragma unroll
+            for (int s = 0; s < 6; ++s) {
+                a0 -= kr[KR_GQ + 6 * r + s] * zk[s];
+                a1 -= kr[KR_GV + 6 * r + s] * zk[6 + s];
+            }
+            tmp[6 * k + r] = a0 + a1;
+        }
+        __syncthreads();
+        for (int t = tid; t < 6 * nk; t += NT) {
+            const int r = t / nk, k = t - r * nk;
+            const T* kr = M.kr + KR_STRIDE * k;
+            T acc = T(0);
+#pragma unroll
+            for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * r + s] * tmp[6 * k + s];
+            z[18 * k + 12 + r] = acc;
+        }
+        __syncthreads();
+    }
+    if (prof && tid == 0) prof[13] = clock64() - tt;
 }
 
 // -----------------------------------------------------------------------------------------------------------
-// merit terms of knot k of the trajectory  x = xa + alpha (xb - xa):  comps = {qcost, vcost, ucost, integ_err}
-template <typename T>
-I7_DEV void merit_knot(const Robot<T>& rob, const SolveParams<T>& P, const T* xa, const T* xb, T alpha, int k,
-                       const T* goal, const T* fext, T* comps) {
-    const int N = P.N;
-    T x[18], xn[12];
-    const int nloc = (k < N - 1) ? 18 : 12;
-#pragma unroll
-    for (int i = 0; i < 18; ++i) x[i] = (i < nloc) ? xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]) : T(0);
-    T cs[12];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) sincos_t<T>(x[i], &cs[6 + i], &cs[i]);
-    T pee[3];
-    fk_ee_only<T>(rob, cs, pee);
-    const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
-    const T Qk = (k == N - 1) ? P.QN : T(1);
-    comps[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
-    T vv = T(0), uu = T(0);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) { vv += x[6 + i] * x[6 + i]; uu += x[12 + i] * x[12 + i]; }
-    comps[1] = P.dQ * vv;
-    comps[2] = P.R * uu;
-    comps[3] = T(0);
-    if (k < N - 1) {
-#pragma unroll
-        for (int i = 0; i < 12; ++i) xn[i] = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
-        T qdd[6];
-        aba<T, false>(rob, cs, x + 6, x + 12, fext, qdd, nullptr, nullptr, nullptr);
-        T qe = T(0), ve = T(0);
-#pragma unroll
-        for (int i = 0; i < 6; ++i) {
-            const T dq = x[i] + x[6 + i] * P.dt - xn[i];
-            const T dv = x[6 + i] + qdd[i] * P.dt - xn[6 + i];
-            qe += dq * dq; ve += dv * dv;
-        }
-        comps[3] = sqrt_t<T>(qe) + sqrt_t<T>(ve);
-    }
-}
-
-// fixed-order block reduction helper: sum of vals[0..n) by one warp (lane-strided partial sums + xor tree)
+// fixed-order reduction helper: sum of vals[0..n) by one warp (lane-strided partial sums + xor tree)
 template <typename T> I7_DEV T warp_sum_strided(const T* vals, int n, int lane) {
     T s = T(0);
     for (int i = lane; i < n; i += 32) s += vals[i];
@@ -469,29 +503,122 @@ template <typename T> I7_DEV T warp_sum_strided(const T* vals, int n, int lane) 
     return s;
 }
 
-// merits of the nine candidates (index 0 = base) between xa (current iterate) and xb (full step)
+// Merit terms of the candidates c0 .. c0+nc-1 (index into c_alphas; 0 = base) of the line  xa + alpha (xb - xa):
+// comps[4 * (ci * N + k) + {0,1,2,3}] = {qcost, vcost, ucost, integrator_err} of knot k   (src/osqp_sqp.py:13-47).
+// Forward dynamics per point: M columns + bias by 7 parallel tasks, then one 6x6 LDL' solve.
 template <typename T, int NT>
-__device__ void phase_merits(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* xa,
-                             const T* xb, const T* fext, T* merits /*9, shared*/) {
-    const int tid = threadIdx.x, N = P.N;
-    T* part = M.ls;
-    for (int t = tid; t < 9 * N; t += NT) {
-        const int c = t / N, k = t - c * N;
-        const T alpha = T(c_alphas[c]);
-        T comps[4];
-        merit_knot<T>(rob, P, xa, xb, alpha, k, M.goals + 3 * k, fext, comps);
-        part[t] = comps[0] + comps[1] + comps[2] + P.mu * comps[3];
+__device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* xa, const T* xb,
+                             const T* fext, int c0, int nc, T* comps) {
+    const int tid = threadIdx.x, N = P.N, nk = N - 1;
+    const int npts = nc * N;
+    T* scr = M.kr;
+    // M0: cos / sin
+    for (int t = tid; t < 6 * npts; t += NT) {
+        const int i = t / npts, p = t - i * npts;
+        const int ci = p / N, k = p - ci * N;
+        const T alpha = T(c_alphas[c0 + ci]);
+        const T q = xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]);
+        T s, c;
+        sincos_t<T>(q, &s, &c);
+        scr[MP_STRIDE * p + MP_CS + i] = c; scr[MP_STRIDE * p + MP_CS + 6 + i] = s;
     }
     __syncthreads();
+    // M1: mass-matrix columns and bias torques at every point with dynamics (k < N-1)
+    for (int t = tid; t < 7 * nc * nk; t += NT) {
+        const int type = t / (nc * nk), rem = t - type * nc * nk;
+        const int ci = rem / nk, k = rem - ci * nk;
+        const int p = ci * N + k;
+        T* sp = scr + MP_STRIDE * p;
+        T cs[12], out[6];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) cs[i] = sp[MP_CS + i];
+        if (type < 6) {
+            crba_column<T>(rob, cs, type, out);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) sp[MP_M + 6 * r + type] = out[r];
+        } else {
+            const T alpha = T(c_alphas[c0 + ci]);
+            T qd[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) qd[i] = xa[18 * k + 6 + i] + alpha * (xb[18 * k + 6 + i] - xa[18 * k + 6 + i]);
+            rnea_bias<T>(rob, cs, qd, fext, out);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) sp[MP_B + r] = out[r];
+        }
+    }
+    __syncthreads();
+    // M2: per point: FK cost, quadratic costs, qdd = M^-1 (u - b), integrator error
+    for (int p = tid; p < npts; p += NT) {
+        const int ci = p / N, k = p - ci * N;
+        const T alpha = T(c_alphas[c0 + ci]);
+        const T* sp = scr + MP_STRIDE * p;
+        T x[18];
+        const int nloc = (k < nk) ? 18 : 12;
+#pragma unroll
+        for (int i = 0; i < 18; ++i) x[i] = (i < nloc) ? xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]) : T(0);
+        T cs[12], pee[3];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) cs[i] = sp[MP_CS + i];
+        fk_ee_only<T>(rob, cs, pee);
+        const T* goal = M.goals + 3 * k;
+        const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
+        const T Qk = (k == N - 1) ? P.QN : T(1);
+        T* out = comps + 4 * p;
+        out[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+        T vv = T(0), uu = T(0);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { vv += x[6 + i] * x[6 + i]; uu += x[12 + i] * x[12 + i]; }
+        out[1] = P.dQ * vv;
+        out[2] = P.R * uu;
+        T ie = T(0);
+        if (k < nk) {
+            T A[6][6], dinv[6], b[6];
+#pragma unroll
+            for (int r = 0; r < 6; ++r)
+#pragma unroll
+                for (int q = 0; q <= r; ++q) A[r][q] = sp[MP_M + 6 * r + q];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) b[r] = x[12 + r] - sp[MP_B + r];
+            spd6_factor<T>(A, dinv);
+            spd6_solve_factored<T>(A, dinv, b);
+            T qe = T(0), ve = T(0);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const T xnq = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
+                const T xnv = xa[18 * (k + 1) + 6 + i] + alpha * (xb[18 * (k + 1) + 6 + i] - xa[18 * (k + 1) + 6 + i]);
+                const T dq = x[i] + x[6 + i] * P.dt - xnq;
+                const T dv = x[6 + i] + b[i] * P.dt - xnv;
+                qe += dq * dq; ve += dv * dv;
+            }
+            ie = sqrt_t<T>(qe) + sqrt_t<T>(ve);
+        }
+        out[3] = ie;
+    }
+    __syncthreads();
+}
+
+// merits[c] for c in [c0, c0 + nc): sum over knots + initial-state violation term
+template <typename T, int NT>
+__device__ void merit_reduce(const SolveParams<T>& P, const T* xa, const T* xb, int c0, int nc, const T* comps, T* merits,
+                             T* comps_out /* 4 sums of candidate c0 or nullptr */) {
+    const int tid = threadIdx.x, N = P.N;
     const int warp = tid >> 5, lane = tid & 31;
-    for (int c = warp; c < 9; c += NT / 32) {
-        T s = warp_sum_strided<T>(part + c * N, N, lane);
+    for (int ci = warp; ci < nc; ci += NT / 32) {
+        T s[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            T a = T(0);
+            for (int k = lane; k < N; k += 32) a += comps[4 * (ci * N + k) + j];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            s[j] = a;
+        }
         if (lane == 0) {
-            // initial-state violation || x_new[:12] - x[:12] ||  (src/osqp_sqp.py:54,64)
-            const T alpha = T(c_alphas[c]);
+            const T alpha = T(c_alphas[c0 + ci]);
             T d2 = T(0);
             for (int i = 0; i < 12; ++i) { const T d = alpha * (xb[i] - xa[i]); d2 += d * d; }
-            merits[c] = s + P.mu * sqrt_t<T>(d2);
+            merits[c0 + ci] = s[0] + s[1] + s[2] + P.mu * (s[3] + sqrt_t<T>(d2));
+            if (comps_out && ci == 0) { comps_out[0] = s[0]; comps_out[1] = s[1]; comps_out[2] = s[2]; comps_out[3] = s[3]; }
         }
     }
     __syncthreads();
@@ -512,17 +639,17 @@ template <typename T> __device__ void dump_qp(const SolveParams<T>& P, const Ptr
                 v = (e2 / 12 == e2 % 12) ? T(-1) : T(0);
             } else if (e < 288) {
                 const int c = e / 24, r = e - 24 * c;
-                const T* lk = M.lin + LIN_STRIDE * k;
+                const T* kr = M.kr + KR_STRIDE * k;
                 if (r < 12) v = (r == c) ? T(-1) : T(0);
                 else {
                     const int rr = r - 12;
                     if (rr < 6) v = (c < 6) ? (rr == c ? T(1) : T(0)) : (rr == c - 6 ? P.dt : T(0));
-                    else v = (c < 6) ? lk[LIN_GQ + 6 * (rr - 6) + c] : lk[LIN_GV + 6 * (rr - 6) + c - 6];
+                    else v = (c < 6) ? kr[KR_GQ + 6 * (rr - 6) + c] : kr[KR_GV + 6 * (rr - 6) + c - 6];
                 }
             } else {
                 const int e2 = e - 288, c = e2 / 12, r = e2 - 12 * c;
-                const T* lk = M.lin + LIN_STRIDE * k;
-                v = (r < 6) ? T(0) : lk[LIN_H + 6 * (r - 6) + c];
+                const T* kr = M.kr + KR_STRIDE * k;
+                v = (r < 6) ? T(0) : kr[KR_S + 6 * (r - 6) + c];      // H = dt Minv (dump mode of phase_setup)
             }
             A[t] = v;
         }
@@ -533,7 +660,7 @@ template <typename T> __device__ void dump_qp(const SolveParams<T>& P, const Ptr
             const int k = t / 12, r = t - 12 * k;
             T v;
             if (k == 0) v = -M.x0[r];
-            else v = (r < 6) ? T(0) : -M.lin[LIN_STRIDE * (k - 1) + LIN_CV + r - 6];
+            else v = (r < 6) ? T(0) : -M.kr[KR_STRIDE * (k - 1) + KR_CV + r - 6];
             l[t] = v;
         }
     }
@@ -576,10 +703,13 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
     const bool spill = P.spill_ws != nullptr;
     const Layout L = make_layout(N, spill);
     Ptrs<T> M;
-    M.xu = sm + L.xu; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.lin = sm + L.lin; M.cost = sm + L.cost;
+    M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
     M.work = sm + L.work; M.ls = sm + L.ls;
-    T* reg = spill ? P.spill_ws + (size_t)blockIdx.x * L.reg_size : sm + L.reg;
-    M.gains = reg; M.z = reg + GAIN_STRIDE * (N - 1); M.scr = reg;
+    M.kr = spill ? P.spill_ws + (size_t)blockIdx.x * L.reg_size : sm + L.reg;
+    {
+        int cap = L.reg_size / (MP_STRIDE * N);
+        M.merit_cap = cap > 5 ? 5 : (cap < 1 ? 1 : cap);
+    }
     __shared__ T s_merits[9];
     __shared__ T s_alpha;
     __shared__ T s_merit_acc;
@@ -596,39 +726,28 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
         }
         if (tid < 12) M.x0[tid] = P.x0 ? P.x0[(size_t)b * 12 + tid] : T(0);
         if (tid < 6) s_fext[tid] = P.fext ? P.fext[(size_t)b * 6 + tid] : T(0);
-        __syncthreads();
-        const T* fext = P.fext ? s_fext : nullptr;
-
         if (P.mode == MODE_LINESEARCH || P.mode == MODE_MERIT) {
             for (int t = tid; t < nz; t += NT) M.z[t] = P.xu_full[(size_t)b * nz + t];
             if (tid < 6) M.z[nz + tid] = T(0);
-            __syncthreads();
-            if (P.mode == MODE_MERIT) {
-                // xu against the reference iterate z: comps summed per term
-                T* part = M.ls;   // reuse: 4 sums need 4N entries -> use lin area instead
-                T* buf = M.lin;
-                for (int k = tid; k < N; k += NT) {
-                    T comps[4];
-                    merit_knot<T>(rob, P, M.xu, M.xu, T(0), k, M.goals + 3 * k, fext, comps);
-                    buf[k] = comps[0]; buf[N + k] = comps[1]; buf[2 * N + k] = comps[2]; buf[3 * N + k] = comps[3];
-                }
-                __syncthreads();
-                const int warp = tid >> 5, lane = tid & 31;
-                for (int c = warp; c < 4; c += NT / 32) {
-                    T s = warp_sum_strided<T>(buf + c * N, N, lane);
-                    if (lane == 0) part[c] = s;
-                }
-                __syncthreads();
-                if (tid == 0) {
-                    T d2 = T(0);
-                    for (int i = 0; i < 12; ++i) { const T d = M.xu[i] - M.z[i]; d2 += d * d; }
-                    T* o = P.merits_out + (size_t)b * 6;
-                    o[0] = part[0]; o[1] = part[1]; o[2] = part[2]; o[3] = part[3]; o[4] = sqrt_t<T>(d2);
-                    o[5] = part[0] + part[1] + part[2] + P.mu * (part[3] + o[4]);
-                }
-                __syncthreads();
-                continue;
+        }
+        __syncthreads();
+        const T* fext = P.fext ? s_fext : nullptr;
+
+        if (P.mode == MODE_MERIT) {
+            // merit terms of xu; the initial-state term is taken against the reference iterate z
+            T* comps = M.ls;
+            merit_points<T, NT>(rob, P, M, M.xu, M.xu, fext, 0, 1, comps);
+            merit_reduce<T, NT>(P, M.xu, M.xu, 0, 1, comps, s_merits, M.work);
+            if (tid == 0) {
+                T d2 = T(0);
+                for (int i = 0; i < 12; ++i) { const T d = M.xu[i] - M.z[i]; d2 += d * d; }
+                T* o = P.merits_out + (size_t)b * 6;
+                const T* part = M.work;
+                o[0] = part[0]; o[1] = part[1]; o[2] = part[2]; o[3] = part[3]; o[4] = sqrt_t<T>(d2);
+                o[5] = part[0] + part[1] + part[2] + P.mu * (part[3] + o[4]);
             }
+            __syncthreads();
+            continue;
         }
 
         int qp_iters = 0, n_ls = 0, n_steps = 0, status = 0;
@@ -636,29 +755,41 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
         T merit_final = T(0), merit_first = T(0);
         for (int qp = 0; qp < P.max_qp; ++qp) {
             qp_iters = qp + 1;
+            if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 0] = clock64();
             if (P.mode != MODE_LINESEARCH) {
-                phase_setup<T, NT>(rob, P, M, fext);
+                phase_setup<T, NT>(rob, P, M, fext, P.mode == MODE_DUMP, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
+                if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 1] = clock64();
                 if (P.mode == MODE_DUMP) { dump_qp<T>(P, M, b); break; }
-                phase_riccati<T, NT>(P, M);
+                phase_riccati<T, NT>(P, M, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
+                if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 2] = clock64();
                 if (P.mode == MODE_QP) {
                     for (int t = tid; t < nz; t += NT) P.z_out[(size_t)b * nz + t] = M.z[t];
                     break;
                 }
             }
-            phase_merits<T, NT>(rob, P, M, M.xu, M.z, fext, s_merits);
-            if (tid == 0) {
-                // first alpha (in decreasing order) with merit <= base, else 0   (src/osqp_sqp.py:59-72)
-                T a = T(0);
-                int bad = !(s_merits[0] == s_merits[0]);
-                for (int c = 1; c <= 8; ++c) {
-                    if (s_merits[c] <= s_merits[0]) { a = T(c_alphas[c]); break; }
+            // ---- line search: candidates evaluated in waves, stopping at the first wave that holds an accepted
+            //      alpha (src/osqp_sqp.py:59-72 takes the first alpha, in decreasing order, with merit <= base) ----
+            {
+                const bool all = (P.mode == MODE_LINESEARCH);     // the debug entry point reports all nine merits
+                int c0 = 0;
+                if (tid == 0) { s_alpha = T(0); s_flag = 0; }
+                while (c0 < 9) {
+                    int nc = 9 - c0 < M.merit_cap ? 9 - c0 : M.merit_cap;
+                    merit_points<T, NT>(rob, P, M, M.xu, M.z, fext, c0, nc, M.ls);
+                    merit_reduce<T, NT>(P, M.xu, M.z, c0, nc, M.ls, s_merits, nullptr);
+                    if (tid == 0 && s_alpha == T(0)) {
+                        if (!(s_merits[0] == s_merits[0])) s_flag = 1;
+                        for (int c = (c0 == 0 ? 1 : c0); c < c0 + nc; ++c)
+                            if (s_merits[c] <= s_merits[0]) { s_alpha = T(c_alphas[c]); s_merit_acc = s_merits[c]; break; }
+                    }
+                    __syncthreads();
+                    c0 += nc;
+                    if (!all && s_alpha != T(0)) break;
                 }
-                s_alpha = a;
-                s_flag = bad;
-                s_merit_acc = s_merits[0];
-                for (int c = 1; c <= 8; ++c) if (a != T(0) && a == T(c_alphas[c])) s_merit_acc = s_merits[c];
+                if (tid == 0 && s_alpha == T(0)) s_merit_acc = s_merits[0];
+                __syncthreads();
             }
-            __syncthreads();
+            if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 3] = clock64();
             const T alpha = s_alpha;
             merit_final = s_merit_acc;
             if (qp == 0) merit_first = s_merits[0];
@@ -677,6 +808,7 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
                 for (int q2 = qp + 1; q2 < P.max_qp; ++q2) { if (q2 < 2) alphas[q2] = T(0); ++n_ls; qp_iters = q2 + 1; }
                 break;
             }
+            __syncthreads();
             // XU += alpha (z - XU); step norm
             T* part = M.ls;
             T loc = T(0);
@@ -685,14 +817,15 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
                 M.xu[t] += st;
                 loc += st * st;
             }
-            part[tid] = loc;   // NT <= 9N+16 is guaranteed by the launcher
+            part[tid] = loc;
             __syncthreads();
             if (tid < 32) {
                 T s = warp_sum_strided<T>(part, NT, tid);
-                if (tid == 0) s_merits[0] = sqrt_t<T>(s);
+                if (tid == 0) s_merit_acc = sqrt_t<T>(s);
             }
             __syncthreads();
-            const T stepsize = s_merits[0];
+            const T stepsize = s_merit_acc;
+            if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 4] = clock64();
             if (n_steps < 2) steps[n_steps] = stepsize;
             ++n_steps;
             __syncthreads();
@@ -725,19 +858,29 @@ __global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, con
 #pragma unroll
         for (int a = 0; a < 3; ++a) { fx[a] = fext_pin[6 * i + 3 + a]; fx[3 + a] = fext_pin[6 * i + a]; }
     }
-    T qdd[6], U[36], D[6], F[36];
-    aba<T, true>(rob, cs, qd, u, fext_pin ? fx : nullptr, qdd, U, D, F);
-    T Mi[36];
+    const T* fext = fext_pin ? fx : nullptr;
+    // the same building blocks as the fused kernel: CRBA columns, bias, LDL' solves, dID columns
+    T A[6][6], dinv[6], bias[6], qdd[6], Mi[36];
     for (int c = 0; c < 6; ++c) {
         T out[6];
-        minv_column<T>(rob, cs, U, D, c, out);
-        for (int r = 0; r < 6; ++r) Mi[6 * r + c] = out[r];
+        crba_column<T>(rob, cs, c, out);
+        for (int r = 0; r < 6; ++r) A[r][c] = out[r];
+    }
+    rnea_bias<T>(rob, cs, qd, fext, bias);
+    spd6_factor<T>(A, dinv);
+    for (int r = 0; r < 6; ++r) qdd[r] = u[r] - bias[r];
+    spd6_solve_factored<T>(A, dinv, qdd);
+    for (int c = 0; c < 6; ++c) {
+        T b[6];
+        for (int r = 0; r < 6; ++r) b[r] = (r == c) ? T(1) : T(0);
+        spd6_solve_factored<T>(A, dinv, b);
+        for (int r = 0; r < 6; ++r) Mi[6 * r + c] = b[r];
     }
     if (qdd_out) for (int a = 0; a < 6; ++a) qdd_out[6 * i + a] = qdd[a];
     if (minv_out) for (int a = 0; a < 36; ++a) minv_out[36 * i + a] = Mi[a];
     for (int j = 0; j < 6; ++j) {
         T cq[6], cv[6];
-        rnea_dcolumn<T, true>(rob, cs, qd, qdd, F, j, cq);
+        rnea_dcolumn<T, true>(rob, cs, qd, qdd, fext, j, cq);
         rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, j, cv);
         for (int r = 0; r < 6; ++r) {
             T aq = T(0), av = T(0);
@@ -804,7 +947,6 @@ __global__ void sim_forward_kernel(const __grid_constant__ Robot<T> rob, int n, 
         x_next[12 * i + 6 + a] = vn;
     }
 }
-
 
 // -----------------------------------------------------------------------------------------------------------
 // best-trajectory selection: one CTA; packed = [costs | best_cost, best_index, XU_best]

@@ -228,6 +228,15 @@ class Engine:
         self._check(self.lib.i7_measure_fma_peak(self._h, C.byref(tf)))
         return tf.value
 
+    def profile_phases(self, enable=True, batch=None):
+        """Enable the phase clocks, or (batch given) fetch the (batch, 32) clock64 stamps of the latest solve."""
+        if batch is None:
+            self._check(self.lib.i7_profile_phases(self._h, int(enable), None, 0))
+            return None
+        buf = np.zeros((batch, 32), dtype=np.int64)
+        self._check(self.lib.i7_profile_phases(self._h, int(enable), buf.ctypes.data_as(C.POINTER(C.c_int64)), batch))
+        return buf
+
     def set_external_wrench(self, f_ext):
         if f_ext is None:
             self._check(self.lib.i7_set_external_wrench(self._h, None, 0))
