@@ -625,7 +625,10 @@ __device__ void merit_reduce(const SolveParams<T>& P, const T* xa, const T* xb, 
 }
 
 // -----------------------------------------------------------------------------------------------------------
-template <typename T> __device__ void dump_qp(const SolveParams<T>& P, const Ptrs<T>& M, int b) {
+struct BlockRecLayout {       // record offsets of the CTA-per-problem kernel, for dump_qp
+    static constexpr int GQ = KR_GQ, GV = KR_GV, CV = KR_CV, S = KR_S, STRIDE = KR_STRIDE;
+};
+template <typename T, typename Lay> __device__ void dump_qp(const SolveParams<T>& P, const Ptrs<T>& M, int b) {
     const int N = P.N, tid = threadIdx.x, NT = blockDim.x;
     const T* xu = M.xu;
     const int nA = 360 * (N - 1) + 144, nP = 27 * N + 6 * (N - 1), nz = 18 * N - 6, nl = 12 * N;
@@ -639,17 +642,17 @@ template <typename T> __device__ void dump_qp(const SolveParams<T>& P, const Ptr
                 v = (e2 / 12 == e2 % 12) ? T(-1) : T(0);
             } else if (e < 288) {
                 const int c = e / 24, r = e - 24 * c;
-                const T* kr = M.kr + KR_STRIDE * k;
+                const T* kr = M.kr + (size_t)Lay::STRIDE * k;
                 if (r < 12) v = (r == c) ? T(-1) : T(0);
                 else {
                     const int rr = r - 12;
                     if (rr < 6) v = (c < 6) ? (rr == c ? T(1) : T(0)) : (rr == c - 6 ? P.dt : T(0));
-                    else v = (c < 6) ? kr[KR_GQ + 6 * (rr - 6) + c] : kr[KR_GV + 6 * (rr - 6) + c - 6];
+                    else v = (c < 6) ? kr[Lay::GQ + 6 * (rr - 6) + c] : kr[Lay::GV + 6 * (rr - 6) + c - 6];
                 }
             } else {
                 const int e2 = e - 288, c = e2 / 12, r = e2 - 12 * c;
-                const T* kr = M.kr + KR_STRIDE * k;
-                v = (r < 6) ? T(0) : kr[KR_S + 6 * (r - 6) + c];      // H = dt Minv (dump mode of phase_setup)
+                const T* kr = M.kr + (size_t)Lay::STRIDE * k;
+                v = (r < 6) ? T(0) : kr[Lay::S + 6 * (r - 6) + c];      // H = dt Minv (dump mode of phase_setup)
             }
             A[t] = v;
         }
@@ -660,7 +663,7 @@ template <typename T> __device__ void dump_qp(const SolveParams<T>& P, const Ptr
             const int k = t / 12, r = t - 12 * k;
             T v;
             if (k == 0) v = -M.x0[r];
-            else v = (r < 6) ? T(0) : -M.kr[KR_STRIDE * (k - 1) + KR_CV + r - 6];
+            else v = (r < 6) ? T(0) : -M.kr[(size_t)Lay::STRIDE * (k - 1) + Lay::CV + r - 6];
             l[t] = v;
         }
     }
@@ -759,7 +762,7 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
             if (P.mode != MODE_LINESEARCH) {
                 phase_setup<T, NT>(rob, P, M, fext, P.mode == MODE_DUMP, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 1] = clock64();
-                if (P.mode == MODE_DUMP) { dump_qp<T>(P, M, b); break; }
+                if (P.mode == MODE_DUMP) { dump_qp<T, BlockRecLayout>(P, M, b); break; }
                 phase_riccati<T, NT>(P, M, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 2] = clock64();
                 if (P.mode == MODE_QP) {
