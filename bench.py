@@ -199,6 +199,7 @@ def run_b200(args):
     import torch.distributed as dist
     from indy7_mpc_b200 import Engine, Indy7SQP
     from indy7_mpc_b200 import _lib
+    from indy7_mpc_b200 import dist as i7d
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -238,11 +239,7 @@ def run_b200(args):
     def tick(xu, x0, goals):
         out, st = eng.solve(xu, x0, goals)
         packed = eng.pack_best(st, out, index_offset=rank * B)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, packed)
-            best = eng.reduce_best(gathered, world)
-        else:
-            best = packed[B:]
+        best, _ = i7d.gather_best(packed, B, world, eng.reduce_best, gathered)
         return out, st, best
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
@@ -272,11 +269,7 @@ def run_b200(args):
         out, st = eng.solve(xu, x0, goals)               # dominant kernel timed on its own as well
         kev[i][1].record()
         packed = eng.pack_best(st, out, index_offset=rank * B)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, packed)
-            best = eng.reduce_best(gathered, world)
-        else:
-            best = packed[B:]
+        best, _ = i7d.gather_best(packed, B, world, eng.reduce_best, gathered)   # ONE all-gather (NCCL) when world > 1
         ev[i][1].record()
         xu, x0 = shift_dev(out)
         xu[:, :12] = x0
@@ -429,7 +422,9 @@ def single_problem_latency(args, local):
         x = xn
         xu = np.concatenate([out[:, 18:], out[:, -18:]], axis=1)
         xu[0, :12] = x
-    p = lambda a, q: float(np.percentile(a, q))
+    p = lambda a, q: float(np.percentile(a, q)) if len(a) else None
+    if not dev_us:
+        return {"config": "skipped (--latency-ticks 0)"}
     return {"config": f"fig-8 tracking, N={N}, 1 problem, closed loop with rk4 plant, {n_ticks} warm ticks",
             "device_us": {"p50": p(dev_us, 50), "p99": p(dev_us, 99), "mean": float(np.mean(dev_us))},
             "host_wall_us": {"p50": p(wall_us, 50), "p99": p(wall_us, 99), "mean": float(np.mean(wall_us))},
