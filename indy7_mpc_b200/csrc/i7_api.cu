@@ -1,7 +1,8 @@
 // i7_api.cu — C ABI of the B200-native SQP-MPC solve loop (see include/indy7_b200.h for the boundary).
 #include "../../include/indy7_b200.h"
 #undef I7_NJ
-#include "i7_sqp.cuh"
+#include "i7_launch.h"
+#include "i7_aux.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -131,31 +132,23 @@ template <typename T> const i7::Robot<T>& get_rob(const i7_handle* h);
 template <> const i7::Robot<double>& get_rob<double>(const i7_handle* h) { return h->rob64; }
 template <> const i7::Robot<float>& get_rob<float>(const i7_handle* h) { return h->rob32; }
 
-template <typename T, int NT>
-i7_status launch_sqp_nt(i7_handle* h, const i7::Robot<T>& rob, const i7::SolveParams<T>& P, cudaStream_t s) {
-    i7::sqp_kernel<T, NT><<<P.batch, NT, h->smem_bytes, s>>>(rob, P);
-    ++h->launches;
-    I7_CUDA(h, cudaGetLastError());
-    return I7_OK;
-}
-
-// raise the dynamic shared-memory cap of the kernel to everything the SM offers beyond its static usage;
-// returns that cap in *cap
-template <typename T, int NT>
-cudaError_t allow_big_smem(int optin_bytes, int* cap) {
-    cudaFuncAttributes fa;
-    cudaError_t e = cudaFuncGetAttributes(&fa, i7::sqp_kernel<T, NT>);
-    if (e != cudaSuccess) return e;
-    *cap = optin_bytes - (int)fa.sharedSizeBytes;
-    return cudaFuncSetAttribute(i7::sqp_kernel<T, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, *cap);
-}
-
 template <typename T>
 i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& P, cudaStream_t s) {
     P.spill_ws = h->spill ? (T*)h->d_spill : nullptr;
-    if (h->threads == 384) return launch_sqp_nt<T, 384>(h, rob, P, s);
-    if (h->threads == 256) return launch_sqp_nt<T, 256>(h, rob, P, s);
-    return launch_sqp_nt<T, 128>(h, rob, P, s);
+    cudaError_t e;
+    if (h->threads == 384) e = i7::launch_sqp_cta<T, 384>(rob, P, h->smem_bytes, s);
+    else if (h->threads == 256) e = i7::launch_sqp_cta<T, 256>(rob, P, h->smem_bytes, s);
+    else e = i7::launch_sqp_cta<T, 128>(rob, P, h->smem_bytes, s);
+    ++h->launches;
+    I7_CUDA(h, e);
+    return I7_OK;
+}
+
+template <typename T>
+cudaError_t allow_big_smem(int threads, int optin_bytes, int* cap) {
+    if (threads == 384) return i7::smem_cap_sqp_cta<T, 384>(optin_bytes, cap);
+    if (threads == 256) return i7::smem_cap_sqp_cta<T, 256>(optin_bytes, cap);
+    return i7::smem_cap_sqp_cta<T, 128>(optin_bytes, cap);
 }
 
 template <typename T>
@@ -286,10 +279,7 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
     {
         cudaError_t ea;
         const int o = h->max_smem_optin;
-        if (cfg->dtype == I7_F64)
-            ea = h->threads == 384 ? allow_big_smem<double, 384>(o, &cap) : h->threads == 256 ? allow_big_smem<double, 256>(o, &cap) : allow_big_smem<double, 128>(o, &cap);
-        else
-            ea = h->threads == 384 ? allow_big_smem<float, 384>(o, &cap) : h->threads == 256 ? allow_big_smem<float, 256>(o, &cap) : allow_big_smem<float, 128>(o, &cap);
+        ea = cfg->dtype == I7_F64 ? allow_big_smem<double>(h->threads, o, &cap) : allow_big_smem<float>(h->threads, o, &cap);
         if (ea != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea); return fail(I7_ERR_CUDA); }
     }
     i7::Layout L = i7::make_layout(cfg->N, false);

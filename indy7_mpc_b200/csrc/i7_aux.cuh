@@ -1,0 +1,180 @@
+// i7_aux.cuh — sample-level kernels (one thread per sample) next to the fused solve: forward dynamics and its
+// derivatives, end-effector position / Jacobian, the rk4 plant step, best-trajectory selection, FMA-peak probe.
+#pragma once
+#include "i7_rbd.cuh"
+
+namespace i7 {
+
+// -----------------------------------------------------------------------------------------------------------
+// sample-level kernels (one thread per sample): forward dynamics + derivatives, end-effector, rk4 plant step
+template <typename T>
+__global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, const T* q, const T* v, const T* tau,
+                                const T* fext_pin, T* qdd_out, T* dq_out, T* dv_out, T* minv_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    T cs[12], qd[6], u[6], fx[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { sincos_t<T>(q[6 * i + a], &cs[6 + a], &cs[a]); qd[a] = v[6 * i + a]; u[a] = tau[6 * i + a]; }
+    if (fext_pin) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { fx[a] = fext_pin[6 * i + 3 + a]; fx[3 + a] = fext_pin[6 * i + a]; }
+    }
+    const T* fext = fext_pin ? fx : nullptr;
+    // the same building blocks as the fused kernel: CRBA columns, bias, LDL' solves, dID columns
+    T A[6][6], dinv[6], bias[6], qdd[6], Mi[36];
+    for (int c = 0; c < 6; ++c) {
+        T out[6];
+        crba_column<T>(rob, cs, c, out);
+        for (int r = 0; r < 6; ++r) A[r][c] = out[r];
+    }
+    rnea_bias<T>(rob, cs, qd, fext, bias);
+    spd6_factor<T>(A, dinv);
+    for (int r = 0; r < 6; ++r) qdd[r] = u[r] - bias[r];
+    spd6_solve_factored<T>(A, dinv, qdd);
+    for (int c = 0; c < 6; ++c) {
+        T b[6];
+        for (int r = 0; r < 6; ++r) b[r] = (r == c) ? T(1) : T(0);
+        spd6_solve_factored<T>(A, dinv, b);
+        for (int r = 0; r < 6; ++r) Mi[6 * r + c] = b[r];
+    }
+    if (qdd_out) for (int a = 0; a < 6; ++a) qdd_out[6 * i + a] = qdd[a];
+    if (minv_out) for (int a = 0; a < 36; ++a) minv_out[36 * i + a] = Mi[a];
+    for (int j = 0; j < 6; ++j) {
+        T cq[6], cv[6];
+        rnea_dcolumn<T, true>(rob, cs, qd, qdd, fext, j, cq);
+        rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, j, cv);
+        for (int r = 0; r < 6; ++r) {
+            T aq = T(0), av = T(0);
+            for (int s = 0; s < 6; ++s) { aq -= Mi[6 * r + s] * cq[s]; av -= Mi[6 * r + s] * cv[s]; }
+            if (dq_out) dq_out[36 * i + 6 * r + j] = aq;
+            if (dv_out) dv_out[36 * i + 6 * r + j] = av;
+        }
+    }
+}
+
+template <typename T>
+__global__ void eepos_kernel(const __grid_constant__ Robot<T> rob, int n, const T* q, T* p_out, T* J_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    T cs[12];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) sincos_t<T>(q[6 * i + a], &cs[6 + a], &cs[a]);
+    T pee[3], zs[18], ps[18];
+    fk_ee<T>(rob, cs, pee, zs, ps);
+    for (int a = 0; a < 3; ++a) p_out[3 * i + a] = pee[a];
+    if (J_out) {
+        T J[18];
+        ee_jacobian<T>(pee, zs, ps, J);
+        for (int a = 0; a < 18; ++a) J_out[18 * i + a] = J[a];
+    }
+}
+
+template <typename T>
+I7_DEV void aba_at(const Robot<T>& rob, const T* q, const T* qd, const T* u, const T* fx, T* qdd) {
+    T cs[12];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) sincos_t<T>(q[a], &cs[6 + a], &cs[a]);
+    aba<T, false>(rob, cs, qd, u, fx, qdd, nullptr, nullptr, nullptr);
+}
+
+// rk4 plant step, literal stage order of src/utils.py:3-18 (pin.integrate == q + dq for revolute joints)
+template <typename T>
+__global__ void sim_forward_kernel(const __grid_constant__ Robot<T> rob, int n, const T* x, const T* u, int bcast,
+                                   const T* fext /*Featherstone order or nullptr*/, T dt, T* x_next) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const T* xi = x + (bcast ? 0 : 12 * i);
+    const T* ui = u + (bcast ? 0 : 6 * i);
+    T q[6], v[6], uu[6], fx[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { q[a] = xi[a]; v[a] = xi[6 + a]; uu[a] = ui[a]; fx[a] = fext ? fext[6 * i + a] : T(0); }
+    const T* f = fext ? fx : nullptr;
+    T k1v[6], k2v[6], k3v[6], k4v[6], k2q[6], k3q[6], k4q[6], qt[6];
+    aba_at<T>(rob, q, v, uu, f, k1v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + v[a] * dt / T(2); k2q[a] = v[a] + k1v[a] * dt / T(2); }
+    aba_at<T>(rob, qt, k2q, uu, f, k2v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + k2q[a] * dt / T(2); k3q[a] = v[a] + k2v[a] * dt / T(2); }
+    aba_at<T>(rob, qt, k3q, uu, f, k3v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + k3q[a] * dt; k4q[a] = v[a] + k3v[a] * dt; }
+    aba_at<T>(rob, qt, k4q, uu, f, k4v);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+        const T vn = v[a] + (dt / T(6)) * (k1v[a] + T(2) * k2v[a] + T(2) * k3v[a] + k4v[a]);
+        const T av = (v[a] + T(2) * k2q[a] + T(2) * k3q[a] + k4q[a]) / T(6);
+        x_next[12 * i + a] = q[a] + av * dt;
+        x_next[12 * i + 6 + a] = vn;
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// best-trajectory selection: one CTA; packed = [costs | best_cost, best_index, XU_best]
+template <typename T>
+__global__ void pack_best_kernel(int batch, int nz, const T* stats, int stats_stride, int cost_col, const T* xu,
+                                 int index_offset, T* packed) {
+    __shared__ T s_val[32];
+    __shared__ int s_idx[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    T best = T(0); int bi = -1;
+    for (int b = tid; b < batch; b += blockDim.x) {
+        const T c = stats[(size_t)b * stats_stride + cost_col];
+        packed[b] = c;
+        if (c == c && (bi < 0 || c < best)) { best = c; bi = b; }      // strided scan keeps the lowest index on ties
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const T ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (oi >= 0 && (bi < 0 || ov < best || (ov == best && oi < bi))) { best = ov; bi = oi; }
+    }
+    if (lane == 0) { s_val[warp] = best; s_idx[warp] = bi; }
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+        best = lane < nw ? s_val[lane] : T(0); bi = lane < nw ? s_idx[lane] : -1;
+        for (int o = 16; o > 0; o >>= 1) {
+            const T ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (oi >= 0 && (bi < 0 || ov < best || (ov == best && oi < bi))) { best = ov; bi = oi; }
+        }
+        if (lane == 0) { s_val[0] = best; s_idx[0] = bi; }
+    }
+    __syncthreads();
+    bi = s_idx[0];
+    T* tail = packed + batch;
+    if (tid == 0) { tail[0] = s_val[0]; tail[1] = T(bi < 0 ? -1 : bi + index_offset); }
+    for (int t = tid; t < nz; t += blockDim.x) tail[2 + t] = bi < 0 ? T(0) : xu[(size_t)bi * nz + t];
+}
+
+// gathered: nranks records of `stride` elements; the last 2 + nz of each are [best_cost, best_index, XU_best]
+template <typename T>
+__global__ void reduce_best_kernel(int nranks, int stride, int nz, const T* gathered, T* out) {
+    __shared__ int s_win;
+    if (threadIdx.x == 0) {
+        int win = -1; T best = T(0);
+        for (int r = 0; r < nranks; ++r) {
+            const T* tail = gathered + (size_t)r * stride + (stride - 2 - nz);
+            if (tail[1] >= T(0) && (win < 0 || tail[0] < best)) { best = tail[0]; win = r; }
+        }
+        s_win = win < 0 ? 0 : win;
+    }
+    __syncthreads();
+    const T* tail = gathered + (size_t)s_win * stride + (stride - 2 - nz);
+    for (int t = threadIdx.x; t < 2 + nz; t += blockDim.x) out[t] = tail[t];
+}
+
+// FMA-pipe peak: 8 independent chains per thread, 2 flop per FMA
+template <typename T>
+__global__ void fma_peak_kernel(int iters, T seed, T* sink) {
+    T a0 = seed, a1 = seed + T(1), a2 = seed + T(2), a3 = seed + T(3), a4 = seed + T(4), a5 = seed + T(5), a6 = seed + T(6), a7 = seed + T(7);
+    const T m = T(0.999999), c = T(1e-6);
+    for (int i = 0; i < iters; ++i) {
+        a0 = a0 * m + c; a1 = a1 * m + c; a2 = a2 * m + c; a3 = a3 * m + c;
+        a4 = a4 * m + c; a5 = a5 * m + c; a6 = a6 * m + c; a7 = a7 * m + c;
+    }
+    const T s = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+    if (s == T(-12345)) sink[0] = s;
+}
+
+}  // namespace i7

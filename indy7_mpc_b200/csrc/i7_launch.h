@@ -1,0 +1,15 @@
+// i7_launch.h — host-side launch entry points of the fused kernels.  Each (arithmetic type, CTA size) instance of
+// the big kernels is compiled in its own translation unit (i7_sqp_inst.cu / i7_cluster_inst.cu with -DI7_T / -DI7_NT)
+// so that the instances build in parallel; i7_api.cu only sees these declarations.
+#pragma once
+#include "i7_sqp.cuh"
+
+namespace i7 {
+
+// CTA-per-problem kernel (throughput form): grid = batch
+template <typename T, int NT> cudaError_t launch_sqp_cta(const Robot<T>& rob, const SolveParams<T>& P, int smem_bytes,
+                                                         cudaStream_t s);
+// raises the dynamic shared-memory cap of that instance to everything the SM offers; returns the cap
+template <typename T, int NT> cudaError_t smem_cap_sqp_cta(int optin_bytes, int* cap);
+
+}  // namespace i7

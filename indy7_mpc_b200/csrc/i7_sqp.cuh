@@ -64,7 +64,7 @@ constexpr int COST_STRIDE = 9;                       // j[6], Q, dQ, R
 // merit scratch per evaluated point (aliases the knot records, dead after the QP solve)
 constexpr int MP_CS = 0, MP_M = 12, MP_B = 48, MP_STRIDE = 55;
 // Riccati work area
-constexpr int WK_P = 0;        // 2 x 144 value matrices (double buffered)
+constexpr int WK_P = 0;        // 2 x 36 qq blocks of the value matrix (double buffered; the rest of the 288 is spare)
 constexpr int WK_PV = 288;     // 2 x 12
 constexpr int WK_AUG = 312;    // 2 x (6 x 19): [Hww | Hwx | hw]
 constexpr int WK_X = 540;      // 6 x 13
@@ -97,12 +97,12 @@ struct Ptrs {
     int merit_cap;      // candidates per merit wave that fit the scratch region
 };
 
-__device__ __constant__ double c_alphas[9] = {0.0, 1.0, 0.5, 0.25, 0.125, 0.0625, 0.03125, 0.015625, 0.0078125};
+static __device__ __constant__ double c_alphas[9] = {0.0, 1.0, 0.5, 0.25, 0.125, 0.0625, 0.03125, 0.015625, 0.0078125};
 // upper triangle of a 12x12 matrix, row-major enumeration
-__device__ __constant__ unsigned char c_tri_r[78] = {
+static __device__ __constant__ unsigned char c_tri_r[78] = {
     0,0,0,0,0,0,0,0,0,0,0,0, 1,1,1,1,1,1,1,1,1,1,1, 2,2,2,2,2,2,2,2,2,2, 3,3,3,3,3,3,3,3,3, 4,4,4,4,4,4,4,4,
     5,5,5,5,5,5,5, 6,6,6,6,6,6, 7,7,7,7,7, 8,8,8,8, 9,9,9, 10,10, 11};
-__device__ __constant__ unsigned char c_tri_c[78] = {
+static __device__ __constant__ unsigned char c_tri_c[78] = {
     0,1,2,3,4,5,6,7,8,9,10,11, 1,2,3,4,5,6,7,8,9,10,11, 2,3,4,5,6,7,8,9,10,11, 3,4,5,6,7,8,9,10,11, 4,5,6,7,8,9,10,11,
     5,6,7,8,9,10,11, 6,7,8,9,10,11, 7,8,9,10,11, 8,9,10,11, 9,10,11, 10,11, 11};
 
@@ -343,93 +343,130 @@ I7_DEV void aug_from_P_entry(T* aug, const T* kr, int r, int c, T val, T dt) {
 }
 
 // riccati: backward recursion for the gains, forward roll-out for z.  x0 = measured state (l[:12] = -xs).
+//
+// Thread roles are fixed for the whole recursion and decoded once:
+//   warp 0, lanes 0..12   R2: X = Hww^-1 [Hwx | hw], one right-hand side each (LDL' in registers); the negated
+//                         column goes straight into the stage record as the gain Kw[:, c] / kw
+//   threads 32..121       R3: one entry of the new value function each (78 upper-triangle entries of P, 12 of p).
+//                         The part that does not depend on X (L + Qx + T'PT, hx + T'p) and the operands of the next
+//                         stage's [Hww | Hwx | hw] are fetched while R2 runs; after the barrier only the rank-6
+//                         correction (12 loads, 6 FMAs in two chains) is left.
+// Only the qq block of P is exchanged between threads (T'PT reads nothing else); the qv / vv blocks and p_v flow
+// directly into the next stage's augmented matrix.
 template <typename T, int NT>
 __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long long* prof) {
+    static_assert(NT >= 128, "phase_riccati needs at least 4 warps");
     const int tid = threadIdx.x;
     long long acc_r2 = 0, acc_r3 = 0, tt = 0;
     const int N = P.N;
     const T dt = P.dt;
     T* wk = M.work;
     const T* xu = M.xu;
+    // ---- role decode (once) ----
+    const int e = tid - 32;
+    const bool is_P = (e >= 0 && e < 78), is_p = (e >= 78 && e < 90);
+    int r = 0, c = 0;
+    if (is_P) {
+        int rem = e, len = 12;
+        while (rem >= len) { rem -= len; --len; ++r; }
+        c = r + rem;
+    } else if (is_p) {
+        r = e - 78;
+    }
+    const int ra = r < 6 ? r : r - 6, ca = c < 6 ? c : c - 6;
+    const T tfac = (r < 6 ? T(1) : dt) * ((is_P && c >= 6) ? dt : T(1));   // T'PT scale (P entry) / T'p scale (p entry)
+    const int offA = 6 + r;                                  // Hwx[s][r] = aug[AUGW s + 6 + r]
+    const int offB = is_P ? KR_SG + c : KR_D;                // Kw[s][c] (stride 12) or kw[s] (stride 1)
+    const int strB = is_P ? 12 : 1;
     int cur = 0;
     // terminal value function: P_N = blkdiag(QN j j', dQ_N I), p_N = [QN j; dQ_N v]; aug for stage N-2
     {
         const T* cN = M.cost + COST_STRIDE * (N - 1);
         const T* xN = xu + 18 * (N - 1);
         const T* kr = M.kr + KR_STRIDE * (N - 2);
-        for (int t = tid; t < 90; t += NT) {
-            if (t < 78) {
-                const int r = c_tri_r[t], c = c_tri_c[t];
-                T v = T(0);
-                if (c < 6) v = cN[6] * cN[r] * cN[c];
-                else if (r == c) v = cN[7];
-                wk[WK_P + 12 * r + c] = v;
-                wk[WK_P + 12 * c + r] = v;
-                aug_from_P_entry<T>(wk + WK_AUG, kr, r, c, v, dt);
-            } else {
-                const int r = t - 78;
-                const T v = r < 6 ? cN[6] * cN[r] : cN[7] * xN[r];
-                wk[WK_PV + r] = v;
-                if (r >= 6) wk[WK_AUG + AUGW * (r - 6) + 18] = v - kr[KR_D + r - 6];
-            }
+        if (is_P) {
+            T v = T(0);
+            if (c < 6) v = cN[6] * cN[r] * cN[c];
+            else if (r == c) v = cN[7];
+            if (c < 6) { wk[WK_P + 6 * r + c] = v; wk[WK_P + 6 * c + r] = v; }
+            aug_from_P_entry<T>(wk + WK_AUG, kr, r, c, v, dt);
+        } else if (is_p) {
+            const T v = r < 6 ? cN[6] * cN[r] : cN[7] * xN[r];
+            wk[WK_PV + r] = v;
+            if (r >= 6) wk[WK_AUG + AUGW * (r - 6) + 18] = v - kr[KR_D + r - 6];
         }
     }
     __syncthreads();
     for (int k = N - 2; k >= 0; --k) {
         T* kr = M.kr + KR_STRIDE * k;
         T* aug = wk + WK_AUG + 114 * cur;
-        // R2: X = Hww^-1 [Hwx | hw]: 13 independent right-hand sides, LDL' in registers
         if (prof && tid == 0) tt = clock64();
-        for (int t = tid; t < 13; t += NT) {
+        T base = T(0), n0 = T(0), n1 = T(0);   // R3 operands that do not depend on this stage's solve
+        if (tid < 13) {
+            // R2: one right-hand side of X = Hww^-1 [Hwx | hw]
             T A[6][6], dinv[6], b[6];
 #pragma unroll
-            for (int r = 0; r < 6; ++r)
+            for (int i = 0; i < 6; ++i)
 #pragma unroll
-                for (int q = 0; q <= r; ++q) A[r][q] = aug[AUGW * r + q];
+                for (int q = 0; q <= i; ++q) A[i][q] = aug[AUGW * i + q];
 #pragma unroll
-            for (int r = 0; r < 6; ++r) b[r] = aug[AUGW * r + 6 + t];
+            for (int i = 0; i < 6; ++i) b[i] = aug[AUGW * i + 6 + tid];
             spd6_factor<T>(A, dinv);
             spd6_solve_factored<T>(A, dinv, b);
+            // feedback / feed-forward of w = v_{k+1}: Kw = -X[:, :12], kw = -X[:, 12] (overwrites SG, d)
+            if (tid < 12) {
 #pragma unroll
-            for (int r = 0; r < 6; ++r) wk[WK_X + 13 * r + t] = b[r];
+                for (int i = 0; i < 6; ++i) kr[KR_SG + 12 * i + tid] = -b[i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) kr[KR_D + i] = -b[i];
+            }
+        } else if (is_P) {
+            const T* ck = M.cost + COST_STRIDE * k;
+            base = kr[KR_L + e] + wk[WK_P + 36 * cur + 6 * ra + ca] * tfac;
+            if (c < 6) base += ck[6] * ck[r] * ck[c];
+            else if (r == c) base += ck[7];
+            if (k > 0) {
+                const T* krn = kr - KR_STRIDE;
+                if (r < 6 && c >= 6) { n0 = krn[KR_SG + 12 * (c - 6) + r]; n1 = krn[KR_SG + 12 * (c - 6) + 6 + r]; }
+                else if (r >= 6) { n0 = krn[KR_S + 6 * (r - 6) + (c - 6)]; n1 = krn[KR_S + 6 * (c - 6) + (r - 6)]; }
+            }
+        } else if (is_p) {
+            base = kr[KR_HX + r] + wk[WK_PV + 12 * cur + ra] * tfac;
+            if (k > 0 && r >= 6) n0 = (kr - KR_STRIDE)[KR_D + r - 6];
         }
         __syncthreads();
         if (prof && tid == 0) { const long long n = clock64(); acc_r2 += n - tt; tt = n; }
-        // R3: P = Qx + L + T'aT - Hwx'X, p = hx + [pq; dt pq] - Hwx' x13; gains into the record; aug of stage k-1
-        {
-            const T* Pm = wk + WK_P + 144 * cur;
-            const T* pv = wk + WK_PV + 12 * cur;
-            T* Pn = wk + WK_P + 144 * (cur ^ 1);
-            T* pn = wk + WK_PV + 12 * (cur ^ 1);
+        // R3: P = Qx + L + T'aT - Hwx'X, p = hx + [pq; dt pq] - Hwx' x13 (X = -K); aug of stage k-1
+        if (is_P || is_p) {
+            T a0 = base, a1 = T(0);
+            const T* hb = aug + offA;
+            const T* kb = kr + offB;
+#pragma unroll
+            for (int s = 0; s < 3; ++s) {
+                a0 += hb[AUGW * s] * kb[strB * s];
+                a1 += hb[AUGW * (s + 3)] * kb[strB * (s + 3)];
+            }
+            const T acc = a0 + a1;
             T* augn = wk + WK_AUG + 114 * (cur ^ 1);
-            const T* X = wk + WK_X;
-            const T* ck = M.cost + COST_STRIDE * k;
-            const T* krn = M.kr + KR_STRIDE * (k > 0 ? k - 1 : 0);
-            for (int t = tid; t < 168; t += NT) {
-                if (t < 78) {
-                    const int r = c_tri_r[t], c = c_tri_c[t];
-                    const int ra = r < 6 ? r : r - 6, ca = c < 6 ? c : c - 6;
-                    T acc = kr[KR_L + t] + Pm[12 * ra + ca] * ((r < 6 ? T(1) : dt) * (c < 6 ? T(1) : dt));
-                    if (c < 6) acc += ck[6] * ck[r] * ck[c];
-                    else if (r == c) acc += ck[7];
-#pragma unroll
-                    for (int s = 0; s < 6; ++s) acc -= aug[AUGW * s + 6 + r] * X[13 * s + c];
-                    Pn[12 * r + c] = acc;
-                    Pn[12 * c + r] = acc;
-                    if (k > 0) aug_from_P_entry<T>(augn, krn, r, c, acc, dt);
-                } else if (t < 90) {
-                    const int r = t - 78;
-                    T acc = kr[KR_HX + r] + (r < 6 ? pv[r] : dt * pv[r - 6]);
-#pragma unroll
-                    for (int s = 0; s < 6; ++s) acc -= aug[AUGW * s + 6 + r] * X[13 * s + 12];
-                    pn[r] = acc;
-                    if (k > 0 && r >= 6) augn[AUGW * (r - 6) + 18] = acc - krn[KR_D + r - 6];
-                } else {
-                    // feedback / feed-forward of w = v_{k+1}: Kw = -X[:, :12], kw = -X[:, 12] (overwrites SG, d)
-                    const int e = t - 90, r = e / 13, c = e - 13 * r;
-                    const T v = -X[13 * r + c];
-                    if (c < 12) kr[KR_SG + 12 * r + c] = v; else kr[KR_D + r] = v;
+            if (is_P) {
+                if (c < 6) {
+                    T* Pn = wk + WK_P + 36 * (cur ^ 1);
+                    Pn[6 * r + c] = acc; Pn[6 * c + r] = acc;
+                } else if (k > 0) {
+                    if (r < 6) {
+                        const int i = c - 6;
+                        augn[AUGW * i + 6 + r] = acc - n0;
+                        augn[AUGW * i + 12 + r] = dt * acc - n1;
+                    } else {
+                        const int i = r - 6, j = c - 6;
+                        augn[AUGW * i + j] = acc + n0;
+                        if (i != j) augn[AUGW * j + i] = acc + n1;
+                    }
                 }
+            } else {
+                if (r < 6) wk[WK_PV + 12 * (cur ^ 1) + r] = acc;
+                else if (k > 0) augn[AUGW * (r - 6) + 18] = acc - n0;
             }
         }
         __syncthreads();
@@ -437,26 +474,49 @@ __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long lo
         cur ^= 1;
     }
     if (prof && tid == 0) { prof[10] = acc_r2; prof[11] = acc_r3; tt = clock64(); }
-    // forward roll-out by warp 0: x_0 = xs, v_{k+1} = Kw_k x_k + kw_k, q_{k+1} = q_k + dt v_k
+    // forward roll-out by warp 0: x_0 = xs, v_{k+1} = Kw_k x_k + kw_k, q_{k+1} = q_k + dt v_k.  The gain row of the
+    // next stage is fetched before the current state is read back, so only the state round trip is serial.
     if (tid < 32) {
         T* z = M.z;
         if (tid < 12) z[tid] = M.x0[tid];
+        const int row = tid < 6 ? tid : 0;
+        T g[12], ff;
+        {
+            const T* kr = M.kr;
+#pragma unroll
+            for (int i = 0; i < 12; ++i) g[i] = kr[KR_SG + 12 * row + i];
+            ff = kr[KR_D + row];
+        }
         __syncwarp();
         for (int k = 0; k < N - 1; ++k) {
-            const T* kr = M.kr + KR_STRIDE * k;
             T* zk = z + 18 * k;
-            if (tid < 6) {
-                T a0 = kr[KR_D + tid], a1 = T(0);
+            T gn[12], ffn = T(0);
+            if (k + 1 < N - 1) {
+                const T* krn = M.kr + KR_STRIDE * (k + 1);
 #pragma unroll
-                for (int c = 0; c < 6; ++c) {
-                    a0 += kr[KR_SG + 12 * tid + c] * zk[c];
-                    a1 += kr[KR_SG + 12 * tid + 6 + c] * zk[6 + c];
-                }
-                zk[18 + 6 + tid] = a0 + a1;
-            } else if (tid < 12) {
-                const int r = tid - 6;
-                zk[18 + r] = zk[r] + dt * zk[6 + r];
+                for (int i = 0; i < 12; ++i) gn[i] = krn[KR_SG + 12 * row + i];
+                ffn = krn[KR_D + row];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 12; ++i) gn[i] = T(0);
             }
+            if (tid < 6) {
+                T a0 = ff, a1 = T(0), a2 = T(0), a3 = T(0);
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    a0 += g[i] * zk[i];
+                    a1 += g[3 + i] * zk[3 + i];
+                    a2 += g[6 + i] * zk[6 + i];
+                    a3 += g[9 + i] * zk[9 + i];
+                }
+                zk[18 + 6 + tid] = (a0 + a1) + (a2 + a3);
+            } else if (tid < 12) {
+                const int q = tid - 6;
+                zk[18 + q] = zk[q] + dt * zk[6 + q];
+            }
+#pragma unroll
+            for (int i = 0; i < 12; ++i) g[i] = gn[i];
+            ff = ffn;
             __syncwarp();
         }
     }
@@ -468,25 +528,25 @@ __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long lo
         T* z = M.z;
         T* tmp = M.ls;
         for (int t = tid; t < 6 * nk; t += NT) {
-            const int r = t / nk, k = t - r * nk;
+            const int rr = t / nk, k = t - rr * nk;
             const T* kr = M.kr + KR_STRIDE * k;
             const T* zk = z + 18 * k;
-            T a0 = zk[18 + 6 + r] - kr[KR_CV + r], a1 = T(0);
+            T a0 = zk[18 + 6 + rr] - kr[KR_CV + rr], a1 = T(0);
 #pragma unroll
             for (int s = 0; s < 6; ++s) {
-                a0 -= kr[KR_GQ + 6 * r + s] * zk[s];
-                a1 -= kr[KR_GV + 6 * r + s] * zk[6 + s];
+                a0 -= kr[KR_GQ + 6 * rr + s] * zk[s];
+                a1 -= kr[KR_GV + 6 * rr + s] * zk[6 + s];
             }
-            tmp[6 * k + r] = a0 + a1;
+            tmp[6 * k + rr] = a0 + a1;
         }
         __syncthreads();
         for (int t = tid; t < 6 * nk; t += NT) {
-            const int r = t / nk, k = t - r * nk;
+            const int rr = t / nk, k = t - rr * nk;
             const T* kr = M.kr + KR_STRIDE * k;
             T acc = T(0);
 #pragma unroll
-            for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * r + s] * tmp[6 * k + s];
-            z[18 * k + 12 + r] = acc;
+            for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * rr + s] * tmp[6 * k + s];
+            z[18 * k + 12 + rr] = acc;
         }
         __syncthreads();
     }
@@ -845,178 +905,6 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
         }
         __syncthreads();
     }
-}
-
-// -----------------------------------------------------------------------------------------------------------
-// sample-level kernels (one thread per sample): forward dynamics + derivatives, end-effector, rk4 plant step
-template <typename T>
-__global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, const T* q, const T* v, const T* tau,
-                                const T* fext_pin, T* qdd_out, T* dq_out, T* dv_out, T* minv_out) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    T cs[12], qd[6], u[6], fx[6];
-#pragma unroll
-    for (int a = 0; a < 6; ++a) { sincos_t<T>(q[6 * i + a], &cs[6 + a], &cs[a]); qd[a] = v[6 * i + a]; u[a] = tau[6 * i + a]; }
-    if (fext_pin) {
-#pragma unroll
-        for (int a = 0; a < 3; ++a) { fx[a] = fext_pin[6 * i + 3 + a]; fx[3 + a] = fext_pin[6 * i + a]; }
-    }
-    const T* fext = fext_pin ? fx : nullptr;
-    // the same building blocks as the fused kernel: CRBA columns, bias, LDL' solves, dID columns
-    T A[6][6], dinv[6], bias[6], qdd[6], Mi[36];
-    for (int c = 0; c < 6; ++c) {
-        T out[6];
-        crba_column<T>(rob, cs, c, out);
-        for (int r = 0; r < 6; ++r) A[r][c] = out[r];
-    }
-    rnea_bias<T>(rob, cs, qd, fext, bias);
-    spd6_factor<T>(A, dinv);
-    for (int r = 0; r < 6; ++r) qdd[r] = u[r] - bias[r];
-    spd6_solve_factored<T>(A, dinv, qdd);
-    for (int c = 0; c < 6; ++c) {
-        T b[6];
-        for (int r = 0; r < 6; ++r) b[r] = (r == c) ? T(1) : T(0);
-        spd6_solve_factored<T>(A, dinv, b);
-        for (int r = 0; r < 6; ++r) Mi[6 * r + c] = b[r];
-    }
-    if (qdd_out) for (int a = 0; a < 6; ++a) qdd_out[6 * i + a] = qdd[a];
-    if (minv_out) for (int a = 0; a < 36; ++a) minv_out[36 * i + a] = Mi[a];
-    for (int j = 0; j < 6; ++j) {
-        T cq[6], cv[6];
-        rnea_dcolumn<T, true>(rob, cs, qd, qdd, fext, j, cq);
-        rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, j, cv);
-        for (int r = 0; r < 6; ++r) {
-            T aq = T(0), av = T(0);
-            for (int s = 0; s < 6; ++s) { aq -= Mi[6 * r + s] * cq[s]; av -= Mi[6 * r + s] * cv[s]; }
-            if (dq_out) dq_out[36 * i + 6 * r + j] = aq;
-            if (dv_out) dv_out[36 * i + 6 * r + j] = av;
-        }
-    }
-}
-
-template <typename T>
-__global__ void eepos_kernel(const __grid_constant__ Robot<T> rob, int n, const T* q, T* p_out, T* J_out) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    T cs[12];
-#pragma unroll
-    for (int a = 0; a < 6; ++a) sincos_t<T>(q[6 * i + a], &cs[6 + a], &cs[a]);
-    T pee[3], zs[18], ps[18];
-    fk_ee<T>(rob, cs, pee, zs, ps);
-    for (int a = 0; a < 3; ++a) p_out[3 * i + a] = pee[a];
-    if (J_out) {
-        T J[18];
-        ee_jacobian<T>(pee, zs, ps, J);
-        for (int a = 0; a < 18; ++a) J_out[18 * i + a] = J[a];
-    }
-}
-
-template <typename T>
-I7_DEV void aba_at(const Robot<T>& rob, const T* q, const T* qd, const T* u, const T* fx, T* qdd) {
-    T cs[12];
-#pragma unroll
-    for (int a = 0; a < 6; ++a) sincos_t<T>(q[a], &cs[6 + a], &cs[a]);
-    aba<T, false>(rob, cs, qd, u, fx, qdd, nullptr, nullptr, nullptr);
-}
-
-// rk4 plant step, literal stage order of src/utils.py:3-18 (pin.integrate == q + dq for revolute joints)
-template <typename T>
-__global__ void sim_forward_kernel(const __grid_constant__ Robot<T> rob, int n, const T* x, const T* u, int bcast,
-                                   const T* fext /*Featherstone order or nullptr*/, T dt, T* x_next) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const T* xi = x + (bcast ? 0 : 12 * i);
-    const T* ui = u + (bcast ? 0 : 6 * i);
-    T q[6], v[6], uu[6], fx[6];
-#pragma unroll
-    for (int a = 0; a < 6; ++a) { q[a] = xi[a]; v[a] = xi[6 + a]; uu[a] = ui[a]; fx[a] = fext ? fext[6 * i + a] : T(0); }
-    const T* f = fext ? fx : nullptr;
-    T k1v[6], k2v[6], k3v[6], k4v[6], k2q[6], k3q[6], k4q[6], qt[6];
-    aba_at<T>(rob, q, v, uu, f, k1v);
-#pragma unroll
-    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + v[a] * dt / T(2); k2q[a] = v[a] + k1v[a] * dt / T(2); }
-    aba_at<T>(rob, qt, k2q, uu, f, k2v);
-#pragma unroll
-    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + k2q[a] * dt / T(2); k3q[a] = v[a] + k2v[a] * dt / T(2); }
-    aba_at<T>(rob, qt, k3q, uu, f, k3v);
-#pragma unroll
-    for (int a = 0; a < 6; ++a) { qt[a] = q[a] + k3q[a] * dt; k4q[a] = v[a] + k3v[a] * dt; }
-    aba_at<T>(rob, qt, k4q, uu, f, k4v);
-#pragma unroll
-    for (int a = 0; a < 6; ++a) {
-        const T vn = v[a] + (dt / T(6)) * (k1v[a] + T(2) * k2v[a] + T(2) * k3v[a] + k4v[a]);
-        const T av = (v[a] + T(2) * k2q[a] + T(2) * k3q[a] + k4q[a]) / T(6);
-        x_next[12 * i + a] = q[a] + av * dt;
-        x_next[12 * i + 6 + a] = vn;
-    }
-}
-
-// -----------------------------------------------------------------------------------------------------------
-// best-trajectory selection: one CTA; packed = [costs | best_cost, best_index, XU_best]
-template <typename T>
-__global__ void pack_best_kernel(int batch, int nz, const T* stats, int stats_stride, int cost_col, const T* xu,
-                                 int index_offset, T* packed) {
-    __shared__ T s_val[32];
-    __shared__ int s_idx[32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    T best = T(0); int bi = -1;
-    for (int b = tid; b < batch; b += blockDim.x) {
-        const T c = stats[(size_t)b * stats_stride + cost_col];
-        packed[b] = c;
-        if (c == c && (bi < 0 || c < best)) { best = c; bi = b; }      // strided scan keeps the lowest index on ties
-    }
-    for (int o = 16; o > 0; o >>= 1) {
-        const T ov = __shfl_xor_sync(0xffffffffu, best, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (oi >= 0 && (bi < 0 || ov < best || (ov == best && oi < bi))) { best = ov; bi = oi; }
-    }
-    if (lane == 0) { s_val[warp] = best; s_idx[warp] = bi; }
-    __syncthreads();
-    if (warp == 0) {
-        const int nw = blockDim.x >> 5;
-        best = lane < nw ? s_val[lane] : T(0); bi = lane < nw ? s_idx[lane] : -1;
-        for (int o = 16; o > 0; o >>= 1) {
-            const T ov = __shfl_xor_sync(0xffffffffu, best, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (oi >= 0 && (bi < 0 || ov < best || (ov == best && oi < bi))) { best = ov; bi = oi; }
-        }
-        if (lane == 0) { s_val[0] = best; s_idx[0] = bi; }
-    }
-    __syncthreads();
-    bi = s_idx[0];
-    T* tail = packed + batch;
-    if (tid == 0) { tail[0] = s_val[0]; tail[1] = T(bi < 0 ? -1 : bi + index_offset); }
-    for (int t = tid; t < nz; t += blockDim.x) tail[2 + t] = bi < 0 ? T(0) : xu[(size_t)bi * nz + t];
-}
-
-// gathered: nranks records of `stride` elements; the last 2 + nz of each are [best_cost, best_index, XU_best]
-template <typename T>
-__global__ void reduce_best_kernel(int nranks, int stride, int nz, const T* gathered, T* out) {
-    __shared__ int s_win;
-    if (threadIdx.x == 0) {
-        int win = -1; T best = T(0);
-        for (int r = 0; r < nranks; ++r) {
-            const T* tail = gathered + (size_t)r * stride + (stride - 2 - nz);
-            if (tail[1] >= T(0) && (win < 0 || tail[0] < best)) { best = tail[0]; win = r; }
-        }
-        s_win = win < 0 ? 0 : win;
-    }
-    __syncthreads();
-    const T* tail = gathered + (size_t)s_win * stride + (stride - 2 - nz);
-    for (int t = threadIdx.x; t < 2 + nz; t += blockDim.x) out[t] = tail[t];
-}
-
-// FMA-pipe peak: 8 independent chains per thread, 2 flop per FMA
-template <typename T>
-__global__ void fma_peak_kernel(int iters, T seed, T* sink) {
-    T a0 = seed, a1 = seed + T(1), a2 = seed + T(2), a3 = seed + T(3), a4 = seed + T(4), a5 = seed + T(5), a6 = seed + T(6), a7 = seed + T(7);
-    const T m = T(0.999999), c = T(1e-6);
-    for (int i = 0; i < iters; ++i) {
-        a0 = a0 * m + c; a1 = a1 * m + c; a2 = a2 * m + c; a3 = a3 * m + c;
-        a4 = a4 * m + c; a5 = a5 * m + c; a6 = a6 * m + c; a7 = a7 * m + c;
-    }
-    const T s = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
-    if (s == T(-12345)) sink[0] = s;
 }
 
 }  // namespace i7
