@@ -22,7 +22,7 @@ class I7Config(C.Structure):
     _fields_ = [("N", C.c_int32), ("batch", C.c_int32), ("dtype", C.c_int32), ("device", C.c_int32),
                 ("dt", C.c_double), ("dQ_cost", C.c_double), ("R_cost", C.c_double), ("QN_cost", C.c_double),
                 ("eps", C.c_double), ("regularize", C.c_int32), ("max_qp", C.c_int32), ("mu", C.c_double),
-                ("step_tol", C.c_double), ("threads", C.c_int32), ("reserved", C.c_int32), ("model", I7Model)]
+                ("step_tol", C.c_double), ("threads", C.c_int32), ("cluster", C.c_int32), ("model", I7Model)]
 
 
 # every symbol include/indy7_b200.h declares: name -> (restype, argtypes)

@@ -18,7 +18,7 @@ except Exception:  # pragma: no cover
 
 class Indy7SQP:
     def __init__(self, urdf=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
-                 dtype="fp64", device="cuda", batch=1, threads=0):
+                 dtype="fp64", device="cuda", batch=1, threads=0, cluster=0):
         if isinstance(urdf, RobotModel):
             self.model = urdf
         else:
@@ -30,7 +30,8 @@ class Indy7SQP:
         self.N, self.dt, self.batch, self.dtype = int(N), float(dt), int(batch), dtype
         self.nz = 18 * self.N - 6
         self.engine = Engine(self.model, N=N, dt=dt, dQ_cost=dQ_cost, R_cost=R_cost, QN_cost=QN_cost,
-                             regularize=regularize, eps=eps, batch=batch, dtype=dtype, device=device, threads=threads)
+                             regularize=regularize, eps=eps, batch=batch, dtype=dtype, device=device, threads=threads,
+                             cluster=cluster)
         self._warm = None
 
     def reset(self):

@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libindy7_b200.so")
-HEADERS = ["i7_rbd.cuh", "i7_sqp.cuh", "i7_aux.cuh", "i7_launch.h", os.path.join("..", "..", "include", "indy7_b200.h")]
+HEADERS = ["i7_rbd.cuh", "i7_sqp.cuh", "i7_cluster.cuh", "i7_aux.cuh", "i7_launch.h", os.path.join("..", "..", "include", "indy7_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 
 # (object name, source, extra defines)
@@ -20,6 +20,10 @@ UNITS = [("i7_api", "i7_api.cu", [])]
 for tname, t in (("f64", "double"), ("f32", "float")):
     for nt in (128, 256, 384):
         UNITS.append((f"i7_sqp_{tname}_{nt}", "i7_sqp_inst.cu", [f"-DI7_T={t}", f"-DI7_NT={nt}"]))
+
+
+UNITS.append(("i7_cluster_f64", "i7_cluster_inst.cu", ["-DI7_T=double", "-DI7_CLUSTER_DEFINE_LAYOUT"]))
+UNITS.append(("i7_cluster_f32", "i7_cluster_inst.cu", ["-DI7_T=float"]))
 
 
 def nvcc_path():

@@ -36,6 +36,9 @@ struct i7_handle {
     int smem_bytes = 0;
     int threads = 0;
     int max_smem_optin = 0;
+    bool use_cluster = false;    // i7_solve runs the cluster-per-problem (latency) kernel
+    int cluster_smem_bytes = 0;
+    void* d_xbuf = nullptr;      // exchange buffer of the cluster kernel (batch x cluster_xbuf_len(N))
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
     int64_t launches = 0;
@@ -136,7 +139,8 @@ template <typename T>
 i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& P, cudaStream_t s) {
     P.spill_ws = h->spill ? (T*)h->d_spill : nullptr;
     cudaError_t e;
-    if (h->threads == 384) e = i7::launch_sqp_cta<T, 384>(rob, P, h->smem_bytes, s);
+    if (h->use_cluster && P.mode == i7::MODE_SOLVE) e = i7::launch_sqp_cluster<T>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
+    else if (h->threads == 384) e = i7::launch_sqp_cta<T, 384>(rob, P, h->smem_bytes, s);
     else if (h->threads == 256) e = i7::launch_sqp_cta<T, 256>(rob, P, h->smem_bytes, s);
     else e = i7::launch_sqp_cta<T, 128>(rob, P, h->smem_bytes, s);
     ++h->launches;
@@ -239,6 +243,7 @@ void i7_destroy(i7_handle* h) {
     if (h->out.host) cudaFreeHost(h->out.host);
     if (h->d_fext) cudaFree(h->d_fext);
     if (h->d_spill) cudaFree(h->d_spill);
+    if (h->d_xbuf) cudaFree(h->d_xbuf);
     if (h->d_prof) cudaFree(h->d_prof);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -294,6 +299,26 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
         I7_CUDA_C(cudaMalloc(&h->d_spill, (size_t)cfg->batch * L.reg_size * h->esize));
     }
     h->smem_bytes = L.total * h->esize;
+    // latency regime: a cluster of 8 CTAs per problem when every cluster is resident at once
+    {
+        int sms = 0;
+        I7_CUDA_C(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device));
+        if (cfg->cluster != 0 && cfg->cluster != 1 && cfg->cluster != i7::kClusterSize) { h->err = "cluster must be 0, 1 or 8"; return fail(I7_ERR_INVALID); }
+        h->use_cluster = cfg->cluster == i7::kClusterSize || (cfg->cluster == 0 && cfg->batch * i7::kClusterSize <= sms);
+        if (h->use_cluster) {
+            int ccap = 0;
+            cudaError_t ec = cfg->dtype == I7_F64 ? i7::smem_cap_sqp_cluster<double>(h->max_smem_optin, &ccap)
+                                                  : i7::smem_cap_sqp_cluster<float>(h->max_smem_optin, &ccap);
+            if (ec != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute(cluster): ") + cudaGetErrorString(ec); return fail(I7_ERR_CUDA); }
+            h->cluster_smem_bytes = i7::cluster_smem_len(cfg->N) * h->esize;
+            if (h->cluster_smem_bytes > ccap) {
+                if (cfg->cluster == i7::kClusterSize) { h->err = "horizon too long for the cluster kernel"; return fail(I7_ERR_UNSUPPORTED); }
+                h->use_cluster = false;
+            } else {
+                I7_CUDA_C(cudaMalloc(&h->d_xbuf, (size_t)cfg->batch * i7::cluster_xbuf_len(cfg->N) * h->esize));
+            }
+        }
+    }
     const size_t B = cfg->batch, N = cfg->N, es = h->esize;
     // worst case over all entry points: inputs xu, x0, goals(6), xu_full; outputs of the dump mode
     const size_t in_bytes = B * (2 * h->nz + 12 + 6 * N) * es + 256;

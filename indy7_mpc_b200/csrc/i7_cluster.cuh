@@ -1,0 +1,200 @@
+// i7_cluster.cuh — latency form of the fused SQP-MPC solve: one thread-block CLUSTER of 8 CTAs (8 SMs) per problem.
+//
+// With one or a handful of problems the CTA-per-problem kernel leaves 147 SMs idle while one SM grinds through the
+// per-knot phases at the rate of its FP64 pipe.  Here the knots of a problem are dealt out to the 8 CTAs of a
+// cluster (contiguous windows of ceil(N/8) knots): linearisation, cost terms and the stage-local QP products
+// (setup), the controls and every line-search candidate (merit) run on 8 SMs at once; only the inherently serial
+// backward sweep + roll-out runs on the lead CTA.  The CTAs meet at three cluster barriers per SQP iteration and
+// exchange data through a small L2-resident buffer (barrier.cluster release/acquire orders the global accesses;
+// cross-CTA reads use ld.global.cg):
+//     setup  -> export [L | SG | S | d | hx | cost] per knot ............ barrier 1
+//     lead CTA: backward sweep (streams the exported records) + roll-out -> publish the states x_k ... barrier 2
+//     all: controls u_k of the own knots (published) + merit terms of all 9 candidates at the own knots .. barrier 3
+//     all (redundantly, bit-identical): sum the merit terms, pick alpha, update XU, step norm, stop test
+// Same arithmetic per knot / per stage as the CTA-per-problem kernel (same device functions), reference call
+// stack src/osqp_sqp.py:76-93.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "i7_sqp.cuh"
+
+namespace i7 {
+
+constexpr int CL = 8;          // CTAs per cluster = per problem (portable maximum)
+constexpr int CL_NT = 384;     // threads per CTA
+
+struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, gains, total, chunk; };
+__host__ __device__ inline CLayout make_clayout(int N) {
+    CLayout L;
+    L.chunk = (N + CL - 1) / CL;
+    const int recw = KR_STRIDE > 9 * MP_STRIDE ? KR_STRIDE : 9 * MP_STRIDE;   // records, later the merit scratch
+    int o = 0;
+    L.xu = o; o += 18 * N;
+    L.z = o; o += 18 * N;
+    L.goals = o; o += 3 * N + (N & 1);
+    L.x0 = o; o += 12;
+    L.cost = o; o += COST_STRIDE * L.chunk + ((COST_STRIDE * L.chunk) & 1);
+    L.work = o; o += WK_SIZE;
+    L.ls = o; o += CL_NT + 16;
+    L.kr = o; o += recw * L.chunk + ((recw * L.chunk) & 1);
+    L.gains = o; o += GAIN_STRIDE * N;
+    L.total = o;
+    return L;
+}
+// exchange buffer of one problem (global, L2-resident): ric | zx | zu | mcomps
+__host__ __device__ inline int xbuf_ric(int) { return 0; }
+__host__ __device__ inline int xbuf_zx(int N) { return RIC_STRIDE * N; }
+__host__ __device__ inline int xbuf_zu(int N) { return RIC_STRIDE * N + 12 * N; }
+__host__ __device__ inline int xbuf_mc(int N) { return RIC_STRIDE * N + 18 * N; }
+__host__ __device__ inline int xbuf_size(int N) { return RIC_STRIDE * N + 18 * N + 36 * N; }
+
+template <typename T>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(CL_NT)
+sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__ SolveParams<T> P, T* xbuf_all) {
+    constexpr int NT = CL_NT;
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* sm = reinterpret_cast<T*>(smem_raw);
+    const int tid = threadIdx.x, N = P.N;
+    const int rank = (int)cluster.block_rank();
+    const int b = blockIdx.x / CL;
+    const int nz = 18 * N - 6;
+    const CLayout L = make_clayout(N);
+    Ptrs<T> M;
+    M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
+    M.work = sm + L.work; M.ls = sm + L.ls; M.kr = sm + L.kr; M.merit_cap = 9;
+    T* gains = sm + L.gains;
+    T* xbuf = xbuf_all + (size_t)b * xbuf_size(N);
+    T* ric = xbuf + xbuf_ric(N);
+    T* zx = xbuf + xbuf_zx(N);
+    T* zu = xbuf + xbuf_zu(N);
+    T* mcomps = xbuf + xbuf_mc(N);
+    Win W;
+    W.k0 = rank * L.chunk;
+    W.nc = N - W.k0 < 0 ? 0 : (N - W.k0 > L.chunk ? L.chunk : N - W.k0);
+    W.nd = N - 1 - W.k0 < 0 ? 0 : (N - 1 - W.k0 > L.chunk ? L.chunk : N - 1 - W.k0);
+    __shared__ T s_merits[9];
+    __shared__ T s_alpha;
+    __shared__ T s_merit_acc;
+    __shared__ T s_fext[6];
+    __shared__ int s_flag;
+    long long* prof = (P.prof && rank == 0) ? P.prof + (size_t)b * 32 : nullptr;
+
+    // ---- load inputs (every CTA keeps the whole iterate; it is 4.6 KB) ----
+    for (int t = tid; t < nz; t += NT) M.xu[t] = P.xu_in[(size_t)b * nz + t];
+    if (tid < 6) M.xu[nz + tid] = T(0);                          // padded u_{N-1}
+    for (int t = tid; t < 18 * N; t += NT) M.z[t] = T(0);
+    for (int t = tid; t < 3 * N; t += NT) {
+        const int k = t / 3, a = t - 3 * k;
+        M.goals[t] = P.goals[(size_t)b * N * P.goal_stride + k * P.goal_stride + a];
+    }
+    if (tid < 12) M.x0[tid] = P.x0[(size_t)b * 12 + tid];
+    if (tid < 6) s_fext[tid] = P.fext ? P.fext[(size_t)b * 6 + tid] : T(0);
+    __syncthreads();
+    const T* fext = P.fext ? s_fext : nullptr;
+
+    int qp_iters = 0, n_ls = 0, n_steps = 0, status = 0;
+    T alphas[2] = {T(0), T(0)}, steps[2] = {T(0), T(0)};
+    T merit_final = T(0), merit_first = T(0);
+    for (int qp = 0; qp < P.max_qp; ++qp) {
+        qp_iters = qp + 1;
+        if (prof && tid == 0) prof[5 * qp + 0] = clock64();
+        // ---- setup of the own knots; export what the backward sweep needs ----
+        phase_setup<T, NT>(rob, P, M, W, fext, false, qp == 0 ? prof : nullptr);
+        for (int t = tid; t < RIC_STRIDE * W.nc; t += NT) {
+            const int k = t / RIC_STRIDE, e = t - RIC_STRIDE * k;
+            const T* kr = M.kr + KR_STRIDE * k;
+            T v = T(0);
+            if (e >= RIC_COST) { if (e < RIC_COST + COST_STRIDE) v = M.cost[COST_STRIDE * k + e - RIC_COST]; }
+            else if (k < W.nd) {
+                if (e < RIC_SG) v = kr[KR_L + e];
+                else if (e < RIC_S) v = kr[KR_SG + e - RIC_SG];
+                else if (e < RIC_D) v = kr[KR_S + e - RIC_S];
+                else if (e < RIC_HX) v = kr[KR_D + e - RIC_D];
+                else v = kr[KR_HX + e - RIC_HX];
+            }
+            ric[RIC_STRIDE * (W.k0 + k) + e] = v;
+        }
+        cluster.sync();                                                             // barrier 1
+        if (prof && tid == 0) prof[5 * qp + 1] = clock64();
+        // ---- lead CTA: exact QP solve (backward sweep + roll-out), publish the states ----
+        if (rank == 0) {
+            riccati_sweep<T, NT, RicGlobal<T>>(P, M, RicGlobal<T>{ric, gains}, qp == 0 ? prof : nullptr);
+            for (int t = tid; t < 12 * N; t += NT) {
+                const int k = t / 12, i = t - 12 * k;
+                zx[t] = M.z[18 * k + i];
+            }
+        }
+        cluster.sync();                                                             // barrier 2
+        if (rank != 0) {
+            for (int t = tid; t < 12 * N; t += NT) {
+                const int k = t / 12, i = t - 12 * k;
+                M.z[18 * k + i] = __ldcg(zx + t);
+            }
+        }
+        __syncthreads();
+        phase_controls<T, NT>(P, M, W, zu);
+        if (prof && tid == 0) prof[5 * qp + 2] = clock64();
+        // ---- line search: all nine candidates at the own knots ----
+        merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, 0, 9, mcomps);
+        cluster.sync();                                                             // barrier 3
+        for (int t = tid; t < 6 * (N - 1); t += NT) {
+            const int k = t / 6, i = t - 6 * k;
+            if (k < W.k0 || k >= W.k0 + W.nd) M.z[18 * k + 12 + i] = __ldcg(zu + t);
+        }
+        if (tid == 0) { s_alpha = T(0); s_flag = 0; }
+        merit_reduce<T, NT, true>(P, M.xu, M.z, 0, 9, mcomps, s_merits, nullptr);
+        if (tid == 0) {
+            if (!(s_merits[0] == s_merits[0])) s_flag = 1;
+            s_merit_acc = s_merits[0];
+            for (int c = 1; c < 9; ++c)
+                if (s_merits[c] <= s_merits[0]) { s_alpha = T(c_alphas[c]); s_merit_acc = s_merits[c]; break; }
+        }
+        __syncthreads();
+        if (prof && tid == 0) prof[5 * qp + 3] = clock64();
+        const T alpha = s_alpha;
+        merit_final = s_merit_acc;
+        if (qp == 0) merit_first = s_merits[0];
+        if (s_flag) status = 2;
+        if (qp < 2) alphas[qp] = alpha;
+        ++n_ls;
+        if (alpha == T(0)) {
+            // src/osqp_sqp.py:81-82 `continue`: the remaining passes would re-solve the identical QP; counted, skipped
+            if (status == 0) status = 1;
+            for (int q2 = qp + 1; q2 < P.max_qp; ++q2) { if (q2 < 2) alphas[q2] = T(0); ++n_ls; qp_iters = q2 + 1; }
+            break;
+        }
+        // XU += alpha (z - XU); step norm (every CTA, identically)
+        T* part = M.ls;
+        T loc = T(0);
+        for (int t = tid; t < nz; t += NT) {
+            const T st = alpha * (M.z[t] - M.xu[t]);
+            M.xu[t] += st;
+            loc += st * st;
+        }
+        part[tid] = loc;
+        __syncthreads();
+        if (tid < 32) {
+            T s = warp_sum_strided<T>(part, NT, tid);
+            if (tid == 0) s_merit_acc = sqrt_t<T>(s);
+        }
+        __syncthreads();
+        const T stepsize = s_merit_acc;
+        if (prof && tid == 0) prof[5 * qp + 4] = clock64();
+        if (n_steps < 2) steps[n_steps] = stepsize;
+        ++n_steps;
+        __syncthreads();
+        if (stepsize < P.step_tol) break;
+    }
+    // ---- outputs: every CTA writes a slice of the trajectory, the lead CTA the statistics ----
+    for (int t = rank * NT + tid; t < nz; t += CL * NT) P.xu_out[(size_t)b * nz + t] = M.xu[t];
+    if (P.stats && rank == 0 && tid == 0) {
+        T* st = P.stats + (size_t)b * 12;
+        st[0] = T(qp_iters); st[1] = T(n_ls); st[2] = T(n_steps); st[3] = T(status);
+        st[4] = alphas[0]; st[5] = alphas[1]; st[6] = steps[0]; st[7] = steps[1];
+        st[8] = merit_final; st[9] = merit_first; st[10] = T(0); st[11] = T(0);
+    }
+}
+
+}  // namespace i7

@@ -1,0 +1,32 @@
+// i7_cluster_inst.cu — one instance of the cluster-per-problem (latency) kernel; compiled once per I7_T.
+#include "i7_cluster.cuh"
+#include "i7_launch.h"
+
+#ifndef I7_T
+#error "compile with -DI7_T=double|float"
+#endif
+
+namespace i7 {
+
+template <>
+cudaError_t launch_sqp_cluster<I7_T>(const Robot<I7_T>& rob, const SolveParams<I7_T>& P, I7_T* xbuf, int smem_bytes,
+                                     cudaStream_t s) {
+    sqp_cluster_kernel<I7_T><<<P.batch * CL, CL_NT, smem_bytes, s>>>(rob, P, xbuf);
+    return cudaGetLastError();
+}
+
+template <>
+cudaError_t smem_cap_sqp_cluster<I7_T>(int optin_bytes, int* cap) {
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, sqp_cluster_kernel<I7_T>);
+    if (e != cudaSuccess) return e;
+    *cap = optin_bytes - (int)fa.sharedSizeBytes;
+    return cudaFuncSetAttribute(sqp_cluster_kernel<I7_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, *cap);
+}
+
+#ifdef I7_CLUSTER_DEFINE_LAYOUT
+int cluster_smem_len(int N) { return make_clayout(N).total; }
+int cluster_xbuf_len(int N) { return xbuf_size(N); }
+#endif
+
+}  // namespace i7

@@ -97,6 +97,10 @@ struct Ptrs {
     int merit_cap;      // candidates per merit wave that fit the scratch region
 };
 
+// the knots a CTA works on in the per-knot phases: [k0, k0 + nc) for cost terms, [k0, k0 + nd) for dynamics;
+// the whole horizon (0, N-1, N) when one CTA owns the problem.  Records / cost terms are indexed window-relative.
+struct Win { int k0, nd, nc; };
+
 static __device__ __constant__ double c_alphas[9] = {0.0, 1.0, 0.5, 0.25, 0.125, 0.0625, 0.03125, 0.015625, 0.0078125};
 // upper triangle of a 12x12 matrix, row-major enumeration
 static __device__ __constant__ unsigned char c_tri_r[78] = {
@@ -109,18 +113,19 @@ static __device__ __constant__ unsigned char c_tri_c[78] = {
 // -----------------------------------------------------------------------------------------------------------
 // setup: linearised dynamics, cost terms and all stage-local QP products at the current iterate
 template <typename T, int NT>
-__device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* fext, bool for_dump,
-                            long long* prof) {
+__device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const Win W, const T* fext,
+                            bool for_dump, long long* prof) {
     const int tid = threadIdx.x;
     int pi = 16;
 #define I7_STAMP() do { if (prof && tid == 0) prof[pi++] = clock64(); } while (0)
     I7_STAMP();
-    const int N = P.N, nk = N - 1;
-    const T* xu = M.xu;
+    const int N = P.N, nk = W.nd, nc = W.nc;      // dynamics knots / cost knots of this CTA's window
+    const T* xu = M.xu + 18 * W.k0;               // window-relative: knot index k below is local, records are local
+    const T* goals = M.goals + 3 * W.k0;
     const T dt = P.dt;
     // S0: cos / sin of every joint angle
-    for (int t = tid; t < 6 * N; t += NT) {
-        const int i = t / N, k = t - i * N;
+    for (int t = tid; t < 6 * nc; t += NT) {
+        const int i = t / nc, k = t - i * nc;
         T s, c;
         sincos_t<T>(xu[18 * k + i], &s, &c);
         T* kr = M.kr + KR_STRIDE * k;
@@ -129,7 +134,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     __syncthreads();
     I7_STAMP();
     // S1: 6 mass-matrix columns + bias torques per knot (k < N-1), FK / cost terms per knot (k < N)
-    for (int t = tid; t < 7 * nk + N; t += NT) {
+    for (int t = tid; t < 7 * nk + nc; t += NT) {
         const int type = t < 7 * nk ? t / nk : 7;
         const int k = t < 7 * nk ? t - type * nk : t - 7 * nk;
         T* kr = M.kr + KR_STRIDE * k;
@@ -151,7 +156,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
         } else {
             T pee[3], zs[18], ps[18];
             fk_ee<T>(rob, cs, pee, zs, ps);
-            const T* gk = M.goals + 3 * k;
+            const T* gk = goals + 3 * k;
             const T e[3] = {pee[0] - gk[0], pee[1] - gk[1], pee[2] - gk[2]};
             T* ck = M.cost + COST_STRIDE * k;
 #pragma unroll
@@ -163,7 +168,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
             }
             const T nrm = sqrt_t<T>(e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
             const T sc = P.regularize ? T(1) / (nrm + P.eps) : T(1);
-            ck[6] = (k == N - 1) ? P.QN : T(1);
+            ck[6] = (W.k0 + k == N - 1) ? P.QN : T(1);
             ck[7] = P.dQ * sc;
             ck[8] = P.R * sc;
         }
@@ -326,21 +331,34 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
 }
 
 // -----------------------------------------------------------------------------------------------------------
-// Hww / Hwx / hw of stage k from the value function (Pm, pv) of stage k+1:
-//   Hww = P_vv + S,  Hwx = [P_qv' - SG_q, dt P_qv' - SG_v],  hw = p_v - d
-template <typename T>
-I7_DEV void aug_from_P_entry(T* aug, const T* kr, int r, int c, T val, T dt) {
-    // called by the thread that owns P[r][c], r <= c
-    if (r < 6 && c >= 6) {
-        const int i = c - 6;   // Hwx[i][r] = P[r][6+i] - SG[i][r] ;  Hwx[i][6+r] = dt P[r][6+i] - SG[i][6+r]
-        aug[AUGW * i + 6 + r] = val - kr[KR_SG + 12 * i + r];
-        aug[AUGW * i + 12 + r] = dt * val - kr[KR_SG + 12 * i + 6 + r];
-    } else if (r >= 6) {
-        const int i = r - 6, j = c - 6;
-        aug[AUGW * i + j] = val + kr[KR_S + 6 * i + j];
-        if (i != j) aug[AUGW * j + i] = val + kr[KR_S + 6 * j + i];
-    }
-}
+// Stage k of the backward sweep works on  [Hww | Hwx | hw]  (6 x 19) built from the value function (Pm, pv) of
+// stage k+1:   Hww = P_vv + S,  Hwx = [P_qv' - SG_q, dt P_qv' - SG_v],  hw = p_v - d
+// Where the sweep finds the stage data and keeps the gains.
+//   RicLocal   one CTA owns the problem: per-knot records in its shared memory (or its spill workspace); the gains
+//              overwrite the SG / d slots of the record once the stage is eliminated
+//   RicGlobal  cluster form: the owners of the knots exported [L | SG | S | d | hx | cost] to an L2-resident
+//              exchange buffer; the lead CTA streams it (ld.global.cg, issued while the 6x6 solves run) and keeps the
+//              gains in its own shared memory
+constexpr int RIC_L = 0, RIC_SG = 78, RIC_S = 150, RIC_D = 186, RIC_HX = 192, RIC_COST = 204, RIC_STRIDE = 216;
+constexpr int GAIN_STRIDE = 80;     // Kw (6 x 12 row-major), kw (6), 2 pad
+template <typename T> struct RicLocal {
+    T* kr; const T* cost;
+    static constexpr int oL = KR_L, oSG = KR_SG, oS = KR_S, oD = KR_D, oHX = KR_HX;
+    I7_DEV const T* rec(int k) const { return kr + KR_STRIDE * k; }
+    I7_DEV const T* ck(int k) const { return cost + COST_STRIDE * k; }
+    I7_DEV T* gK(int k) const { return kr + KR_STRIDE * k + KR_SG; }
+    I7_DEV T* gk(int k) const { return kr + KR_STRIDE * k + KR_D; }
+    static I7_DEV T ld(const T* p) { return *p; }
+};
+template <typename T> struct RicGlobal {
+    const T* ric; T* gains;
+    static constexpr int oL = RIC_L, oSG = RIC_SG, oS = RIC_S, oD = RIC_D, oHX = RIC_HX;
+    I7_DEV const T* rec(int k) const { return ric + RIC_STRIDE * k; }
+    I7_DEV const T* ck(int k) const { return ric + RIC_STRIDE * k + RIC_COST; }
+    I7_DEV T* gK(int k) const { return gains + GAIN_STRIDE * k; }
+    I7_DEV T* gk(int k) const { return gains + GAIN_STRIDE * k + 72; }
+    static I7_DEV T ld(const T* p) { return __ldcg(p); }
+};
 
 // riccati: backward recursion for the gains, forward roll-out for z.  x0 = measured state (l[:12] = -xs).
 //
@@ -353,9 +371,9 @@ I7_DEV void aug_from_P_entry(T* aug, const T* kr, int r, int c, T val, T dt) {
 //                         correction (12 loads, 6 FMAs in two chains) is left.
 // Only the qq block of P is exchanged between threads (T'PT reads nothing else); the qv / vv blocks and p_v flow
 // directly into the next stage's augmented matrix.
-template <typename T, int NT>
-__device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long long* prof) {
-    static_assert(NT >= 128, "phase_riccati needs at least 4 warps");
+template <typename T, int NT, typename Src>
+__device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, const Ptrs<T>& M, const Src src, long long* prof) {
+    static_assert(NT >= 128, "riccati_sweep needs at least 4 warps");
     const int tid = threadIdx.x;
     long long acc_r2 = 0, acc_r3 = 0, tt = 0;
     const int N = P.N;
@@ -376,32 +394,74 @@ __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long lo
     const int ra = r < 6 ? r : r - 6, ca = c < 6 ? c : c - 6;
     const T tfac = (r < 6 ? T(1) : dt) * ((is_P && c >= 6) ? dt : T(1));   // T'PT scale (P entry) / T'p scale (p entry)
     const int offA = 6 + r;                                  // Hwx[s][r] = aug[AUGW s + 6 + r]
-    const int offB = is_P ? KR_SG + c : KR_D;                // Kw[s][c] (stride 12) or kw[s] (stride 1)
-    const int strB = is_P ? 12 : 1;
+    const int strB = is_P ? 12 : 1;                          // Kw[s][c] (stride 12) or kw[s] (stride 1)
+    // operands of the NEXT stage's augmented matrix that this thread's entry feeds (record offsets, -1 = none)
+    int on0 = -1, on1 = -1;
+    if (is_P && c >= 6) {
+        if (r < 6) { on0 = Src::oSG + 12 * (c - 6) + r; on1 = Src::oSG + 12 * (c - 6) + 6 + r; }
+        else { on0 = Src::oS + 6 * (r - 6) + (c - 6); on1 = Src::oS + 6 * (c - 6) + (r - 6); }
+    } else if (is_p && r >= 6) {
+        on0 = Src::oD + r - 6;
+    }
     int cur = 0;
     // terminal value function: P_N = blkdiag(QN j j', dQ_N I), p_N = [QN j; dQ_N v]; aug for stage N-2
     {
-        const T* cN = M.cost + COST_STRIDE * (N - 1);
+        const T* cN = src.ck(N - 1);
         const T* xN = xu + 18 * (N - 1);
-        const T* kr = M.kr + KR_STRIDE * (N - 2);
+        const T* rn = src.rec(N - 2);
+        T* augn = wk + WK_AUG;
         if (is_P) {
+            const T n0 = on0 >= 0 ? Src::ld(rn + on0) : T(0), n1 = on1 >= 0 ? Src::ld(rn + on1) : T(0);
             T v = T(0);
-            if (c < 6) v = cN[6] * cN[r] * cN[c];
-            else if (r == c) v = cN[7];
+            if (c < 6) v = Src::ld(cN + 6) * Src::ld(cN + r) * Src::ld(cN + c);
+            else if (r == c) v = Src::ld(cN + 7);
             if (c < 6) { wk[WK_P + 6 * r + c] = v; wk[WK_P + 6 * c + r] = v; }
-            aug_from_P_entry<T>(wk + WK_AUG, kr, r, c, v, dt);
+            else if (r < 6) {
+                augn[AUGW * (c - 6) + 6 + r] = v - n0;
+                augn[AUGW * (c - 6) + 12 + r] = dt * v - n1;
+            } else {
+                augn[AUGW * (r - 6) + (c - 6)] = v + n0;
+                if (r != c) augn[AUGW * (c - 6) + (r - 6)] = v + n1;
+            }
         } else if (is_p) {
-            const T v = r < 6 ? cN[6] * cN[r] : cN[7] * xN[r];
+            const T v = r < 6 ? Src::ld(cN + 6) * Src::ld(cN + r) : Src::ld(cN + 7) * xN[r];
             wk[WK_PV + r] = v;
-            if (r >= 6) wk[WK_AUG + AUGW * (r - 6) + 18] = v - kr[KR_D + r - 6];
+            if (r >= 6) augn[AUGW * (r - 6) + 18] = v - Src::ld(rn + on0);
         }
     }
+    // Stage operands that do not depend on the recursion are fetched ONE STAGE AHEAD (they may sit in L2 when the
+    // records were exported by other CTAs): cL/cQ = L + Qx entry (or hx) of the current stage, cn0/cn1 = operands of
+    // the next stage's augmented matrix.
+    T cL = T(0), cQ = T(0), cn0 = T(0), cn1 = T(0);
+    auto fetch = [&](int k, T& fL, T& fQ, T& f0, T& f1) {
+        fL = T(0); fQ = T(0); f0 = T(0); f1 = T(0);
+        if (k < 0) return;
+        const T* rk = src.rec(k);
+        if (is_P) {
+            const T* ck = src.ck(k);
+            fL = Src::ld(rk + Src::oL + e);
+            if (c < 6) fQ = Src::ld(ck + 6) * Src::ld(ck + r) * Src::ld(ck + c);
+            else if (r == c) fQ = Src::ld(ck + 7);
+        } else if (is_p) {
+            fL = Src::ld(rk + Src::oHX + r);
+        }
+        if (k > 0 && on0 >= 0) {
+            const T* rn = src.rec(k - 1);
+            f0 = Src::ld(rn + on0);
+            if (on1 >= 0) f1 = Src::ld(rn + on1);
+        }
+    };
+    fetch(N - 2, cL, cQ, cn0, cn1);
     __syncthreads();
     for (int k = N - 2; k >= 0; --k) {
-        T* kr = M.kr + KR_STRIDE * k;
+        T* gK = src.gK(k);
+        T* gk = src.gk(k);
         T* aug = wk + WK_AUG + 114 * cur;
         if (prof && tid == 0) tt = clock64();
-        T base = T(0), n0 = T(0), n1 = T(0);   // R3 operands that do not depend on this stage's solve
+        T pL, pQ, pn0, pn1;
+        fetch(k - 1, pL, pQ, pn0, pn1);        // consumed in the next iteration
+        T base = T(0);
+        const T n0 = cn0, n1 = cn1;
         if (tid < 13) {
             // R2: one right-hand side of X = Hww^-1 [Hwx | hw]
             T A[6][6], dinv[6], b[6];
@@ -413,27 +473,18 @@ __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long lo
             for (int i = 0; i < 6; ++i) b[i] = aug[AUGW * i + 6 + tid];
             spd6_factor<T>(A, dinv);
             spd6_solve_factored<T>(A, dinv, b);
-            // feedback / feed-forward of w = v_{k+1}: Kw = -X[:, :12], kw = -X[:, 12] (overwrites SG, d)
+            // feedback / feed-forward of w = v_{k+1}: Kw = -X[:, :12], kw = -X[:, 12]
             if (tid < 12) {
 #pragma unroll
-                for (int i = 0; i < 6; ++i) kr[KR_SG + 12 * i + tid] = -b[i];
+                for (int i = 0; i < 6; ++i) gK[12 * i + tid] = -b[i];
             } else {
 #pragma unroll
-                for (int i = 0; i < 6; ++i) kr[KR_D + i] = -b[i];
+                for (int i = 0; i < 6; ++i) gk[i] = -b[i];
             }
         } else if (is_P) {
-            const T* ck = M.cost + COST_STRIDE * k;
-            base = kr[KR_L + e] + wk[WK_P + 36 * cur + 6 * ra + ca] * tfac;
-            if (c < 6) base += ck[6] * ck[r] * ck[c];
-            else if (r == c) base += ck[7];
-            if (k > 0) {
-                const T* krn = kr - KR_STRIDE;
-                if (r < 6 && c >= 6) { n0 = krn[KR_SG + 12 * (c - 6) + r]; n1 = krn[KR_SG + 12 * (c - 6) + 6 + r]; }
-                else if (r >= 6) { n0 = krn[KR_S + 6 * (r - 6) + (c - 6)]; n1 = krn[KR_S + 6 * (c - 6) + (r - 6)]; }
-            }
+            base = (cL + cQ) + wk[WK_P + 36 * cur + 6 * ra + ca] * tfac;
         } else if (is_p) {
-            base = kr[KR_HX + r] + wk[WK_PV + 12 * cur + ra] * tfac;
-            if (k > 0 && r >= 6) n0 = (kr - KR_STRIDE)[KR_D + r - 6];
+            base = cL + wk[WK_PV + 12 * cur + ra] * tfac;
         }
         __syncthreads();
         if (prof && tid == 0) { const long long n = clock64(); acc_r2 += n - tt; tt = n; }
@@ -441,7 +492,7 @@ __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long lo
         if (is_P || is_p) {
             T a0 = base, a1 = T(0);
             const T* hb = aug + offA;
-            const T* kb = kr + offB;
+            const T* kb = is_P ? gK + c : gk;
 #pragma unroll
             for (int s = 0; s < 3; ++s) {
                 a0 += hb[AUGW * s] * kb[strB * s];
@@ -472,85 +523,93 @@ __device__ void phase_riccati(const SolveParams<T>& P, const Ptrs<T>& M, long lo
         __syncthreads();
         if (prof && tid == 0) acc_r3 += clock64() - tt;
         cur ^= 1;
+        cL = pL; cQ = pQ; cn0 = pn0; cn1 = pn1;
     }
     if (prof && tid == 0) { prof[10] = acc_r2; prof[11] = acc_r3; tt = clock64(); }
-    // forward roll-out by warp 0: x_0 = xs, v_{k+1} = Kw_k x_k + kw_k, q_{k+1} = q_k + dt v_k.  The gain row of the
-    // next stage is fetched before the current state is read back, so only the state round trip is serial.
+    // forward roll-out by warp 0: x_0 = xs, v_{k+1} = Kw_k x_k + kw_k, q_{k+1} = q_k + dt v_k.  The state lives in
+    // registers, replicated in every lane; lane r (mod 6) evaluates row r of the gain and the six results are
+    // exchanged with shuffles, so the serial chain per stage is 3 FMAs + 2 adds + one shuffle (no shared-memory
+    // round trip); the gain row of the next stage is fetched while the current one is applied.
     if (tid < 32) {
         T* z = M.z;
+        const int row = tid % 6;
+        T x[12], g[12], ff, my_q = M.x0[row], my_v = M.x0[6 + row];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) x[i] = M.x0[i];
         if (tid < 12) z[tid] = M.x0[tid];
-        const int row = tid < 6 ? tid : 0;
-        T g[12], ff;
         {
-            const T* kr = M.kr;
+            const T* gK = src.gK(0);
 #pragma unroll
-            for (int i = 0; i < 12; ++i) g[i] = kr[KR_SG + 12 * row + i];
-            ff = kr[KR_D + row];
+            for (int i = 0; i < 12; ++i) g[i] = gK[12 * row + i];
+            ff = src.gk(0)[row];
         }
-        __syncwarp();
         for (int k = 0; k < N - 1; ++k) {
-            T* zk = z + 18 * k;
             T gn[12], ffn = T(0);
-            if (k + 1 < N - 1) {
-                const T* krn = M.kr + KR_STRIDE * (k + 1);
+            const int kn = k + 1 < N - 1 ? k + 1 : k;
+            {
+                const T* gK = src.gK(kn);
 #pragma unroll
-                for (int i = 0; i < 12; ++i) gn[i] = krn[KR_SG + 12 * row + i];
-                ffn = krn[KR_D + row];
-            } else {
-#pragma unroll
-                for (int i = 0; i < 12; ++i) gn[i] = T(0);
+                for (int i = 0; i < 12; ++i) gn[i] = gK[12 * row + i];
+                ffn = src.gk(kn)[row];
             }
-            if (tid < 6) {
-                T a0 = ff, a1 = T(0), a2 = T(0), a3 = T(0);
+            T a0 = ff, a1 = T(0), a2 = T(0), a3 = T(0);
 #pragma unroll
-                for (int i = 0; i < 3; ++i) {
-                    a0 += g[i] * zk[i];
-                    a1 += g[3 + i] * zk[3 + i];
-                    a2 += g[6 + i] * zk[6 + i];
-                    a3 += g[9 + i] * zk[9 + i];
-                }
-                zk[18 + 6 + tid] = (a0 + a1) + (a2 + a3);
-            } else if (tid < 12) {
-                const int q = tid - 6;
-                zk[18 + q] = zk[q] + dt * zk[6 + q];
+            for (int i = 0; i < 3; ++i) {
+                a0 += g[i] * x[i];
+                a1 += g[3 + i] * x[3 + i];
+                a2 += g[6 + i] * x[6 + i];
+                a3 += g[9 + i] * x[9 + i];
+            }
+            const T vn = (a0 + a1) + (a2 + a3);
+            my_q = my_q + dt * my_v;
+            my_v = vn;
+            if (tid < 6) { z[18 * (k + 1) + row] = my_q; z[18 * (k + 1) + 6 + row] = vn; }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                x[i] = x[i] + dt * x[6 + i];
+                x[6 + i] = __shfl_sync(0xffffffffu, vn, i);
             }
 #pragma unroll
             for (int i = 0; i < 12; ++i) g[i] = gn[i];
             ff = ffn;
-            __syncwarp();
         }
     }
     __syncthreads();
     if (prof && tid == 0) { prof[12] = clock64() - tt; tt = clock64(); }
-    // controls for all knots in parallel: u_k = Y_k (v_{k+1} - Gq q_k - Gv v_k - cv_k)
-    {
-        const int nk = N - 1;
-        T* z = M.z;
-        T* tmp = M.ls;
-        for (int t = tid; t < 6 * nk; t += NT) {
-            const int rr = t / nk, k = t - rr * nk;
-            const T* kr = M.kr + KR_STRIDE * k;
-            const T* zk = z + 18 * k;
-            T a0 = zk[18 + 6 + rr] - kr[KR_CV + rr], a1 = T(0);
+    (void)tt;
+}
+
+// controls of the window's knots: u_k = Y_k (v_{k+1} - Gq q_k - Gv v_k - cv_k); needs the x part of z for knots k, k+1.
+// zu_out (cluster form): the controls are also published to the exchange buffer, 6 per knot.
+template <typename T, int NT>
+__device__ __noinline__ void phase_controls(const SolveParams<T>& P, const Ptrs<T>& M, const Win W, T* zu_out) {
+    const int tid = threadIdx.x;
+    const int nk = W.nd;
+    T* z = M.z + 18 * W.k0;
+    T* tmp = M.ls;
+    for (int t = tid; t < 6 * nk; t += NT) {
+        const int rr = t / nk, k = t - rr * nk;
+        const T* kr = M.kr + KR_STRIDE * k;
+        const T* zk = z + 18 * k;
+        T a0 = zk[18 + 6 + rr] - kr[KR_CV + rr], a1 = T(0);
 #pragma unroll
-            for (int s = 0; s < 6; ++s) {
-                a0 -= kr[KR_GQ + 6 * rr + s] * zk[s];
-                a1 -= kr[KR_GV + 6 * rr + s] * zk[6 + s];
-            }
-            tmp[6 * k + rr] = a0 + a1;
+        for (int s = 0; s < 6; ++s) {
+            a0 -= kr[KR_GQ + 6 * rr + s] * zk[s];
+            a1 -= kr[KR_GV + 6 * rr + s] * zk[6 + s];
         }
-        __syncthreads();
-        for (int t = tid; t < 6 * nk; t += NT) {
-            const int rr = t / nk, k = t - rr * nk;
-            const T* kr = M.kr + KR_STRIDE * k;
-            T acc = T(0);
-#pragma unroll
-            for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * rr + s] * tmp[6 * k + s];
-            z[18 * k + 12 + rr] = acc;
-        }
-        __syncthreads();
+        tmp[6 * k + rr] = a0 + a1;
     }
-    if (prof && tid == 0) prof[13] = clock64() - tt;
+    __syncthreads();
+    for (int t = tid; t < 6 * nk; t += NT) {
+        const int rr = t / nk, k = t - rr * nk;
+        const T* kr = M.kr + KR_STRIDE * k;
+        T acc = T(0);
+#pragma unroll
+        for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * rr + s] * tmp[6 * k + s];
+        z[18 * k + 12 + rr] = acc;
+        if (zu_out) zu_out[6 * (W.k0 + k) + rr] = acc;
+    }
+    __syncthreads();
 }
 
 // -----------------------------------------------------------------------------------------------------------
@@ -563,31 +622,33 @@ template <typename T> I7_DEV T warp_sum_strided(const T* vals, int n, int lane) 
     return s;
 }
 
-// Merit terms of the candidates c0 .. c0+nc-1 (index into c_alphas; 0 = base) of the line  xa + alpha (xb - xa):
-// comps[4 * (ci * N + k) + {0,1,2,3}] = {qcost, vcost, ucost, integrator_err} of knot k   (src/osqp_sqp.py:13-47).
-// Forward dynamics per point: M columns + bias by 7 parallel tasks, then one 6x6 LDL' solve.
+// Merit terms of the candidates c0 .. c0+nc-1 (index into c_alphas; 0 = base) of the line  xa + alpha (xb - xa) at the
+// knots of the window W:  comps[4 * (ci * N + k) + {0,1,2,3}] = {qcost, vcost, ucost, integrator_err} of knot k
+// (k = horizon index; src/osqp_sqp.py:13-47).  Forward dynamics per point: M columns + bias by 7 parallel tasks,
+// then one 6x6 LDL' solve.  scr: MP_STRIDE numbers of scratch per point.
 template <typename T, int NT>
-__device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const T* xa, const T* xb,
-                             const T* fext, int c0, int nc, T* comps) {
-    const int tid = threadIdx.x, N = P.N, nk = N - 1;
-    const int npts = nc * N;
-    T* scr = M.kr;
+__device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const Win W, T* scr,
+                             const T* xa_, const T* xb_, const T* fext, int c0, int nc, T* comps) {
+    const int tid = threadIdx.x, N = P.N, nk = W.nd, nw = W.nc;
+    const int npts = nc * nw;
+    const T* xa = xa_ + 18 * W.k0;
+    const T* xb = xb_ + 18 * W.k0;
     // M0: cos / sin
     for (int t = tid; t < 6 * npts; t += NT) {
         const int i = t / npts, p = t - i * npts;
-        const int ci = p / N, k = p - ci * N;
+        const int ci = p / nw, k = p - ci * nw;
         const T alpha = T(c_alphas[c0 + ci]);
         const T q = xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]);
-        T s, c;
-        sincos_t<T>(q, &s, &c);
-        scr[MP_STRIDE * p + MP_CS + i] = c; scr[MP_STRIDE * p + MP_CS + 6 + i] = s;
+        T sn, cs;
+        sincos_t<T>(q, &sn, &cs);
+        scr[MP_STRIDE * p + MP_CS + i] = cs; scr[MP_STRIDE * p + MP_CS + 6 + i] = sn;
     }
     __syncthreads();
-    // M1: mass-matrix columns and bias torques at every point with dynamics (k < N-1)
+    // M1: mass-matrix columns and bias torques at every point with dynamics
     for (int t = tid; t < 7 * nc * nk; t += NT) {
         const int type = t / (nc * nk), rem = t - type * nc * nk;
         const int ci = rem / nk, k = rem - ci * nk;
-        const int p = ci * N + k;
+        const int p = ci * nw + k;
         T* sp = scr + MP_STRIDE * p;
         T cs[12], out[6];
 #pragma unroll
@@ -609,7 +670,8 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
     __syncthreads();
     // M2: per point: FK cost, quadratic costs, qdd = M^-1 (u - b), integrator error
     for (int p = tid; p < npts; p += NT) {
-        const int ci = p / N, k = p - ci * N;
+        const int ci = p / nw, k = p - ci * nw;
+        const int kg = W.k0 + k;
         const T alpha = T(c_alphas[c0 + ci]);
         const T* sp = scr + MP_STRIDE * p;
         T x[18];
@@ -620,10 +682,10 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
 #pragma unroll
         for (int i = 0; i < 12; ++i) cs[i] = sp[MP_CS + i];
         fk_ee_only<T>(rob, cs, pee);
-        const T* goal = M.goals + 3 * k;
+        const T* goal = M.goals + 3 * kg;
         const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
-        const T Qk = (k == N - 1) ? P.QN : T(1);
-        T* out = comps + 4 * p;
+        const T Qk = (kg == N - 1) ? P.QN : T(1);
+        T* out = comps + 4 * (ci * N + kg);
         out[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
         T vv = T(0), uu = T(0);
 #pragma unroll
@@ -657,8 +719,9 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
     __syncthreads();
 }
 
-// merits[c] for c in [c0, c0 + nc): sum over knots + initial-state violation term
-template <typename T, int NT>
+// merits[c] for c in [c0, c0 + nc): sum over all N knots (fixed order) + initial-state violation term.
+// CG: comps live in the global exchange buffer written by other CTAs of the cluster (read with ld.global.cg).
+template <typename T, int NT, bool CG>
 __device__ void merit_reduce(const SolveParams<T>& P, const T* xa, const T* xb, int c0, int nc, const T* comps, T* merits,
                              T* comps_out /* 4 sums of candidate c0 or nullptr */) {
     const int tid = threadIdx.x, N = P.N;
@@ -668,7 +731,7 @@ __device__ void merit_reduce(const SolveParams<T>& P, const T* xa, const T* xb, 
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             T a = T(0);
-            for (int k = lane; k < N; k += 32) a += comps[4 * (ci * N + k) + j];
+            for (int k = lane; k < N; k += 32) a += CG ? __ldcg(comps + 4 * (ci * N + k) + j) : comps[4 * (ci * N + k) + j];
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
             s[j] = a;
@@ -778,6 +841,7 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
     __shared__ T s_merit_acc;
     __shared__ T s_fext[6];
     __shared__ int s_flag;
+    const Win W{0, N - 1, N};
 
     for (int b = blockIdx.x; b < P.batch; b += gridDim.x) {
         // ---- load inputs ----
@@ -799,8 +863,8 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
         if (P.mode == MODE_MERIT) {
             // merit terms of xu; the initial-state term is taken against the reference iterate z
             T* comps = M.ls;
-            merit_points<T, NT>(rob, P, M, M.xu, M.xu, fext, 0, 1, comps);
-            merit_reduce<T, NT>(P, M.xu, M.xu, 0, 1, comps, s_merits, M.work);
+            merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.xu, fext, 0, 1, comps);
+            merit_reduce<T, NT, false>(P, M.xu, M.xu, 0, 1, comps, s_merits, M.work);
             if (tid == 0) {
                 T d2 = T(0);
                 for (int i = 0; i < 12; ++i) { const T d = M.xu[i] - M.z[i]; d2 += d * d; }
@@ -820,10 +884,17 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
             qp_iters = qp + 1;
             if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 0] = clock64();
             if (P.mode != MODE_LINESEARCH) {
-                phase_setup<T, NT>(rob, P, M, fext, P.mode == MODE_DUMP, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
+                phase_setup<T, NT>(rob, P, M, W, fext, P.mode == MODE_DUMP, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 1] = clock64();
                 if (P.mode == MODE_DUMP) { dump_qp<T, BlockRecLayout>(P, M, b); break; }
-                phase_riccati<T, NT>(P, M, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
+                {
+                    long long* pr = (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr;
+                    long long tc = 0;
+                    riccati_sweep<T, NT, RicLocal<T>>(P, M, RicLocal<T>{M.kr, M.cost}, pr);
+                    if (pr && tid == 0) tc = clock64();
+                    phase_controls<T, NT>(P, M, W, nullptr);
+                    if (pr && tid == 0) pr[13] = clock64() - tc;
+                }
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 2] = clock64();
                 if (P.mode == MODE_QP) {
                     for (int t = tid; t < nz; t += NT) P.z_out[(size_t)b * nz + t] = M.z[t];
@@ -838,8 +909,8 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
                 if (tid == 0) { s_alpha = T(0); s_flag = 0; }
                 while (c0 < 9) {
                     int nc = 9 - c0 < M.merit_cap ? 9 - c0 : M.merit_cap;
-                    merit_points<T, NT>(rob, P, M, M.xu, M.z, fext, c0, nc, M.ls);
-                    merit_reduce<T, NT>(P, M.xu, M.z, c0, nc, M.ls, s_merits, nullptr);
+                    merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, nc, M.ls);
+                    merit_reduce<T, NT, false>(P, M.xu, M.z, c0, nc, M.ls, s_merits, nullptr);
                     if (tid == 0 && s_alpha == T(0)) {
                         if (!(s_merits[0] == s_merits[0])) s_flag = 1;
                         for (int c = (c0 == 0 ? 1 : c0); c < c0 + nc; ++c)

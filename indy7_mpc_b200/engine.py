@@ -23,7 +23,7 @@ def _is_torch(x):
 
 class Engine:
     def __init__(self, model=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
-                 batch=1, dtype="fp64", device=0, max_qp=2, mu=10.0, step_tol=1e-3, threads=0):
+                 batch=1, dtype="fp64", device=0, max_qp=2, mu=10.0, step_tol=1e-3, threads=0, cluster=0):
         self.lib = _lib.load()
         if model is None:
             model = build_model_from_urdf()
@@ -43,6 +43,7 @@ class Engine:
         cfg.N, cfg.batch, cfg.dtype, cfg.device = self.N, self.batch, (_lib.I7_F64 if dtype == "fp64" else _lib.I7_F32), self.device
         cfg.dt, cfg.dQ_cost, cfg.R_cost, cfg.QN_cost, cfg.eps = float(dt), float(dQ_cost), float(R_cost), float(QN_cost), float(eps)
         cfg.regularize, cfg.max_qp, cfg.mu, cfg.step_tol, cfg.threads = int(bool(regularize)), int(max_qp), float(mu), float(step_tol), int(threads)
+        cfg.cluster = int(cluster)      # 0 auto, 1 one CTA per problem, 8 cluster of 8 CTAs per problem (latency form)
         cfg.model = model.to_c()
         self._h = C.c_void_p()
         rc = self.lib.i7_create(C.byref(cfg), C.byref(self._h))

@@ -286,3 +286,55 @@ def test_best_selection_kernels(engine, oracle_model):
     red = engine.reduce_best(two, 2)
     assert red[0] == packed[16] - 1.0 and red[1] == 7.0
 
+
+
+# ---- the cluster-per-problem (latency) form of i7_solve: 8 CTAs per problem --------------------------------------
+def test_cluster_kernel_matches_oracle(pkg, oracle_model):
+    xu, x0, goals = make_cases(oracle_model, 6, seed=21)
+    f = np.zeros((6, 6)); f[1] = [5.0, 0, 15, 0, 0, 0]; f[4] = [-6, 2, -4, 0.5, 0, -0.3]
+    eng = pkg.Engine(N=32, batch=6, cluster=8)
+    eng.set_external_wrench(f)
+    out, st = eng.solve(xu, x0, goals)
+    for b in range(6):
+        ref, stats = _oracle_sqp(oracle_model, xu[b], x0[b], goals[b], f_ext=f[b])
+        assert int(st[b, 0]) == stats["qp_iters"]["values"][0]
+        n_ls = int(st[b, 1])
+        assert list(st[b, 4:4 + n_ls]) == stats["linesearch_alphas"]["values"], b
+        assert rel(out[b], ref) < 1e-6, (b, rel(out[b], ref))
+        n_st = int(st[b, 2])
+        assert rel(st[b, 6:6 + n_st], stats["sqp_stepsizes"]["values"]) < 1e-6 if n_st else True
+
+
+def test_cluster_kernel_equals_cta_kernel(pkg, oracle_model):
+    """Same device functions per knot / per stage: the two kernel forms agree to rounding, with identical
+    line-search decisions; repeated cluster solves are bit-identical (fixed reduction order)."""
+    xu, x0, goals = make_cases(oracle_model, 16, seed=22)
+    a = pkg.Engine(N=32, batch=16, cluster=8)
+    c = pkg.Engine(N=32, batch=16, cluster=1, threads=384)
+    oa, sa = a.solve(xu, x0, goals)
+    oc, sc = c.solve(xu, x0, goals)
+    assert np.array_equal(sa[:, :6], sc[:, :6])                  # iteration counts, status, alphas
+    assert rel(oa, oc) < 1e-11
+    oa2, sa2 = a.solve(xu, x0, goals)
+    assert np.array_equal(oa, oa2) and np.array_equal(sa, sa2)
+    # the auto choice at batch 1 is the cluster form and returns the same trajectory
+    one = pkg.Engine(N=32, batch=1)
+    o1, _ = one.solve(xu[3], x0[3], goals[3])
+    assert np.array_equal(o1[0], oa[3])
+
+
+@pytest.mark.parametrize("N,dtype,tol", [(8, "fp64", 1e-6), (5, "fp64", 1e-6), (64, "fp64", 1e-6), (128, "fp64", 1e-6),
+                                         (32, "fp32", 1e-4)])
+def test_cluster_kernel_horizons_and_fp32(pkg, oracle_model, N, dtype, tol):
+    xu, x0, goals = make_cases(oracle_model, 2, N=N, seed=23)
+    eng = pkg.Engine(N=N, batch=2, dtype=dtype, cluster=8)
+    out, st = eng.solve(xu, x0, goals)
+    cta = pkg.Engine(N=N, batch=2, dtype="fp64", cluster=1)
+    ref, sr = cta.solve(xu, x0, goals)
+    if dtype == "fp64":
+        assert np.array_equal(np.asarray(st)[:, :6], np.asarray(sr)[:, :6])
+        assert rel(out, ref) < 1e-10
+    if N <= 32:
+        for b in range(2):
+            want, _ = _oracle_sqp(oracle_model, xu[b], x0[b], goals[b], N=N)
+            assert rel(out[b], want) < tol, (b, rel(out[b], want))
