@@ -20,14 +20,15 @@ __global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, con
         for (int a = 0; a < 3; ++a) { fx[a] = fext_pin[6 * i + 3 + a]; fx[3 + a] = fext_pin[6 * i + a]; }
     }
     const T* fext = fext_pin ? fx : nullptr;
-    // the same building blocks as the fused kernel: CRBA columns, bias, LDL' solves, dID columns
+    // the same building blocks as the fused kernel (world-frame link records, mass columns, LDL', dID columns)
+    T S[36], V[36], Aa[36], F[36], IW[54];
+    for (int l = 0; l < 6; ++l) wf_link<T>(rob, cs, qd, fext, l, S + 6 * l, V + 6 * l, Aa + 6 * l, IW + 9 * l, F + 6 * l);
     T A[6][6], dinv[6], bias[6], qdd[6], Mi[36];
-    for (int c = 0; c < 6; ++c) {
-        T out[6];
-        crba_column<T>(rob, cs, c, out);
-        for (int r = 0; r < 6; ++r) A[r][c] = out[r];
+    for (int j = 0; j < 6; ++j) {
+        T col[6];
+        wf_mass_column<T>(rob, S, IW, F, j, col, &bias[j]);
+        for (int r = 0; r <= j; ++r) { A[r][j] = col[r]; A[j][r] = col[r]; }
     }
-    rnea_bias<T>(rob, cs, qd, fext, bias);
     spd6_factor<T>(A, dinv);
     for (int r = 0; r < 6; ++r) qdd[r] = u[r] - bias[r];
     spd6_solve_factored<T>(A, dinv, qdd);
@@ -39,10 +40,11 @@ __global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, con
     }
     if (qdd_out) for (int a = 0; a < 6; ++a) qdd_out[6 * i + a] = qdd[a];
     if (minv_out) for (int a = 0; a < 36; ++a) minv_out[36 * i + a] = Mi[a];
+    for (int l = 0; l < 6; ++l) wf_add_qdd<T>(rob, S, qdd, l, IW + 9 * l, Aa + 6 * l, F + 6 * l);
     for (int j = 0; j < 6; ++j) {
         T cq[6], cv[6];
-        rnea_dcolumn<T, true>(rob, cs, qd, qdd, fext, j, cq);
-        rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, j, cv);
+        wf_dcolumn<T, true>(rob, S, V, Aa, F, IW, j, cq);
+        wf_dcolumn<T, false>(rob, S, V, Aa, F, IW, j, cv);
         for (int r = 0; r < 6; ++r) {
             T aq = T(0), av = T(0);
             for (int s = 0; s < 6; ++s) { aq -= Mi[6 * r + s] * cq[s]; av -= Mi[6 * r + s] * cv[s]; }

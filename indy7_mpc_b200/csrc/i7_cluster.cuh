@@ -23,7 +23,7 @@ namespace i7 {
 constexpr int CL = 8;          // CTAs per cluster = per problem (portable maximum)
 constexpr int CL_NT = 384;     // threads per CTA
 
-struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, gains, total, chunk; };
+struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, aux, gains, total, chunk; };
 __host__ __device__ inline CLayout make_clayout(int N) {
     CLayout L;
     L.chunk = (N + CL - 1) / CL;
@@ -37,6 +37,7 @@ __host__ __device__ inline CLayout make_clayout(int N) {
     L.work = o; o += WK_SIZE;
     L.ls = o; o += CL_NT + 16;
     L.kr = o; o += recw * L.chunk + ((recw * L.chunk) & 1);
+    L.aux = o; o += AUX_STRIDE * L.chunk;
     L.gains = o; o += GAIN_STRIDE * N;
     L.total = o;
     return L;
@@ -63,7 +64,7 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
     const CLayout L = make_clayout(N);
     Ptrs<T> M;
     M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
-    M.work = sm + L.work; M.ls = sm + L.ls; M.kr = sm + L.kr; M.merit_cap = 9;
+    M.work = sm + L.work; M.ls = sm + L.ls; M.kr = sm + L.kr; M.aux = sm + L.aux; M.merit_cap = 9;
     T* gains = sm + L.gains;
     T* xbuf = xbuf_all + (size_t)b * xbuf_size(N);
     T* ric = xbuf + xbuf_ric(N);

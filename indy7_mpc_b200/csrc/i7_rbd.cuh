@@ -571,4 +571,254 @@ I7_DEV void rnea_dcolumn(const Robot<T>& rob, const T* cs, const T* qd, const T*
     }
 }
 
+// =========================================================================================================
+// World-frame formulation (spatial vectors [angular; linear] expressed in world axes at ONE fixed spatial origin).
+// In these coordinates the recursions over the links lose their transforms:  v_l = sum_{k<=l} S_k qd_k,
+// a_l = a_base + sum_{k<=l} (S_k qdd_k + v_k x S_k qd_k),  F_i = sum_{l>=i} f_l,  tau_i = S_i . F_i,
+// M_ij = S_i . (sum_{l>=max(i,j)} I_l) S_j,  and the partial derivatives of inverse dynamics have closed forms per
+// (joint j, link l >= j) pair — so every quantity is a short prefix / suffix sum of independent terms instead of a
+// 6-deep chain of 6x6 transforms.  Replaces pin.computeABADerivatives (src/osqp_solver.py:71); the recursion is the
+// world-frame one of Carpentier & Mansard 2018, re-derived so that each (knot, link) and (knot, column) is an
+// independent task.  World inertia of a link: IO (xx xy xz yy yz zz about the world origin) and the first moment H;
+// the mass is the model constant.
+// =========================================================================================================
+
+// o = v x m (spatial motion cross product)
+template <typename T> I7_DEV void crm6(const T* v, const T* m, T* o) {
+    cross3(v, m, o);
+    cross3(v, m + 3, o + 3);
+    cross3_acc(v + 3, m, o + 3);
+}
+// o = I x for a world inertia (IO, H, ms):  [IO w + H x v ; ms v - H x w]
+template <typename T> I7_DEV void winertia_mul(const T* IW, T ms, const T* x, T* o) {
+    const T* H = IW + 6;
+    o[0] = IW[0] * x[0] + IW[1] * x[1] + IW[2] * x[2] + (H[1] * x[5] - H[2] * x[4]);
+    o[1] = IW[1] * x[0] + IW[3] * x[1] + IW[4] * x[2] + (H[2] * x[3] - H[0] * x[5]);
+    o[2] = IW[2] * x[0] + IW[4] * x[1] + IW[5] * x[2] + (H[0] * x[4] - H[1] * x[3]);
+    o[3] = ms * x[3] - (H[1] * x[2] - H[2] * x[1]);
+    o[4] = ms * x[4] - (H[2] * x[0] - H[0] * x[2]);
+    o[5] = ms * x[5] - (H[0] * x[1] - H[1] * x[0]);
+}
+
+// Task (knot, link l): forward kinematics of the whole chain (joint axes z_i and origins p_i), then — with the
+// spatial origin placed at the last joint's position p_ref (a fixed point of space for the purpose of every
+// derivative; it keeps the parallel-axis terms of the light wrist links small, which is what fp32 needs) — the
+// velocity and the acceleration at qdd = 0 of link l (gravity as base acceleration), the link's axis S_l, inertia
+// IW_l (9 numbers) and force f0_l = I_l a0_l + v_l x* I_l v_l (minus the external wrench on the last link, given in
+// link coordinates).
+template <typename T>
+I7_DEV void wf_link(const Robot<T>& rob, const T* cs, const T* qd, const T* fext, int l, T* S_o, T* v_o, T* a_o,
+                    T* IW_o, T* f_o) {
+    T Rc[9] = {T(1), T(0), T(0), T(0), T(1), T(0), T(0), T(0), T(1)};
+    T Rw[9], zs[I7_NJ][3], ps[I7_NJ][3];
+    T pc[3] = {T(0), T(0), T(0)};
+#pragma unroll
+    for (int i = 0; i < I7_NJ; ++i) {
+        T d[3];
+        rot(Rc, rob.p[i], d);
+        pc[0] += d[0]; pc[1] += d[1]; pc[2] += d[2];
+        T E[9], Rn[9];
+        joint_E(rob, i, cs[i], cs[6 + i], E);
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                Rn[3 * r + c] = Rc[3 * r] * E[3 * c] + Rc[3 * r + 1] * E[3 * c + 1] + Rc[3 * r + 2] * E[3 * c + 2];
+#pragma unroll
+        for (int r = 0; r < 9; ++r) Rc[r] = Rn[r];
+        zs[i][0] = Rc[2]; zs[i][1] = Rc[5]; zs[i][2] = Rc[8];
+        ps[i][0] = pc[0]; ps[i][1] = pc[1]; ps[i][2] = pc[2];
+        if (i == l) {
+#pragma unroll
+            for (int r = 0; r < 9; ++r) Rw[r] = Rc[r];
+        }
+    }
+    T p[3] = {T(0), T(0), T(0)};
+    T v[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    T a[6] = {T(0), T(0), T(0), -rob.g[0], -rob.g[1], -rob.g[2]};
+    T S[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+    for (int i = 0; i < I7_NJ; ++i) {
+        if (i <= l) {
+            p[0] = ps[i][0] - pc[0]; p[1] = ps[i][1] - pc[1]; p[2] = ps[i][2] - pc[2];
+            S[0] = zs[i][0]; S[1] = zs[i][1]; S[2] = zs[i][2];
+            cross3(p, S, S + 3);
+            T vj[6], c6[6];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) { vj[r] = S[r] * qd[i]; v[r] += vj[r]; }
+            crm6(v, vj, c6);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) a[r] += c6[r];
+        }
+    }
+    // inertia about the spatial origin from (Ib about the link origin, h = m c, m) of link l; p = link origin
+    const T* Ib = rob.Ib[l]; const T* h = rob.h[l]; const T ms = rob.m[l];
+    T IW[9];
+    {
+        // B = Rw Ib (Ib symmetric), IO = B Rw^T
+        const T I3[9] = {Ib[0], Ib[1], Ib[2], Ib[1], Ib[3], Ib[4], Ib[2], Ib[4], Ib[5]};
+        T B[9];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                B[3 * r + c] = Rw[3 * r] * I3[c] + Rw[3 * r + 1] * I3[3 + c] + Rw[3 * r + 2] * I3[6 + c];
+        T hw[3];
+        rot(Rw, h, hw);
+        const T pp = p[0] * p[0] + p[1] * p[1] + p[2] * p[2];
+        const T ph = p[0] * hw[0] + p[1] * hw[1] + p[2] * hw[2];
+        const T dg = ms * pp + T(2) * ph;
+        const int rr[6] = {0, 0, 0, 1, 1, 2}, cc[6] = {0, 1, 2, 1, 2, 2};
+#pragma unroll
+        for (int e = 0; e < 6; ++e) {
+            const int r = rr[e], c = cc[e];
+            T x = B[3 * r] * Rw[3 * c] + B[3 * r + 1] * Rw[3 * c + 1] + B[3 * r + 2] * Rw[3 * c + 2];
+            x -= ms * p[r] * p[c] + p[r] * hw[c] + hw[r] * p[c];
+            if (r == c) x += dg;
+            IW[e] = x;
+        }
+#pragma unroll
+        for (int r = 0; r < 3; ++r) IW[6 + r] = hw[r] + ms * p[r];
+    }
+    T Ia[6], Iv[6];
+    winertia_mul(IW, ms, a, Ia);
+    winertia_mul(IW, ms, v, Iv);
+    crf<T, true>(v, Iv, Ia);
+    if (l == I7_NJ - 1 && fext) {
+        T nw[3], fw[3];
+        rot(Rw, fext, nw);              // the spatial origin IS the last joint's origin: no moment arm
+        rot(Rw, fext + 3, fw);
+#pragma unroll
+        for (int r = 0; r < 3; ++r) { Ia[r] -= nw[r]; Ia[3 + r] -= fw[r]; }
+    }
+#pragma unroll
+    for (int r = 0; r < 6; ++r) { S_o[r] = S[r]; v_o[r] = v[r]; a_o[r] = a[r]; f_o[r] = Ia[r]; }
+#pragma unroll
+    for (int r = 0; r < 9; ++r) IW_o[r] = IW[r];
+}
+
+// Task (knot, j): column j of the joint-space inertia matrix for rows i <= j and the bias torque b_j, from the
+// per-link records:  M_ij = S_i . (sum_{l>=j} I_l) S_j,  b_j = S_j . sum_{l>=j} f0_l.   Mcol[i] for i <= j.
+template <typename T>
+I7_DEV void wf_mass_column(const Robot<T>& rob, const T* S /*36*/, const T* IW /*54*/, const T* f0 /*36*/, int j,
+                           T* Mcol, T* bj) {
+    T IC[9] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
+    T F[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    T mc = T(0);
+#pragma unroll
+    for (int l = I7_NJ - 1; l >= 0; --l) {
+        if (l >= j) {
+#pragma unroll
+            for (int r = 0; r < 9; ++r) IC[r] += IW[9 * l + r];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) F[r] += f0[6 * l + r];
+            mc += rob.m[l];
+        }
+    }
+    T Sj[6], y[6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r) Sj[r] = S[6 * j + r];
+    winertia_mul(IC, mc, Sj, y);
+    T b = T(0);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) b += Sj[r] * F[r];
+    *bj = b;
+#pragma unroll
+    for (int i = 0; i < I7_NJ; ++i) {
+        T d = T(0);
+        if (i <= j) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) d += S[6 * i + r] * y[r];
+        }
+        Mcol[i] = d;
+    }
+}
+
+// Task (knot, l): fold the solved accelerations into the link record:  a_l += sum_{k<=l} S_k qdd_k,
+// f_l += I_l (that sum).
+template <typename T>
+I7_DEV void wf_add_qdd(const Robot<T>& rob, const T* S /*36*/, const T* qdd, int l, const T* IW_l, T* a_l, T* f_l) {
+    T s[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+    for (int k = 0; k < I7_NJ; ++k) {
+        if (k <= l) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) s[r] += S[6 * k + r] * qdd[k];
+        }
+    }
+    T Is[6];
+    winertia_mul(IW_l, rob.m[l], s, Is);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) { a_l[r] += s[r]; f_l[r] += Is[r]; }
+}
+
+// Task (knot, j, kind): column j of d tau/dq (WRT_Q) or d tau/dqd at (q, qd, qdd), from the per-link records
+// S, v, a, f (at the solved qdd), IW.  For every link l >= j
+//     rest_l = I_l da_l + dv x* (I_l v_l) + v_l x* (I_l dv),      da_l = a0 + B x (v_l - v_j)
+//   d/dq_j :  dv = -S_j x v_j,  a0 = -S_j x a_j,  B = v_j x S_j    (the rigid rotation S_j x* f_l of the whole
+//             sub-chain cancels against d S_i/dq_j for i > j and is added once, as S_j x* F_j, for i <= j)
+//   d/dqd_j:  dv = S_j,         a0 = v_j x S_j,   B = S_j
+//   out_i = S_i . sum_{l >= max(i,j)} rest_l  (+ S_i . (S_j x* F_j) for i <= j, WRT_Q)
+template <typename T, bool WRT_Q>
+I7_DEV void wf_dcolumn(const Robot<T>& rob, const T* S, const T* V, const T* A, const T* F_, const T* IW, int j, T* out) {
+    T Sj[6], vj[6], vjS[6], dv[6], a0[6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r) { Sj[r] = S[6 * j + r]; vj[r] = V[6 * j + r]; }
+    crm6(vj, Sj, vjS);
+    if (WRT_Q) {
+        T aj[6];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) aj[r] = A[6 * j + r];
+        crm6(Sj, vj, dv);
+        crm6(Sj, aj, a0);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) { dv[r] = -dv[r]; a0[r] = -a0[r]; }
+    } else {
+#pragma unroll
+        for (int r = 0; r < 6; ++r) { dv[r] = Sj[r]; a0[r] = vjS[r]; }
+    }
+    T rest[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    T Fs[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+    for (int l = I7_NJ - 1; l >= 0; --l) {
+        if (l >= j) {
+            const T ms = rob.m[l];
+            const T* IWl = IW + 9 * l;
+            T vl[6], W[6], da[6], t[6];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) { vl[r] = V[6 * l + r]; W[r] = vl[r] - vj[r]; }
+            crm6(WRT_Q ? vjS : Sj, W, da);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) da[r] += a0[r];
+            winertia_mul(IWl, ms, da, t);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) rest[r] += t[r];
+            winertia_mul(IWl, ms, vl, t);
+            crf<T, true>(dv, t, rest);
+            winertia_mul(IWl, ms, dv, t);
+            crf<T, true>(vl, t, rest);
+            if (WRT_Q) {
+#pragma unroll
+                for (int r = 0; r < 6; ++r) Fs[r] += F_[6 * l + r];
+            }
+            if (l > j) {
+                T d = T(0);
+#pragma unroll
+                for (int r = 0; r < 6; ++r) d += S[6 * l + r] * rest[r];
+                out[l] = d;
+            }
+        }
+    }
+    if (WRT_Q) crf<T, true>(Sj, Fs, rest);
+#pragma unroll
+    for (int i = 0; i < I7_NJ; ++i) {
+        if (i <= j) {
+            T d = T(0);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) d += S[6 * i + r] * rest[r];
+            out[i] = d;
+        }
+    }
+}
+
 }  // namespace i7

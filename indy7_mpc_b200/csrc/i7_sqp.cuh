@@ -52,10 +52,6 @@ constexpr int KR_CV = 72;     // 6   affine term of the velocity rows  (c_k = [0
 constexpr int KR_Y = 78;      // 36  M during setup, then Y = H^-1 = M / dt
 constexpr int KR_S = 114;     // 36  S = R_k Y'Y   (MODE_DUMP: H = dt M^-1)
 constexpr int KR_L = 150;     // 78  upper triangle of L = G'SG; setup scratch before that:
-constexpr int KR_CS = 150;    //     12 cos/sin of q_k
-constexpr int KR_MINV = 162;  //     36 M^-1
-constexpr int KR_QDD = 198;   //     6  forward dynamics
-constexpr int KR_BIAS = 204;  //     6  ID(q, qd, 0)
 constexpr int KR_SG = 228;    // 72  S G ; after the stage is eliminated: feedback gain Kw (6x12)
 constexpr int KR_D = 300;     // 6   d = S cv - R Y u ; after elimination: feed-forward kw
 constexpr int KR_HX = 306;    // 12  gx + G'd
@@ -78,11 +74,11 @@ __host__ __device__ inline Layout make_layout(int N, bool spill) {
     Layout L;
     int o = 0;
     L.xu = o; o += 18 * N;
-    L.z = o; o += 18 * N;
     L.goals = o; o += 3 * N;
     L.x0 = o; o += 12;
     L.cost = o; o += COST_STRIDE * N;
     L.work = o; o += WK_SIZE;
+    L.z = o; o += 18 * N;            // z and ls are adjacent: during setup (both dead) they hold the aux side array
     L.ls = o; o += (4 * 5 * N > 400 ? 4 * 5 * N : 400) + 16;
     L.reg = o;
     L.reg_size = KR_STRIDE * N;
@@ -93,9 +89,16 @@ __host__ __device__ inline Layout make_layout(int N, bool spill) {
 
 template <typename T>
 struct Ptrs {
-    T *xu, *z, *goals, *x0, *cost, *work, *ls, *kr;
+    T *xu, *z, *goals, *x0, *cost, *work, *ls, *kr, *aux;
     int merit_cap;      // candidates per merit wave that fit the scratch region
 };
+
+// Re-derive a pointer that is known to address shared memory (after a non-inlined call the compiler only sees a
+// generic pointer): the round trip through the shared window lets it emit LDS / STS instead of generic accesses.
+template <typename T> I7_DEV T* as_shared(T* p) {
+    return reinterpret_cast<T*>(__cvta_shared_to_generic(__cvta_generic_to_shared(p)));
+}
+template <typename T> I7_DEV const T* as_shared(const T* p) { return as_shared(const_cast<T*>(p)); }
 
 // the knots a CTA works on in the per-knot phases: [k0, k0 + nc) for cost terms, [k0, k0 + nd) for dynamics;
 // the whole horizon (0, N-1, N) when one CTA owns the problem.  Records / cost terms are indexed window-relative.
@@ -111,7 +114,19 @@ static __device__ __constant__ unsigned char c_tri_c[78] = {
     5,6,7,8,9,10,11, 6,7,8,9,10,11, 7,8,9,10,11, 8,9,10,11, 9,10,11, 10,11, 11};
 
 // -----------------------------------------------------------------------------------------------------------
-// setup: linearised dynamics, cost terms and all stage-local QP products at the current iterate
+// setup: linearised dynamics, cost terms and all stage-local QP products at the current iterate.
+// The dynamics part works in world-frame coordinates (i7_rbd.cuh, wf_*): every wave below is a set of independent
+// (knot, link) / (knot, column) tasks with a dependency depth of a few dozen FMAs.
+// Scratch of a knot while its record is being built (dead before S / SG / d / L / hx are written):
+constexpr int WS_CS = KR_GQ;    // 12  cos / sin of q                 (raw dID columns land in GQ / GV afterwards)
+constexpr int WS_S = 114;       // 36  world joint axes S_l
+constexpr int WS_V = 150;       // 36  link velocities v_l
+constexpr int WS_A = 186;       // 36  link accelerations a_l
+constexpr int WS_F = 222;       // 36  link forces f_l
+constexpr int WS_I = 258;       // 54  world inertias (IO[6], H[3]) per link          -> 312 <= KR_STRIDE
+constexpr int AX_L = 0, AX_DINV = 15, AX_MU = 21, AUX_STRIDE = 28;   // LDL' of M, M^-1 u  (side array, per knot)
+static_assert(WS_I + 54 <= KR_STRIDE, "setup scratch overflows the knot record");
+
 template <typename T, int NT>
 __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const Win W, const T* fext,
                             bool for_dump, long long* prof) {
@@ -123,36 +138,34 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     const T* xu = M.xu + 18 * W.k0;               // window-relative: knot index k below is local, records are local
     const T* goals = M.goals + 3 * W.k0;
     const T dt = P.dt;
-    // S0: cos / sin of every joint angle
+    const int np = (nk + 31) & ~31;               // knots padded to whole warps: the lanes of a warp share (link | column)
+    // W0: cos / sin of every joint angle
     for (int t = tid; t < 6 * nc; t += NT) {
         const int i = t / nc, k = t - i * nc;
         T s, c;
         sincos_t<T>(xu[18 * k + i], &s, &c);
         T* kr = M.kr + KR_STRIDE * k;
-        kr[KR_CS + i] = c; kr[KR_CS + 6 + i] = s;
+        kr[WS_CS + i] = c; kr[WS_CS + 6 + i] = s;
     }
     __syncthreads();
     I7_STAMP();
-    // S1: 6 mass-matrix columns + bias torques per knot (k < N-1), FK / cost terms per knot (k < N)
-    for (int t = tid; t < 7 * nk + nc; t += NT) {
-        const int type = t < 7 * nk ? t / nk : 7;
-        const int k = t < 7 * nk ? t - type * nk : t - 7 * nk;
+    // W1: per (knot, link): world axis, velocity, acceleration at qdd = 0, world inertia, force;  per cost knot: FK,
+    //     j = J'e and the scaled weights
+    for (int t = tid; t < 6 * np + nc; t += NT) {
+        const bool dyn = t < 6 * np;
+        const int l = dyn ? t / np : 0;
+        const int k = dyn ? t - l * np : t - 6 * np;
+        if (dyn && k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
         T cs[12];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) cs[i] = kr[KR_CS + i];
-        if (type < 6) {
-            T out[6];
-            crba_column<T>(rob, cs, type, out);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) kr[KR_Y + 6 * r + type] = out[r];
-        } else if (type == 6) {
-            T qd[6], out[6];
+        for (int i = 0; i < 12; ++i) cs[i] = kr[WS_CS + i];
+        if (dyn) {
+            T qd[6];
 #pragma unroll
             for (int i = 0; i < 6; ++i) qd[i] = xu[18 * k + 6 + i];
-            rnea_bias<T>(rob, cs, qd, fext, out);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) kr[KR_BIAS + r] = out[r];
+            wf_link<T>(rob, cs, qd, fext, l, kr + WS_S + 6 * l, kr + WS_V + 6 * l, kr + WS_A + 6 * l, kr + WS_I + 9 * l,
+                       kr + WS_F + 6 * l);
         } else {
             T pee[3], zs[18], ps[18];
             fk_ee<T>(rob, cs, pee, zs, ps);
@@ -175,96 +188,129 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     }
     __syncthreads();
     I7_STAMP();
-    // S2: M^-1 columns and qdd = M^-1 (tau - bias): every task factors M in registers (LDL') and solves one rhs
-    for (int t = tid; t < 7 * nk; t += NT) {
-        const int c = t / nk, k = t - c * nk;
+    // W2: per (knot, j): column j of M (rows <= j, mirrored) and the bias torque b_j (parked in the cv slot)
+    for (int t = tid; t < 6 * np; t += NT) {
+        const int j = t / np, k = t - j * np;
+        if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
-        T A[6][6], dinv[6], b[6];
+        T col[6], bj;
+        wf_mass_column<T>(rob, kr + WS_S, kr + WS_I, kr + WS_F, j, col, &bj);
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (i <= j) { kr[KR_Y + 6 * i + j] = col[i]; kr[KR_Y + 6 * j + i] = col[i]; }
+        kr[KR_CV + j] = bj;
+    }
+    __syncthreads();
+    I7_STAMP();
+    // W3: per knot: LDL' of M (kept), qdd = M^-1 (u - b) (into the cv slot), M^-1 u
+    for (int k = tid; k < nk; k += NT) {
+        T* kr = M.kr + KR_STRIDE * k;
+        T* ax = M.aux + AUX_STRIDE * k;
+        T A[6][6], dinv[6], b[6], u[6];
 #pragma unroll
         for (int r = 0; r < 6; ++r)
 #pragma unroll
             for (int q = 0; q <= r; ++q) A[r][q] = kr[KR_Y + 6 * r + q];
-        if (c < 6) {
 #pragma unroll
-            for (int r = 0; r < 6; ++r) b[r] = (r == c) ? T(1) : T(0);
-        } else {
-#pragma unroll
-            for (int r = 0; r < 6; ++r) b[r] = xu[18 * k + 12 + r] - kr[KR_BIAS + r];
-        }
+        for (int r = 0; r < 6; ++r) { u[r] = xu[18 * k + 12 + r]; b[r] = u[r] - kr[KR_CV + r]; }
         spd6_factor<T>(A, dinv);
         spd6_solve_factored<T>(A, dinv, b);
-        if (c < 6) {
+        spd6_solve_factored<T>(A, dinv, u);
+        int o = 0;
 #pragma unroll
-            for (int r = 0; r < 6; ++r) kr[KR_MINV + 6 * r + c] = b[r];
-        } else {
+        for (int r = 1; r < 6; ++r)
 #pragma unroll
-            for (int r = 0; r < 6; ++r) kr[KR_QDD + r] = b[r];
-        }
+            for (int q = 0; q < r; ++q) ax[AX_L + o++] = A[r][q];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) { ax[AX_DINV + r] = dinv[r]; ax[AX_MU + r] = u[r]; kr[KR_CV + r] = b[r]; }
     }
     __syncthreads();
     I7_STAMP();
-    // S3: 12 analytic inverse-dynamics derivative columns per knot (raw d tau/dq, d tau/dqd into the G slots)
-    for (int t = tid; t < 12 * nk; t += NT) {
-        const int col = t / nk, k = t - col * nk;
+    // W4: per (knot, link): fold qdd into the link accelerations / forces
+    for (int t = tid; t < 6 * np; t += NT) {
+        const int l = t / np, k = t - l * np;
+        if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
-        T cs[12], qd[6], qdd[6], out[6];
+        T qdd[6];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) cs[i] = kr[KR_CS + i];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) { qd[i] = xu[18 * k + 6 + i]; qdd[i] = kr[KR_QDD + i]; }
+        for (int i = 0; i < 6; ++i) qdd[i] = kr[KR_CV + i];
+        wf_add_qdd<T>(rob, kr + WS_S, qdd, l, kr + WS_I + 9 * l, kr + WS_A + 6 * l, kr + WS_F + 6 * l);
+    }
+    __syncthreads();
+    I7_STAMP();
+    // W5: per (knot, column): 12 analytic inverse-dynamics derivative columns (raw d tau/dq, d tau/dqd into G slots)
+    for (int t = tid; t < 12 * np; t += NT) {
+        const int col = t / np, k = t - col * np;
+        if (k >= nk) continue;
+        T* kr = M.kr + KR_STRIDE * k;
+        T out[6];
         if (col < 6) {
-            rnea_dcolumn<T, true>(rob, cs, qd, qdd, fext, col, out);
+            wf_dcolumn<T, true>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_F, kr + WS_I, col, out);
 #pragma unroll
             for (int r = 0; r < 6; ++r) kr[KR_GQ + 6 * r + col] = out[r];
         } else {
-            rnea_dcolumn<T, false>(rob, cs, qd, qdd, nullptr, col - 6, out);
+            wf_dcolumn<T, false>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_F, kr + WS_I, col - 6, out);
 #pragma unroll
             for (int r = 0; r < 6; ++r) kr[KR_GV + 6 * r + (col - 6)] = out[r];
         }
     }
     __syncthreads();
     I7_STAMP();
-    // S4: G = -dt Minv dID (+ I on the velocity block), in place, one column per task
+    // W6: G = -dt M^-1 dID (+ I on the velocity block), in place, one column per task, with the stored LDL'
     for (int t = tid; t < 12 * nk; t += NT) {
         const int col = t / nk, k = t - col * nk;
         T* kr = M.kr + KR_STRIDE * k;
+        const T* ax = M.aux + AUX_STRIDE * k;
         T* G = kr + (col < 6 ? KR_GQ : KR_GV);
         const int c = col < 6 ? col : col - 6;
-        T raw[6], y[6];
+        T A[6][6], dinv[6], y[6];
+        int o = 0;
 #pragma unroll
-        for (int s = 0; s < 6; ++s) raw[s] = G[6 * s + c];
+        for (int r = 1; r < 6; ++r)
 #pragma unroll
-        for (int r = 0; r < 6; ++r) {
-            T acc = T(0);
+            for (int q = 0; q < r; ++q) A[r][q] = ax[AX_L + o++];
 #pragma unroll
-            for (int s = 0; s < 6; ++s) acc -= kr[KR_MINV + 6 * r + s] * raw[s];
-            y[r] = dt * acc;
-        }
+        for (int r = 0; r < 6; ++r) { dinv[r] = ax[AX_DINV + r]; y[r] = G[6 * r + c]; }
+        spd6_solve_factored<T>(A, dinv, y);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) y[r] = -dt * y[r];
         if (col >= 6) y[c] += T(1);
 #pragma unroll
         for (int r = 0; r < 6; ++r) G[6 * r + c] = y[r];
     }
     __syncthreads();
     I7_STAMP();
-    // S5: cv = v + dt qdd - Gq q - Gv v - dt Minv u ;  S = R Y'Y with Y = M / dt  (dump mode: H = dt Minv instead)
+    // W7: cv = v + dt qdd - Gq q - Gv v - dt M^-1 u ;  S = R Y'Y with Y = M / dt  (dump mode: H = dt M^-1 instead)
     for (int t = tid; t < 42 * nk; t += NT) {
         const int e = t / nk, k = t - e * nk;
         T* kr = M.kr + KR_STRIDE * k;
+        const T* ax = M.aux + AUX_STRIDE * k;
         const T* xk = xu + 18 * k;
         if (e < 6) {
             const int r = e;
-            T a0 = xk[6 + r] + dt * kr[KR_QDD + r], a1 = T(0), a2 = T(0);
+            T a0 = xk[6 + r] + dt * (kr[KR_CV + r] - ax[AX_MU + r]), a1 = T(0);
 #pragma unroll
             for (int s = 0; s < 6; ++s) {
                 a0 -= kr[KR_GQ + 6 * r + s] * xk[s];
                 a1 -= kr[KR_GV + 6 * r + s] * xk[6 + s];
-                a2 -= kr[KR_MINV + 6 * r + s] * xk[12 + s];
             }
-            kr[KR_CV + r] = a0 + a1 + dt * a2;
+            kr[KR_CV + r] = a0 + a1;
         } else {
             const int e2 = e - 6, r = e2 / 6, c = e2 - 6 * r;
             if (for_dump) {
-                kr[KR_S + e2] = dt * kr[KR_MINV + e2];
+                if (r == 0) {           // column c of H = dt M^-1 with the stored factor
+                    T A[6][6], dinv[6], y[6];
+                    int o = 0;
+#pragma unroll
+                    for (int i = 1; i < 6; ++i)
+#pragma unroll
+                        for (int q = 0; q < i; ++q) A[i][q] = ax[AX_L + o++];
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) { dinv[i] = ax[AX_DINV + i]; y[i] = (i == c) ? T(1) : T(0); }
+                    spd6_solve_factored<T>(A, dinv, y);
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) kr[KR_S + 6 * i + c] = dt * y[i];
+                }
             } else {
                 T acc = T(0);
 #pragma unroll
@@ -276,7 +322,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     __syncthreads();
     I7_STAMP();
     if (for_dump) return;
-    // S6: SG = S G (6x12),  d = S cv - (R/dt) M u
+    // W8: SG = S G (6x12),  d = S cv - (R/dt) M u
     for (int t = tid; t < 78 * nk; t += NT) {
         const int e = t / nk, k = t - e * nk;
         T* kr = M.kr + KR_STRIDE * k;
@@ -301,7 +347,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     }
     __syncthreads();
     I7_STAMP();
-    // S7: L = G'(SG) (upper triangle, overwrites the setup scratch), hx = gx + G'd, Y = M / dt in place
+    // W9: L = G'(SG) (upper triangle, overwrites the setup scratch), hx = gx + G'd, Y = M / dt in place
     for (int t = tid; t < 126 * nk; t += NT) {
         const int e = t / nk, k = t - e * nk;
         T* kr = M.kr + KR_STRIDE * k;
@@ -355,8 +401,8 @@ template <typename T> struct RicGlobal {
     static constexpr int oL = RIC_L, oSG = RIC_SG, oS = RIC_S, oD = RIC_D, oHX = RIC_HX;
     I7_DEV const T* rec(int k) const { return ric + RIC_STRIDE * k; }
     I7_DEV const T* ck(int k) const { return ric + RIC_STRIDE * k + RIC_COST; }
-    I7_DEV T* gK(int k) const { return gains + GAIN_STRIDE * k; }
-    I7_DEV T* gk(int k) const { return gains + GAIN_STRIDE * k + 72; }
+    I7_DEV T* gK(int k) const { return as_shared(gains) + GAIN_STRIDE * k; }
+    I7_DEV T* gk(int k) const { return as_shared(gains) + GAIN_STRIDE * k + 72; }
     static I7_DEV T ld(const T* p) { return __ldcg(p); }
 };
 
@@ -378,8 +424,10 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, const Ptrs<T
     long long acc_r2 = 0, acc_r3 = 0, tt = 0;
     const int N = P.N;
     const T dt = P.dt;
-    T* wk = M.work;
-    const T* xu = M.xu;
+    T* wk = as_shared(M.work);
+    const T* xu = as_shared(M.xu);
+    const T* x0s = as_shared(M.x0);
+    T* zs = as_shared(M.z);
     // ---- role decode (once) ----
     const int e = tid - 32;
     const bool is_P = (e >= 0 && e < 78), is_p = (e >= 78 && e < 90);
@@ -531,12 +579,12 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, const Ptrs<T
     // exchanged with shuffles, so the serial chain per stage is 3 FMAs + 2 adds + one shuffle (no shared-memory
     // round trip); the gain row of the next stage is fetched while the current one is applied.
     if (tid < 32) {
-        T* z = M.z;
+        T* z = zs;
         const int row = tid % 6;
-        T x[12], g[12], ff, my_q = M.x0[row], my_v = M.x0[6 + row];
+        T x[12], g[12], ff, my_q = x0s[row], my_v = x0s[6 + row];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) x[i] = M.x0[i];
-        if (tid < 12) z[tid] = M.x0[tid];
+        for (int i = 0; i < 12; ++i) x[i] = x0s[i];
+        if (tid < 12) z[tid] = x0s[tid];
         {
             const T* gK = src.gK(0);
 #pragma unroll
@@ -832,6 +880,7 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
     M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
     M.work = sm + L.work; M.ls = sm + L.ls;
     M.kr = spill ? P.spill_ws + (size_t)blockIdx.x * L.reg_size : sm + L.reg;
+    M.aux = M.z;
     {
         int cap = L.reg_size / (MP_STRIDE * N);
         M.merit_cap = cap > 5 ? 5 : (cap < 1 ? 1 : cap);

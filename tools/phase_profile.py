@@ -31,5 +31,5 @@ for i in range(2):
     d = np.diff(c[:, 5 * i:5 * i + 5], axis=1)
     print(f"  qp {i}: " + ", ".join(f"{n} {np.median(d[:, j]):.0f}" for j, n in enumerate(names)) + f"   total {np.median(c[:, 5*i+4]-c[:, 5*i]):.0f}")
 print(f"  first QP: 6x6 solves {np.median(c[:,10]):.0f}, value update {np.median(c[:,11]):.0f}, roll-out {np.median(c[:,12]):.0f}, controls {np.median(c[:,13]):.0f}")
-print("  first setup sub-phases S0..S7: " + ", ".join(f"{v:.0f}" for v in np.median(np.diff(c[:, 16:25], axis=1), axis=0)))
+print("  first setup waves W0..W9: " + ", ".join(f"{v:.0f}" for v in np.median(np.diff(c[:, 16:27], axis=1), axis=0)))
 print(f"  whole solve (first stamp -> last): median {np.median(c[:, 9] - c[:, 0]):.0f} cycles; alphas {st[0,4:6]}")
