@@ -140,9 +140,8 @@ i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& 
     P.spill_ws = h->spill ? (T*)h->d_spill : nullptr;
     cudaError_t e;
     if (h->use_cluster && P.mode == i7::MODE_SOLVE) e = i7::launch_sqp_cluster<T>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
-    else if (h->threads == 384) e = i7::launch_sqp_cta<T, 384>(rob, P, h->smem_bytes, s);
-    else if (h->threads == 256) e = i7::launch_sqp_cta<T, 256>(rob, P, h->smem_bytes, s);
-    else e = i7::launch_sqp_cta<T, 128>(rob, P, h->smem_bytes, s);
+    else if (h->threads == 384) e = h->spill ? i7::launch_sqp_cta<T, 384, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 384, false>(rob, P, h->smem_bytes, s);
+    else e = h->spill ? i7::launch_sqp_cta<T, 128, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 128, false>(rob, P, h->smem_bytes, s);
     ++h->launches;
     I7_CUDA(h, e);
     return I7_OK;
@@ -150,9 +149,11 @@ i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& 
 
 template <typename T>
 cudaError_t allow_big_smem(int threads, int optin_bytes, int* cap) {
-    if (threads == 384) return i7::smem_cap_sqp_cta<T, 384>(optin_bytes, cap);
-    if (threads == 256) return i7::smem_cap_sqp_cta<T, 256>(optin_bytes, cap);
-    return i7::smem_cap_sqp_cta<T, 128>(optin_bytes, cap);
+    // the spill / no-spill instances of one CTA size have the same static footprint; raise the cap of both
+    cudaError_t e;
+    if (threads == 384) { e = i7::smem_cap_sqp_cta<T, 384, true>(optin_bytes, cap); if (e == cudaSuccess) e = i7::smem_cap_sqp_cta<T, 384, false>(optin_bytes, cap); }
+    else { e = i7::smem_cap_sqp_cta<T, 128, true>(optin_bytes, cap); if (e == cudaSuccess) e = i7::smem_cap_sqp_cta<T, 128, false>(optin_bytes, cap); }
+    return e;
 }
 
 template <typename T>
@@ -278,8 +279,8 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
 #define I7_CUDA_C(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(I7_ERR_CUDA); } } while (0)
     I7_CUDA_C(cudaSetDevice(cfg->device));
     I7_CUDA_C(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
-    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 148 ? 384 : (cfg->batch <= 296 ? 256 : 128));
-    if (h->threads != 128 && h->threads != 256 && h->threads != 384) { h->err = "threads must be 0, 128, 256 or 384"; return fail(I7_ERR_INVALID); }
+    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 148 ? 384 : 128);
+    if (h->threads != 128 && h->threads != 384) { h->err = "threads must be 0, 128 or 384"; return fail(I7_ERR_INVALID); }
     int cap = 0;
     {
         cudaError_t ea;

@@ -29,12 +29,12 @@ __host__ __device__ inline CLayout make_clayout(int N) {
     L.chunk = (N + CL - 1) / CL;
     const int recw = KR_STRIDE > 9 * MP_STRIDE ? KR_STRIDE : 9 * MP_STRIDE;   // records, later the merit scratch
     int o = 0;
+    L.work = o; o += WK_SIZE;
     L.xu = o; o += 18 * N;
     L.z = o; o += 18 * N;
     L.goals = o; o += 3 * N + (N & 1);
     L.x0 = o; o += 12;
     L.cost = o; o += COST_STRIDE * L.chunk + ((COST_STRIDE * L.chunk) & 1);
-    L.work = o; o += WK_SIZE;
     L.ls = o; o += CL_NT + 16;
     L.kr = o; o += recw * L.chunk + ((recw * L.chunk) & 1);
     L.aux = o; o += AUX_STRIDE * L.chunk;
@@ -65,7 +65,6 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
     Ptrs<T> M;
     M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
     M.work = sm + L.work; M.ls = sm + L.ls; M.kr = sm + L.kr; M.aux = sm + L.aux; M.merit_cap = 9;
-    T* gains = sm + L.gains;
     T* xbuf = xbuf_all + (size_t)b * xbuf_size(N);
     T* ric = xbuf + xbuf_ric(N);
     T* zx = xbuf + xbuf_zx(N);
@@ -121,13 +120,16 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
         if (prof && tid == 0) prof[5 * qp + 1] = clock64();
         // ---- lead CTA: exact QP solve (backward sweep + roll-out), publish the states ----
         if (rank == 0) {
-            riccati_sweep<T, NT, RicGlobal<T>>(P, M, RicGlobal<T>{ric, gains}, qp == 0 ? prof : nullptr);
+            riccati_sweep<T, NT, RicGlobal<T>>(P, L.work, L.z, L.x0, L.xu, RicGlobal<T>{ric, L.gains}, qp == 0 ? prof : nullptr);
+            if (prof && qp == 0 && tid == 0) prof[27] = clock64();
             for (int t = tid; t < 12 * N; t += NT) {
                 const int k = t / 12, i = t - 12 * k;
                 zx[t] = M.z[18 * k + i];
             }
         }
+        if (prof && qp == 0 && tid == 0) prof[28] = clock64();
         cluster.sync();                                                             // barrier 2
+        if (prof && qp == 0 && tid == 0) prof[29] = clock64();
         if (rank != 0) {
             for (int t = tid; t < 12 * N; t += NT) {
                 const int k = t / 12, i = t - 12 * k;
@@ -135,7 +137,8 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
             }
         }
         __syncthreads();
-        phase_controls<T, NT>(P, M, W, zu);
+        if (prof && qp == 0 && tid == 0) prof[30] = clock64();
+        phase_controls<T, NT, false>(P, L.z, L.ls, L.kr, nullptr, W, zu);
         if (prof && tid == 0) prof[5 * qp + 2] = clock64();
         // ---- line search: all nine candidates at the own knots ----
         merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, 0, 9, mcomps);

@@ -7,10 +7,10 @@
 namespace i7 {
 
 // CTA-per-problem kernel (throughput form): grid = batch
-template <typename T, int NT> cudaError_t launch_sqp_cta(const Robot<T>& rob, const SolveParams<T>& P, int smem_bytes,
+template <typename T, int NT, bool SPILL> cudaError_t launch_sqp_cta(const Robot<T>& rob, const SolveParams<T>& P, int smem_bytes,
                                                          cudaStream_t s);
 // raises the dynamic shared-memory cap of that instance to everything the SM offers; returns the cap
-template <typename T, int NT> cudaError_t smem_cap_sqp_cta(int optin_bytes, int* cap);
+template <typename T, int NT, bool SPILL> cudaError_t smem_cap_sqp_cta(int optin_bytes, int* cap);
 
 // cluster-per-problem kernel (latency form): grid = batch x 8 CTAs; xbuf = batch x cluster_xbuf_len(N) exchange buffer
 template <typename T> cudaError_t launch_sqp_cluster(const Robot<T>& rob, const SolveParams<T>& P, T* xbuf, int smem_bytes,

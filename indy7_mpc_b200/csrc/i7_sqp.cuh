@@ -51,7 +51,7 @@ constexpr int KR_GV = 36;     // 36  I + dt dqdd/dv                    (A_k lowe
 constexpr int KR_CV = 72;     // 6   affine term of the velocity rows  (c_k = [0; cv])
 constexpr int KR_Y = 78;      // 36  M during setup, then Y = H^-1 = M / dt
 constexpr int KR_S = 114;     // 36  S = R_k Y'Y   (MODE_DUMP: H = dt M^-1)
-constexpr int KR_L = 150;     // 78  upper triangle of L = G'SG; setup scratch before that:
+constexpr int KR_L = 150;     // 78  upper triangle of L = G'SG + Qx; setup scratch before that
 constexpr int KR_SG = 228;    // 72  S G ; after the stage is eliminated: feedback gain Kw (6x12)
 constexpr int KR_D = 300;     // 6   d = S cv - R Y u ; after elimination: feed-forward kw
 constexpr int KR_HX = 306;    // 12  gx + G'd
@@ -59,13 +59,8 @@ constexpr int KR_STRIDE = 319;
 constexpr int COST_STRIDE = 9;                       // j[6], Q, dQ, R
 // merit scratch per evaluated point (aliases the knot records, dead after the QP solve)
 constexpr int MP_CS = 0, MP_M = 12, MP_B = 48, MP_STRIDE = 55;
-// Riccati work area
-constexpr int WK_P = 0;        // 2 x 36 qq blocks of the value matrix (double buffered; the rest of the 288 is spare)
-constexpr int WK_PV = 288;     // 2 x 12
-constexpr int WK_AUG = 312;    // 2 x (6 x 19): [Hww | Hwx | hw]
-constexpr int WK_X = 540;      // 6 x 13
-constexpr int WK_SIZE = 620;
-constexpr int AUGW = 19;
+// Riccati work area (first in the layouts: 16-byte aligned)
+constexpr int WK_SIZE = 296;   // two sweep-state blocks (SB_*), see riccati_sweep
 
 struct Layout {
     int xu, z, goals, x0, cost, work, ls, reg, reg_size, total;
@@ -73,11 +68,11 @@ struct Layout {
 __host__ __device__ inline Layout make_layout(int N, bool spill) {
     Layout L;
     int o = 0;
+    L.work = o; o += WK_SIZE;
     L.xu = o; o += 18 * N;
     L.goals = o; o += 3 * N;
     L.x0 = o; o += 12;
     L.cost = o; o += COST_STRIDE * N;
-    L.work = o; o += WK_SIZE;
     L.z = o; o += 18 * N;            // z and ls are adjacent: during setup (both dead) they hold the aux side array
     L.ls = o; o += (4 * 5 * N > 400 ? 4 * 5 * N : 400) + 16;
     L.reg = o;
@@ -92,13 +87,6 @@ struct Ptrs {
     T *xu, *z, *goals, *x0, *cost, *work, *ls, *kr, *aux;
     int merit_cap;      // candidates per merit wave that fit the scratch region
 };
-
-// Re-derive a pointer that is known to address shared memory (after a non-inlined call the compiler only sees a
-// generic pointer): the round trip through the shared window lets it emit LDS / STS instead of generic accesses.
-template <typename T> I7_DEV T* as_shared(T* p) {
-    return reinterpret_cast<T*>(__cvta_shared_to_generic(__cvta_generic_to_shared(p)));
-}
-template <typename T> I7_DEV const T* as_shared(const T* p) { return as_shared(const_cast<T*>(p)); }
 
 // the knots a CTA works on in the per-knot phases: [k0, k0 + nc) for cost terms, [k0, k0 + nd) for dynamics;
 // the whole horizon (0, N-1, N) when one CTA owns the problem.  Records / cost terms are indexed window-relative.
@@ -357,6 +345,11 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
             T acc = T(0);
 #pragma unroll
             for (int s = 0; s < 6; ++s) acc += Gr[6 * s] * kr[KR_SG + 12 * s + c];
+            {   // + Qx: the stage cost Hessian (rank-1 position block, dQ on the velocity diagonal)
+                const T* ck = M.cost + COST_STRIDE * k;
+                if (c < 6) acc += ck[6] * ck[r] * ck[c];
+                else if (r == c) acc += ck[7];
+            }
             kr[KR_L + e] = acc;
         } else if (e < 90) {
             const int r = e - 78;
@@ -377,201 +370,222 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
 }
 
 // -----------------------------------------------------------------------------------------------------------
-// Stage k of the backward sweep works on  [Hww | Hwx | hw]  (6 x 19) built from the value function (Pm, pv) of
-// stage k+1:   Hww = P_vv + S,  Hwx = [P_qv' - SG_q, dt P_qv' - SG_v],  hw = p_v - d
+// Stage k of the backward sweep solves  Hww X = [Hwx | hw]  (6 x 6, 13 right-hand sides) built from the value
+// function (P, p) of stage k+1:   Hww = P_vv + S,  Hwx = [P_qv' - SG_q, dt P_qv' - SG_v],  hw = p_v - d.
+// Double-buffered sweep state in the work area (one block per parity of the stage):
+constexpr int SB_P = 0;       // 36  qq block of the value matrix (the only block other entries read back)
+constexpr int SB_PV = 36;     // 12  value gradient (q part)
+constexpr int SB_H = 48;      // 22  Hww, packed lower triangle row-major (21) + pad
+constexpr int SB_R = 70;      // 78  right-hand sides, column-major: R[c][s] = SB_R + 6 c + s  (c = 12: hw)
+constexpr int SB_SIZE = 148;  // even: both blocks 16-byte aligned
+static_assert(2 * SB_SIZE <= WK_SIZE, "work area too small for the sweep state");
+constexpr int GAIN_LEN = 78;  // gains of a stage, column-major like the right-hand sides: K[c][s] = 6 c + s, c = 12: kw
+
+// shared-memory base of the dynamic allocation, typed: every function re-derives it from the symbol so that the
+// compiler can prove the address space (LDS / STS instead of generic accesses) even across non-inlined calls
+template <typename T> I7_DEV T* smem_base() {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    return reinterpret_cast<T*>(smem_raw);
+}
+
 // Where the sweep finds the stage data and keeps the gains.
-//   RicLocal   one CTA owns the problem: per-knot records in its shared memory (or its spill workspace); the gains
-//              overwrite the SG / d slots of the record once the stage is eliminated
+//   RicLocal   one CTA owns the problem: per-knot records in its shared memory (SPILL: in its global workspace);
+//              the gains overwrite the SG / d slots of the record once the stage is eliminated
 //   RicGlobal  cluster form: the owners of the knots exported [L | SG | S | d | hx | cost] to an L2-resident
-//              exchange buffer; the lead CTA streams it (ld.global.cg, issued while the 6x6 solves run) and keeps the
-//              gains in its own shared memory
+//              exchange buffer; the lead CTA streams it (ld.global.cg, one stage ahead) and keeps the gains in its
+//              own shared memory
 constexpr int RIC_L = 0, RIC_SG = 78, RIC_S = 150, RIC_D = 186, RIC_HX = 192, RIC_COST = 204, RIC_STRIDE = 216;
-constexpr int GAIN_STRIDE = 80;     // Kw (6 x 12 row-major), kw (6), 2 pad
-template <typename T> struct RicLocal {
-    T* kr; const T* cost;
+constexpr int GAIN_STRIDE = 80;
+template <typename T, bool SPILL> struct RicLocal {
+    int o_kr, o_cost; T* krg;
     static constexpr int oL = KR_L, oSG = KR_SG, oS = KR_S, oD = KR_D, oHX = KR_HX;
-    I7_DEV const T* rec(int k) const { return kr + KR_STRIDE * k; }
-    I7_DEV const T* ck(int k) const { return cost + COST_STRIDE * k; }
-    I7_DEV T* gK(int k) const { return kr + KR_STRIDE * k + KR_SG; }
-    I7_DEV T* gk(int k) const { return kr + KR_STRIDE * k + KR_D; }
+    I7_DEV const T* rec(int k) const { return (SPILL ? krg : smem_base<T>() + o_kr) + KR_STRIDE * k; }
+    I7_DEV const T* ck(int k) const { return smem_base<T>() + o_cost + COST_STRIDE * k; }
+    I7_DEV T* gain(int k) const { return (SPILL ? krg : smem_base<T>() + o_kr) + KR_STRIDE * k + KR_SG; }
     static I7_DEV T ld(const T* p) { return *p; }
 };
 template <typename T> struct RicGlobal {
-    const T* ric; T* gains;
+    const T* ric; int o_gains;
     static constexpr int oL = RIC_L, oSG = RIC_SG, oS = RIC_S, oD = RIC_D, oHX = RIC_HX;
     I7_DEV const T* rec(int k) const { return ric + RIC_STRIDE * k; }
     I7_DEV const T* ck(int k) const { return ric + RIC_STRIDE * k + RIC_COST; }
-    I7_DEV T* gK(int k) const { return as_shared(gains) + GAIN_STRIDE * k; }
-    I7_DEV T* gk(int k) const { return as_shared(gains) + GAIN_STRIDE * k + 72; }
+    I7_DEV T* gain(int k) const { return smem_base<T>() + o_gains + GAIN_STRIDE * k; }
     static I7_DEV T ld(const T* p) { return __ldcg(p); }
 };
+static_assert(KR_D == KR_SG + 72, "the gains (Kw | kw) must be contiguous in the record");
+
+// reciprocal on the serial path: hardware seed + two Newton steps (a few ulp; 10+ cycles shorter than the IEEE divide)
+template <typename T> I7_DEV T rcp_serial(T x) { return T(1) / x; }
+template <> I7_DEV double rcp_serial<double>(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0); r = fma(r, e, r);
+    e = fma(-x, r, 1.0); r = fma(r, e, r);
+    return r;
+}
+template <typename T> I7_DEV void spd6_factor_serial(T (&A)[6][6], T (&dinv)[6]) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        dinv[j] = rcp_serial<T>(A[j][j]);
+        T col[6];
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) col[i] = A[i][j];
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) {
+            const T l = col[i] * dinv[j];
+#pragma unroll
+            for (int k = j + 1; k <= i; ++k) A[i][k] -= l * col[k];
+            A[i][j] = l;
+        }
+    }
+}
 
 // riccati: backward recursion for the gains, forward roll-out for z.  x0 = measured state (l[:12] = -xs).
 //
-// Thread roles are fixed for the whole recursion and decoded once:
+// Thread roles are fixed for the whole recursion and decoded once into small per-lane "programs" (offsets and
+// scales), so the stage loop itself is branch-light and free of index arithmetic:
 //   warp 0, lanes 0..12   R2: X = Hww^-1 [Hwx | hw], one right-hand side each (LDL' in registers); the negated
-//                         column goes straight into the stage record as the gain Kw[:, c] / kw
-//   threads 32..121       R3: one entry of the new value function each (78 upper-triangle entries of P, 12 of p).
-//                         The part that does not depend on X (L + Qx + T'PT, hx + T'p) and the operands of the next
-//                         stage's [Hww | Hwx | hw] are fetched while R2 runs; after the barrier only the rank-6
-//                         correction (12 loads, 6 FMAs in two chains) is left.
-// Only the qq block of P is exchanged between threads (T'PT reads nothing else); the qv / vv blocks and p_v flow
-// directly into the next stage's augmented matrix.
+//                         column is stored as the gain column K[c][:] / kw
+//   warp 1                the 21 qq entries of the new value matrix and p_q          (stay in the P / PV slots)
+//   warp 2                the 36 qv entries: each feeds two entries of the next Hwx
+//   warp 3                the 21 vv entries (-> next Hww, packed) and p_v (-> next hw)
+// Every entry is  base + Hwx[:, r] . K[c][:]  with base = (L + Qx)[r][c] + (T'PT)[r][c] (resp. hx + T'p), 6-term dot
+// products over contiguous columns; the stage-local operands (L + Qx, S, SG, d of the next stage) are fetched one
+// stage ahead while the 6x6 solves run.
 template <typename T, int NT, typename Src>
-__device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, const Ptrs<T>& M, const Src src, long long* prof) {
+__device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, int o_work, int o_z, int o_x0, int o_xu,
+                                           const Src src, long long* prof) {
     static_assert(NT >= 128, "riccati_sweep needs at least 4 warps");
     const int tid = threadIdx.x;
     long long acc_r2 = 0, acc_r3 = 0, tt = 0;
     const int N = P.N;
     const T dt = P.dt;
-    T* wk = as_shared(M.work);
-    const T* xu = as_shared(M.xu);
-    const T* x0s = as_shared(M.x0);
-    T* zs = as_shared(M.z);
-    // ---- role decode (once) ----
-    const int e = tid - 32;
-    const bool is_P = (e >= 0 && e < 78), is_p = (e >= 78 && e < 90);
+    T* sm = smem_base<T>();
+    T* wk = sm + o_work;
+    T* z = sm + o_z;
+    const T* x0 = sm + o_x0;
+    const T* xu = sm + o_xu;
+    // ---- lane programs (decoded once) ----
+    const int warp = tid >> 5, lane = tid & 31;
     int r = 0, c = 0;
-    if (is_P) {
-        int rem = e, len = 12;
-        while (rem >= len) { rem -= len; --len; ++r; }
-        c = r + rem;
-    } else if (is_p) {
-        r = e - 78;
+    bool act = false, is_p = false;
+    if (warp == 1) {                                   // qq: 21 entries r <= c < 6, then p_q
+        if (lane < 21) { int rem = lane, len = 6; while (rem >= len) { rem -= len; --len; ++r; } c = r + rem; act = true; }
+        else if (lane < 27) { r = lane - 21; is_p = true; act = true; }
+    } else if (warp == 2) {                            // qv: r < 6 <= c   (36 entries -> lanes 0..31 and warp 3 lanes 27..30)
+        if (lane < 32) { r = lane / 6; c = 6 + lane % 6; act = true; }
+    } else if (warp == 3) {                            // vv: 21 entries 6 <= r <= c, then p_v, then the last 4 qv entries
+        if (lane < 21) { int rem = lane, len = 6; while (rem >= len) { rem -= len; --len; ++r; } c = r + rem; r += 6; c += 6; act = true; }
+        else if (lane < 27) { r = 6 + lane - 21; is_p = true; act = true; }
+        else if (lane < 31) { const int e = 32 + lane - 27; r = e / 6; c = 6 + e % 6; act = true; }
     }
     const int ra = r < 6 ? r : r - 6, ca = c < 6 ? c : c - 6;
-    const T tfac = (r < 6 ? T(1) : dt) * ((is_P && c >= 6) ? dt : T(1));   // T'PT scale (P entry) / T'p scale (p entry)
-    const int offA = 6 + r;                                  // Hwx[s][r] = aug[AUGW s + 6 + r]
-    const int strB = is_P ? 12 : 1;                          // Kw[s][c] (stride 12) or kw[s] (stride 1)
-    // operands of the NEXT stage's augmented matrix that this thread's entry feeds (record offsets, -1 = none)
-    int on0 = -1, on1 = -1;
-    if (is_P && c >= 6) {
-        if (r < 6) { on0 = Src::oSG + 12 * (c - 6) + r; on1 = Src::oSG + 12 * (c - 6) + 6 + r; }
-        else { on0 = Src::oS + 6 * (r - 6) + (c - 6); on1 = Src::oS + 6 * (c - 6) + (r - 6); }
-    } else if (is_p && r >= 6) {
-        on0 = Src::oD + r - 6;
+    const bool is_P = act && !is_p;
+    // entry index e78 of (r, c) in the row-major upper triangle of a 12 x 12 matrix (layout of L)
+    const int e78 = r * 12 - (r * (r - 1)) / 2 + (c - r);
+    const int oA = SB_R + 6 * r;                                   // Hwx[:, r], contiguous
+    const int oB = is_P ? 6 * c : 72;                              // K[c][:] resp. kw
+    const int oOld = is_P ? SB_P + 6 * ra + ca : SB_PV + ra;       // (T'PT) resp. (T'p) operand
+    const T tfac = (r < 6 ? T(1) : dt) * ((is_P && c >= 6) ? dt : T(1));
+    const int oL = is_P ? Src::oL + e78 : Src::oHX + r;            // base term in the record of the stage
+    int on0 = -1, on1 = -1, st0 = -1, st1 = -1;                    // next-stage operands (record) / stores (sweep block)
+    T m1 = T(1), sg = T(1);
+    if (is_P && c < 6) {
+        st0 = SB_P + 6 * r + c;
+        if (r != c) st1 = SB_P + 6 * c + r;
+    } else if (is_P && r < 6) {
+        const int i = c - 6;
+        st0 = SB_R + 6 * r + i; st1 = SB_R + 6 * (6 + r) + i; m1 = dt; sg = T(-1);
+        on0 = Src::oSG + 12 * i + r; on1 = Src::oSG + 12 * i + 6 + r;
+    } else if (is_P) {
+        const int i = r - 6, j = c - 6;
+        st0 = SB_H + (j * (j + 1)) / 2 + i;
+        on0 = Src::oS + 6 * i + j;
+    } else if (is_p && r < 6) {
+        st0 = SB_PV + r;
+    } else if (is_p) {
+        st0 = SB_R + 72 + (r - 6); sg = T(-1);
+        on0 = Src::oD + (r - 6);
     }
-    int cur = 0;
-    // terminal value function: P_N = blkdiag(QN j j', dQ_N I), p_N = [QN j; dQ_N v]; aug for stage N-2
-    {
-        const T* cN = src.ck(N - 1);
-        const T* xN = xu + 18 * (N - 1);
-        const T* rn = src.rec(N - 2);
-        T* augn = wk + WK_AUG;
-        if (is_P) {
-            const T n0 = on0 >= 0 ? Src::ld(rn + on0) : T(0), n1 = on1 >= 0 ? Src::ld(rn + on1) : T(0);
-            T v = T(0);
-            if (c < 6) v = Src::ld(cN + 6) * Src::ld(cN + r) * Src::ld(cN + c);
-            else if (r == c) v = Src::ld(cN + 7);
-            if (c < 6) { wk[WK_P + 6 * r + c] = v; wk[WK_P + 6 * c + r] = v; }
-            else if (r < 6) {
-                augn[AUGW * (c - 6) + 6 + r] = v - n0;
-                augn[AUGW * (c - 6) + 12 + r] = dt * v - n1;
-            } else {
-                augn[AUGW * (r - 6) + (c - 6)] = v + n0;
-                if (r != c) augn[AUGW * (c - 6) + (r - 6)] = v + n1;
-            }
-        } else if (is_p) {
-            const T v = r < 6 ? Src::ld(cN + 6) * Src::ld(cN + r) : Src::ld(cN + 7) * xN[r];
-            wk[WK_PV + r] = v;
-            if (r >= 6) augn[AUGW * (r - 6) + 18] = v - Src::ld(rn + on0);
-        }
-    }
-    // Stage operands that do not depend on the recursion are fetched ONE STAGE AHEAD (they may sit in L2 when the
-    // records were exported by other CTAs): cL/cQ = L + Qx entry (or hx) of the current stage, cn0/cn1 = operands of
-    // the next stage's augmented matrix.
-    T cL = T(0), cQ = T(0), cn0 = T(0), cn1 = T(0);
-    auto fetch = [&](int k, T& fL, T& fQ, T& f0, T& f1) {
-        fL = T(0); fQ = T(0); f0 = T(0); f1 = T(0);
-        if (k < 0) return;
-        const T* rk = src.rec(k);
-        if (is_P) {
-            const T* ck = src.ck(k);
-            fL = Src::ld(rk + Src::oL + e);
-            if (c < 6) fQ = Src::ld(ck + 6) * Src::ld(ck + r) * Src::ld(ck + c);
-            else if (r == c) fQ = Src::ld(ck + 7);
-        } else if (is_p) {
-            fL = Src::ld(rk + Src::oHX + r);
-        }
-        if (k > 0 && on0 >= 0) {
+    // store an entry of the value function into the block of the next stage
+    auto emit = [&](T* blk, T acc, T n0, T n1) {
+        if (st0 >= 0) blk[st0] = acc + sg * n0;
+        if (st1 >= 0) blk[st1] = m1 * acc + sg * n1;
+    };
+    // stage-local operands, fetched ONE STAGE AHEAD (they may sit in L2 when the records were exported by other CTAs)
+    auto fetch = [&](int k, T& fL, T& f0, T& f1) {
+        fL = T(0); f0 = T(0); f1 = T(0);
+        if (k < 0 || !act) return;
+        fL = Src::ld(src.rec(k) + oL);
+        if (k > 0) {
             const T* rn = src.rec(k - 1);
-            f0 = Src::ld(rn + on0);
+            if (on0 >= 0) f0 = Src::ld(rn + on0);
             if (on1 >= 0) f1 = Src::ld(rn + on1);
         }
     };
-    fetch(N - 2, cL, cQ, cn0, cn1);
+    int cur = 0;
+    // terminal value function: P_N = blkdiag(QN j j', dQ_N I), p_N = [QN j; dQ_N v]; block 0 <- operands of stage N-2
+    if (act) {
+        const T* cN = src.ck(N - 1);
+        const T* xN = xu + 18 * (N - 1);
+        const T* rn = src.rec(N - 2);
+        const T n0 = on0 >= 0 ? Src::ld(rn + on0) : T(0), n1 = on1 >= 0 ? Src::ld(rn + on1) : T(0);
+        T v = T(0);
+        if (is_P) {
+            if (c < 6) v = Src::ld(cN + 6) * Src::ld(cN + r) * Src::ld(cN + c);
+            else if (r == c) v = Src::ld(cN + 7);
+        } else {
+            v = r < 6 ? Src::ld(cN + 6) * Src::ld(cN + r) : Src::ld(cN + 7) * xN[r];
+        }
+        emit(wk, v, n0, n1);
+    }
+    T cL, cn0, cn1;
+    fetch(N - 2, cL, cn0, cn1);
     __syncthreads();
+    if (prof && tid == 0) prof[14] = clock64();            // end of the terminal-stage initialisation
     for (int k = N - 2; k >= 0; --k) {
-        T* gK = src.gK(k);
-        T* gk = src.gk(k);
-        T* aug = wk + WK_AUG + 114 * cur;
+        T* G = src.gain(k);
+        T* blk = wk + SB_SIZE * cur;
+        T* blkn = wk + SB_SIZE * (cur ^ 1);
         if (prof && tid == 0) tt = clock64();
-        T pL, pQ, pn0, pn1;
-        fetch(k - 1, pL, pQ, pn0, pn1);        // consumed in the next iteration
+        T pL, pn0, pn1;
+        fetch(k - 1, pL, pn0, pn1);            // consumed in the next iteration
         T base = T(0);
-        const T n0 = cn0, n1 = cn1;
         if (tid < 13) {
             // R2: one right-hand side of X = Hww^-1 [Hwx | hw]
             T A[6][6], dinv[6], b[6];
 #pragma unroll
             for (int i = 0; i < 6; ++i)
 #pragma unroll
-                for (int q = 0; q <= i; ++q) A[i][q] = aug[AUGW * i + q];
+                for (int q = 0; q <= i; ++q) A[i][q] = blk[SB_H + (i * (i + 1)) / 2 + q];
 #pragma unroll
-            for (int i = 0; i < 6; ++i) b[i] = aug[AUGW * i + 6 + tid];
-            spd6_factor<T>(A, dinv);
+            for (int i = 0; i < 6; ++i) b[i] = blk[SB_R + 6 * tid + i];
+            spd6_factor_serial<T>(A, dinv);
             spd6_solve_factored<T>(A, dinv, b);
             // feedback / feed-forward of w = v_{k+1}: Kw = -X[:, :12], kw = -X[:, 12]
-            if (tid < 12) {
 #pragma unroll
-                for (int i = 0; i < 6; ++i) gK[12 * i + tid] = -b[i];
-            } else {
-#pragma unroll
-                for (int i = 0; i < 6; ++i) gk[i] = -b[i];
-            }
-        } else if (is_P) {
-            base = (cL + cQ) + wk[WK_P + 36 * cur + 6 * ra + ca] * tfac;
-        } else if (is_p) {
-            base = cL + wk[WK_PV + 12 * cur + ra] * tfac;
+            for (int i = 0; i < 6; ++i) G[6 * tid + i] = -b[i];
+        } else if (act) {
+            base = cL + blk[oOld] * tfac;
         }
         __syncthreads();
         if (prof && tid == 0) { const long long n = clock64(); acc_r2 += n - tt; tt = n; }
-        // R3: P = Qx + L + T'aT - Hwx'X, p = hx + [pq; dt pq] - Hwx' x13 (X = -K); aug of stage k-1
-        if (is_P || is_p) {
+        // R3: P = Qx + L + T'aT - Hwx'X, p = hx + [pq; dt pq] - Hwx' x13 (X = -K); operands of stage k-1
+        if (act) {
             T a0 = base, a1 = T(0);
-            const T* hb = aug + offA;
-            const T* kb = is_P ? gK + c : gk;
+            const T* hb = blk + oA;
+            const T* kb = G + oB;
 #pragma unroll
             for (int s = 0; s < 3; ++s) {
-                a0 += hb[AUGW * s] * kb[strB * s];
-                a1 += hb[AUGW * (s + 3)] * kb[strB * (s + 3)];
+                a0 += hb[s] * kb[s];
+                a1 += hb[s + 3] * kb[s + 3];
             }
-            const T acc = a0 + a1;
-            T* augn = wk + WK_AUG + 114 * (cur ^ 1);
-            if (is_P) {
-                if (c < 6) {
-                    T* Pn = wk + WK_P + 36 * (cur ^ 1);
-                    Pn[6 * r + c] = acc; Pn[6 * c + r] = acc;
-                } else if (k > 0) {
-                    if (r < 6) {
-                        const int i = c - 6;
-                        augn[AUGW * i + 6 + r] = acc - n0;
-                        augn[AUGW * i + 12 + r] = dt * acc - n1;
-                    } else {
-                        const int i = r - 6, j = c - 6;
-                        augn[AUGW * i + j] = acc + n0;
-                        if (i != j) augn[AUGW * j + i] = acc + n1;
-                    }
-                }
-            } else {
-                if (r < 6) wk[WK_PV + 12 * (cur ^ 1) + r] = acc;
-                else if (k > 0) augn[AUGW * (r - 6) + 18] = acc - n0;
-            }
+            emit(blkn, a0 + a1, cn0, cn1);
         }
         __syncthreads();
         if (prof && tid == 0) acc_r3 += clock64() - tt;
         cur ^= 1;
-        cL = pL; cQ = pQ; cn0 = pn0; cn1 = pn1;
+        cL = pL; cn0 = pn0; cn1 = pn1;
     }
     if (prof && tid == 0) { prof[10] = acc_r2; prof[11] = acc_r3; tt = clock64(); }
     // forward roll-out by warp 0: x_0 = xs, v_{k+1} = Kw_k x_k + kw_k, q_{k+1} = q_k + dt v_k.  The state lives in
@@ -579,26 +593,24 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, const Ptrs<T
     // exchanged with shuffles, so the serial chain per stage is 3 FMAs + 2 adds + one shuffle (no shared-memory
     // round trip); the gain row of the next stage is fetched while the current one is applied.
     if (tid < 32) {
-        T* z = zs;
         const int row = tid % 6;
-        T x[12], g[12], ff, my_q = x0s[row], my_v = x0s[6 + row];
+        T x[12], g[12], ff, my_q = x0[row], my_v = x0[6 + row];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) x[i] = x0s[i];
-        if (tid < 12) z[tid] = x0s[tid];
+        for (int i = 0; i < 12; ++i) x[i] = x0[i];
+        if (tid < 12) z[tid] = x0[tid];
         {
-            const T* gK = src.gK(0);
+            const T* G = src.gain(0);
 #pragma unroll
-            for (int i = 0; i < 12; ++i) g[i] = gK[12 * row + i];
-            ff = src.gk(0)[row];
+            for (int i = 0; i < 12; ++i) g[i] = G[6 * i + row];
+            ff = G[72 + row];
         }
         for (int k = 0; k < N - 1; ++k) {
-            T gn[12], ffn = T(0);
-            const int kn = k + 1 < N - 1 ? k + 1 : k;
+            T gn[12], ffn;
             {
-                const T* gK = src.gK(kn);
+                const T* G = src.gain(k + 1 < N - 1 ? k + 1 : k);
 #pragma unroll
-                for (int i = 0; i < 12; ++i) gn[i] = gK[12 * row + i];
-                ffn = src.gk(kn)[row];
+                for (int i = 0; i < 12; ++i) gn[i] = G[6 * i + row];
+                ffn = G[72 + row];
             }
             T a0 = ff, a1 = T(0), a2 = T(0), a3 = T(0);
 #pragma unroll
@@ -629,15 +641,18 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, const Ptrs<T
 
 // controls of the window's knots: u_k = Y_k (v_{k+1} - Gq q_k - Gv v_k - cv_k); needs the x part of z for knots k, k+1.
 // zu_out (cluster form): the controls are also published to the exchange buffer, 6 per knot.
-template <typename T, int NT>
-__device__ __noinline__ void phase_controls(const SolveParams<T>& P, const Ptrs<T>& M, const Win W, T* zu_out) {
+template <typename T, int NT, bool SPILL>
+__device__ __noinline__ void phase_controls(const SolveParams<T>& P, int o_z, int o_ls, int o_kr, T* krg, const Win W,
+                                            T* zu_out) {
     const int tid = threadIdx.x;
     const int nk = W.nd;
-    T* z = M.z + 18 * W.k0;
-    T* tmp = M.ls;
+    T* sm = smem_base<T>();
+    T* z = sm + o_z + 18 * W.k0;
+    T* tmp = sm + o_ls;
+    const T* krb = SPILL ? krg : sm + o_kr;
     for (int t = tid; t < 6 * nk; t += NT) {
         const int rr = t / nk, k = t - rr * nk;
-        const T* kr = M.kr + KR_STRIDE * k;
+        const T* kr = krb + KR_STRIDE * k;
         const T* zk = z + 18 * k;
         T a0 = zk[18 + 6 + rr] - kr[KR_CV + rr], a1 = T(0);
 #pragma unroll
@@ -650,7 +665,7 @@ __device__ __noinline__ void phase_controls(const SolveParams<T>& P, const Ptrs<
     __syncthreads();
     for (int t = tid; t < 6 * nk; t += NT) {
         const int rr = t / nk, k = t - rr * nk;
-        const T* kr = M.kr + KR_STRIDE * k;
+        const T* kr = krb + KR_STRIDE * k;
         T acc = T(0);
 #pragma unroll
         for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * rr + s] * tmp[6 * k + s];
@@ -868,18 +883,18 @@ template <typename T, typename Lay> __device__ void dump_qp(const SolveParams<T>
 }
 
 // -----------------------------------------------------------------------------------------------------------
-template <typename T, int NT>
+template <typename T, int NT, bool SPILL>
 __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__ SolveParams<T> P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* sm = reinterpret_cast<T*>(smem_raw);
     const int tid = threadIdx.x, N = P.N;
     const int nz = 18 * N - 6;
-    const bool spill = P.spill_ws != nullptr;
-    const Layout L = make_layout(N, spill);
+    const Layout L = make_layout(N, SPILL);
     Ptrs<T> M;
     M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
     M.work = sm + L.work; M.ls = sm + L.ls;
-    M.kr = spill ? P.spill_ws + (size_t)blockIdx.x * L.reg_size : sm + L.reg;
+    T* const krg = SPILL ? P.spill_ws + (size_t)blockIdx.x * L.reg_size : nullptr;
+    M.kr = SPILL ? krg : sm + L.reg;
     M.aux = M.z;
     {
         int cap = L.reg_size / (MP_STRIDE * N);
@@ -939,9 +954,9 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
                 {
                     long long* pr = (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr;
                     long long tc = 0;
-                    riccati_sweep<T, NT, RicLocal<T>>(P, M, RicLocal<T>{M.kr, M.cost}, pr);
+                    riccati_sweep<T, NT, RicLocal<T, SPILL>>(P, L.work, L.z, L.x0, L.xu, RicLocal<T, SPILL>{L.reg, L.cost, krg}, pr);
                     if (pr && tid == 0) tc = clock64();
-                    phase_controls<T, NT>(P, M, W, nullptr);
+                    phase_controls<T, NT, SPILL>(P, L.z, L.ls, L.reg, krg, W, nullptr);
                     if (pr && tid == 0) pr[13] = clock64() - tc;
                 }
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 2] = clock64();

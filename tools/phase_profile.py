@@ -33,3 +33,8 @@ for i in range(2):
 print(f"  first QP: 6x6 solves {np.median(c[:,10]):.0f}, value update {np.median(c[:,11]):.0f}, roll-out {np.median(c[:,12]):.0f}, controls {np.median(c[:,13]):.0f}")
 print("  first setup waves W0..W9: " + ", ".join(f"{v:.0f}" for v in np.median(np.diff(c[:, 16:27], axis=1), axis=0)))
 print(f"  whole solve (first stamp -> last): median {np.median(c[:, 9] - c[:, 0]):.0f} cycles; alphas {st[0,4:6]}")
+if np.any(c[:, 27] > 0):       # cluster kernel: finer stamps of the first QP phase (lead CTA)
+    m = lambda a: float(np.median(a))
+    print(f"  first QP (cluster): barrier1->init done {m(c[:,14]-c[:,1]):.0f}, sweep loop+roll-out {m(c[:,27]-c[:,14]):.0f}, "
+          f"publish {m(c[:,28]-c[:,27]):.0f}, barrier2 {m(c[:,29]-c[:,28]):.0f}, zx load {m(c[:,30]-c[:,29]):.0f}, "
+          f"controls {m(c[:,2]-c[:,30]):.0f}")
