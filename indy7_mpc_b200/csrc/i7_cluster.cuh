@@ -23,11 +23,14 @@ namespace i7 {
 constexpr int CL = 8;          // CTAs per cluster = per problem (portable maximum)
 constexpr int CL_NT = 384;     // threads per CTA
 
-struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, aux, gains, total, chunk; };
+__host__ __device__ inline int cluster_merit_cap(int chunk) { return chunk <= 4 ? 8 : (chunk <= 8 ? 4 : 2); }
+struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, aux, pair, gains, total, chunk; };
 __host__ __device__ inline CLayout make_clayout(int N) {
     CLayout L;
     L.chunk = (N + CL - 1) / CL;
-    const int recw = KR_STRIDE > 9 * MP_STRIDE ? KR_STRIDE : 9 * MP_STRIDE;   // records, later the merit scratch
+    // knot records, later the merit scratch (as many line-search candidates per wave as fit: 8 up to N = 32)
+    const int mcap = cluster_merit_cap(L.chunk);
+    const int recw = KR_STRIDE > mcap * MP_STRIDE ? KR_STRIDE : mcap * MP_STRIDE;
     int o = 0;
     L.work = o; o += WK_SIZE;
     L.xu = o; o += 18 * N;
@@ -38,6 +41,8 @@ __host__ __device__ inline CLayout make_clayout(int N) {
     L.ls = o; o += CL_NT + 16;
     L.kr = o; o += recw * L.chunk + ((recw * L.chunk) & 1);
     L.aux = o; o += AUX_STRIDE * L.chunk;
+    L.pair = -1;
+    if (L.chunk <= 8) { L.pair = o; o += 432 * L.chunk; }     // per-(column, link) derivative terms (latency form)
     L.gains = o; o += GAIN_STRIDE * N;
     L.total = o;
     return L;
@@ -64,7 +69,7 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
     const CLayout L = make_clayout(N);
     Ptrs<T> M;
     M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
-    M.work = sm + L.work; M.ls = sm + L.ls; M.kr = sm + L.kr; M.aux = sm + L.aux; M.merit_cap = 9;
+    M.work = sm + L.work; M.ls = sm + L.ls; M.kr = sm + L.kr; M.aux = sm + L.aux; M.pair = L.pair >= 0 ? sm + L.pair : nullptr; M.merit_cap = cluster_merit_cap(L.chunk);
     T* xbuf = xbuf_all + (size_t)b * xbuf_size(N);
     T* ric = xbuf + xbuf_ric(N);
     T* zx = xbuf + xbuf_zx(N);
@@ -140,22 +145,31 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
         if (prof && qp == 0 && tid == 0) prof[30] = clock64();
         phase_controls<T, NT, false>(P, L.z, L.ls, L.kr, nullptr, W, zu);
         if (prof && tid == 0) prof[5 * qp + 2] = clock64();
-        // ---- line search: all nine candidates at the own knots ----
-        merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, 0, 9, mcomps);
+        // ---- line search: candidates 0..7 (base, alpha = 1 .. 1/64) at the own knots — with 4 knots per CTA that is
+        //      exactly one warp per task type; the last candidate (1/128) only if none of those is accepted ----
+        for (int c0 = 0; c0 < 8; c0 += M.merit_cap)
+            merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, 8 - c0 < M.merit_cap ? 8 - c0 : M.merit_cap, mcomps, c0);
         cluster.sync();                                                             // barrier 3
         for (int t = tid; t < 6 * (N - 1); t += NT) {
             const int k = t / 6, i = t - 6 * k;
             if (k < W.k0 || k >= W.k0 + W.nd) M.z[18 * k + 12 + i] = __ldcg(zu + t);
         }
         if (tid == 0) { s_alpha = T(0); s_flag = 0; }
-        merit_reduce<T, NT, true>(P, M.xu, M.z, 0, 9, mcomps, s_merits, nullptr);
+        merit_reduce<T, NT, true>(P, M.xu, M.z, 0, 8, mcomps, 0, s_merits, nullptr);
         if (tid == 0) {
             if (!(s_merits[0] == s_merits[0])) s_flag = 1;
             s_merit_acc = s_merits[0];
-            for (int c = 1; c < 9; ++c)
+            for (int c = 1; c < 8; ++c)
                 if (s_merits[c] <= s_merits[0]) { s_alpha = T(c_alphas[c]); s_merit_acc = s_merits[c]; break; }
         }
         __syncthreads();
+        if (s_alpha == T(0)) {          // identical decision in every CTA of the cluster (same data, same arithmetic)
+            merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, 8, 1, mcomps, 8);
+            cluster.sync();                                                         // barrier 3b (rare)
+            merit_reduce<T, NT, true>(P, M.xu, M.z, 8, 1, mcomps, 8, s_merits, nullptr);
+            if (tid == 0 && s_merits[8] <= s_merits[0]) { s_alpha = T(c_alphas[8]); s_merit_acc = s_merits[8]; }
+            __syncthreads();
+        }
         if (prof && tid == 0) prof[5 * qp + 3] = clock64();
         const T alpha = s_alpha;
         merit_final = s_merit_acc;

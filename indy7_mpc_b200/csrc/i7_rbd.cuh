@@ -759,66 +759,116 @@ I7_DEV void wf_add_qdd(const Robot<T>& rob, const T* S /*36*/, const T* qdd, int
 //             sub-chain cancels against d S_i/dq_j for i > j and is added once, as S_j x* F_j, for i <= j)
 //   d/dqd_j:  dv = S_j,         a0 = v_j x S_j,   B = S_j
 //   out_i = S_i . sum_{l >= max(i,j)} rest_l  (+ S_i . (S_j x* F_j) for i <= j, WRT_Q)
+template <typename T> struct DSeed { T Sj[6], vj[6], B[6], dv[6], a0[6]; };
 template <typename T, bool WRT_Q>
-I7_DEV void wf_dcolumn(const Robot<T>& rob, const T* S, const T* V, const T* A, const T* F_, const T* IW, int j, T* out) {
-    T Sj[6], vj[6], vjS[6], dv[6], a0[6];
+I7_DEV void wf_dseed(const T* S, const T* V, const T* A, int j, DSeed<T>& d) {
+    T vjS[6];
 #pragma unroll
-    for (int r = 0; r < 6; ++r) { Sj[r] = S[6 * j + r]; vj[r] = V[6 * j + r]; }
-    crm6(vj, Sj, vjS);
+    for (int r = 0; r < 6; ++r) { d.Sj[r] = S[6 * j + r]; d.vj[r] = V[6 * j + r]; }
+    crm6(d.vj, d.Sj, vjS);
     if (WRT_Q) {
         T aj[6];
 #pragma unroll
         for (int r = 0; r < 6; ++r) aj[r] = A[6 * j + r];
-        crm6(Sj, vj, dv);
-        crm6(Sj, aj, a0);
+        crm6(d.Sj, d.vj, d.dv);
+        crm6(d.Sj, aj, d.a0);
 #pragma unroll
-        for (int r = 0; r < 6; ++r) { dv[r] = -dv[r]; a0[r] = -a0[r]; }
+        for (int r = 0; r < 6; ++r) { d.dv[r] = -d.dv[r]; d.a0[r] = -d.a0[r]; d.B[r] = vjS[r]; }
     } else {
 #pragma unroll
-        for (int r = 0; r < 6; ++r) { dv[r] = Sj[r]; a0[r] = vjS[r]; }
+        for (int r = 0; r < 6; ++r) { d.dv[r] = d.Sj[r]; d.a0[r] = vjS[r]; d.B[r] = d.Sj[r]; }
     }
+}
+// rest += I_l da_l + dv x* (I_l v_l) + v_l x* (I_l dv)   for one link l >= j
+template <typename T>
+I7_DEV void wf_drest(const Robot<T>& rob, const T* V, const T* IW, int l, const DSeed<T>& d, T* rest) {
+    const T ms = rob.m[l];
+    const T* IWl = IW + 9 * l;
+    T vl[6], W[6], da[6], t[6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r) { vl[r] = V[6 * l + r]; W[r] = vl[r] - d.vj[r]; }
+    crm6(d.B, W, da);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) da[r] += d.a0[r];
+    winertia_mul(IWl, ms, da, t);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) rest[r] += t[r];
+    winertia_mul(IWl, ms, vl, t);
+    crf<T, true>(d.dv, t, rest);
+    winertia_mul(IWl, ms, d.dv, t);
+    crf<T, true>(vl, t, rest);
+}
+template <typename T, bool WRT_Q>
+I7_DEV void wf_dcolumn(const Robot<T>& rob, const T* S, const T* V, const T* A, const T* F_, const T* IW, int j, T* out) {
+    DSeed<T> d;
+    wf_dseed<T, WRT_Q>(S, V, A, j, d);
     T rest[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
     T Fs[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
 #pragma unroll
     for (int l = I7_NJ - 1; l >= 0; --l) {
         if (l >= j) {
-            const T ms = rob.m[l];
-            const T* IWl = IW + 9 * l;
-            T vl[6], W[6], da[6], t[6];
-#pragma unroll
-            for (int r = 0; r < 6; ++r) { vl[r] = V[6 * l + r]; W[r] = vl[r] - vj[r]; }
-            crm6(WRT_Q ? vjS : Sj, W, da);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) da[r] += a0[r];
-            winertia_mul(IWl, ms, da, t);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) rest[r] += t[r];
-            winertia_mul(IWl, ms, vl, t);
-            crf<T, true>(dv, t, rest);
-            winertia_mul(IWl, ms, dv, t);
-            crf<T, true>(vl, t, rest);
+            wf_drest<T>(rob, V, IW, l, d, rest);
             if (WRT_Q) {
 #pragma unroll
                 for (int r = 0; r < 6; ++r) Fs[r] += F_[6 * l + r];
             }
             if (l > j) {
-                T d = T(0);
+                T dd = T(0);
 #pragma unroll
-                for (int r = 0; r < 6; ++r) d += S[6 * l + r] * rest[r];
-                out[l] = d;
+                for (int r = 0; r < 6; ++r) dd += S[6 * l + r] * rest[r];
+                out[l] = dd;
             }
         }
     }
-    if (WRT_Q) crf<T, true>(Sj, Fs, rest);
+    if (WRT_Q) crf<T, true>(d.Sj, Fs, rest);
 #pragma unroll
     for (int i = 0; i < I7_NJ; ++i) {
         if (i <= j) {
-            T d = T(0);
+            T dd = T(0);
 #pragma unroll
-            for (int r = 0; r < 6; ++r) d += S[6 * i + r] * rest[r];
-            out[i] = d;
+            for (int r = 0; r < 6; ++r) dd += S[6 * i + r] * rest[r];
+            out[i] = dd;
         }
     }
+}
+
+// Finer split of the same column (latency form): wf_dpair is the (j, l) term on its own, wf_dgather sums the
+// terms of links >= max(i, j) for output row i (same order of additions as wf_dcolumn: from the tip inwards).
+template <typename T, bool WRT_Q>
+I7_DEV void wf_dpair(const Robot<T>& rob, const T* S, const T* V, const T* A, const T* IW, int j, int l, T* rest6) {
+    DSeed<T> d;
+    wf_dseed<T, WRT_Q>(S, V, A, j, d);
+    T rest[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    wf_drest<T>(rob, V, IW, l, d, rest);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) rest6[r] = rest[r];
+}
+template <typename T, bool WRT_Q>
+I7_DEV T wf_dgather(const T* S, const T* F_, const T* pairs /* [l][6] of this (knot, column) */, int j, int i) {
+    const int i0 = i > j ? i : j;
+    T rest[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+    T Fs[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+    for (int l = I7_NJ - 1; l >= 0; --l) {
+        if (l >= i0) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) rest[r] += pairs[6 * l + r];
+        }
+        if (WRT_Q && l >= j) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) Fs[r] += F_[6 * l + r];
+        }
+    }
+    if (WRT_Q && i <= j) {
+        T Sj[6];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) Sj[r] = S[6 * j + r];
+        crf<T, true>(Sj, Fs, rest);
+    }
+    T dd = T(0);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) dd += S[6 * i + r] * rest[r];
+    return dd;
 }
 
 }  // namespace i7

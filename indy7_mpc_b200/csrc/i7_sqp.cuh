@@ -85,6 +85,7 @@ __host__ __device__ inline Layout make_layout(int N, bool spill) {
 template <typename T>
 struct Ptrs {
     T *xu, *z, *goals, *x0, *cost, *work, *ls, *kr, *aux;
+    T* pair;            // latency form only: 432 numbers per knot for the per-(column, link) derivative terms, or nullptr
     int merit_cap;      // candidates per merit wave that fit the scratch region
 };
 
@@ -226,7 +227,33 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     }
     __syncthreads();
     I7_STAMP();
-    // W5: per (knot, column): 12 analytic inverse-dynamics derivative columns (raw d tau/dq, d tau/dqd into G slots)
+    // W5: 12 analytic inverse-dynamics derivative columns per knot (raw d tau/dq, d tau/dqd into the G slots).
+    if (M.pair) {
+        // latency form: one task per (column, knot, link) term, then one per (column, knot, row) — with few knots per
+        // CTA this fills the lanes that whole-column tasks would leave idle
+        const int slots = (6 * nk + 31) & ~31;
+        for (int t = tid; t < 12 * slots; t += NT) {
+            const int col = t / slots, rem = t - col * slots;
+            const int k = rem / 6, l = rem - 6 * k;
+            const int j = col < 6 ? col : col - 6;
+            if (k >= nk || l < j) continue;
+            const T* kr = M.kr + KR_STRIDE * k;
+            T* pr = M.pair + ((col * nk + k) * 6 + l) * 6;
+            if (col < 6) wf_dpair<T, true>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_I, j, l, pr);
+            else wf_dpair<T, false>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_I, j, l, pr);
+        }
+        __syncthreads();
+        for (int t = tid; t < 12 * slots; t += NT) {
+            const int col = t / slots, rem = t - col * slots;
+            const int k = rem / 6, i = rem - 6 * k;
+            const int j = col < 6 ? col : col - 6;
+            if (k >= nk) continue;
+            T* kr = M.kr + KR_STRIDE * k;
+            const T* pr = M.pair + (col * nk + k) * 36;
+            if (col < 6) kr[KR_GQ + 6 * i + j] = wf_dgather<T, true>(kr + WS_S, kr + WS_F, pr, j, i);
+            else kr[KR_GV + 6 * i + j] = wf_dgather<T, false>(kr + WS_S, kr + WS_F, pr, j, i);
+        }
+    } else {
     for (int t = tid; t < 12 * np; t += NT) {
         const int col = t / np, k = t - col * np;
         if (k >= nk) continue;
@@ -241,6 +268,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
 #pragma unroll
             for (int r = 0; r < 6; ++r) kr[KR_GV + 6 * r + (col - 6)] = out[r];
         }
+    }
     }
     __syncthreads();
     I7_STAMP();
@@ -686,12 +714,12 @@ template <typename T> I7_DEV T warp_sum_strided(const T* vals, int n, int lane) 
 }
 
 // Merit terms of the candidates c0 .. c0+nc-1 (index into c_alphas; 0 = base) of the line  xa + alpha (xb - xa) at the
-// knots of the window W:  comps[4 * (ci * N + k) + {0,1,2,3}] = {qcost, vcost, ucost, integrator_err} of knot k
+// knots of the window W:  comps[4 * ((cbase + ci) * N + k) + {0,1,2,3}] = {qcost, vcost, ucost, integrator_err} of knot k
 // (k = horizon index; src/osqp_sqp.py:13-47).  Forward dynamics per point: M columns + bias by 7 parallel tasks,
 // then one 6x6 LDL' solve.  scr: MP_STRIDE numbers of scratch per point.
 template <typename T, int NT>
 __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const Win W, T* scr,
-                             const T* xa_, const T* xb_, const T* fext, int c0, int nc, T* comps) {
+                             const T* xa_, const T* xb_, const T* fext, int c0, int nc, T* comps, int cbase) {
     const int tid = threadIdx.x, N = P.N, nk = W.nd, nw = W.nc;
     const int npts = nc * nw;
     const T* xa = xa_ + 18 * W.k0;
@@ -707,11 +735,16 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
         scr[MP_STRIDE * p + MP_CS + i] = cs; scr[MP_STRIDE * p + MP_CS + 6 + i] = sn;
     }
     __syncthreads();
-    // M1: mass-matrix columns and bias torques at every point with dynamics
-    for (int t = tid; t < 7 * nc * nk; t += NT) {
-        const int type = t / (nc * nk), rem = t - type * nc * nk;
-        const int ci = rem / nk, k = rem - ci * nk;
-        const int p = ci * nw + k;
+    // M1: eight task types per point, laid out type-major with the points padded to whole warps so that the lanes
+    //     of a warp run the same code: 0..5 mass-matrix column, 6 bias torques (points with dynamics), 7 FK + the
+    //     cost terms of the point (all points)
+    const int npd = (npts + 31) & ~31;
+    for (int t = tid; t < 8 * npd; t += NT) {
+        const int type = t / npd, p = t - type * npd;
+        if (p >= npts) continue;
+        const int ci = p / nw, k = p - ci * nw;
+        if (type < 7 && k >= nk) continue;
+        const T alpha = T(c_alphas[c0 + ci]);
         T* sp = scr + MP_STRIDE * p;
         T cs[12], out[6];
 #pragma unroll
@@ -720,64 +753,64 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
             crba_column<T>(rob, cs, type, out);
 #pragma unroll
             for (int r = 0; r < 6; ++r) sp[MP_M + 6 * r + type] = out[r];
-        } else {
-            const T alpha = T(c_alphas[c0 + ci]);
+        } else if (type == 6) {
             T qd[6];
 #pragma unroll
             for (int i = 0; i < 6; ++i) qd[i] = xa[18 * k + 6 + i] + alpha * (xb[18 * k + 6 + i] - xa[18 * k + 6 + i]);
             rnea_bias<T>(rob, cs, qd, fext, out);
 #pragma unroll
             for (int r = 0; r < 6; ++r) sp[MP_B + r] = out[r];
+        } else {
+            const int kg = W.k0 + k;
+            T pee[3];
+            fk_ee_only<T>(rob, cs, pee);
+            const T* goal = M.goals + 3 * kg;
+            const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
+            const T Qk = (kg == N - 1) ? P.QN : T(1);
+            T* o = comps + 4 * ((cbase + ci) * N + kg);
+            o[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+            T vv = T(0), uu = T(0);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const T xv = xa[18 * k + 6 + i] + alpha * (xb[18 * k + 6 + i] - xa[18 * k + 6 + i]);
+                const T xc = (k < nk) ? xa[18 * k + 12 + i] + alpha * (xb[18 * k + 12 + i] - xa[18 * k + 12 + i]) : T(0);
+                vv += xv * xv; uu += xc * xc;
+            }
+            o[1] = P.dQ * vv;
+            o[2] = P.R * uu;
+            if (k >= nk) o[3] = T(0);
         }
     }
     __syncthreads();
-    // M2: per point: FK cost, quadratic costs, qdd = M^-1 (u - b), integrator error
+    // M2: per point with dynamics: qdd = M^-1 (u - b), integrator error
     for (int p = tid; p < npts; p += NT) {
         const int ci = p / nw, k = p - ci * nw;
+        if (k >= nk) continue;
         const int kg = W.k0 + k;
         const T alpha = T(c_alphas[c0 + ci]);
         const T* sp = scr + MP_STRIDE * p;
         T x[18];
-        const int nloc = (k < nk) ? 18 : 12;
 #pragma unroll
-        for (int i = 0; i < 18; ++i) x[i] = (i < nloc) ? xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]) : T(0);
-        T cs[12], pee[3];
+        for (int i = 0; i < 18; ++i) x[i] = xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]);
+        T A[6][6], dinv[6], b[6];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) cs[i] = sp[MP_CS + i];
-        fk_ee_only<T>(rob, cs, pee);
-        const T* goal = M.goals + 3 * kg;
-        const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
-        const T Qk = (kg == N - 1) ? P.QN : T(1);
-        T* out = comps + 4 * (ci * N + kg);
-        out[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
-        T vv = T(0), uu = T(0);
+        for (int r = 0; r < 6; ++r)
 #pragma unroll
-        for (int i = 0; i < 6; ++i) { vv += x[6 + i] * x[6 + i]; uu += x[12 + i] * x[12 + i]; }
-        out[1] = P.dQ * vv;
-        out[2] = P.R * uu;
-        T ie = T(0);
-        if (k < nk) {
-            T A[6][6], dinv[6], b[6];
+            for (int q = 0; q <= r; ++q) A[r][q] = sp[MP_M + 6 * r + q];
 #pragma unroll
-            for (int r = 0; r < 6; ++r)
+        for (int r = 0; r < 6; ++r) b[r] = x[12 + r] - sp[MP_B + r];
+        spd6_factor<T>(A, dinv);
+        spd6_solve_factored<T>(A, dinv, b);
+        T qe = T(0), ve = T(0);
 #pragma unroll
-                for (int q = 0; q <= r; ++q) A[r][q] = sp[MP_M + 6 * r + q];
-#pragma unroll
-            for (int r = 0; r < 6; ++r) b[r] = x[12 + r] - sp[MP_B + r];
-            spd6_factor<T>(A, dinv);
-            spd6_solve_factored<T>(A, dinv, b);
-            T qe = T(0), ve = T(0);
-#pragma unroll
-            for (int i = 0; i < 6; ++i) {
-                const T xnq = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
-                const T xnv = xa[18 * (k + 1) + 6 + i] + alpha * (xb[18 * (k + 1) + 6 + i] - xa[18 * (k + 1) + 6 + i]);
-                const T dq = x[i] + x[6 + i] * P.dt - xnq;
-                const T dv = x[6 + i] + b[i] * P.dt - xnv;
-                qe += dq * dq; ve += dv * dv;
-            }
-            ie = sqrt_t<T>(qe) + sqrt_t<T>(ve);
+        for (int i = 0; i < 6; ++i) {
+            const T xnq = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
+            const T xnv = xa[18 * (k + 1) + 6 + i] + alpha * (xb[18 * (k + 1) + 6 + i] - xa[18 * (k + 1) + 6 + i]);
+            const T dq = x[i] + x[6 + i] * P.dt - xnq;
+            const T dv = x[6 + i] + b[i] * P.dt - xnv;
+            qe += dq * dq; ve += dv * dv;
         }
-        out[3] = ie;
+        comps[4 * ((cbase + ci) * N + kg) + 3] = sqrt_t<T>(qe) + sqrt_t<T>(ve);
     }
     __syncthreads();
 }
@@ -785,8 +818,8 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
 // merits[c] for c in [c0, c0 + nc): sum over all N knots (fixed order) + initial-state violation term.
 // CG: comps live in the global exchange buffer written by other CTAs of the cluster (read with ld.global.cg).
 template <typename T, int NT, bool CG>
-__device__ void merit_reduce(const SolveParams<T>& P, const T* xa, const T* xb, int c0, int nc, const T* comps, T* merits,
-                             T* comps_out /* 4 sums of candidate c0 or nullptr */) {
+__device__ void merit_reduce(const SolveParams<T>& P, const T* xa, const T* xb, int c0, int nc, const T* comps, int cbase,
+                             T* merits, T* comps_out /* 4 sums of candidate c0 or nullptr */) {
     const int tid = threadIdx.x, N = P.N;
     const int warp = tid >> 5, lane = tid & 31;
     for (int ci = warp; ci < nc; ci += NT / 32) {
@@ -794,7 +827,7 @@ __device__ void merit_reduce(const SolveParams<T>& P, const T* xa, const T* xb, 
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             T a = T(0);
-            for (int k = lane; k < N; k += 32) a += CG ? __ldcg(comps + 4 * (ci * N + k) + j) : comps[4 * (ci * N + k) + j];
+            for (int k = lane; k < N; k += 32) a += CG ? __ldcg(comps + 4 * ((cbase + ci) * N + k) + j) : comps[4 * ((cbase + ci) * N + k) + j];
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
             s[j] = a;
@@ -895,7 +928,7 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
     M.work = sm + L.work; M.ls = sm + L.ls;
     T* const krg = SPILL ? P.spill_ws + (size_t)blockIdx.x * L.reg_size : nullptr;
     M.kr = SPILL ? krg : sm + L.reg;
-    M.aux = M.z;
+    M.aux = M.z; M.pair = nullptr;
     {
         int cap = L.reg_size / (MP_STRIDE * N);
         M.merit_cap = cap > 5 ? 5 : (cap < 1 ? 1 : cap);
@@ -927,8 +960,8 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
         if (P.mode == MODE_MERIT) {
             // merit terms of xu; the initial-state term is taken against the reference iterate z
             T* comps = M.ls;
-            merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.xu, fext, 0, 1, comps);
-            merit_reduce<T, NT, false>(P, M.xu, M.xu, 0, 1, comps, s_merits, M.work);
+            merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.xu, fext, 0, 1, comps, 0);
+            merit_reduce<T, NT, false>(P, M.xu, M.xu, 0, 1, comps, 0, s_merits, M.work);
             if (tid == 0) {
                 T d2 = T(0);
                 for (int i = 0; i < 12; ++i) { const T d = M.xu[i] - M.z[i]; d2 += d * d; }
@@ -973,8 +1006,8 @@ __global__ void __launch_bounds__(NT) sqp_kernel(const __grid_constant__ Robot<T
                 if (tid == 0) { s_alpha = T(0); s_flag = 0; }
                 while (c0 < 9) {
                     int nc = 9 - c0 < M.merit_cap ? 9 - c0 : M.merit_cap;
-                    merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, nc, M.ls);
-                    merit_reduce<T, NT, false>(P, M.xu, M.z, c0, nc, M.ls, s_merits, nullptr);
+                    merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, nc, M.ls, 0);
+                    merit_reduce<T, NT, false>(P, M.xu, M.z, c0, nc, M.ls, 0, s_merits, nullptr);
                     if (tid == 0 && s_alpha == T(0)) {
                         if (!(s_merits[0] == s_merits[0])) s_flag = 1;
                         for (int c = (c0 == 0 ? 1 : c0); c < c0 + nc; ++c)
