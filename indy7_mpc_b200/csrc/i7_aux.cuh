@@ -1,7 +1,7 @@
 // i7_aux.cuh — sample-level kernels (one thread per sample) next to the fused solve: forward dynamics and its
 // derivatives, end-effector position / Jacobian, the rk4 plant step, best-trajectory selection, FMA-peak probe.
 #pragma once
-#include "i7_rbd.cuh"
+#include "i7_wf.cuh"
 
 namespace i7 {
 
@@ -21,14 +21,13 @@ __global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, con
     }
     const T* fext = fext_pin ? fx : nullptr;
     // the same building blocks as the fused kernel (world-frame link records, mass columns, LDL', dID columns)
-    T S[36], V[36], Aa[36], F[36], IW[54];
-    for (int l = 0; l < 6; ++l) wf_link<T>(rob, cs, qd, fext, l, S + 6 * l, V + 6 * l, Aa + 6 * l, IW + 9 * l, F + 6 * l);
+    T S[36], V[36], Aa[36], F[36], IW[54], pee[3], Mm[36];
+    wf_tip<T>(rob, cs, pee);
+    for (int l = 0; l < 6; ++l) wf_link<T>(rob, cs, qd, fext, pee, l, S + 6 * l, V + 6 * l, Aa + 6 * l, IW + 9 * l, F + 6 * l);
     T A[6][6], dinv[6], bias[6], qdd[6], Mi[36];
-    for (int j = 0; j < 6; ++j) {
-        T col[6];
-        wf_mass_column<T>(rob, S, IW, F, j, col, &bias[j]);
-        for (int r = 0; r <= j; ++r) { A[r][j] = col[r]; A[j][r] = col[r]; }
-    }
+    for (int j = 0; j < 6; ++j) wf_mass_column<T>(rob, S, IW, F, j, Mm, &bias[j]);
+    for (int r = 0; r < 6; ++r)
+        for (int c = 0; c <= r; ++c) A[r][c] = Mm[6 * r + c];
     spd6_factor<T>(A, dinv);
     for (int r = 0; r < 6; ++r) qdd[r] = u[r] - bias[r];
     spd6_solve_factored<T>(A, dinv, qdd);
@@ -43,8 +42,8 @@ __global__ void dynamics_kernel(const __grid_constant__ Robot<T> rob, int n, con
     for (int l = 0; l < 6; ++l) wf_add_qdd<T>(rob, S, qdd, l, IW + 9 * l, Aa + 6 * l, F + 6 * l);
     for (int j = 0; j < 6; ++j) {
         T cq[6], cv[6];
-        wf_dcolumn<T, true>(rob, S, V, Aa, F, IW, j, cq);
-        wf_dcolumn<T, false>(rob, S, V, Aa, F, IW, j, cv);
+        wf_dcolumn<T, true>(rob, S, V, Aa, F, IW, j, cq, 1);
+        wf_dcolumn<T, false>(rob, S, V, Aa, F, IW, j, cv, 1);
         for (int r = 0; r < 6; ++r) {
             T aq = T(0), av = T(0);
             for (int s = 0; s < 6; ++s) { aq -= Mi[6 * r + s] * cq[s]; av -= Mi[6 * r + s] * cv[s]; }

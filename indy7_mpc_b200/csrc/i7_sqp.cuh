@@ -15,7 +15,7 @@
 //   merit     line-search candidates x knots in parallel, evaluated lazily in two waves  (src/osqp_sqp.py:13-74)
 //   update    first-accept alpha selection, XU += alpha (z - XU), statistics              (src/osqp_sqp.py:80-92)
 #pragma once
-#include "i7_rbd.cuh"
+#include "i7_wf.cuh"
 
 namespace i7 {
 
@@ -58,7 +58,7 @@ constexpr int KR_HX = 306;    // 12  gx + G'd
 constexpr int KR_STRIDE = 319;
 constexpr int COST_STRIDE = 9;                       // j[6], Q, dQ, R
 // merit scratch per evaluated point (aliases the knot records, dead after the QP solve)
-constexpr int MP_CS = 0, MP_M = 12, MP_B = 48, MP_STRIDE = 55;
+constexpr int MP_CS = 0, MP_X = 12, MP_S = 30, MP_I = 66, MP_F = 120, MP_STRIDE = 157;
 // Riccati work area (first in the layouts: 16-byte aligned)
 constexpr int WK_SIZE = 296;   // two sweep-state blocks (SB_*), see riccati_sweep
 
@@ -108,6 +108,7 @@ static __device__ __constant__ unsigned char c_tri_c[78] = {
 // (knot, link) / (knot, column) tasks with a dependency depth of a few dozen FMAs.
 // Scratch of a knot while its record is being built (dead before S / SG / d / L / hx are written):
 constexpr int WS_CS = KR_GQ;    // 12  cos / sin of q                 (raw dID columns land in GQ / GV afterwards)
+constexpr int WS_PEE = KR_GQ + 12;  // 3  position of the last joint = spatial origin of the knot
 constexpr int WS_S = 114;       // 36  world joint axes S_l
 constexpr int WS_V = 150;       // 36  link velocities v_l
 constexpr int WS_A = 186;       // 36  link accelerations a_l
@@ -137,57 +138,59 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
         kr[WS_CS + i] = c; kr[WS_CS + 6 + i] = s;
     }
     __syncthreads();
-    I7_STAMP();
-    // W1: per (knot, link): world axis, velocity, acceleration at qdd = 0, world inertia, force;  per cost knot: FK,
-    //     j = J'e and the scaled weights
-    for (int t = tid; t < 6 * np + nc; t += NT) {
-        const bool dyn = t < 6 * np;
-        const int l = dyn ? t / np : 0;
-        const int k = dyn ? t - l * np : t - 6 * np;
-        if (dyn && k >= nk) continue;
+    // W0b: per knot: position of the last joint (the spatial origin of the knot, and eepos of the cost)
+    for (int k = tid; k < nc; k += NT) {
         T* kr = M.kr + KR_STRIDE * k;
-        T cs[12];
-#pragma unroll
-        for (int i = 0; i < 12; ++i) cs[i] = kr[WS_CS + i];
-        if (dyn) {
-            T qd[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) qd[i] = xu[18 * k + 6 + i];
-            wf_link<T>(rob, cs, qd, fext, l, kr + WS_S + 6 * l, kr + WS_V + 6 * l, kr + WS_A + 6 * l, kr + WS_I + 9 * l,
-                       kr + WS_F + 6 * l);
+        T pee[3];
+        wf_tip<T>(rob, kr + WS_CS, pee);
+        kr[WS_PEE] = pee[0]; kr[WS_PEE + 1] = pee[1]; kr[WS_PEE + 2] = pee[2];
+    }
+    __syncthreads();
+    I7_STAMP();
+    // W1: per (knot, link): world axis, velocity, acceleration at qdd = 0, world inertia, force
+    for (int t = tid; t < 6 * np; t += NT) {
+        const int l = t / np, k = t - l * np;
+        if (k >= nk) continue;
+        T* kr = M.kr + KR_STRIDE * k;
+        wf_link<T>(rob, kr + WS_CS, xu + 18 * k + 6, fext, kr + WS_PEE, l, kr + WS_S + 6 * l, kr + WS_V + 6 * l,
+                   kr + WS_A + 6 * l, kr + WS_I + 9 * l, kr + WS_F + 6 * l);
+    }
+    // the last knot of the horizon has a cost but no dynamics: only its joint axes are needed (for J'e below)
+    if (W.k0 + nc == N) {
+        for (int l = tid; l < 6; l += NT) {
+            T* kr = M.kr + KR_STRIDE * (nc - 1);
+            T dummy_v[6], dummy_a[6], dummy_I[9], dummy_f[6];
+            wf_link<T>(rob, kr + WS_CS, xu + 18 * (nc - 1) + 6, nullptr, kr + WS_PEE, l, kr + WS_S + 6 * l, dummy_v, dummy_a,
+                       dummy_I, dummy_f);
+        }
+    }
+    __syncthreads();
+    I7_STAMP();
+    // W2: per (knot, j): column j of M (rows <= j, mirrored) and the bias torque b_j (parked in the cv slot);
+    //     per cost knot: j = J'e (column i of the translational Jacobian is the linear part of S_i) and the weights
+    for (int t = tid; t < 6 * np + nc; t += NT) {
+        if (t < 6 * np) {
+            const int j = t / np, k = t - j * np;
+            if (k >= nk) continue;
+            T* kr = M.kr + KR_STRIDE * k;
+            T bj;
+            wf_mass_column<T>(rob, kr + WS_S, kr + WS_I, kr + WS_F, j, kr + KR_Y, &bj);
+            kr[KR_CV + j] = bj;
         } else {
-            T pee[3], zs[18], ps[18];
-            fk_ee<T>(rob, cs, pee, zs, ps);
+            const int k = t - 6 * np;
+            const T* kr = M.kr + KR_STRIDE * k;
             const T* gk = goals + 3 * k;
-            const T e[3] = {pee[0] - gk[0], pee[1] - gk[1], pee[2] - gk[2]};
+            const T e[3] = {kr[WS_PEE] - gk[0], kr[WS_PEE + 1] - gk[1], kr[WS_PEE + 2] - gk[2]};
             T* ck = M.cost + COST_STRIDE * k;
 #pragma unroll
-            for (int i = 0; i < 6; ++i) {
-                const T d[3] = {pee[0] - ps[3 * i], pee[1] - ps[3 * i + 1], pee[2] - ps[3 * i + 2]};
-                T c[3];
-                cross3(zs + 3 * i, d, c);
-                ck[i] = e[0] * c[0] + e[1] * c[1] + e[2] * c[2];
-            }
+            for (int i = 0; i < 6; ++i)
+                ck[i] = e[0] * kr[WS_S + 6 * i + 3] + e[1] * kr[WS_S + 6 * i + 4] + e[2] * kr[WS_S + 6 * i + 5];
             const T nrm = sqrt_t<T>(e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
             const T sc = P.regularize ? T(1) / (nrm + P.eps) : T(1);
             ck[6] = (W.k0 + k == N - 1) ? P.QN : T(1);
             ck[7] = P.dQ * sc;
             ck[8] = P.R * sc;
         }
-    }
-    __syncthreads();
-    I7_STAMP();
-    // W2: per (knot, j): column j of M (rows <= j, mirrored) and the bias torque b_j (parked in the cv slot)
-    for (int t = tid; t < 6 * np; t += NT) {
-        const int j = t / np, k = t - j * np;
-        if (k >= nk) continue;
-        T* kr = M.kr + KR_STRIDE * k;
-        T col[6], bj;
-        wf_mass_column<T>(rob, kr + WS_S, kr + WS_I, kr + WS_F, j, col, &bj);
-#pragma unroll
-        for (int i = 0; i < 6; ++i)
-            if (i <= j) { kr[KR_Y + 6 * i + j] = col[i]; kr[KR_Y + 6 * j + i] = col[i]; }
-        kr[KR_CV + j] = bj;
     }
     __syncthreads();
     I7_STAMP();
@@ -220,10 +223,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
         const int l = t / np, k = t - l * np;
         if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
-        T qdd[6];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) qdd[i] = kr[KR_CV + i];
-        wf_add_qdd<T>(rob, kr + WS_S, qdd, l, kr + WS_I + 9 * l, kr + WS_A + 6 * l, kr + WS_F + 6 * l);
+        wf_add_qdd<T>(rob, kr + WS_S, kr + KR_CV, l, kr + WS_I + 9 * l, kr + WS_A + 6 * l, kr + WS_F + 6 * l);
     }
     __syncthreads();
     I7_STAMP();
@@ -258,16 +258,10 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
         const int col = t / np, k = t - col * np;
         if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
-        T out[6];
-        if (col < 6) {
-            wf_dcolumn<T, true>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_F, kr + WS_I, col, out);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) kr[KR_GQ + 6 * r + col] = out[r];
-        } else {
-            wf_dcolumn<T, false>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_F, kr + WS_I, col - 6, out);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) kr[KR_GV + 6 * r + (col - 6)] = out[r];
-        }
+        // the raw columns land in the GQ / GV slots, which hold cos / sin and the origin until here: every column
+        // task of a knot has read what it needs from the link records, not from those slots
+        if (col < 6) wf_dcolumn<T, true>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_F, kr + WS_I, col, kr + KR_GQ + col, 6);
+        else wf_dcolumn<T, false>(rob, kr + WS_S, kr + WS_V, kr + WS_A, kr + WS_F, kr + WS_I, col - 6, kr + KR_GV + (col - 6), 6);
     }
     }
     __syncthreads();
@@ -715,8 +709,8 @@ template <typename T> I7_DEV T warp_sum_strided(const T* vals, int n, int lane) 
 
 // Merit terms of the candidates c0 .. c0+nc-1 (index into c_alphas; 0 = base) of the line  xa + alpha (xb - xa) at the
 // knots of the window W:  comps[4 * ((cbase + ci) * N + k) + {0,1,2,3}] = {qcost, vcost, ucost, integrator_err} of knot k
-// (k = horizon index; src/osqp_sqp.py:13-47).  Forward dynamics per point: M columns + bias by 7 parallel tasks,
-// then one 6x6 LDL' solve.  scr: MP_STRIDE numbers of scratch per point.
+// (k = horizon index; src/osqp_sqp.py:13-47).  One thread per point: kinematic chain, link records (world frame),
+// M and b from composite inertias, one 6x6 LDL' solve.  scr: MP_STRIDE numbers of scratch per point.
 template <typename T, int NT>
 __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const Win W, T* scr,
                              const T* xa_, const T* xb_, const T* fext, int c0, int nc, T* comps, int cbase) {
@@ -724,93 +718,59 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
     const int npts = nc * nw;
     const T* xa = xa_ + 18 * W.k0;
     const T* xb = xb_ + 18 * W.k0;
-    // M0: cos / sin
-    for (int t = tid; t < 6 * npts; t += NT) {
+    // M0: the point itself (18 numbers) and cos / sin of its joint angles
+    for (int t = tid; t < 18 * npts; t += NT) {
         const int i = t / npts, p = t - i * npts;
         const int ci = p / nw, k = p - ci * nw;
         const T alpha = T(c_alphas[c0 + ci]);
-        const T q = xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]);
-        T sn, cs;
-        sincos_t<T>(q, &sn, &cs);
-        scr[MP_STRIDE * p + MP_CS + i] = cs; scr[MP_STRIDE * p + MP_CS + 6 + i] = sn;
-    }
-    __syncthreads();
-    // M1: eight task types per point, laid out type-major with the points padded to whole warps so that the lanes
-    //     of a warp run the same code: 0..5 mass-matrix column, 6 bias torques (points with dynamics), 7 FK + the
-    //     cost terms of the point (all points)
-    const int npd = (npts + 31) & ~31;
-    for (int t = tid; t < 8 * npd; t += NT) {
-        const int type = t / npd, p = t - type * npd;
-        if (p >= npts) continue;
-        const int ci = p / nw, k = p - ci * nw;
-        if (type < 7 && k >= nk) continue;
-        const T alpha = T(c_alphas[c0 + ci]);
+        const bool has = (i < 12) || (k < nk) || (W.k0 + k < N - 1);     // u of the padded last knot is not part of XU
+        const T x = has ? xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]) : T(0);
         T* sp = scr + MP_STRIDE * p;
-        T cs[12], out[6];
-#pragma unroll
-        for (int i = 0; i < 12; ++i) cs[i] = sp[MP_CS + i];
-        if (type < 6) {
-            crba_column<T>(rob, cs, type, out);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) sp[MP_M + 6 * r + type] = out[r];
-        } else if (type == 6) {
-            T qd[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) qd[i] = xa[18 * k + 6 + i] + alpha * (xb[18 * k + 6 + i] - xa[18 * k + 6 + i]);
-            rnea_bias<T>(rob, cs, qd, fext, out);
-#pragma unroll
-            for (int r = 0; r < 6; ++r) sp[MP_B + r] = out[r];
-        } else {
-            const int kg = W.k0 + k;
-            T pee[3];
-            fk_ee_only<T>(rob, cs, pee);
-            const T* goal = M.goals + 3 * kg;
-            const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
-            const T Qk = (kg == N - 1) ? P.QN : T(1);
-            T* o = comps + 4 * ((cbase + ci) * N + kg);
-            o[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
-            T vv = T(0), uu = T(0);
-#pragma unroll
-            for (int i = 0; i < 6; ++i) {
-                const T xv = xa[18 * k + 6 + i] + alpha * (xb[18 * k + 6 + i] - xa[18 * k + 6 + i]);
-                const T xc = (k < nk) ? xa[18 * k + 12 + i] + alpha * (xb[18 * k + 12 + i] - xa[18 * k + 12 + i]) : T(0);
-                vv += xv * xv; uu += xc * xc;
-            }
-            o[1] = P.dQ * vv;
-            o[2] = P.R * uu;
-            if (k >= nk) o[3] = T(0);
+        sp[MP_X + i] = x;
+        if (i < 6) {
+            T sn, cs;
+            sincos_t<T>(x, &sn, &cs);
+            sp[MP_CS + i] = cs; sp[MP_CS + 6 + i] = sn;
         }
     }
     __syncthreads();
-    // M2: per point with dynamics: qdd = M^-1 (u - b), integrator error
+    // M1: per point
     for (int p = tid; p < npts; p += NT) {
         const int ci = p / nw, k = p - ci * nw;
-        if (k >= nk) continue;
         const int kg = W.k0 + k;
         const T alpha = T(c_alphas[c0 + ci]);
-        const T* sp = scr + MP_STRIDE * p;
-        T x[18];
+        T* sp = scr + MP_STRIDE * p;
+        T pee[3];
+        wf_tip<T>(rob, sp + MP_CS, pee);
+        const T* goal = M.goals + 3 * kg;
+        const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
+        const T Qk = (kg == N - 1) ? P.QN : T(1);
+        T* out = comps + 4 * ((cbase + ci) * N + kg);
+        out[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+        T vv = T(0), uu = T(0);
 #pragma unroll
-        for (int i = 0; i < 18; ++i) x[i] = xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]);
-        T A[6][6], dinv[6], b[6];
+        for (int i = 0; i < 6; ++i) { vv += sp[MP_X + 6 + i] * sp[MP_X + 6 + i]; uu += sp[MP_X + 12 + i] * sp[MP_X + 12 + i]; }
+        out[1] = P.dQ * vv;
+        out[2] = P.R * uu;
+        T ie = T(0);
+        if (k < nk) {
+            wf_links_all<T>(rob, sp + MP_CS, sp + MP_X + 6, fext, pee, sp + MP_S, sp + MP_I, sp + MP_F);
+            T u[6], qdd[6];
 #pragma unroll
-        for (int r = 0; r < 6; ++r)
+            for (int i = 0; i < 6; ++i) u[i] = sp[MP_X + 12 + i];
+            wf_forward_dynamics<T>(rob, sp + MP_S, sp + MP_I, sp + MP_F, u, qdd);
+            T qe = T(0), ve = T(0);
 #pragma unroll
-            for (int q = 0; q <= r; ++q) A[r][q] = sp[MP_M + 6 * r + q];
-#pragma unroll
-        for (int r = 0; r < 6; ++r) b[r] = x[12 + r] - sp[MP_B + r];
-        spd6_factor<T>(A, dinv);
-        spd6_solve_factored<T>(A, dinv, b);
-        T qe = T(0), ve = T(0);
-#pragma unroll
-        for (int i = 0; i < 6; ++i) {
-            const T xnq = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
-            const T xnv = xa[18 * (k + 1) + 6 + i] + alpha * (xb[18 * (k + 1) + 6 + i] - xa[18 * (k + 1) + 6 + i]);
-            const T dq = x[i] + x[6 + i] * P.dt - xnq;
-            const T dv = x[6 + i] + b[i] * P.dt - xnv;
-            qe += dq * dq; ve += dv * dv;
+            for (int i = 0; i < 6; ++i) {
+                const T xnq = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
+                const T xnv = xa[18 * (k + 1) + 6 + i] + alpha * (xb[18 * (k + 1) + 6 + i] - xa[18 * (k + 1) + 6 + i]);
+                const T dq = sp[MP_X + i] + sp[MP_X + 6 + i] * P.dt - xnq;
+                const T dv = sp[MP_X + 6 + i] + qdd[i] * P.dt - xnv;
+                qe += dq * dq; ve += dv * dv;
+            }
+            ie = sqrt_t<T>(qe) + sqrt_t<T>(ve);
         }
-        comps[4 * ((cbase + ci) * N + kg) + 3] = sqrt_t<T>(qe) + sqrt_t<T>(ve);
+        out[3] = ie;
     }
     __syncthreads();
 }
