@@ -83,11 +83,15 @@ class Indy7SQP:
             goals = goals.contiguous()
         out, st = self.engine.solve(xu, x0a, goals)
         self._warm = out
+        # views into the solver's [x0 u0 x1 u1 ... x_{N-1}] layout (no copy)
         if tens:
-            pad = torch.cat([out, out.new_zeros(B, 6)], dim=1).reshape(B, self.N, 18)
+            x_traj = torch.as_strided(out, (B, self.N, 12), (self.nz, 18, 1))
+            u_traj = torch.as_strided(out, (B, self.N - 1, 6), (self.nz, 18, 1), 12)
         else:
-            pad = np.concatenate([out, np.zeros((B, 6), out.dtype)], axis=1).reshape(B, self.N, 18)
-        x_traj, u_traj = pad[:, :, :12], pad[:, :-1, 12:]
+            es = out.itemsize
+            x_traj = np.lib.stride_tricks.as_strided(out, (B, self.N, 12), (self.nz * es, 18 * es, es), writeable=False)
+            u_traj = np.lib.stride_tricks.as_strided(out[:, 12:], (B, self.N - 1, 6), (self.nz * es, 18 * es, es),
+                                                     writeable=False)
         stn = st.cpu().numpy() if _is_torch(st) else st
         stats = {
             'qp_iters': stn[:, 0].astype(int), 'n_linesearch': stn[:, 1].astype(int), 'n_steps': stn[:, 2].astype(int),

@@ -75,12 +75,16 @@ void fill_robot(const i7_model& m, i7::Robot<T>& r) {
     for (int a = 0; a < 3; ++a) r.g[a] = T(m.gravity[a]);
 }
 
-bool is_device_ptr(const void* p) {
-    if (!p) return false;
+// 0 = pageable host memory, 1 = device / managed memory, 2 = page-locked (pinned / registered) host memory
+int ptr_kind(const void* p) {
+    if (!p) return 0;
     cudaPointerAttributes at;
-    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
-    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) return 1;
+    if (at.type == cudaMemoryTypeHost) return 2;
+    return 0;
 }
+bool is_device_ptr(const void* p) { return ptr_kind(p) == 1; }
 
 i7_status arena_reserve(i7_handle* h, Arena& a, size_t bytes) {
     if (bytes <= a.bytes) return I7_OK;
@@ -93,40 +97,51 @@ i7_status arena_reserve(i7_handle* h, Arena& a, size_t bytes) {
     return I7_OK;
 }
 
-// One staged input: either the caller's device pointer, or a slice of the input arena filled from host memory.
+// Staging of the buffers of one call.  Device pointers are used as they are.  Page-locked host buffers are copied
+// straight to / from their slice of the device arena with cudaMemcpyAsync (no intermediate copy).  Pageable host
+// buffers go through the pinned mirror of the arena (one memcpy + one bulk transfer per direction).
 struct Stage {
     size_t in_off = 0, out_off = 0;
     i7_handle* h;
     explicit Stage(i7_handle* h_) : h(h_) {}
-    // returns the device pointer to use; host data is packed into the pinned arena (copied to the device by flush_in)
+    struct Xfer { void* user; size_t off; size_t bytes; bool pinned; };
+    Xfer ins[8], outs[10];
+    int nin = 0, nout = 0;
     const void* in(const void* p, size_t bytes) {
         if (!p) return nullptr;
-        if (is_device_ptr(p)) return p;
-        std::memcpy((char*)h->in.host + in_off, p, bytes);
+        const int kind = ptr_kind(p);
+        if (kind == 1) return p;
+        if (kind == 0) std::memcpy((char*)h->in.host + in_off, p, bytes);
+        ins[nin++] = Xfer{const_cast<void*>(p), in_off, bytes, kind == 2};
         const void* d = (char*)h->in.dev + in_off;
         in_off += (bytes + 15) & ~size_t(15);
         return d;
     }
-    struct Out { void* user; size_t off; size_t bytes; };
-    Out outs[8];
-    int nout = 0;
     void* out(void* p, size_t bytes) {
         if (!p) return nullptr;
-        if (is_device_ptr(p)) return p;
-        outs[nout++] = Out{p, out_off, bytes};
+        const int kind = ptr_kind(p);
+        if (kind == 1) return p;
+        outs[nout++] = Xfer{p, out_off, bytes, kind == 2};
         void* d = (char*)h->out.dev + out_off;
         out_off += (bytes + 15) & ~size_t(15);
         return d;
     }
     i7_status flush_in(cudaStream_t s) {
-        if (in_off) I7_CUDA(h, cudaMemcpyAsync(h->in.dev, h->in.host, in_off, cudaMemcpyHostToDevice, s));
+        for (int i = 0; i < nin; ++i) {
+            const void* src = ins[i].pinned ? ins[i].user : (const void*)((char*)h->in.host + ins[i].off);
+            I7_CUDA(h, cudaMemcpyAsync((char*)h->in.dev + ins[i].off, src, ins[i].bytes, cudaMemcpyHostToDevice, s));
+        }
         return I7_OK;
     }
     i7_status flush_out(cudaStream_t s) {
         if (!nout) return I7_OK;
-        I7_CUDA(h, cudaMemcpyAsync(h->out.host, h->out.dev, out_off, cudaMemcpyDeviceToHost, s));
+        for (int i = 0; i < nout; ++i) {
+            void* dst = outs[i].pinned ? outs[i].user : (void*)((char*)h->out.host + outs[i].off);
+            I7_CUDA(h, cudaMemcpyAsync(dst, (char*)h->out.dev + outs[i].off, outs[i].bytes, cudaMemcpyDeviceToHost, s));
+        }
         I7_CUDA(h, cudaStreamSynchronize(s));
-        for (int i = 0; i < nout; ++i) std::memcpy(outs[i].user, (char*)h->out.host + outs[i].off, outs[i].bytes);
+        for (int i = 0; i < nout; ++i)
+            if (!outs[i].pinned) std::memcpy(outs[i].user, (char*)h->out.host + outs[i].off, outs[i].bytes);
         return I7_OK;
     }
 };

@@ -25,6 +25,7 @@ class Engine:
     def __init__(self, model=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
                  batch=1, dtype="fp64", device=0, max_qp=2, mu=10.0, step_tol=1e-3, threads=0, cluster=0):
         self.lib = _lib.load()
+        self._pinned = {}
         if model is None:
             model = build_model_from_urdf()
         if not isinstance(model, RobotModel):
@@ -90,9 +91,19 @@ class Engine:
         keep.append(a)
         return C.c_void_p(a.ctypes.data)
 
-    def _out(self, shape, like, keep):
+    def _out(self, shape, like, keep, tag=""):
         if _is_torch(like) and like.is_cuda:
             t = torch.empty(shape, dtype=self._torch_dtype(), device=like.device)
+            keep.append(t)
+            return t, C.c_void_p(t.data_ptr())
+        if _is_torch(like) and like.is_pinned():
+            # page-locked inputs get page-locked outputs (the C ABI then copies without staging); the buffers are
+            # cached per call site and shape, so a result is valid until the next call of the same kind
+            key = (tag, tuple(shape))
+            t = self._pinned.get(key)
+            if t is None:
+                t = torch.empty(shape, dtype=self._torch_dtype(), pin_memory=True)
+                self._pinned[key] = t
             keep.append(t)
             return t, C.c_void_p(t.data_ptr())
         a = np.empty(shape, dtype=self.np_dtype)
@@ -128,8 +139,8 @@ class Engine:
         gs = self._goal_stride(goals, B)
         keep = []
         p_xu, p_x0, p_g = self._in(xu, (B, self.nz), keep), self._in(x0, (B, 12), keep), self._in(goals, (B, gs * self.N), keep)
-        out, p_out = self._out((B, self.nz), xu, keep)
-        stats, p_st = self._out((B, _lib.I7_STATS_LEN), xu, keep) if want_stats else (None, None)
+        out, p_out = self._out((B, self.nz), xu, keep, "solve.xu")
+        stats, p_st = self._out((B, _lib.I7_STATS_LEN), xu, keep, "solve.st") if want_stats else (None, None)
         self._check(self.lib.i7_solve(self._h, B, p_xu, p_x0, p_g, gs, p_out, p_st, self._stream(xu)))
         return out, stats
 
