@@ -396,7 +396,7 @@ def run_b200(args):
 
 
 def eng_threads(eng, B, args):
-    return args.threads if args.threads else (384 if B <= 148 else 128)
+    return args.threads if args.threads else (384 if B <= 148 else 256)
 
 
 def single_problem_latency(args, local):

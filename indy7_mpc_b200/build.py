@@ -18,7 +18,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 # (object name, source, extra defines)
 UNITS = [("i7_api", "i7_api.cu", [])]
 for tname, t in (("f64", "double"), ("f32", "float")):
-    for nt in (128, 384):
+    for nt in (128, 256, 384):
         for sp in ("false", "true"):
             UNITS.append((f"i7_sqp_{tname}_{nt}_{sp[0]}", "i7_sqp_inst.cu", [f"-DI7_T={t}", f"-DI7_NT={nt}", f"-DI7_SPILL={sp}"]))
 

@@ -156,6 +156,7 @@ i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& 
     cudaError_t e;
     if (h->use_cluster && P.mode == i7::MODE_SOLVE) e = i7::launch_sqp_cluster<T>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
     else if (h->threads == 384) e = h->spill ? i7::launch_sqp_cta<T, 384, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 384, false>(rob, P, h->smem_bytes, s);
+    else if (h->threads == 256) e = h->spill ? i7::launch_sqp_cta<T, 256, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 256, false>(rob, P, h->smem_bytes, s);
     else e = h->spill ? i7::launch_sqp_cta<T, 128, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 128, false>(rob, P, h->smem_bytes, s);
     ++h->launches;
     I7_CUDA(h, e);
@@ -167,6 +168,7 @@ cudaError_t allow_big_smem(int threads, int optin_bytes, int* cap) {
     // the spill / no-spill instances of one CTA size have the same static footprint; raise the cap of both
     cudaError_t e;
     if (threads == 384) { e = i7::smem_cap_sqp_cta<T, 384, true>(optin_bytes, cap); if (e == cudaSuccess) e = i7::smem_cap_sqp_cta<T, 384, false>(optin_bytes, cap); }
+    else if (threads == 256) { e = i7::smem_cap_sqp_cta<T, 256, true>(optin_bytes, cap); if (e == cudaSuccess) e = i7::smem_cap_sqp_cta<T, 256, false>(optin_bytes, cap); }
     else { e = i7::smem_cap_sqp_cta<T, 128, true>(optin_bytes, cap); if (e == cudaSuccess) e = i7::smem_cap_sqp_cta<T, 128, false>(optin_bytes, cap); }
     return e;
 }
@@ -294,8 +296,8 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
 #define I7_CUDA_C(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(I7_ERR_CUDA); } } while (0)
     I7_CUDA_C(cudaSetDevice(cfg->device));
     I7_CUDA_C(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
-    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 148 ? 384 : 128);
-    if (h->threads != 128 && h->threads != 384) { h->err = "threads must be 0, 128 or 384"; return fail(I7_ERR_INVALID); }
+    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 148 ? 384 : 256);
+    if (h->threads != 128 && h->threads != 256 && h->threads != 384) { h->err = "threads must be 0, 128, 256 or 384"; return fail(I7_ERR_INVALID); }
     int cap = 0;
     {
         cudaError_t ea;
