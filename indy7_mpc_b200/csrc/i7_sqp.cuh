@@ -94,14 +94,6 @@ struct Ptrs {
 struct Win { int k0, nd, nc; };
 
 static __device__ __constant__ double c_alphas[9] = {0.0, 1.0, 0.5, 0.25, 0.125, 0.0625, 0.03125, 0.015625, 0.0078125};
-// upper triangle of a 12x12 matrix, row-major enumeration
-static __device__ __constant__ unsigned char c_tri_r[78] = {
-    0,0,0,0,0,0,0,0,0,0,0,0, 1,1,1,1,1,1,1,1,1,1,1, 2,2,2,2,2,2,2,2,2,2, 3,3,3,3,3,3,3,3,3, 4,4,4,4,4,4,4,4,
-    5,5,5,5,5,5,5, 6,6,6,6,6,6, 7,7,7,7,7, 8,8,8,8, 9,9,9, 10,10, 11};
-static __device__ __constant__ unsigned char c_tri_c[78] = {
-    0,1,2,3,4,5,6,7,8,9,10,11, 1,2,3,4,5,6,7,8,9,10,11, 2,3,4,5,6,7,8,9,10,11, 3,4,5,6,7,8,9,10,11, 4,5,6,7,8,9,10,11,
-    5,6,7,8,9,10,11, 6,7,8,9,10,11, 7,8,9,10,11, 8,9,10,11, 9,10,11, 10,11, 11};
-
 // -----------------------------------------------------------------------------------------------------------
 // setup: linearised dynamics, cost terms and all stage-local QP products at the current iterate.
 // The dynamics part works in world-frame coordinates (i7_rbd.cuh, wf_*): every wave below is a set of independent
@@ -127,8 +119,11 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     const int N = P.N, nk = W.nd, nc = W.nc;      // dynamics knots / cost knots of this CTA's window
     const T* xu = M.xu + 18 * W.k0;               // window-relative: knot index k below is local, records are local
     const T* goals = M.goals + 3 * W.k0;
-    const T dt = P.dt;
-    const int np = (nk + 31) & ~31;               // knots padded to whole warps: the lanes of a warp share (link | column)
+    const T dt = P.dt, rdt = T(1) / P.dt;
+    // task index = major * np + knot.  With a whole horizon per CTA the knots are padded to whole warps so that the
+    // lanes of a warp share the major index (link | column: uniform trip counts and predicates); with a few knots
+    // per CTA (cluster form) the tasks are packed densely instead — idle lanes would only waste FP64 issue slots
+    const int np = nk > 16 ? (nk + 31) & ~31 : nk;
     // W0: cos / sin of every joint angle
     for (int t = tid; t < 6 * nc; t += NT) {
         const int i = t / nc, k = t - i * nc;
@@ -290,9 +285,11 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     }
     __syncthreads();
     I7_STAMP();
-    // W7: cv = v + dt qdd - Gq q - Gv v - dt M^-1 u ;  S = R Y'Y with Y = M / dt  (dump mode: H = dt M^-1 instead)
-    for (int t = tid; t < 42 * nk; t += NT) {
-        const int e = t / nk, k = t - e * nk;
+    // W7: cv = v + dt qdd - Gq q - Gv v - dt M^-1 u  (row tasks);  S = R Y'Y with Y = M / dt, one ROW of S per task
+    //     (six independent accumulators) — dump mode: a column of H = dt M^-1 instead
+    for (int t = tid; t < 12 * np; t += NT) {
+        const int e = t / np, k = t - e * np;
+        if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
         const T* ax = M.aux + AUX_STRIDE * k;
         const T* xk = xu + 18 * k;
@@ -306,84 +303,115 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
             }
             kr[KR_CV + r] = a0 + a1;
         } else {
-            const int e2 = e - 6, r = e2 / 6, c = e2 - 6 * r;
-            if (for_dump) {
-                if (r == 0) {           // column c of H = dt M^-1 with the stored factor
-                    T A[6][6], dinv[6], y[6];
-                    int o = 0;
+            const int r = e - 6;
+            if (for_dump) {             // column r of H = dt M^-1 with the stored factor
+                T A[6][6], dinv[6], y[6];
+                int o = 0;
 #pragma unroll
-                    for (int i = 1; i < 6; ++i)
+                for (int i = 1; i < 6; ++i)
 #pragma unroll
-                        for (int q = 0; q < i; ++q) A[i][q] = ax[AX_L + o++];
+                    for (int q = 0; q < i; ++q) A[i][q] = ax[AX_L + o++];
 #pragma unroll
-                    for (int i = 0; i < 6; ++i) { dinv[i] = ax[AX_DINV + i]; y[i] = (i == c) ? T(1) : T(0); }
-                    spd6_solve_factored<T>(A, dinv, y);
+                for (int i = 0; i < 6; ++i) { dinv[i] = ax[AX_DINV + i]; y[i] = (i == r) ? T(1) : T(0); }
+                spd6_solve_factored<T>(A, dinv, y);
 #pragma unroll
-                    for (int i = 0; i < 6; ++i) kr[KR_S + 6 * i + c] = dt * y[i];
-                }
+                for (int i = 0; i < 6; ++i) kr[KR_S + 6 * i + r] = dt * y[i];
             } else {
-                T acc = T(0);
+                T acc[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
 #pragma unroll
-                for (int s = 0; s < 6; ++s) acc += kr[KR_Y + 6 * s + r] * kr[KR_Y + 6 * s + c];
-                kr[KR_S + e2] = (M.cost[COST_STRIDE * k + 8] / (dt * dt)) * acc;
+                for (int s = 0; s < 6; ++s) {
+                    const T ysr = kr[KR_Y + 6 * s + r];
+#pragma unroll
+                    for (int c = 0; c < 6; ++c) acc[c] += ysr * kr[KR_Y + 6 * s + c];
+                }
+                const T sc = M.cost[COST_STRIDE * k + 8] * (rdt * rdt);
+#pragma unroll
+                for (int c = 0; c < 6; ++c) kr[KR_S + 6 * r + c] = sc * acc[c];
             }
         }
     }
     __syncthreads();
     I7_STAMP();
     if (for_dump) return;
-    // W8: SG = S G (6x12),  d = S cv - (R/dt) M u
-    for (int t = tid; t < 78 * nk; t += NT) {
-        const int e = t / nk, k = t - e * nk;
+    // W8: one COLUMN of SG = S G per task (12 per knot), plus d = S cv - (R/dt) M u as a 13th
+    for (int t = tid; t < 13 * np; t += NT) {
+        const int c = t / np, k = t - c * np;
+        if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
-        if (e < 72) {
-            const int r = e / 12, c = e - 12 * r;
+        T g[6], acc[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+        if (c < 12) {
             const T* G = kr + (c < 6 ? KR_GQ + c : KR_GV + c - 6);
-            T acc = T(0);
 #pragma unroll
-            for (int s = 0; s < 6; ++s) acc += kr[KR_S + 6 * r + s] * G[6 * s];
-            kr[KR_SG + e] = acc;
+            for (int s = 0; s < 6; ++s) g[s] = G[6 * s];
         } else {
-            const int r = e - 72;
+#pragma unroll
+            for (int s = 0; s < 6; ++s) g[s] = kr[KR_CV + s];
+        }
+#pragma unroll
+        for (int s = 0; s < 6; ++s)
+#pragma unroll
+            for (int r = 0; r < 6; ++r) acc[r] += kr[KR_S + 6 * r + s] * g[s];
+        if (c < 12) {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) kr[KR_SG + 12 * r + c] = acc[r];
+        } else {
             const T* xk = xu + 18 * k;
-            T a0 = T(0), a1 = T(0);
+            const T sc = M.cost[COST_STRIDE * k + 8] * rdt;
+            T mu[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
 #pragma unroll
             for (int s = 0; s < 6; ++s) {
-                a0 += kr[KR_S + 6 * r + s] * kr[KR_CV + s];
-                a1 += kr[KR_Y + 6 * r + s] * xk[12 + s];
+                const T us = xk[12 + s];
+#pragma unroll
+                for (int r = 0; r < 6; ++r) mu[r] += kr[KR_Y + 6 * r + s] * us;
             }
-            kr[KR_D + r] = a0 - (M.cost[COST_STRIDE * k + 8] / dt) * a1;
+#pragma unroll
+            for (int r = 0; r < 6; ++r) kr[KR_D + r] = acc[r] - sc * mu[r];
         }
     }
     __syncthreads();
     I7_STAMP();
-    // W9: L = G'(SG) (upper triangle, overwrites the setup scratch), hx = gx + G'd, Y = M / dt in place
-    for (int t = tid; t < 126 * nk; t += NT) {
-        const int e = t / nk, k = t - e * nk;
+    // W9: half a COLUMN c of L = G'(SG) + Qx per task (rows 6h .. 6h+5 of the upper triangle, r <= c; overwrites the
+    //     setup scratch); the h = 0 tasks also do hx[c] = gx[c] + G[:, c] . d and, for c < 6, row c of Y = M / dt
+    for (int t = tid; t < 24 * np; t += NT) {
+        const int ch = t / np, k = t - ch * np;
+        if (k >= nk) continue;
+        const int c = ch >> 1, hf = ch & 1;
+        if (hf && c < 6) continue;                       // rows 6..11 of a column c < 6 lie below the diagonal
         T* kr = M.kr + KR_STRIDE * k;
-        if (e < 78) {
-            const int r = c_tri_r[e], c = c_tri_c[e];
-            const T* Gr = kr + (r < 6 ? KR_GQ + r : KR_GV + r - 6);
+        const T* ck = M.cost + COST_STRIDE * k;
+        T sg[6];
+#pragma unroll
+        for (int s = 0; s < 6; ++s) sg[s] = kr[KR_SG + 12 * s + c];
+        const T* Gh = kr + (hf ? KR_GV : KR_GQ);         // rows r = 6 hf + rr  <->  columns rr of Gq | Gv
+        T lcol[6];
+#pragma unroll
+        for (int rr = 0; rr < 6; ++rr) {
             T acc = T(0);
 #pragma unroll
-            for (int s = 0; s < 6; ++s) acc += Gr[6 * s] * kr[KR_SG + 12 * s + c];
-            {   // + Qx: the stage cost Hessian (rank-1 position block, dQ on the velocity diagonal)
-                const T* ck = M.cost + COST_STRIDE * k;
-                if (c < 6) acc += ck[6] * ck[r] * ck[c];
-                else if (r == c) acc += ck[7];
-            }
-            kr[KR_L + e] = acc;
-        } else if (e < 90) {
-            const int r = e - 78;
-            const T* ck = M.cost + COST_STRIDE * k;
-            const T* Gr = kr + (r < 6 ? KR_GQ + r : KR_GV + r - 6);
-            T acc = r < 6 ? ck[6] * ck[r] : ck[7] * xu[18 * k + r];
+            for (int s = 0; s < 6; ++s) acc += Gh[6 * s + rr] * sg[s];
+            lcol[rr] = acc;
+        }
+        const T qc = c < 6 ? ck[6] * ck[c] : T(0);      // + Qx: rank-1 position block, dQ on the velocity diagonal
 #pragma unroll
-            for (int s = 0; s < 6; ++s) acc += Gr[6 * s] * kr[KR_D + s];
-            kr[KR_HX + r] = acc;
-        } else {
-            const int e2 = e - 90;
-            kr[KR_Y + e2] = kr[KR_Y + e2] / dt;
+        for (int rr = 0; rr < 6; ++rr) {
+            const int r = 6 * hf + rr;
+            if (r <= c) {
+                T v = lcol[rr];
+                if (c < 6) v += qc * ck[r];
+                else if (r == c) v += ck[7];
+                kr[KR_L + r * 12 - (r * (r - 1)) / 2 + (c - r)] = v;
+            }
+        }
+        if (!hf) {
+            const T* Gc = kr + (c < 6 ? KR_GQ + c : KR_GV + c - 6);
+            T h = c < 6 ? ck[6] * ck[c] : ck[7] * xu[18 * k + c];
+#pragma unroll
+            for (int s = 0; s < 6; ++s) h += Gc[6 * s] * kr[KR_D + s];
+            kr[KR_HX + c] = h;
+            if (c < 6) {
+#pragma unroll
+                for (int s = 0; s < 6; ++s) kr[KR_Y + 6 * c + s] = kr[KR_Y + 6 * c + s] * rdt;
+            }
         }
     }
     __syncthreads();
@@ -460,6 +488,76 @@ template <typename T> I7_DEV void spd6_factor_serial(T (&A)[6][6], T (&dinv)[6])
             A[i][j] = l;
         }
     }
+}
+
+// x = H^-1 b for a 6x6 SPD matrix given as packed lower triangle (row-major, 21 numbers), b overwritten by x.
+// Generic version: LDL' in registers (6 dependent reciprocals on the critical path).
+template <typename T> I7_DEV void spd6_solve_packed(const T* Hp, T* b) {
+    T A[6][6], dinv[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int q = 0; q <= i; ++q) A[i][q] = Hp[(i * (i + 1)) / 2 + q];
+    spd6_factor_serial<T>(A, dinv);
+    spd6_solve_factored<T>(A, dinv, b);
+}
+// fp64: block elimination with 3x3 blocks H = [A B'; B D] through cofactor matrices, everything scaled by the
+// determinants so that only ONE reciprocal sits on the dependency chain (and one beside it):
+//   C = cof(A), dA = det A;  Ss = dA D - (B C) B'  (= dA x Schur complement);  Cs = cof(Ss), dS = det Ss
+//   x2 = Cs (dA b2 - (B C) b1) / dS;   x1 = C (b1 - B' x2) / dA
+// Depth ~22 dependent FMAs + 1 reciprocal (~235 cycles) against ~690 for the LDL' chain; the conditioning of the
+// stage matrices (<= 1e7) leaves 1e-9 relative accuracy in fp64.  Not used in fp32 (range and accuracy).
+template <> I7_DEV void spd6_solve_packed<double>(const double* H, double* b) {
+    const double a00 = H[0], a10 = H[1], a11 = H[2], a20 = H[3], a21 = H[4], a22 = H[5];
+    const double B[3][3] = {{H[6], H[7], H[8]}, {H[10], H[11], H[12]}, {H[15], H[16], H[17]}};
+    const double d33 = H[9], d43 = H[13], d44 = H[14], d53 = H[18], d54 = H[19], d55 = H[20];
+    // cofactor matrix of A (symmetric)
+    double C[3][3];
+    C[0][0] = a11 * a22 - a21 * a21;
+    C[0][1] = a21 * a20 - a10 * a22;
+    C[0][2] = a10 * a21 - a11 * a20;
+    C[1][1] = a00 * a22 - a20 * a20;
+    C[1][2] = a10 * a20 - a00 * a21;
+    C[2][2] = a00 * a11 - a10 * a10;
+    C[1][0] = C[0][1]; C[2][0] = C[0][2]; C[2][1] = C[1][2];
+    const double dA = a00 * C[0][0] + a10 * C[0][1] + a20 * C[0][2];
+    const double rdA = rcp_serial<double>(dA);                 // off the critical path
+    // W = B C
+    double W[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) W[i][j] = B[i][0] * C[0][j] + B[i][1] * C[1][j] + B[i][2] * C[2][j];
+    // Ss = dA D - W B'  (symmetric: lower part)
+    const double s00 = dA * d33 - (W[0][0] * B[0][0] + W[0][1] * B[0][1] + W[0][2] * B[0][2]);
+    const double s10 = dA * d43 - (W[1][0] * B[0][0] + W[1][1] * B[0][1] + W[1][2] * B[0][2]);
+    const double s11 = dA * d44 - (W[1][0] * B[1][0] + W[1][1] * B[1][1] + W[1][2] * B[1][2]);
+    const double s20 = dA * d53 - (W[2][0] * B[0][0] + W[2][1] * B[0][1] + W[2][2] * B[0][2]);
+    const double s21 = dA * d54 - (W[2][0] * B[1][0] + W[2][1] * B[1][1] + W[2][2] * B[1][2]);
+    const double s22 = dA * d55 - (W[2][0] * B[2][0] + W[2][1] * B[2][1] + W[2][2] * B[2][2]);
+    double Cs[3][3];
+    Cs[0][0] = s11 * s22 - s21 * s21;
+    Cs[0][1] = s21 * s20 - s10 * s22;
+    Cs[0][2] = s10 * s21 - s11 * s20;
+    Cs[1][1] = s00 * s22 - s20 * s20;
+    Cs[1][2] = s10 * s20 - s00 * s21;
+    Cs[2][2] = s00 * s11 - s10 * s10;
+    Cs[1][0] = Cs[0][1]; Cs[2][0] = Cs[0][2]; Cs[2][1] = Cs[1][2];
+    const double dS = s00 * Cs[0][0] + s10 * Cs[0][1] + s20 * Cs[0][2];
+    const double rdS = rcp_serial<double>(dS);
+    // r2s = dA b2 - W b1 ; x2 = Cs r2s / dS
+    double r2[3], x2[3], t1[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) r2[i] = dA * b[3 + i] - (W[i][0] * b[0] + W[i][1] * b[1] + W[i][2] * b[2]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) x2[i] = (Cs[i][0] * r2[0] + Cs[i][1] * r2[1] + Cs[i][2] * r2[2]) * rdS;
+    // x1 = C (b1 - B' x2) / dA
+#pragma unroll
+    for (int j = 0; j < 3; ++j) t1[j] = b[j] - (B[0][j] * x2[0] + B[1][j] * x2[1] + B[2][j] * x2[2]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) b[i] = (C[i][0] * t1[0] + C[i][1] * t1[1] + C[i][2] * t1[2]) * rdA;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) b[3 + i] = x2[i];
 }
 
 // riccati: backward recursion for the gains, forward roll-out for z.  x0 = measured state (l[:12] = -xs).
@@ -575,15 +673,10 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, int o_work, 
         T base = T(0);
         if (tid < 13) {
             // R2: one right-hand side of X = Hww^-1 [Hwx | hw]
-            T A[6][6], dinv[6], b[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i)
-#pragma unroll
-                for (int q = 0; q <= i; ++q) A[i][q] = blk[SB_H + (i * (i + 1)) / 2 + q];
+            T b[6];
 #pragma unroll
             for (int i = 0; i < 6; ++i) b[i] = blk[SB_R + 6 * tid + i];
-            spd6_factor_serial<T>(A, dinv);
-            spd6_solve_factored<T>(A, dinv, b);
+            spd6_solve_packed<T>(blk + SB_H, b);
             // feedback / feed-forward of w = v_{k+1}: Kw = -X[:, :12], kw = -X[:, 12]
 #pragma unroll
             for (int i = 0; i < 6; ++i) G[6 * tid + i] = -b[i];
