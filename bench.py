@@ -127,12 +127,21 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------- CPU baseline
+def host_cores():
+    """Host threads this process may use (the affinity mask, not OMP_NUM_THREADS, which torchrun forces to 1)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_baseline(N, wl, tick_goals, seconds, sample_cap, nthreads=0):
     """The plain-C restatement of osqp_sqp (OSQP-style ADMM) on the host cores, OpenMP across problems."""
     from oracle.cport import COracle
     from oracle.model import load_model
     model = load_model()
-    cores = os.cpu_count() or 1
+    cores = host_cores()
+    nthreads = nthreads or cores      # explicit: torchrun exports OMP_NUM_THREADS=1 to every rank
     chunk = max(8, min(sample_cap, 8 * cores))
     orc = COracle(model, N=N, backend="admm", batch=chunk)
     done, t0 = 0, time.perf_counter()
@@ -146,7 +155,7 @@ def cpu_baseline(N, wl, tick_goals, seconds, sample_cap, nthreads=0):
         el = time.perf_counter() - t0
         if el >= seconds or done >= sample_cap:
             break
-    return {"value": done / el, "unit": UNIT, "cores": orc.threads() if nthreads == 0 else nthreads, "kind": "port",
+    return {"value": done / el, "unit": UNIT, "cores": nthreads, "kind": "port",
             "sample": f"{done} cold-start problems of the same workload (tick 0) in {el:.1f} s, C restatement of "
                       f"osqp_sqp with OSQP-style ADMM (oracle/c), OpenMP over problems"}
 
@@ -162,7 +171,7 @@ def run_reference(args):
     N = args.horizon
     wl = make_workload(args.batch, N)
     model = load_model()
-    cores = os.cpu_count() or 1
+    cores = host_cores()
     per_step = max(8, min(args.batch, 4 * cores))
     orc = COracle(model, N=N, backend="admm", batch=per_step)
     idx = np.arange(per_step)
@@ -171,7 +180,7 @@ def run_reference(args):
     for t in range(args.warmup + args.steps):
         goals = goals_at(wl["fig"], wl["offsets"][idx], t, N)
         t0 = time.perf_counter()
-        out, st, _ = orc.sqp(x0, goals, xu, f_ext=wl["f_ext"][idx])
+        out, st, _ = orc.sqp(x0, goals, xu, f_ext=wl["f_ext"][idx], nthreads=cores)
         dt = time.perf_counter() - t0
         if t >= args.warmup:
             times.append(dt)
@@ -186,7 +195,7 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"batch {args.batch} sampled Indy7 SQP-MPC problems, N={N} (bounded sample on CPU)",
                    "horizon": N, "batch_total": args.batch, "sample_per_step": per_step},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": orc.threads(), "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -347,7 +356,10 @@ def run_b200(args):
     fma_peak = eng.measure_fma_peak()
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"sqp_kernel_B{B}_N{N}_{args.dtype}")
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get(f"sqp_kernel_B{B}_N{N}_{args.dtype}")
+        if traffic is None and f"sqp_kernel_B4096_N{N}_{args.dtype}" in tj:      # per-launch, scaled by problems
+            traffic = tj[f"sqp_kernel_B4096_N{N}_{args.dtype}"] * B // 4096
     except Exception:
         pass
     roofline = {
