@@ -332,7 +332,16 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
             if (h->cluster_smem_bytes > ccap) {
                 if (cfg->cluster == i7::kClusterSize) { h->err = "horizon too long for the cluster kernel"; return fail(I7_ERR_UNSUPPORTED); }
                 h->use_cluster = false;
-            } else {
+            } else if (cfg->cluster == 0) {
+                // automatic choice: only while every cluster is resident at once (a second wave of clusters is slower
+                // than the CTA form); clusters are placed per GPC, so the limit is below SMs / 8 (15 on B200)
+                int nact = 0;
+                cudaError_t eo = cfg->dtype == I7_F64 ? i7::max_active_sqp_clusters<double>(h->cluster_smem_bytes, &nact)
+                                                      : i7::max_active_sqp_clusters<float>(h->cluster_smem_bytes, &nact);
+                if (eo != cudaSuccess) { (void)cudaGetLastError(); nact = sms / i7::kClusterSize - 3; }
+                if (cfg->batch > nact) h->use_cluster = false;
+            }
+            if (h->use_cluster) {
                 I7_CUDA_C(cudaMalloc(&h->d_xbuf, (size_t)cfg->batch * i7::cluster_xbuf_len(cfg->N) * h->esize));
             }
         }

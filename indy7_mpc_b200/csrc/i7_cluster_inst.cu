@@ -24,6 +24,20 @@ cudaError_t smem_cap_sqp_cluster<I7_T>(int optin_bytes, int* cap) {
     return cudaFuncSetAttribute(sqp_cluster_kernel<I7_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, *cap);
 }
 
+// how many clusters of this kernel the device can hold at once (GPC granularity: fewer than SMs / 8 on B200)
+template <>
+cudaError_t max_active_sqp_clusters<I7_T>(int smem_bytes, int* n) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CL, 1, 1);
+    cfg.blockDim = dim3(CL_NT, 1, 1);
+    cfg.dynamicSmemBytes = (size_t)smem_bytes;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaOccupancyMaxActiveClusters(n, sqp_cluster_kernel<I7_T>, &cfg);
+}
+
 #ifdef I7_CLUSTER_DEFINE_LAYOUT
 int cluster_smem_len(int N) { return make_clayout(N).total; }
 int cluster_xbuf_len(int N) { return xbuf_size(N); }

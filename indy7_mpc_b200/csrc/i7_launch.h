@@ -16,6 +16,7 @@ template <typename T, int NT, bool SPILL> cudaError_t smem_cap_sqp_cta(int optin
 template <typename T> cudaError_t launch_sqp_cluster(const Robot<T>& rob, const SolveParams<T>& P, T* xbuf, int smem_bytes,
                                                      cudaStream_t s);
 template <typename T> cudaError_t smem_cap_sqp_cluster(int optin_bytes, int* cap);
+template <typename T> cudaError_t max_active_sqp_clusters(int smem_bytes, int* n);     // co-resident clusters
 int cluster_smem_len(int N);     // shared-memory elements per CTA of the cluster kernel
 int cluster_xbuf_len(int N);     // exchange-buffer elements per problem
 constexpr int kClusterSize = 8;

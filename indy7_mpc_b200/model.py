@@ -57,6 +57,23 @@ class RobotModel:
     def createData(self):
         return None
 
+    def last_joint_placement(self, q):
+        """(R, p) of the last joint frame in the world (Pinocchio ``data.oMi[6]``): frame bookkeeping for the drivers
+        that re-express a world wrench in that frame (src/gato_mpc_batch_sample.py:268-277); not on the solve path."""
+        Rw, pw = np.eye(3), np.zeros(3)
+        for i in range(6):
+            c, s_ = math.cos(float(q[i])), math.sin(float(q[i]))
+            pw = pw + Rw @ self.p[i]
+            Rw = Rw @ self.R[i].reshape(3, 3) @ np.array([[c, -s_, 0.0], [s_, c, 0.0], [0.0, 0.0, 1.0]])
+        return Rw, pw
+
+    def world_wrench_to_last_joint(self, q, wrench):
+        """``oMi[6].actInv(pin.Force(linear, angular))`` for a wrench [fx fy fz tx ty tz] given at the world origin."""
+        Rw, pw = self.last_joint_placement(q)
+        w = np.asarray(wrench, float)
+        f, n = w[..., :3], w[..., 3:]
+        return np.concatenate([f @ Rw, (n - np.cross(pw, f)) @ Rw], axis=-1)
+
     def to_c(self):
         m = I7Model()
         g = np.asarray(getattr(self.gravity, "linear", self.gravity), float).reshape(-1)

@@ -83,3 +83,30 @@ def test_figure8_generator():
     ref = np.load(os.path.join(ROOT, "tests", "golden", "figure8_first_cycle.npy"))
     got = figure8(0.5, 0.55, (0.0, 0.4, 0.45), 10.0, 0.01, cycles=2)
     assert got.shape == (12000,) and np.abs(got[:6000] - ref).max() < 1e-15
+
+
+def test_world_wrench_to_last_joint_matches_oracle_fk():
+    """Frame bookkeeping of the batch-sample driver (oMi[6].actInv, src/gato_mpc_batch_sample.py:268-277)."""
+    import numpy as np
+    from indy7_mpc_b200.model import build_model_from_urdf
+    from oracle.model import load_model
+    from oracle import rbd
+    m, om = build_model_from_urdf(), load_model()
+    rng = np.random.default_rng(3)
+    for _ in range(5):
+        q = rng.uniform(-3, 3, 6)
+        w = rng.normal(0, 2, (4, 6))
+        p, Rw = rbd.forward_kinematics(om, q)
+        ref = np.stack([np.concatenate([Rw[-1].T @ x[:3], Rw[-1].T @ (x[3:] - np.cross(p[-1], x[:3]))]) for x in w])
+        assert np.abs(m.world_wrench_to_last_joint(q, w) - ref).max() < 1e-13
+
+
+def test_oracle_batch_sample_driver_runs():
+    import numpy as np
+    from oracle.model import load_model
+    from oracle.gato_mpc_batch_sample import MPC_GATO_Batch_Sample
+    np.random.seed(1)
+    d = MPC_GATO_Batch_Sample(load_model(), N=8, batch_size=2, constant_f_ext=[1.0, 0.0, 0.0], resample_f_ext=True)
+    x0 = np.concatenate([0.4 * np.ones(6), np.zeros(6)])
+    xp, st = d.run_mpc(x0, [np.array([0.3, 0.4, 0.5])], sim_dt=0.005, sim_time=0.03)
+    assert len(xp) >= 6 and np.all(np.isfinite(np.array(xp))) and len(d.best_ids) == 6
