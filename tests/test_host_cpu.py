@@ -110,3 +110,28 @@ def test_oracle_batch_sample_driver_runs():
     x0 = np.concatenate([0.4 * np.ones(6), np.zeros(6)])
     xp, st = d.run_mpc(x0, [np.array([0.3, 0.4, 0.5])], sim_dt=0.005, sim_time=0.03)
     assert len(xp) >= 6 and np.all(np.isfinite(np.array(xp))) and len(d.best_ids) == 6
+
+
+def test_trajectory_csv_and_stats_formats(tmp_path):
+    """On-disk formats of the reference drivers: the (T x 6) '%.18e' CSV of the C++ driver (byte-exact round trip of
+    the head of trajectories/figure8_traj_eePos_meters.csv) and the six .npy series of gato_controller.py:281-293."""
+    import os
+    import numpy as np
+    from indy7_mpc_b200.reference_traj import (StatsLog, figure8, figure_8, load_trajectory_csv, save_trajectory_csv)
+    src = os.path.join(os.path.dirname(__file__), "golden", "figure8_traj_eePos_meters_head.csv")
+    rows = load_trajectory_csv(src)
+    assert rows.shape == (4, 6) and rows[0, 0] == 4.333333333333333481e-01 and np.all(rows[:, 3:] == 0)
+    out = tmp_path / "t.csv"
+    save_trajectory_csv(out, rows)
+    assert open(out).read() == open(src).read()
+    save_trajectory_csv(out, figure8(cycles=1))
+    assert np.array_equal(load_trajectory_csv(out).reshape(-1), figure8(cycles=1))
+    assert np.allclose(figure_8(0.5, 0.55, (0.0, 0.4, 0.45), 0.01, 10.0, 2), figure8(cycles=2), atol=1e-15)
+    log = StatsLog()
+    for i in range(3):
+        log.record(0.01, 0.1 * i, np.ones(3) * i, np.zeros(6), np.arange(12.0), 1e-4)
+    log.save(str(tmp_path / "120000"))
+    names = sorted(os.listdir(tmp_path))
+    assert [n for n in names if n.endswith(".npy")] == sorted(f"120000_{f}.npy" for f in StatsLog.FIELDS)
+    back = StatsLog.load(str(tmp_path / "120000"))
+    assert np.array(back.joint_positions).shape == (3, 6) and np.array(back.ee_ref_positions).shape == (3, 3)
