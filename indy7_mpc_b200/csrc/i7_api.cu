@@ -40,6 +40,13 @@ struct i7_handle {
     int cluster_smem_bytes = 0;
     void* d_xbuf = nullptr;      // exchange buffer of the cluster kernel (batch x cluster_xbuf_len(N))
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // host-buffer calls on big batches run as a software pipeline of chunks over these streams (copy-in of chunk
+    // i+1 and copy-out of chunk i-1 overlap the kernel of chunk i); pipe_chunk = problems per chunk, 0 = off
+    static constexpr int kPipeStreams = 3, kPipeMaxChunks = 64;
+    cudaStream_t pipe_stream[kPipeStreams] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pipe_fork = nullptr, pipe_join[kPipeStreams] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pipe_done[kPipeMaxChunks] = {};
+    int pipe_chunk = 0;
     bool timed = false;
     int64_t launches = 0;
     std::string err;
@@ -151,8 +158,8 @@ template <> const i7::Robot<double>& get_rob<double>(const i7_handle* h) { retur
 template <> const i7::Robot<float>& get_rob<float>(const i7_handle* h) { return h->rob32; }
 
 template <typename T>
-i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& P, cudaStream_t s) {
-    P.spill_ws = h->spill ? (T*)h->d_spill : nullptr;
+i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& P, cudaStream_t s, size_t first_problem = 0) {
+    P.spill_ws = h->spill ? (T*)h->d_spill + first_problem * (size_t)i7::make_layout(h->cfg.N, true).reg_size : nullptr;
     cudaError_t e;
     if (h->use_cluster && P.mode == i7::MODE_SOLVE) e = i7::launch_sqp_cluster<T>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
     else if (h->threads == 384) e = h->spill ? i7::launch_sqp_cta<T, 384, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 384, false>(rob, P, h->smem_bytes, s);
@@ -229,10 +236,102 @@ i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     return st.flush_out(s);
 }
 
+// i7_solve with every buffer in HOST memory and a batch of several chunks: a software pipeline.  Chunk i's inputs go
+// host -> device on pipe stream i mod 3, its kernel follows on the same stream, then its outputs device -> host; the
+// three streams run concurrently, so the copy engines (both directions) and the SMs are busy at the same time and the
+// tail wave of one chunk's kernel overlaps the head of the next.  Pageable buffers pass through the pinned mirror of
+// the arena chunk by chunk (the host memcpy of chunk i+1 overlaps the GPU work on chunk i).  Synchronous, like every
+// host-buffer call.
+template <typename T>
+i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
+    const int N = h->cfg.N;
+    const size_t nz = h->nz, B = c.batch, es = sizeof(T);
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    const size_t per_in[3] = {nz * es, 12 * es, (size_t)N * c.goal_stride * es};
+    const size_t per_out[2] = {nz * es, (size_t)I7_STATS_LEN * es};
+    const void* uin[3] = {c.xu, c.x0, c.goals};
+    void* uout[2] = {c.xu_out, c.stats};
+    size_t off_in[3], off_out[2], o = 0;
+    for (int a = 0; a < 3; ++a) { off_in[a] = o; o += (B * per_in[a] + 15) & ~size_t(15); }
+    o = 0;
+    for (int a = 0; a < 2; ++a) { off_out[a] = o; o += (B * per_out[a] + 15) & ~size_t(15); }
+    bool pin_in[3], pin_out[2];
+    for (int a = 0; a < 3; ++a) pin_in[a] = ptr_kind(uin[a]) == 2;
+    for (int a = 0; a < 2; ++a) pin_out[a] = uout[a] && ptr_kind(uout[a]) == 2;
+    const size_t chunk = (size_t)h->pipe_chunk;
+    const int nchunks = (int)((B + chunk - 1) / chunk);
+    I7_CUDA(h, cudaEventRecord(h->ev0, s));
+    I7_CUDA(h, cudaEventRecord(h->pipe_fork, s));
+    for (int k = 0; k < i7_handle::kPipeStreams; ++k) I7_CUDA(h, cudaStreamWaitEvent(h->pipe_stream[k], h->pipe_fork, 0));
+    for (int i = 0; i < nchunks; ++i) {
+        cudaStream_t ps = h->pipe_stream[i % i7_handle::kPipeStreams];
+        const size_t b0 = (size_t)i * chunk, nb = B - b0 < chunk ? B - b0 : chunk;
+        for (int a = 0; a < 3; ++a) {
+            char* dev = (char*)h->in.dev + off_in[a] + b0 * per_in[a];
+            const char* src = (const char*)uin[a] + b0 * per_in[a];
+            if (!pin_in[a]) {
+                char* mir = (char*)h->in.host + off_in[a] + b0 * per_in[a];
+                std::memcpy(mir, src, nb * per_in[a]);
+                src = mir;
+            }
+            I7_CUDA(h, cudaMemcpyAsync(dev, src, nb * per_in[a], cudaMemcpyHostToDevice, ps));
+        }
+        i7::SolveParams<T> P;
+        base_params<T>(h, P, (int)nb, c.goal_stride, c.mode);
+        if (P.fext) P.fext += b0 * 6;
+        if (P.prof) P.prof += b0 * 32;
+        P.xu_in = (const T*)((char*)h->in.dev + off_in[0] + b0 * per_in[0]);
+        P.x0 = (const T*)((char*)h->in.dev + off_in[1] + b0 * per_in[1]);
+        P.goals = (const T*)((char*)h->in.dev + off_in[2] + b0 * per_in[2]);
+        P.xu_out = (T*)((char*)h->out.dev + off_out[0] + b0 * per_out[0]);
+        P.stats = uout[1] ? (T*)((char*)h->out.dev + off_out[1] + b0 * per_out[1]) : nullptr;
+        i7_status rc = launch_sqp<T>(h, get_rob<T>(h), P, ps, b0);
+        if (rc) return rc;
+        for (int a = 0; a < 2; ++a) {
+            if (!uout[a]) continue;
+            const char* dev = (const char*)h->out.dev + off_out[a] + b0 * per_out[a];
+            char* dst = pin_out[a] ? (char*)uout[a] + b0 * per_out[a] : (char*)h->out.host + off_out[a] + b0 * per_out[a];
+            I7_CUDA(h, cudaMemcpyAsync(dst, dev, nb * per_out[a], cudaMemcpyDeviceToHost, ps));
+        }
+        I7_CUDA(h, cudaEventRecord(h->pipe_done[i], ps));
+    }
+    for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
+        I7_CUDA(h, cudaEventRecord(h->pipe_join[k], h->pipe_stream[k]));
+        I7_CUDA(h, cudaStreamWaitEvent(s, h->pipe_join[k], 0));
+    }
+    I7_CUDA(h, cudaEventRecord(h->ev1, s));
+    h->timed = true;
+    // pageable outputs: unpack chunk by chunk as they land
+    for (int i = 0; i < nchunks; ++i) {
+        const size_t b0 = (size_t)i * chunk, nb = B - b0 < chunk ? B - b0 : chunk;
+        bool any = false;
+        for (int a = 0; a < 2; ++a) any = any || (uout[a] && !pin_out[a]);
+        if (!any) break;
+        I7_CUDA(h, cudaEventSynchronize(h->pipe_done[i]));
+        for (int a = 0; a < 2; ++a)
+            if (uout[a] && !pin_out[a])
+                std::memcpy((char*)uout[a] + b0 * per_out[a], (char*)h->out.host + off_out[a] + b0 * per_out[a], nb * per_out[a]);
+    }
+    I7_CUDA(h, cudaStreamSynchronize(s));
+    return I7_OK;
+}
+
+bool pipeline_eligible(const i7_handle* h, const SqpCall& c) {
+    if (c.mode != i7::MODE_SOLVE || h->pipe_chunk <= 0 || h->use_cluster) return false;
+    if (c.batch < 2 * h->pipe_chunk || (c.batch + h->pipe_chunk - 1) / h->pipe_chunk > i7_handle::kPipeMaxChunks) return false;
+    if (c.xu_full || c.z_out || c.Adata || c.Pdata || c.g || c.l || c.alpha || c.merits) return false;
+    const void* ptrs[5] = {c.xu, c.x0, c.goals, c.xu_out, c.stats};
+    for (int a = 0; a < 5; ++a)
+        if (ptrs[a] && ptr_kind(ptrs[a]) == 1) return false;      // device-resident buffers: one launch, no copies
+    return true;
+}
+
 i7_status run_sqp(i7_handle* h, const SqpCall& c, void* stream) {
     i7_status rc = check_batch(h, c.batch, c.goal_stride);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
+    if (pipeline_eligible(h, c))
+        return h->cfg.dtype == I7_F64 ? run_solve_pipelined<double>(h, c, s) : run_solve_pipelined<float>(h, c, s);
     return h->cfg.dtype == I7_F64 ? run_sqp_t<double>(h, c, s) : run_sqp_t<float>(h, c, s);
 }
 
@@ -263,6 +362,12 @@ void i7_destroy(i7_handle* h) {
     if (h->d_spill) cudaFree(h->d_spill);
     if (h->d_xbuf) cudaFree(h->d_xbuf);
     if (h->d_prof) cudaFree(h->d_prof);
+    for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
+        if (h->pipe_stream[k]) cudaStreamDestroy(h->pipe_stream[k]);
+        if (h->pipe_join[k]) cudaEventDestroy(h->pipe_join[k]);
+    }
+    for (int k = 0; k < i7_handle::kPipeMaxChunks; ++k) if (h->pipe_done[k]) cudaEventDestroy(h->pipe_done[k]);
+    if (h->pipe_fork) cudaEventDestroy(h->pipe_fork);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     delete h;
@@ -356,6 +461,21 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
     I7_CUDA_C(cudaMemset(h->d_fext, 0, B * 6 * es));
     I7_CUDA_C(cudaEventCreate(&h->ev0));
     I7_CUDA_C(cudaEventCreate(&h->ev1));
+    // chunked host pipeline for big batches (I7_PIPE_CHUNK problems per chunk; 0 disables)
+    {
+        const char* env = std::getenv("I7_PIPE_CHUNK");
+        h->pipe_chunk = env ? std::atoi(env) : 256;
+        if (h->pipe_chunk > 0 && cfg->batch >= 2 * h->pipe_chunk) {
+            for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
+                I7_CUDA_C(cudaStreamCreateWithFlags(&h->pipe_stream[k], cudaStreamNonBlocking));
+                I7_CUDA_C(cudaEventCreateWithFlags(&h->pipe_join[k], cudaEventDisableTiming));
+            }
+            I7_CUDA_C(cudaEventCreateWithFlags(&h->pipe_fork, cudaEventDisableTiming));
+            for (int k = 0; k < i7_handle::kPipeMaxChunks; ++k) I7_CUDA_C(cudaEventCreateWithFlags(&h->pipe_done[k], cudaEventDisableTiming));
+        } else {
+            h->pipe_chunk = 0;
+        }
+    }
 #undef I7_TRY
 #undef I7_CUDA_C
     *out = h;

@@ -396,3 +396,34 @@ def test_sharded_batch_is_bitwise_identical(pkg, oracle_model):
     gathered = np.stack(parts)
     best2 = np.asarray(whole.reduce_best(gathered, 2))
     assert np.array_equal(best, best2)
+
+
+def test_host_pipeline_is_bitwise_identical(pkg, oracle_model, monkeypatch):
+    """Host-buffer solves of big batches run as a chunked copy/compute pipeline (i7_api.cu: run_solve_pipelined):
+    pageable numpy and page-locked torch buffers, a ragged last chunk, per-lane wrenches — all bitwise equal to the
+    single-launch device-resident solve."""
+    import torch
+    xu1, x01, g1 = make_cases(oracle_model, 40, N=16, seed=21)
+    reps = 23
+    xu, x0, goals = (np.tile(a, (reps, 1))[:900] for a in (xu1, x01, g1))
+    rng = np.random.default_rng(2)
+    x0 = x0 + rng.normal(0, 1e-3, x0.shape)
+    fext = np.zeros((900, 6)); fext[:, :3] = rng.normal(0, 3, (900, 3))
+    monkeypatch.setenv("I7_PIPE_CHUNK", "0")
+    plain = pkg.Engine(N=16, batch=900, dtype="fp64")
+    monkeypatch.setenv("I7_PIPE_CHUNK", "128")            # 8 chunks, the last one of 4 problems
+    piped = pkg.Engine(N=16, batch=900, dtype="fp64")
+    for e in (plain, piped):
+        e.set_external_wrench(fext)
+    dev = lambda a: torch.tensor(a, device="cuda")
+    ref, ref_st = plain.solve(dev(xu), dev(x0), dev(goals))
+    ref, ref_st = ref.cpu().numpy(), ref_st.cpu().numpy()
+    n0 = piped.launch_count()
+    out, st = piped.solve(xu, x0, goals)                               # pageable host buffers
+    assert piped.launch_count() - n0 == 8
+    assert np.array_equal(np.asarray(out), ref) and np.array_equal(np.asarray(st), ref_st)
+    pin = lambda a: torch.tensor(a).pin_memory()
+    out2, st2 = piped.solve(pin(xu), pin(x0), pin(goals))              # page-locked host buffers
+    assert np.array_equal(out2.numpy(), ref) and np.array_equal(st2.numpy(), ref_st)
+    out3, _ = plain.solve(xu, x0, goals)                               # pipeline off: one launch
+    assert np.array_equal(np.asarray(out3), ref)
