@@ -58,7 +58,7 @@ constexpr int KR_HX = 306;    // 12  gx + G'd
 constexpr int KR_STRIDE = 319;
 constexpr int COST_STRIDE = 9;                       // j[6], Q, dQ, R
 // merit scratch per evaluated point (aliases the knot records, dead after the QP solve)
-constexpr int MP_CS = 0, MP_X = 12, MP_S = 30, MP_I = 66, MP_F = 120, MP_STRIDE = 157;
+constexpr int MP_STRIDE = WP_STRIDE;      // 97: axes S, world inertias, bias (i7_wf.cuh: wf_point_forward_dynamics)
 // Riccati work area (first in the layouts: 16-byte aligned)
 constexpr int WK_SIZE = 296;   // two sweep-state blocks (SB_*), see riccati_sweep
 
@@ -811,20 +811,16 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
     const int npts = nc * nw;
     const T* xa = xa_ + 18 * W.k0;
     const T* xb = xb_ + 18 * W.k0;
-    // M0: the point itself (18 numbers) and cos / sin of its joint angles
-    for (int t = tid; t < 18 * npts; t += NT) {
+    // M0: cos / sin of the joint angles of every point (parked in the point's scratch, see wf_point_forward_dynamics)
+    for (int t = tid; t < 6 * npts; t += NT) {
         const int i = t / npts, p = t - i * npts;
         const int ci = p / nw, k = p - ci * nw;
         const T alpha = T(c_alphas[c0 + ci]);
-        const bool has = (i < 12) || (k < nk) || (W.k0 + k < N - 1);     // u of the padded last knot is not part of XU
-        const T x = has ? xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]) : T(0);
+        const T x = xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]);
+        T sn, cs;
+        sincos_t<T>(x, &sn, &cs);
         T* sp = scr + MP_STRIDE * p;
-        sp[MP_X + i] = x;
-        if (i < 6) {
-            T sn, cs;
-            sincos_t<T>(x, &sn, &cs);
-            sp[MP_CS + i] = cs; sp[MP_CS + 6 + i] = sn;
-        }
+        sp[wp_cs(i)] = cs; sp[wp_cs(i) + 1] = sn;
     }
     __syncthreads();
     // M1: per point
@@ -834,31 +830,35 @@ __device__ void merit_points(const Robot<T>& rob, const SolveParams<T>& P, const
         const T alpha = T(c_alphas[c0 + ci]);
         T* sp = scr + MP_STRIDE * p;
         T pee[3];
-        wf_tip<T>(rob, sp + MP_CS, pee);
+        wf_tip_scr<T>(rob, sp, pee);
         const T* goal = M.goals + 3 * kg;
         const T e[3] = {pee[0] - goal[0], pee[1] - goal[1], pee[2] - goal[2]};
         const T Qk = (kg == N - 1) ? P.QN : T(1);
         T* out = comps + 4 * ((cbase + ci) * N + kg);
         out[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+        const bool has_u = (kg < N - 1);                    // the last knot carries no control in XU
+        T qv[6], u[6];
         T vv = T(0), uu = T(0);
 #pragma unroll
-        for (int i = 0; i < 6; ++i) { vv += sp[MP_X + 6 + i] * sp[MP_X + 6 + i]; uu += sp[MP_X + 12 + i] * sp[MP_X + 12 + i]; }
+        for (int i = 0; i < 6; ++i) {
+            qv[i] = xa[18 * k + 6 + i] + alpha * (xb[18 * k + 6 + i] - xa[18 * k + 6 + i]);
+            u[i] = has_u ? xa[18 * k + 12 + i] + alpha * (xb[18 * k + 12 + i] - xa[18 * k + 12 + i]) : T(0);
+            vv += qv[i] * qv[i]; uu += u[i] * u[i];
+        }
         out[1] = P.dQ * vv;
         out[2] = P.R * uu;
         T ie = T(0);
         if (k < nk) {
-            wf_links_all<T>(rob, sp + MP_CS, sp + MP_X + 6, fext, pee, sp + MP_S, sp + MP_I, sp + MP_F);
-            T u[6], qdd[6];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) u[i] = sp[MP_X + 12 + i];
-            wf_forward_dynamics<T>(rob, sp + MP_S, sp + MP_I, sp + MP_F, u, qdd);
+            T qdd[6];
+            wf_point_forward_dynamics<T>(rob, sp, qv, u, fext, pee, qdd);
             T qe = T(0), ve = T(0);
 #pragma unroll
             for (int i = 0; i < 6; ++i) {
+                const T q = xa[18 * k + i] + alpha * (xb[18 * k + i] - xa[18 * k + i]);
                 const T xnq = xa[18 * (k + 1) + i] + alpha * (xb[18 * (k + 1) + i] - xa[18 * (k + 1) + i]);
                 const T xnv = xa[18 * (k + 1) + 6 + i] + alpha * (xb[18 * (k + 1) + 6 + i] - xa[18 * (k + 1) + 6 + i]);
-                const T dq = sp[MP_X + i] + sp[MP_X + 6 + i] * P.dt - xnq;
-                const T dv = sp[MP_X + 6 + i] + qdd[i] * P.dt - xnv;
+                const T dq = q + qv[i] * P.dt - xnq;
+                const T dv = qv[i] + qdd[i] * P.dt - xnv;
                 qe += dq * dq; ve += dv * dv;
             }
             ie = sqrt_t<T>(qe) + sqrt_t<T>(ve);

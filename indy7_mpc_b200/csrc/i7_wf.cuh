@@ -382,4 +382,115 @@ I7_DEV void wf_forward_dynamics(const Robot<T>& rob, const T* S, const T* IW, co
     spd6_solve_factored<T>(A, dinv, qdd);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Forward dynamics of one point by ONE thread with 96 numbers of scratch (line-search points: the smaller the
+// scratch, the more candidates fit one wave).  Same quantities as wf_links_all + wf_forward_dynamics, but the bias
+// b_j = sum_{l >= j} S_j . f0_l is accumulated while the chain is walked, so the link forces are never stored.
+// scr: [S 36 | IW 54 | b 6]; on entry cos q_i, sin q_i sit in scr[wp_cs(i)], scr[wp_cs(i) + 1], slots of the
+// inertias of links 4 and 5 that are first written after the last use of those cos / sin.
+constexpr int WP_S = 0, WP_I = 36, WP_B = 90, WP_STRIDE = 97;      // odd stride: conflict-free across points
+I7_DEV int wp_cs(int i) { return WP_I + 36 + 2 * i + (i >= 2 ? 5 : 0); }
+
+template <typename T> I7_DEV void wf_chain_step_cs(const Robot<T>& rob, int i, T c, T s, T* Rc, T* pc) {
+    T d[3];
+    rot(Rc, rob.p[i], d);
+    pc[0] += d[0]; pc[1] += d[1]; pc[2] += d[2];
+    T E[9], Rn[9];
+    joint_E(rob, i, c, s, E);
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc)
+            Rn[3 * r + cc] = Rc[3 * r] * E[3 * cc] + Rc[3 * r + 1] * E[3 * cc + 1] + Rc[3 * r + 2] * E[3 * cc + 2];
+#pragma unroll
+    for (int r = 0; r < 9; ++r) Rc[r] = Rn[r];
+}
+// position of the last joint frame, cos / sin read from the point's scratch
+template <typename T> I7_DEV void wf_tip_scr(const Robot<T>& rob, const T* scr, T* pee) {
+    T Rc[9] = {T(1), T(0), T(0), T(0), T(1), T(0), T(0), T(0), T(1)};
+    T pc[3] = {T(0), T(0), T(0)};
+#pragma unroll 1
+    for (int i = 0; i < I7_NJ; ++i) wf_chain_step_cs(rob, i, scr[wp_cs(i)], scr[wp_cs(i) + 1], Rc, pc);
+    pee[0] = pc[0]; pee[1] = pc[1]; pee[2] = pc[2];
+}
+
+template <typename T>
+I7_DEV void wf_point_forward_dynamics(const Robot<T>& rob, T* scr, const T* qd, const T* u, const T* fext, const T* pee,
+                                      T* qdd) {
+    T* S = scr + WP_S; T* IWs = scr + WP_I; T* bb = scr + WP_B;
+    {
+        T Rc[9] = {T(1), T(0), T(0), T(0), T(1), T(0), T(0), T(0), T(1)};
+        T pc[3] = {T(0), T(0), T(0)};
+        T v[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+        T a[6] = {T(0), T(0), T(0), -rob.g[0], -rob.g[1], -rob.g[2]};
+#pragma unroll 1
+        for (int l = 0; l < I7_NJ; ++l) {
+            wf_chain_step_cs(rob, l, scr[wp_cs(l)], scr[wp_cs(l) + 1], Rc, pc);
+            const T p[3] = {pc[0] - pee[0], pc[1] - pee[1], pc[2] - pee[2]};
+            T Sl[6] = {Rc[2], Rc[5], Rc[8], T(0), T(0), T(0)};
+            cross3(p, Sl, Sl + 3);
+            T ql = T(0);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) if (r == l) ql = qd[r];          // qd lives in registers
+            T vj[6], c6[6];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) { vj[r] = Sl[r] * ql; v[r] += vj[r]; S[6 * l + r] = Sl[r]; }
+            crm6(v, vj, c6);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) a[r] += c6[r];
+            T IW[9];
+            wf_inertia(rob, l, Rc, p, IW);
+            const T ms = rob.m[l];
+            T f[6], Iv[6];
+            winertia_mul(IW, ms, a, f);
+            winertia_mul(IW, ms, v, Iv);
+            crf<T, true>(v, Iv, f);
+            if (l == I7_NJ - 1 && fext) {
+                T nw[3], fw[3];
+                rot(Rc, fext, nw);
+                rot(Rc, fext + 3, fw);
+#pragma unroll
+                for (int r = 0; r < 3; ++r) { f[r] -= nw[r]; f[3 + r] -= fw[r]; }
+            }
+#pragma unroll
+            for (int r = 0; r < 9; ++r) IWs[9 * l + r] = IW[r];
+            // b_j += S_j . f_l for every joint j <= l that carries link l
+            T bl = T(0);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) bl += Sl[r] * f[r];
+            bb[l] = bl;
+#pragma unroll 1
+            for (int j = 0; j < l; ++j) {
+                T d = T(0);
+#pragma unroll
+                for (int r = 0; r < 6; ++r) d += S[6 * j + r] * f[r];
+                bb[j] += d;
+            }
+        }
+    }
+    T A[6][6], dinv[6];
+    T IC[9] = {T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0), T(0)};
+    T mc = T(0);
+#pragma unroll
+    for (int j = I7_NJ - 1; j >= 0; --j) {
+#pragma unroll
+        for (int r = 0; r < 9; ++r) IC[r] += IWs[9 * j + r];
+        mc += rob.m[j];
+        T Sj[6], y[6];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) Sj[r] = S[6 * j + r];
+        winertia_mul(IC, mc, Sj, y);
+        qdd[j] = u[j] - bb[j];
+#pragma unroll
+        for (int i = 0; i <= j; ++i) {
+            T d = T(0);
+#pragma unroll
+            for (int r = 0; r < 6; ++r) d += S[6 * i + r] * y[r];
+            A[j][i] = d;
+        }
+    }
+    spd6_factor<T>(A, dinv);
+    spd6_solve_factored<T>(A, dinv, qdd);
+}
+
 }  // namespace i7
