@@ -83,9 +83,9 @@ typedef struct {
     double mu;              /* merit penalty, src/osqp_sqp.py:50: 10 */
     double step_tol;        /* src/osqp_sqp.py:90: 1e-3 */
     int32_t threads;        /* CTA size of the one-CTA-per-problem kernel: 0 = choose from batch (384 up to 148 problems, else 256 with two CTAs per SM); 128 | 256 | 384 */
-    int32_t cluster;        /* i7_solve kernel form: 0 = auto (cluster of 8 CTAs per problem when batch * 8 fits the SMs,
-                               i.e. the latency regime; one CTA per problem otherwise), 1 = always one CTA per problem,
-                               8 = always the cluster form */
+    int32_t cluster;        /* i7_solve kernel form: 0 = auto (the largest cluster of 8, 4 or 2 CTAs per problem for which
+                               the whole batch is co-resident, else one CTA per problem), 1 = always one CTA per
+                               problem, 2 | 4 | 8 = always that cluster form */
     i7_model model;
 } i7_config;
 

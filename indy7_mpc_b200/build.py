@@ -23,8 +23,10 @@ for tname, t in (("f64", "double"), ("f32", "float")):
             UNITS.append((f"i7_sqp_{tname}_{nt}_{sp[0]}", "i7_sqp_inst.cu", [f"-DI7_T={t}", f"-DI7_NT={nt}", f"-DI7_SPILL={sp}"]))
 
 
-UNITS.append(("i7_cluster_f64", "i7_cluster_inst.cu", ["-DI7_T=double", "-DI7_CLUSTER_DEFINE_LAYOUT"]))
-UNITS.append(("i7_cluster_f32", "i7_cluster_inst.cu", ["-DI7_T=float"]))
+for _cl in (8, 4, 2):
+    UNITS.append((f"i7_cluster_f64_{_cl}", "i7_cluster_inst.cu",
+                  ["-DI7_T=double", f"-DI7_CL={_cl}"] + (["-DI7_CLUSTER_DEFINE_LAYOUT"] if _cl == 8 else [])))
+    UNITS.append((f"i7_cluster_f32_{_cl}", "i7_cluster_inst.cu", ["-DI7_T=float", f"-DI7_CL={_cl}"]))
 
 
 def nvcc_path():

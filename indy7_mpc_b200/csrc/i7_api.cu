@@ -37,6 +37,7 @@ struct i7_handle {
     int threads = 0;
     int max_smem_optin = 0;
     bool use_cluster = false;    // i7_solve runs the cluster-per-problem (latency) kernel
+    int cluster_size = 0;        // CTAs per problem of that kernel: 8, 4 or 2
     int cluster_smem_bytes = 0;
     void* d_xbuf = nullptr;      // exchange buffer of the cluster kernel (batch x cluster_xbuf_len(N))
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -161,7 +162,11 @@ template <typename T>
 i7_status launch_sqp(i7_handle* h, const i7::Robot<T>& rob, i7::SolveParams<T>& P, cudaStream_t s, size_t first_problem = 0) {
     P.spill_ws = h->spill ? (T*)h->d_spill + first_problem * (size_t)i7::make_layout(h->cfg.N, true).reg_size : nullptr;
     cudaError_t e;
-    if (h->use_cluster && P.mode == i7::MODE_SOLVE) e = i7::launch_sqp_cluster<T>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
+    if (h->use_cluster && P.mode == i7::MODE_SOLVE) {
+        if (h->cluster_size == 8) e = i7::launch_sqp_cluster<T, 8>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
+        else if (h->cluster_size == 4) e = i7::launch_sqp_cluster<T, 4>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
+        else e = i7::launch_sqp_cluster<T, 2>(rob, P, (T*)h->d_xbuf, h->cluster_smem_bytes, s);
+    }
     else if (h->threads == 384) e = h->spill ? i7::launch_sqp_cta<T, 384, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 384, false>(rob, P, h->smem_bytes, s);
     else if (h->threads == 256) e = h->spill ? i7::launch_sqp_cta<T, 256, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 256, false>(rob, P, h->smem_bytes, s);
     else e = h->spill ? i7::launch_sqp_cta<T, 128, true>(rob, P, h->smem_bytes, s) : i7::launch_sqp_cta<T, 128, false>(rob, P, h->smem_bytes, s);
@@ -422,34 +427,38 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
         I7_CUDA_C(cudaMalloc(&h->d_spill, (size_t)cfg->batch * L.reg_size * h->esize));
     }
     h->smem_bytes = L.total * h->esize;
-    // latency regime: a cluster of 8 CTAs per problem when every cluster is resident at once
+    // latency regime: a cluster of 8, 4 or 2 CTAs per problem — the largest cluster size for which every cluster of the
+    // batch is resident at once (clusters are placed per GPC, so that is fewer than SMs / size; a second wave of
+    // clusters is slower than the CTA form).  cfg->cluster: 0 automatic, 1 CTA form, 2 | 4 | 8 forced.
     {
-        int sms = 0;
-        I7_CUDA_C(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device));
-        if (cfg->cluster != 0 && cfg->cluster != 1 && cfg->cluster != i7::kClusterSize) { h->err = "cluster must be 0, 1 or 8"; return fail(I7_ERR_INVALID); }
-        h->use_cluster = cfg->cluster == i7::kClusterSize || (cfg->cluster == 0 && cfg->batch * i7::kClusterSize <= sms);
-        if (h->use_cluster) {
-            int ccap = 0;
-            cudaError_t ec = cfg->dtype == I7_F64 ? i7::smem_cap_sqp_cluster<double>(h->max_smem_optin, &ccap)
-                                                  : i7::smem_cap_sqp_cluster<float>(h->max_smem_optin, &ccap);
-            if (ec != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute(cluster): ") + cudaGetErrorString(ec); return fail(I7_ERR_CUDA); }
-            h->cluster_smem_bytes = i7::cluster_smem_len(cfg->N) * h->esize;
-            if (h->cluster_smem_bytes > ccap) {
-                if (cfg->cluster == i7::kClusterSize) { h->err = "horizon too long for the cluster kernel"; return fail(I7_ERR_UNSUPPORTED); }
-                h->use_cluster = false;
-            } else if (cfg->cluster == 0) {
-                // automatic choice: only while every cluster is resident at once (a second wave of clusters is slower
-                // than the CTA form); clusters are placed per GPC, so the limit is below SMs / 8 (15 on B200)
-                int nact = 0;
-                cudaError_t eo = cfg->dtype == I7_F64 ? i7::max_active_sqp_clusters<double>(h->cluster_smem_bytes, &nact)
-                                                      : i7::max_active_sqp_clusters<float>(h->cluster_smem_bytes, &nact);
-                if (eo != cudaSuccess) { (void)cudaGetLastError(); nact = sms / i7::kClusterSize - 3; }
-                if (cfg->batch > nact) h->use_cluster = false;
-            }
-            if (h->use_cluster) {
-                I7_CUDA_C(cudaMalloc(&h->d_xbuf, (size_t)cfg->batch * i7::cluster_xbuf_len(cfg->N) * h->esize));
-            }
+        if (cfg->cluster != 0 && cfg->cluster != 1 && cfg->cluster != 2 && cfg->cluster != 4 && cfg->cluster != 8) {
+            h->err = "cluster must be 0, 1, 2, 4 or 8"; return fail(I7_ERR_INVALID);
         }
+        const bool f64 = cfg->dtype == I7_F64;
+        const int sizes[3] = {8, 4, 2};
+        for (int si = 0; si < 3 && !h->use_cluster && cfg->cluster != 1; ++si) {
+            const int cl = sizes[si];
+            if (cfg->cluster != 0 && cfg->cluster != cl) continue;
+            int ccap = 0, nact = 0;
+            cudaError_t ec = cl == 8 ? (f64 ? i7::smem_cap_sqp_cluster<double, 8>(h->max_smem_optin, &ccap) : i7::smem_cap_sqp_cluster<float, 8>(h->max_smem_optin, &ccap))
+                           : cl == 4 ? (f64 ? i7::smem_cap_sqp_cluster<double, 4>(h->max_smem_optin, &ccap) : i7::smem_cap_sqp_cluster<float, 4>(h->max_smem_optin, &ccap))
+                                     : (f64 ? i7::smem_cap_sqp_cluster<double, 2>(h->max_smem_optin, &ccap) : i7::smem_cap_sqp_cluster<float, 2>(h->max_smem_optin, &ccap));
+            if (ec != cudaSuccess) { h->err = std::string("cudaFuncSetAttribute(cluster): ") + cudaGetErrorString(ec); return fail(I7_ERR_CUDA); }
+            const int bytes = i7::cluster_smem_len(cfg->N, cl) * h->esize;
+            if (bytes > ccap) {
+                if (cfg->cluster == cl) { h->err = "horizon too long for the cluster kernel"; return fail(I7_ERR_UNSUPPORTED); }
+                continue;
+            }
+            if (cfg->cluster == 0) {
+                cudaError_t eo = cl == 8 ? (f64 ? i7::max_active_sqp_clusters<double, 8>(bytes, &nact) : i7::max_active_sqp_clusters<float, 8>(bytes, &nact))
+                               : cl == 4 ? (f64 ? i7::max_active_sqp_clusters<double, 4>(bytes, &nact) : i7::max_active_sqp_clusters<float, 4>(bytes, &nact))
+                                         : (f64 ? i7::max_active_sqp_clusters<double, 2>(bytes, &nact) : i7::max_active_sqp_clusters<float, 2>(bytes, &nact));
+                if (eo != cudaSuccess) { (void)cudaGetLastError(); nact = 0; }
+                if (cfg->batch > nact) continue;
+            }
+            h->use_cluster = true; h->cluster_size = cl; h->cluster_smem_bytes = bytes;
+        }
+        if (h->use_cluster) I7_CUDA_C(cudaMalloc(&h->d_xbuf, (size_t)cfg->batch * i7::cluster_xbuf_len(cfg->N) * h->esize));
     }
     const size_t B = cfg->batch, N = cfg->N, es = h->esize;
     // worst case over all entry points: inputs xu, x0, goals(6), xu_full; outputs of the dump mode

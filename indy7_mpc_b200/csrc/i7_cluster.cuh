@@ -20,12 +20,13 @@
 
 namespace i7 {
 
-constexpr int CL = 8;          // CTAs per cluster = per problem (portable maximum)
+// CTAs per cluster = per problem: template parameter CL in {8 (portable maximum), 4, 2}; the smaller clusters serve
+// batches that no longer fit the device as clusters of 8 (batch 16 / 32 / 64)
 constexpr int CL_NT = 384;     // threads per CTA
 
-__host__ __device__ inline int cluster_merit_cap(int chunk) { return chunk <= 4 ? 8 : (chunk <= 8 ? 4 : 2); }
+__host__ __device__ inline int cluster_merit_cap(int chunk) { return chunk <= 8 ? 8 : (chunk <= 16 ? 4 : 2); }
 struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, aux, pair, gains, total, chunk; };
-__host__ __device__ inline CLayout make_clayout(int N) {
+__host__ __device__ inline CLayout make_clayout(int N, int CL) {
     CLayout L;
     L.chunk = (N + CL - 1) / CL;
     // knot records, later the merit scratch (as many line-search candidates per wave as fit: 8 up to N = 32)
@@ -54,7 +55,7 @@ __host__ __device__ inline int xbuf_zu(int N) { return RIC_STRIDE * N + 12 * N; 
 __host__ __device__ inline int xbuf_mc(int N) { return RIC_STRIDE * N + 18 * N; }
 __host__ __device__ inline int xbuf_size(int N) { return RIC_STRIDE * N + 18 * N + 36 * N; }
 
-template <typename T>
+template <typename T, int CL>
 __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(CL_NT)
 sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__ SolveParams<T> P, T* xbuf_all) {
     constexpr int NT = CL_NT;
@@ -66,7 +67,7 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
     const int rank = (int)cluster.block_rank();
     const int b = blockIdx.x / CL;
     const int nz = 18 * N - 6;
-    const CLayout L = make_clayout(N);
+    const CLayout L = make_clayout(N, CL);
     Ptrs<T> M;
     M.xu = sm + L.xu; M.z = sm + L.z; M.goals = sm + L.goals; M.x0 = sm + L.x0; M.cost = sm + L.cost;
     M.work = sm + L.work; M.ls = sm + L.ls; M.kr = sm + L.kr; M.aux = sm + L.aux; M.pair = L.pair >= 0 ? sm + L.pair : nullptr; M.merit_cap = cluster_merit_cap(L.chunk);

@@ -12,12 +12,13 @@ template <typename T, int NT, bool SPILL> cudaError_t launch_sqp_cta(const Robot
 // raises the dynamic shared-memory cap of that instance to everything the SM offers; returns the cap
 template <typename T, int NT, bool SPILL> cudaError_t smem_cap_sqp_cta(int optin_bytes, int* cap);
 
-// cluster-per-problem kernel (latency form): grid = batch x 8 CTAs; xbuf = batch x cluster_xbuf_len(N) exchange buffer
-template <typename T> cudaError_t launch_sqp_cluster(const Robot<T>& rob, const SolveParams<T>& P, T* xbuf, int smem_bytes,
+// cluster-per-problem kernel (latency form): grid = batch x CL CTAs (CL = 8, 4 or 2); xbuf = batch x cluster_xbuf_len(N)
+// exchange buffer
+template <typename T, int CL> cudaError_t launch_sqp_cluster(const Robot<T>& rob, const SolveParams<T>& P, T* xbuf, int smem_bytes,
                                                      cudaStream_t s);
-template <typename T> cudaError_t smem_cap_sqp_cluster(int optin_bytes, int* cap);
-template <typename T> cudaError_t max_active_sqp_clusters(int smem_bytes, int* n);     // co-resident clusters
-int cluster_smem_len(int N);     // shared-memory elements per CTA of the cluster kernel
+template <typename T, int CL> cudaError_t smem_cap_sqp_cluster(int optin_bytes, int* cap);
+template <typename T, int CL> cudaError_t max_active_sqp_clusters(int smem_bytes, int* n);     // co-resident clusters
+int cluster_smem_len(int N, int CL);     // shared-memory elements per CTA of the cluster kernel
 int cluster_xbuf_len(int N);     // exchange-buffer elements per problem
 constexpr int kClusterSize = 8;
 

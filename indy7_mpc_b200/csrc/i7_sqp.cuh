@@ -250,7 +250,10 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
         }
     } else {
     for (int t = tid; t < 12 * np; t += NT) {
-        const int col = t / np, k = t - col * np;
+        // a column of joint j costs ~ (6 - j) link terms and a warp owns whole columns (slots w, w + NT/32, ...):
+        // the order below gives every warp of a 256-thread CTA at most 6 units of work (10 in natural order)
+        const int slot = t / np, k = t - slot * np;
+        const int col = (int)((0xB9A471605382ull >> (4 * slot)) & 15);       // q2 v2 q3 q5 q0 v0 q1 v1 q4 v4 v3 v5
         if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
         // the raw columns land in the GQ / GV slots, which hold cos / sin and the origin until here: every column

@@ -44,7 +44,7 @@ class Engine:
         cfg.N, cfg.batch, cfg.dtype, cfg.device = self.N, self.batch, (_lib.I7_F64 if dtype == "fp64" else _lib.I7_F32), self.device
         cfg.dt, cfg.dQ_cost, cfg.R_cost, cfg.QN_cost, cfg.eps = float(dt), float(dQ_cost), float(R_cost), float(QN_cost), float(eps)
         cfg.regularize, cfg.max_qp, cfg.mu, cfg.step_tol, cfg.threads = int(bool(regularize)), int(max_qp), float(mu), float(step_tol), int(threads)
-        cfg.cluster = int(cluster)      # 0 auto, 1 one CTA per problem, 8 cluster of 8 CTAs per problem (latency form)
+        cfg.cluster = int(cluster)      # 0 auto, 1 one CTA per problem, 2|4|8 cluster of that many CTAs per problem (latency forms)
         cfg.model = model.to_c()
         self._h = C.c_void_p()
         rc = self.lib.i7_create(C.byref(cfg), C.byref(self._h))

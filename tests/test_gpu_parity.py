@@ -340,6 +340,27 @@ def test_cluster_kernel_horizons_and_fp32(pkg, oracle_model, N, dtype, tol):
             assert rel(out[b], want) < tol, (b, rel(out[b], want))
 
 
+@pytest.mark.parametrize("cl,N,dtype", [(4, 32, "fp64"), (2, 32, "fp64"), (4, 13, "fp64"), (2, 64, "fp64"),
+                                        (4, 128, "fp64"), (4, 32, "fp32"), (2, 32, "fp32")])
+def test_smaller_clusters_equal_cta_kernel(pkg, oracle_model, cl, N, dtype):
+    """Clusters of 4 and 2 CTAs per problem (mid-size batches): same decisions and trajectories as the CTA form."""
+    xu, x0, goals = make_cases(oracle_model, 6, N=N, seed=31)
+    fext = np.zeros((6, 6)); fext[1:, :3] = np.random.default_rng(4).normal(0, 3, (5, 3))
+    eng = pkg.Engine(N=N, batch=6, dtype=dtype, cluster=cl)
+    cta = pkg.Engine(N=N, batch=6, dtype=dtype, cluster=1)
+    for e in (eng, cta):
+        e.set_external_wrench(fext)
+    out, st = eng.solve(xu, x0, goals)
+    ref, sr = cta.solve(xu, x0, goals)
+    if dtype == "fp64":
+        assert np.array_equal(np.asarray(st)[:, :6], np.asarray(sr)[:, :6])
+        assert rel(out, ref) < 1e-10
+    else:
+        assert rel(out, ref) < 2e-4
+    out2, st2 = eng.solve(xu, x0, goals)
+    assert np.array_equal(np.asarray(out), np.asarray(out2))
+
+
 def test_batch_sample_mpc_driver_matches_oracle(pkg, oracle_model):
     """Closed loop of the batched sampled-wrench driver (src/gato_mpc_batch_sample.py:106-300): same seeds, same
     hypothesis selected at every step, same plant path as the CPU restatement (float32 hand-over included)."""
