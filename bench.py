@@ -408,7 +408,7 @@ def run_b200(args):
 
 
 def eng_threads(eng, B, args):
-    return args.threads if args.threads else (384 if B <= 148 else 256)
+    return eng.kernel_form()[0]
 
 
 def single_problem_latency(args, local):

@@ -130,6 +130,10 @@ i7_status i7_solve(i7_handle* h, int32_t batch, const void* xu_in, const void* x
 i7_status i7_last_solve_time_us(i7_handle* h, double* us);
 /* Number of kernel launches issued by this handle so far. */
 int64_t i7_launch_count(const i7_handle* h);
+/* The kernel form i7_solve uses for this handle: threads per CTA, CTAs per problem (1 = CTA form; 2, 4, 8 = cluster
+ * forms) and dynamic shared memory per CTA in bytes.  (The reference picks its kernel at compile time through the
+ * SQPSolverfloat_<B> template instances, gato_controller.py:53-68; here it is a run-time choice, reported for logs.) */
+i7_status i7_kernel_form(const i7_handle* h, int32_t* threads, int32_t* ctas_per_problem, int32_t* smem_bytes);
 
 /* One rk4 plant step of length dt per lane under that lane's external wrench (src/utils.py:3-18):
  * x, u: batch x 12 / batch x 6 (or a single row broadcast to every lane when bcast != 0); out: batch x 12. */

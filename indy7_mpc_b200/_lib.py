@@ -41,6 +41,7 @@ SYMBOLS = {
     "i7_solve": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "i7_last_solve_time_us": (_i32, [_vp, C.POINTER(_dbl)]),
     "i7_launch_count": (C.c_int64, [_vp]),
+    "i7_kernel_form": (C.c_int, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "i7_pack_best": (_i32, [_vp, _i32, _vp, _vp, _i32, _vp, _vp]),
     "i7_reduce_best": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp]),
     "i7_measure_fma_peak": (_i32, [_vp, C.POINTER(_dbl)]),

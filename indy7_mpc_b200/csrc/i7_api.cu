@@ -406,7 +406,18 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
 #define I7_CUDA_C(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(I7_ERR_CUDA); } } while (0)
     I7_CUDA_C(cudaSetDevice(cfg->device));
     I7_CUDA_C(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
-    h->threads = cfg->threads ? cfg->threads : (cfg->batch <= 148 ? 384 : 256);
+    // threads per CTA of the throughput form: 384 while every problem has an SM to itself; for bigger batches 128 when
+    // shared memory lets two or more CTAs share an SM (more independent problems per SM beats wider CTAs: measured
+    // 1.60 -> 1.27 ms for 4096 fp32 problems, four CTAs per SM), 256 when only one fits (long horizons)
+    {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
+        const size_t per_sm = (size_t)h->max_smem_optin + 1024;
+        size_t need = (size_t)i7::make_layout(cfg->N, false).total * h->esize + 1024;
+        if (need > per_sm) need = (size_t)i7::make_layout(cfg->N, true).total * h->esize + 1024;
+        const int fit = (int)(per_sm / need);
+        h->threads = cfg->threads ? cfg->threads : (cfg->batch <= sms ? 384 : (fit >= 2 ? 128 : 256));
+    }
     if (h->threads != 128 && h->threads != 256 && h->threads != 384) { h->err = "threads must be 0, 128, 256 or 384"; return fail(I7_ERR_INVALID); }
     int cap = 0;
     {
@@ -540,6 +551,14 @@ i7_status i7_last_solve_time_us(i7_handle* h, double* us) {
 }
 
 int64_t i7_launch_count(const i7_handle* h) { return h ? h->launches : 0; }
+
+i7_status i7_kernel_form(const i7_handle* h, int32_t* threads, int32_t* ctas_per_problem, int32_t* smem_bytes) {
+    if (!h) return I7_ERR_INVALID;
+    if (threads) *threads = h->use_cluster ? i7::kClusterThreads : h->threads;
+    if (ctas_per_problem) *ctas_per_problem = h->use_cluster ? h->cluster_size : 1;
+    if (smem_bytes) *smem_bytes = h->use_cluster ? h->cluster_smem_bytes : h->smem_bytes;
+    return I7_OK;
+}
 
 i7_status i7_pack_best(i7_handle* h, int32_t batch, const void* stats, const void* xu, int32_t index_offset,
                        void* packed, void* stream) {

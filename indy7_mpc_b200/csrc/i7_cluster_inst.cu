@@ -8,6 +8,8 @@
 
 namespace i7 {
 
+static_assert(CL_NT == kClusterThreads, "i7_launch.h: kClusterThreads out of date");
+
 template <>
 cudaError_t launch_sqp_cluster<I7_T, I7_CL>(const Robot<I7_T>& rob, const SolveParams<I7_T>& P, I7_T* xbuf, int smem_bytes,
                                      cudaStream_t s) {

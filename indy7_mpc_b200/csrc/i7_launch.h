@@ -21,5 +21,6 @@ template <typename T, int CL> cudaError_t max_active_sqp_clusters(int smem_bytes
 int cluster_smem_len(int N, int CL);     // shared-memory elements per CTA of the cluster kernel
 int cluster_xbuf_len(int N);     // exchange-buffer elements per problem
 constexpr int kClusterSize = 8;
+constexpr int kClusterThreads = 384;     // = CL_NT of i7_cluster.cuh (checked in i7_cluster_inst.cu)
 
 }  // namespace i7

@@ -973,7 +973,9 @@ template <typename T, typename Lay> __device__ void dump_qp(const SolveParams<T>
 
 // -----------------------------------------------------------------------------------------------------------
 template <typename T, int NT, bool SPILL>
-__global__ void __launch_bounds__(NT, NT == 256 ? 2 : 1) sqp_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__ SolveParams<T> P) {
+// resident CTAs per SM the register budget is sized for: 2 (shared memory allows no more in fp64); fp32 records are half
+// the size, so four 128-thread CTAs fit
+__global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) == 4) ? 4 : 1)) sqp_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__ SolveParams<T> P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* sm = reinterpret_cast<T*>(smem_raw);
     const int tid = threadIdx.x, N = P.N;

@@ -273,5 +273,11 @@ class Engine:
         self._check(self.lib.i7_last_solve_time_us(self._h, C.byref(us)))
         return us.value
 
+    def kernel_form(self):
+        """(threads per CTA, CTAs per problem, shared-memory bytes per CTA) of the i7_solve kernel of this handle."""
+        t, c, m = C.c_int32(), C.c_int32(), C.c_int32()
+        self._check(self.lib.i7_kernel_form(self._h, C.byref(t), C.byref(c), C.byref(m)))
+        return t.value, c.value, m.value
+
     def launch_count(self):
         return int(self.lib.i7_launch_count(self._h))
