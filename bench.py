@@ -218,6 +218,8 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL writes its version / debug lines to stdout; keep stdout for the ONE JSON line of the contract
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl_debug_%h_%p.log")
         dist.init_process_group("nccl", device_id=dev)
     N, K, W = args.horizon, args.steps, args.warmup
     assert args.batch % world == 0, "batch must divide across ranks"
