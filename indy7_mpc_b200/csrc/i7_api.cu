@@ -134,18 +134,37 @@ struct Stage {
         out_off += (bytes + 15) & ~size_t(15);
         return d;
     }
+    // pageable buffers sit back to back in the pinned mirror: runs of them travel as ONE copy (a single-problem solve
+    // is 1 transfer in and 1 out instead of 3 + 2; each call costs microseconds of host time on the latency path)
+    static size_t al(size_t b) { return (b + 15) & ~size_t(15); }
     i7_status flush_in(cudaStream_t s) {
-        for (int i = 0; i < nin; ++i) {
-            const void* src = ins[i].pinned ? ins[i].user : (const void*)((char*)h->in.host + ins[i].off);
-            I7_CUDA(h, cudaMemcpyAsync((char*)h->in.dev + ins[i].off, src, ins[i].bytes, cudaMemcpyHostToDevice, s));
+        for (int i = 0; i < nin;) {
+            if (ins[i].pinned) {
+                I7_CUDA(h, cudaMemcpyAsync((char*)h->in.dev + ins[i].off, ins[i].user, ins[i].bytes, cudaMemcpyHostToDevice, s));
+                ++i;
+                continue;
+            }
+            int j = i;
+            while (j + 1 < nin && !ins[j + 1].pinned && ins[j + 1].off == ins[j].off + al(ins[j].bytes)) ++j;
+            const size_t span = ins[j].off + ins[j].bytes - ins[i].off;
+            I7_CUDA(h, cudaMemcpyAsync((char*)h->in.dev + ins[i].off, (char*)h->in.host + ins[i].off, span, cudaMemcpyHostToDevice, s));
+            i = j + 1;
         }
         return I7_OK;
     }
     i7_status flush_out(cudaStream_t s) {
         if (!nout) return I7_OK;
-        for (int i = 0; i < nout; ++i) {
-            void* dst = outs[i].pinned ? outs[i].user : (void*)((char*)h->out.host + outs[i].off);
-            I7_CUDA(h, cudaMemcpyAsync(dst, (char*)h->out.dev + outs[i].off, outs[i].bytes, cudaMemcpyDeviceToHost, s));
+        for (int i = 0; i < nout;) {
+            if (outs[i].pinned) {
+                I7_CUDA(h, cudaMemcpyAsync(outs[i].user, (char*)h->out.dev + outs[i].off, outs[i].bytes, cudaMemcpyDeviceToHost, s));
+                ++i;
+                continue;
+            }
+            int j = i;
+            while (j + 1 < nout && !outs[j + 1].pinned && outs[j + 1].off == outs[j].off + al(outs[j].bytes)) ++j;
+            const size_t span = outs[j].off + outs[j].bytes - outs[i].off;
+            I7_CUDA(h, cudaMemcpyAsync((char*)h->out.host + outs[i].off, (char*)h->out.dev + outs[i].off, span, cudaMemcpyDeviceToHost, s));
+            i = j + 1;
         }
         I7_CUDA(h, cudaStreamSynchronize(s));
         for (int i = 0; i < nout; ++i)

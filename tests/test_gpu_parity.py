@@ -448,3 +448,30 @@ def test_host_pipeline_is_bitwise_identical(pkg, oracle_model, monkeypatch):
     assert np.array_equal(out2.numpy(), ref) and np.array_equal(st2.numpy(), ref_st)
     out3, _ = plain.solve(xu, x0, goals)                               # pipeline off: one launch
     assert np.array_equal(np.asarray(out3), ref)
+
+
+def test_ragged_batch_nonfinite_and_failed_linesearch(pkg, oracle_model):
+    """Edge cases of sqp(): fewer problems than the handle was created for; a non-finite lane (status 2) does not
+    disturb its neighbours; an iterate the line search cannot improve returns unchanged with alpha = 0 and
+    status 1, as src/osqp_sqp.py:72,81-82 (not an error)."""
+    xu, x0, goals = make_cases(oracle_model, 5, N=32, seed=41)
+    eng = pkg.Engine(N=32, batch=8, dtype="fp64", cluster=1)
+    full, st_full = (np.asarray(a) for a in eng.solve(xu, x0, goals))
+    part, st_part = (np.asarray(a) for a in eng.solve(xu[:3], x0[:3], goals[:3]))        # ragged: 3 of 8
+    assert part.shape == (3, 570) and np.array_equal(part, full[:3]) and np.array_equal(st_part, st_full[:3])
+    bad = xu.copy(); bad[2, 40] = np.nan
+    out, st = (np.asarray(a) for a in eng.solve(bad, x0, goals))
+    assert st[2, 3] == 2 and np.array_equal(out[[0, 1, 3, 4]], full[[0, 1, 3, 4]])
+    # a converged iterate: solve until the accepted step vanishes, then once more
+    z, g, x = xu[1:2], goals[1:2], x0[1:2]
+    for _ in range(60):
+        z, s = (np.asarray(a) for a in eng.solve(z, x, g))
+        if s[0, 3] == 1:
+            break
+    if s[0, 3] == 1:                                     # line search failed: alpha = 0 recorded, iterate unchanged
+        again, s2 = (np.asarray(a) for a in eng.solve(z, x, g))
+        assert s2[0, 3] == 1 and s2[0, 4] == 0 and np.array_equal(again, z)
+    from oracle.osqp_solver import OSQPSolver as OS
+    from oracle.osqp_sqp import SQP_OSQP as OQ
+    ref = OQ(OS(oracle_model, N=32, qp_backend="kkt")).sqp(x[0], g[0], z[0])
+    assert rel(np.asarray(eng.solve(z, x, g)[0])[0], ref) < 1e-6
