@@ -48,6 +48,7 @@ struct i7_handle {
     cudaEvent_t pipe_fork = nullptr, pipe_join[kPipeStreams] = {nullptr, nullptr, nullptr};
     cudaEvent_t pipe_done[kPipeMaxChunks] = {};
     int pipe_chunk = 0;
+    int direct_max_batch = 0;    // host-buffer solves up to this batch use mapped host memory instead of copies
     bool timed = false;
     int64_t launches = 0;
     std::string err;
@@ -111,7 +112,11 @@ i7_status arena_reserve(i7_handle* h, Arena& a, size_t bytes) {
 struct Stage {
     size_t in_off = 0, out_off = 0;
     i7_handle* h;
-    explicit Stage(i7_handle* h_) : h(h_) {}
+    // direct: the kernel reads its inputs from and writes its results to the page-locked mirror itself (mapped host
+    // memory, same address on the device under unified addressing) — no copy operations in the stream.  For a handful
+    // of problems the two copies cost more stream latency (~10 us) than the few KB cost over PCIe inside the kernel.
+    bool direct = false;
+    explicit Stage(i7_handle* h_, bool direct_ = false) : h(h_), direct(direct_) {}
     struct Xfer { void* user; size_t off; size_t bytes; bool pinned; };
     Xfer ins[8], outs[10];
     int nin = 0, nout = 0;
@@ -119,9 +124,9 @@ struct Stage {
         if (!p) return nullptr;
         const int kind = ptr_kind(p);
         if (kind == 1) return p;
-        if (kind == 0) std::memcpy((char*)h->in.host + in_off, p, bytes);
-        ins[nin++] = Xfer{const_cast<void*>(p), in_off, bytes, kind == 2};
-        const void* d = (char*)h->in.dev + in_off;
+        if (kind == 0 || direct) std::memcpy((char*)h->in.host + in_off, p, bytes);
+        if (!direct) ins[nin++] = Xfer{const_cast<void*>(p), in_off, bytes, kind == 2};
+        const void* d = (char*)(direct ? h->in.host : h->in.dev) + in_off;
         in_off += (bytes + 15) & ~size_t(15);
         return d;
     }
@@ -129,8 +134,8 @@ struct Stage {
         if (!p) return nullptr;
         const int kind = ptr_kind(p);
         if (kind == 1) return p;
-        outs[nout++] = Xfer{p, out_off, bytes, kind == 2};
-        void* d = (char*)h->out.dev + out_off;
+        outs[nout++] = Xfer{p, out_off, bytes, kind == 2 && !direct};
+        void* d = (char*)(direct ? h->out.host : h->out.dev) + out_off;
         out_off += (bytes + 15) & ~size_t(15);
         return d;
     }
@@ -154,7 +159,7 @@ struct Stage {
     }
     i7_status flush_out(cudaStream_t s) {
         if (!nout) return I7_OK;
-        for (int i = 0; i < nout;) {
+        for (int i = 0; i < nout && !direct;) {
             if (outs[i].pinned) {
                 I7_CUDA(h, cudaMemcpyAsync(outs[i].user, (char*)h->out.dev + outs[i].off, outs[i].bytes, cudaMemcpyDeviceToHost, s));
                 ++i;
@@ -235,7 +240,7 @@ i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     const int N = h->cfg.N;
     const size_t nz = h->nz, B = c.batch, es = sizeof(T);
     I7_CUDA(h, cudaSetDevice(h->cfg.device));
-    Stage st(h);
+    Stage st(h, c.mode == i7::MODE_SOLVE && c.batch <= h->direct_max_batch);
     i7::SolveParams<T> P;
     base_params<T>(h, P, c.batch, c.goal_stride, c.mode);
     P.xu_in = (const T*)st.in(c.xu, B * nz * es);
@@ -500,6 +505,12 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
     I7_CUDA_C(cudaMemset(h->d_fext, 0, B * 6 * es));
     I7_CUDA_C(cudaEventCreate(&h->ev0));
     I7_CUDA_C(cudaEventCreate(&h->ev1));
+    {
+        const char* env = std::getenv("I7_DIRECT_MAX_BATCH");
+        int can_map = 0;
+        cudaDeviceGetAttribute(&can_map, cudaDevAttrCanMapHostMemory, cfg->device);
+        h->direct_max_batch = can_map ? (env ? std::atoi(env) : 8) : 0;
+    }
     // chunked host pipeline for big batches (I7_PIPE_CHUNK problems per chunk; 0 disables)
     {
         const char* env = std::getenv("I7_PIPE_CHUNK");

@@ -87,16 +87,38 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
     __shared__ int s_flag;
     long long* prof = (P.prof && rank == 0) ? P.prof + (size_t)b * 32 : nullptr;
 
-    // ---- load inputs (every CTA keeps the whole iterate; it is 4.6 KB) ----
-    for (int t = tid; t < nz; t += NT) M.xu[t] = P.xu_in[(size_t)b * nz + t];
-    if (tid < 6) M.xu[nz + tid] = T(0);                          // padded u_{N-1}
-    for (int t = tid; t < 18 * N; t += NT) M.z[t] = T(0);
-    for (int t = tid; t < 3 * N; t += NT) {
-        const int k = t / 3, a = t - 3 * k;
-        M.goals[t] = P.goals[(size_t)b * N * P.goal_stride + k * P.goal_stride + a];
+    // ---- load inputs (every CTA keeps the whole iterate; it is 4.6 KB).  All global loads are issued before the first
+    //      use: the inputs may sit in mapped HOST memory (small host-buffer solves), where a dependent load-store
+    //      sequence per element would cost one PCIe round trip each ----
+    {
+        const T* gin = P.goals + (size_t)b * N * P.goal_stride;
+        T rg[2] = {T(0), T(0)};
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int t = tid + q * NT;
+            if (t < 3 * N) { const int k = t / 3; rg[q] = gin[k * P.goal_stride + (t - 3 * k)]; }
+        }
+        const T rx = tid < 12 ? P.x0[(size_t)b * 12 + tid] : T(0);
+        const T rf = (tid < 6 && P.fext) ? P.fext[(size_t)b * 6 + tid] : T(0);
+        const T* xin = P.xu_in + (size_t)b * nz;
+        for (int base = 0; base < nz; base += 4 * NT) {
+            T r[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const int t = base + q * NT + tid; r[q] = t < nz ? xin[t] : T(0); }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const int t = base + q * NT + tid; if (t < nz) M.xu[t] = r[q]; }
+        }
+#pragma unroll
+        for (int q = 0; q < 2; ++q) { const int t = tid + q * NT; if (t < 3 * N) M.goals[t] = rg[q]; }
+        for (int t = tid + 2 * NT; t < 3 * N; t += NT) {            // horizons beyond 2 NT / 3 knots
+            const int k = t / 3;
+            M.goals[t] = gin[k * P.goal_stride + (t - 3 * k)];
+        }
+        if (tid < 12) M.x0[tid] = rx;
+        if (tid < 6) s_fext[tid] = rf;
+        if (tid < 6) M.xu[nz + tid] = T(0);                          // padded u_{N-1}
+        for (int t = tid; t < 18 * N; t += NT) M.z[t] = T(0);
     }
-    if (tid < 12) M.x0[tid] = P.x0[(size_t)b * 12 + tid];
-    if (tid < 6) s_fext[tid] = P.fext ? P.fext[(size_t)b * 6 + tid] : T(0);
     __syncthreads();
     const T* fext = P.fext ? s_fext : nullptr;
 

@@ -475,3 +475,22 @@ def test_ragged_batch_nonfinite_and_failed_linesearch(pkg, oracle_model):
     from oracle.osqp_sqp import SQP_OSQP as OQ
     ref = OQ(OS(oracle_model, N=32, qp_backend="kkt")).sqp(x[0], g[0], z[0])
     assert rel(np.asarray(eng.solve(z, x, g)[0])[0], ref) < 1e-6
+
+
+def test_mapped_host_memory_path_is_bitwise_identical(pkg, oracle_model, monkeypatch):
+    """Host-buffer solves of up to 8 problems read / write mapped page-locked memory from the kernel (no copy
+    operations in the stream): same bits as the copy path, for pageable and page-locked callers."""
+    import torch
+    xu, x0, goals = make_cases(oracle_model, 6, N=32, seed=51)
+    monkeypatch.setenv("I7_DIRECT_MAX_BATCH", "0")
+    copy = pkg.Engine(N=32, batch=6, dtype="fp64")
+    monkeypatch.setenv("I7_DIRECT_MAX_BATCH", "8")
+    direct = pkg.Engine(N=32, batch=6, dtype="fp64")
+    ref, ref_st = (np.asarray(a) for a in copy.solve(xu, x0, goals))
+    out, st = (np.asarray(a) for a in direct.solve(xu, x0, goals))
+    assert np.array_equal(out, ref) and np.array_equal(st, ref_st)
+    pin = lambda a: torch.tensor(a).pin_memory()
+    out2, st2 = direct.solve(pin(xu), pin(x0), pin(goals))
+    assert np.array_equal(out2.numpy(), ref) and np.array_equal(st2.numpy(), ref_st)
+    one, _ = direct.solve(xu[4], x0[4], goals[4])
+    assert np.array_equal(np.asarray(one)[0], ref[4])
