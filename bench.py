@@ -443,10 +443,37 @@ def single_problem_latency(args, local):
     p = lambda a, q: float(np.percentile(a, q)) if len(a) else None
     if not dev_us:
         return {"config": "skipped (--latency-ticks 0)"}
-    return {"config": f"fig-8 tracking, N={N}, 1 problem, closed loop with rk4 plant, {n_ticks} warm ticks",
-            "device_us": {"p50": p(dev_us, 50), "p99": p(dev_us, 99), "mean": float(np.mean(dev_us))},
-            "host_wall_us": {"p50": p(wall_us, 50), "p99": p(wall_us, 99), "mean": float(np.mean(wall_us))},
-            "mean_qp_iters": float(np.mean(qp_it))}
+    res = {"config": f"fig-8 tracking, N={N}, 1 problem, closed loop with rk4 plant, {n_ticks} warm ticks",
+           "device_us": {"p50": p(dev_us, 50), "p99": p(dev_us, 99), "mean": float(np.mean(dev_us))},
+           "host_wall_us": {"p50": p(wall_us, 50), "p99": p(wall_us, 99), "mean": float(np.mean(wall_us))},
+           "mean_qp_iters": float(np.mean(qp_it))}
+    if not args.no_cpu_baseline:
+        res["cpu_1thread_us"] = cpu_single_latency(N, fig, min(n_ticks, 100))
+    return res
+
+
+def cpu_single_latency(N, fig, n_ticks):
+    """The same closed loop on ONE host thread: C restatement of osqp_sqp (OSQP-style ADMM, warm-started like the
+    reference's persistent OSQP object) + its rk4 plant (single-problem CPU latency)."""
+    from oracle.cport import COracle
+    from oracle.model import load_model
+    orc = COracle(load_model(), N=N, backend="admm", batch=1)
+    x = np.concatenate([HOME, np.zeros(6)])
+    xu = np.zeros((1, 18 * N - 6)); xu[0, :12] = x
+    us = []
+    for t in range(n_ticks + 5):
+        goals = fig[(t + np.arange(N)) % fig.shape[0]].reshape(1, -1)
+        t0 = time.perf_counter()
+        out, _, _ = orc.sqp(x.reshape(1, 12), goals, xu, nthreads=1)
+        w = (time.perf_counter() - t0) * 1e6
+        if t >= 5:
+            us.append(w)
+        q, v = orc.rk4(x[:6], x[6:], out[0, 12:18], 0.01)
+        x = np.concatenate([q, v])
+        xu = np.concatenate([out[:, 18:], out[:, -18:]], axis=1)
+        xu[0, :12] = x
+    return {"p50": float(np.percentile(us, 50)), "p99": float(np.percentile(us, 99)), "ticks": n_ticks,
+            "kind": "port (oracle/c, ADMM back-end), 1 thread"}
 
 
 def main():
