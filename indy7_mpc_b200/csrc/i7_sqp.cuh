@@ -336,8 +336,32 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     __syncthreads();
     I7_STAMP();
     if (for_dump) return;
-    // W8: one COLUMN of SG = S G per task (12 per knot), plus d = S cv - (R/dt) M u as a 13th
-    for (int t = tid; t < 13 * np; t += NT) {
+    // W8: one COLUMN of SG = S G per task (12 per knot), plus d = S cv - (R/dt) M u as a 13th.  With a whole horizon
+    //     per CTA there are several rounds of these tasks per thread and the wave is bound by shared-memory loads
+    //     (42 per 36 FMAs): TWO columns per task then share every load of S (48 loads per 72 FMAs)
+    const bool wide = nk > 16;
+    if (wide) {
+        for (int t = tid; t < 6 * np; t += NT) {
+            const int cp = t / np, k = t - cp * np;
+            if (k >= nk) continue;
+            T* kr = M.kr + KR_STRIDE * k;
+            const int c0 = 2 * cp;
+            const T* G = kr + (c0 < 6 ? KR_GQ + c0 : KR_GV + c0 - 6);
+            T g0[6], g1[6], a0[6] = {T(0), T(0), T(0), T(0), T(0), T(0)}, a1[6] = {T(0), T(0), T(0), T(0), T(0), T(0)};
+#pragma unroll
+            for (int s = 0; s < 6; ++s) { g0[s] = G[6 * s]; g1[s] = G[6 * s + 1]; }
+#pragma unroll
+            for (int s = 0; s < 6; ++s)
+#pragma unroll
+                for (int r = 0; r < 6; ++r) {
+                    const T srs = kr[KR_S + 6 * r + s];
+                    a0[r] += srs * g0[s]; a1[r] += srs * g1[s];
+                }
+#pragma unroll
+            for (int r = 0; r < 6; ++r) { kr[KR_SG + 12 * r + c0] = a0[r]; kr[KR_SG + 12 * r + c0 + 1] = a1[r]; }
+        }
+    }
+    for (int t = tid + (wide ? 12 * np : 0); t < 13 * np; t += NT) {
         const int c = t / np, k = t - c * np;
         if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
@@ -375,7 +399,60 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     I7_STAMP();
     // W9: half a COLUMN c of L = G'(SG) + Qx per task (rows 6h .. 6h+5 of the upper triangle, r <= c; overwrites the
     //     setup scratch); the h = 0 tasks also do hx[c] = gx[c] + G[:, c] . d and, for c < 6, row c of Y = M / dt
-    for (int t = tid; t < 24 * np; t += NT) {
+    //     Whole horizon per CTA: two columns per task (9 tasks per knot), sharing every load of G.
+    if (wide) {
+        for (int t = tid; t < 9 * np; t += NT) {
+            const int tp = t / np, k = t - tp * np;
+            if (k >= nk) continue;
+            const int hf = tp >= 6 ? 1 : 0;
+            const int c0 = hf ? 6 + 2 * (tp - 6) : 2 * tp;
+            T* kr = M.kr + KR_STRIDE * k;
+            const T* ck = M.cost + COST_STRIDE * k;
+            T sg0[6], sg1[6], l0[6], l1[6];
+#pragma unroll
+            for (int s = 0; s < 6; ++s) { sg0[s] = kr[KR_SG + 12 * s + c0]; sg1[s] = kr[KR_SG + 12 * s + c0 + 1]; }
+            const T* Gh = kr + (hf ? KR_GV : KR_GQ);
+#pragma unroll
+            for (int rr = 0; rr < 6; ++rr) {
+                T b0 = T(0), b1 = T(0);
+#pragma unroll
+                for (int s = 0; s < 6; ++s) { const T g = Gh[6 * s + rr]; b0 += g * sg0[s]; b1 += g * sg1[s]; }
+                l0[rr] = b0; l1[rr] = b1;
+            }
+            // h (hx terms) and the scaling of Y read G, d, Y only: before the stores below, which reuse setup scratch
+            T h0 = T(0), h1 = T(0);
+            if (!hf) {
+                const T* Gc = kr + (c0 < 6 ? KR_GQ + c0 : KR_GV + c0 - 6);
+                h0 = c0 < 6 ? ck[6] * ck[c0] : ck[7] * xu[18 * k + c0];
+                h1 = c0 < 6 ? ck[6] * ck[c0 + 1] : ck[7] * xu[18 * k + c0 + 1];
+#pragma unroll
+                for (int s = 0; s < 6; ++s) { const T dd = kr[KR_D + s]; h0 += Gc[6 * s] * dd; h1 += Gc[6 * s + 1] * dd; }
+            }
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int c = c0 + q;
+                const T qc = c < 6 ? ck[6] * ck[c] : T(0);
+#pragma unroll
+                for (int rr = 0; rr < 6; ++rr) {
+                    const int r = 6 * hf + rr;
+                    if (r <= c) {
+                        T v = q ? l1[rr] : l0[rr];
+                        if (c < 6) v += qc * ck[r];
+                        else if (r == c) v += ck[7];
+                        kr[KR_L + r * 12 - (r * (r - 1)) / 2 + (c - r)] = v;
+                    }
+                }
+                if (!hf) {
+                    kr[KR_HX + c] = q ? h1 : h0;
+                    if (c < 6) {
+#pragma unroll
+                        for (int s = 0; s < 6; ++s) kr[KR_Y + 6 * c + s] = kr[KR_Y + 6 * c + s] * rdt;
+                    }
+                }
+            }
+        }
+    }
+    for (int t = tid + (wide ? 24 * np : 0); t < 24 * np; t += NT) {
         const int ch = t / np, k = t - ch * np;
         if (k >= nk) continue;
         const int c = ch >> 1, hf = ch & 1;
