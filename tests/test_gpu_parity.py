@@ -494,3 +494,70 @@ def test_mapped_host_memory_path_is_bitwise_identical(pkg, oracle_model, monkeyp
     assert np.array_equal(out2.numpy(), ref) and np.array_equal(st2.numpy(), ref_st)
     one, _ = direct.solve(xu[4], x0[4], goals[4])
     assert np.array_equal(np.asarray(one)[0], ref[4])
+
+
+def test_full_size_batch_properties(pkg, oracle_model):
+    """BASELINE.json configs[3] at full size (4096 problems, N=32, the bench workload) through size-independent
+    properties: bitwise repeatability, invariance under a permutation of the problems, the linearised dynamics of
+    the QP solution satisfied far below the reference's eps_abs = eps_rel = 1e-3, no non-finite lane — plus 24 lanes
+    spread over the batch against the CPU oracle (exact-KKT back-end, C port) on two consecutive MPC ticks."""
+    import torch
+    import bench
+    from oracle.cport import COracle
+    B, N = 4096, 32
+    wl = bench.make_workload(B, N)
+    eng = pkg.Engine(N=N, batch=B, dtype="fp64")
+    eng.set_external_wrench(wl["f_ext"])
+    dev = lambda a: torch.tensor(a, device="cuda")
+    goals = bench.goals_at(wl["fig"], wl["offsets"], 0, N)
+    out, st = (a.cpu().numpy() for a in eng.solve(dev(wl["xu"]), dev(wl["x0"]), dev(goals)))
+    out2, st2 = (a.cpu().numpy() for a in eng.solve(dev(wl["xu"]), dev(wl["x0"]), dev(goals)))
+    assert np.array_equal(out, out2) and np.array_equal(st, st2)
+    assert np.all(np.isfinite(out)) and np.all(st[:, 3] <= 1)
+    perm = np.random.default_rng(0).permutation(B)
+    eng.set_external_wrench(wl["f_ext"][perm])
+    outp, _ = (a.cpu().numpy() for a in eng.solve(dev(wl["xu"][perm]), dev(wl["x0"][perm]), dev(goals[perm])))
+    assert np.array_equal(outp, out[perm])
+    eng.set_external_wrench(wl["f_ext"])
+    # equality constraints of the QP at the first iterate: z satisfies x_{k+1} = A_k x_k + B_k u_k + c_k, x_0 = xs
+    lanes = np.arange(0, B, 171)[:24]
+    small = pkg.Engine(N=N, batch=len(lanes), dtype="fp64")
+    small.set_external_wrench(wl["f_ext"][lanes])
+    z = np.asarray(small.solve_qp(wl["xu"][lanes], wl["x0"][lanes], goals[lanes]))
+    Ad, Pd, g, l = (np.asarray(a) for a in small.dump_qp(wl["xu"][lanes], wl["x0"][lanes], goals[lanes]))
+    from oracle.osqp_solver import OSQPSolver as OS
+    tmpl = OS(oracle_model, N=N, qp_backend="kkt")
+    for i in range(len(lanes)):
+        A = tmpl.A.copy(); A.data[:] = Ad[i]
+        res = A @ z[i] - l[i]
+        assert np.abs(res).max() <= 1e-9 * max(1.0, np.abs(l[i]).max())
+    # two ticks against the oracle
+    orc = COracle(oracle_model, N=N, backend="kkt", batch=len(lanes))
+    xu_t, x0_t = wl["xu"][lanes], wl["x0"][lanes]
+    for t in range(2):
+        g_t = bench.goals_at(wl["fig"], wl["offsets"][lanes], t, N)
+        want, _, _ = orc.sqp(x0_t, g_t, xu_t, f_ext=wl["f_ext"][lanes])
+        got = out[lanes] if t == 0 else np.asarray(small.solve(xu_t, x0_t, g_t)[0])
+        assert rel(got, want) < 1e-6
+        xu_t, x0_t = bench.shift_host(want, N)
+        xu_t[:, :12] = x0_t
+
+
+def test_long_horizon_full_size_fp32_tolerance(pkg):
+    """BASELINE.json configs[4] at full size (N=128, 512 problems): fp32 mode within the stated 1e-4 relative of the
+    fp64 mode on identical inputs; both repeatable."""
+    import torch
+    import bench
+    B, N = 512, 128
+    wl = bench.make_workload(B, N)
+    goals = bench.goals_at(wl["fig"], wl["offsets"], 0, N)
+    outs = {}
+    for dt, td in (("fp64", torch.float64), ("fp32", torch.float32)):
+        eng = pkg.Engine(N=N, batch=B, dtype=dt)
+        eng.set_external_wrench(wl["f_ext"])
+        a = [torch.tensor(x, dtype=td, device="cuda") for x in (wl["xu"], wl["x0"], goals)]
+        o, s = eng.solve(*a)
+        o2, _ = eng.solve(*a)
+        assert torch.equal(o, o2) and bool(torch.isfinite(o).all())
+        outs[dt] = o.double().cpu().numpy()
+    assert rel(outs["fp32"], outs["fp64"]) < 1e-4
