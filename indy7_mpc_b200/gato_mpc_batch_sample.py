@@ -150,6 +150,85 @@ class MPC_GATO_Batch_Sample:
             self.constant_f_ext = np.concatenate([new_force, np.zeros(3)])
         return self.xpath, stats
 
+    # ---- figure-8 tracking variant of notebooks/gato_mpc_indy7_fig8.ipynb (cell 2: run_mpc_fig8) ----------------
+    def run_mpc_fig8(self, xstart, fig8_traj, sim_dt=0.001, sim_time=5, verbose=False):
+        """Tracks ``fig8_traj`` (flat [x y z 0 0 0] per sample, one sample per solver dt): the goal window advances
+        by one sample per completed solver step, the plant wrench is ``constant_f_ext`` applied as it is in the last
+        joint frame (the notebook appends the 'world' force unconverted), hypotheses are rolled out by the solver's
+        own ``sim_forward`` (lane wrenches unconverted as well) and ties go to the LAST best lane (`<=`)."""
+        S, nx, nu = self.solver, self.nx, self.nu
+        B, N, stride = S.batch_size, S.N, self.nx + self.nu
+        fig8_traj = np.asarray(fig8_traj, float)
+        xcur = np.array(xstart, float)
+        xcur_batch = np.tile(xcur, (B, 1))
+        eepos_offset = 0
+        eepos_goal = fig8_traj[:6 * N]
+        eepos_goal_batch = np.tile(eepos_goal, (B, 1))
+        stats = {'solve_times': [], 'goal_distances': [], 'control_inputs': []}
+        XU = np.zeros(N * stride - nu)
+        XU[:nx] = xcur
+        XU_batch = np.array(S.solve(xcur_batch, eepos_goal_batch, np.tile(XU, (B, 1))), float)
+        XU_best = XU_batch[0, :].copy()
+        time_accumulated = 0.0
+        for i in range(int(sim_time / sim_dt)):
+            x_last, u_last = xcur, XU_best[nx:nx + nu].copy()
+            sim_time_step = sim_dt
+            q, v = xcur[:self.nq], xcur[self.nq:nx]
+            while sim_time_step > 0:
+                timestep = min(sim_time_step, S.dt - time_accumulated)
+                knot = min(int(time_accumulated / S.dt), N - 1)
+                u = XU_best[knot * stride + nx:(knot + 1) * stride]
+                q, v = rk4(self.model, self.data, q, v, u, timestep, self.constant_f_ext)
+                time_accumulated += timestep
+                sim_time_step -= timestep
+                self.xpath.append(q)
+                if abs(time_accumulated - S.dt) < 1e-10:
+                    eepos_offset += 1
+                    time_accumulated = 0.0
+            xcur = np.hstack([q, v])
+            xcur_batch[:] = xcur
+            XU_batch[:, :nx] = xcur
+            XU_batch[:, nx:] = XU_best[nx:]
+            if eepos_offset < len(fig8_traj) / 6 - 6 * N:
+                eepos_goal = fig8_traj[6 * eepos_offset:6 * (eepos_offset + N)]
+                eepos_goal_batch[:, :] = eepos_goal
+            else:
+                break
+            goaldist = float(np.linalg.norm(self.eepos(xcur[:self.nq]) - eepos_goal[:3]))
+            S.reset()
+            S.solver.resetRho()
+            t0 = time.time()
+            XU_batch_new = np.array(S.solve(xcur_batch, eepos_goal_batch, XU_batch), float)
+            t1 = time.time()
+            best_id = self.find_best_trajectory_id_fig8(x_last, u_last, xcur, sim_dt)
+            XU_best = XU_batch_new[best_id, :].copy()
+            if abs((i * sim_dt) % 0.05) < 1e-5:
+                if verbose:
+                    print(f"t: {i * sim_dt:8.3f}, goal dist: {goaldist:8.5f}, best_id: {best_id}")
+                stats['goal_distances'].append(float(round(goaldist, 5)))
+                stats['control_inputs'].append(np.round(XU_best[nx:nx + nu].copy(), 5))
+                stats['solve_times'].append(float(round(t1 - t0, 5)))
+        return self.xpath, stats
+
+    def find_best_trajectory_id_fig8(self, x_last, u_last, xcur, dt):
+        """The notebook's selection: one ``sim_forward`` of the solver over all lanes, last minimum wins; resampling
+        keeps the best wrench in lane 1 and the zero wrench in lane 0."""
+        S = self.solver
+        S.solver.set_external_wrench_batch(S.f_ext_batch)
+        x_next = np.asarray(S.solver.sim_forward(np.asarray(x_last, float), np.asarray(u_last, float), float(dt)), float)
+        err = np.linalg.norm(x_next - np.asarray(xcur, float)[None, :], axis=1)
+        best_id = int(len(err) - 1 - np.argmin(err[::-1]))
+        if self.resample_f_ext and self.f_ext_resample_std != 0:
+            f_best = S.f_ext_batch[best_id].copy()
+            S.f_ext_batch = np.tile(f_best, (S.batch_size, 1)) + np.random.normal(0, self.f_ext_resample_std,
+                                                                                   S.f_ext_batch.shape)
+            S.f_ext_batch[:, 3:] = 0.0
+            if S.batch_size > 1:
+                S.f_ext_batch[1] = f_best
+            S.f_ext_batch[0] = 0.0
+            S.solver.set_external_wrench_batch(S.f_ext_batch)
+        return best_id
+
     def find_best_trajectory_id(self, x_last, u_last, xcur, dt):
         """Lane whose wrench hypothesis best predicts the measured state over one plant step (:254-300): one
         batched rk4 launch with the B world-frame hypotheses re-expressed in the last joint frame at x_last."""

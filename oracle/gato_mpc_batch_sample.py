@@ -104,3 +104,70 @@ class MPC_GATO_Batch_Sample:
             self.f_ext_batch[:, 3:] = 0.0
             self.f_ext_batch[0] = 0.0
         return best_id
+
+    # ---- notebooks/gato_mpc_indy7_fig8.ipynb cell 2: run_mpc_fig8 / find_best_trajectory_id (sim_forward flavour) ----
+    def run_mpc_fig8(self, xstart, fig8_traj, sim_dt=0.001, sim_time=5):
+        B, N, nq, nx, nu = self.batch_size, self.N, 6, 12, 6
+        fig8_traj = np.asarray(fig8_traj, float)
+        xcur = np.array(xstart, float)
+        xcur_batch = np.tile(xcur, (B, 1))
+        eepos_offset = 0
+        eepos_goal = fig8_traj[:6 * N]
+        goal_batch = np.tile(eepos_goal, (B, 1))
+        stats = {'goal_distances': [], 'control_inputs': []}
+        XU = np.zeros(N * (nx + nu) - nu)
+        XU[:nx] = xcur
+        XU_batch = self._solve(xcur_batch, goal_batch, np.tile(XU, (B, 1)))
+        XU_best = XU_batch[0, :].copy()
+        t_acc = 0.0
+        for i in range(int(sim_time / sim_dt)):
+            x_last, u_last = xcur, XU_best[nx:nx + nu].copy()
+            rem = sim_dt
+            q, v = xcur[:nq], xcur[nq:nx]
+            while rem > 0:
+                h = min(rem, self.dt - t_acc)
+                knot = min(int(t_acc / self.dt), N - 1)
+                u = XU_best[knot * (nx + nu) + nx:(knot + 1) * (nx + nu)]
+                q, v = rbd.rk4(self.model, q, v, u, h, self.constant_f_ext)     # the 'world' force goes in unconverted
+                t_acc += h
+                rem -= h
+                self.xpath.append(q)
+                if abs(t_acc - self.dt) < 1e-10:
+                    eepos_offset += 1
+                    t_acc = 0.0
+            xcur = np.hstack([q, v])
+            for j in range(B):
+                xcur_batch[j, :] = xcur
+                XU_batch[j, :nx] = xcur
+                XU_batch[j, nx:] = XU_best[nx:]
+            if eepos_offset < len(fig8_traj) / 6 - 6 * N:
+                eepos_goal = fig8_traj[6 * eepos_offset:6 * (eepos_offset + N)]
+                goal_batch[:, :] = eepos_goal
+            else:
+                break
+            goaldist = np.linalg.norm(rbd.eepos(self.model, xcur[:nq]) - eepos_goal[:3])
+            XU_new = self._solve(xcur_batch, goal_batch, XU_batch)
+            best_id = self.find_best_trajectory_id_fig8(x_last, u_last, xcur, sim_dt)
+            self.best_ids.append(best_id)
+            XU_best = XU_new[best_id, :].copy()
+            if abs((i * sim_dt) % 0.05) < 1e-5:
+                stats['goal_distances'].append(float(round(goaldist, 5)))
+                stats['control_inputs'].append(np.round(XU_best[nx:nx + nu].copy(), 5))
+        return self.xpath, stats
+
+    def find_best_trajectory_id_fig8(self, x_last, u_last, xcur, dt):
+        best_error, best_id = np.inf, None
+        for i in range(self.batch_size):                 # solver.sim_forward: lane i under its own (unconverted) wrench
+            q, v = rbd.rk4(self.model, x_last[:6], x_last[6:], u_last, dt, self.f_ext_batch[i])
+            error = np.linalg.norm(np.hstack([q, v]) - xcur)
+            if error <= best_error:
+                best_error, best_id = error, i
+        if self.resample_f_ext and self.f_ext_resample_std != 0:
+            f_best = self.f_ext_batch[best_id, :].copy()
+            self.f_ext_batch = np.tile(f_best, (self.batch_size, 1))
+            self.f_ext_batch += np.random.normal(0, self.f_ext_resample_std, self.f_ext_batch.shape)
+            self.f_ext_batch[:, 3:] = 0.0
+            if self.batch_size > 1:
+                self.f_ext_batch[1] = f_best
+            self.f_ext_batch[0] = 0.0
+        return best_id

@@ -561,3 +561,29 @@ def test_long_horizon_full_size_fp32_tolerance(pkg):
         assert torch.equal(o, o2) and bool(torch.isfinite(o).all())
         outs[dt] = o.double().cpu().numpy()
     assert rel(outs["fp32"], outs["fp64"]) < 1e-4
+
+
+def test_fig8_batch_sample_driver_matches_oracle(pkg, oracle_model):
+    """notebooks/gato_mpc_indy7_fig8.ipynb cell 2 (run_mpc_fig8): figure-8 tracking with 8 wrench hypotheses,
+    selection through the solver's sim_forward, resampling around the best lane: same lane picked at every step and
+    the same plant path as the CPU restatement."""
+    from indy7_mpc_b200.gato_mpc_batch_sample import MPC_GATO_Batch_Sample
+    from indy7_mpc_b200.reference_traj import figure8
+    from oracle.gato_mpc_batch_sample import MPC_GATO_Batch_Sample as OracleDriver
+    fig = figure8(0.4, 0.4, (0.0, 0.5, 0.75), 5.0, 0.01, cycles=5)
+    kw = dict(N=32, dt=0.01, batch_size=8, constant_f_ext=[10.0, 15.0, -6.0], resample_f_ext=True, f_ext_std=5.0,
+              f_ext_resample_std=3.0)
+    np.random.seed(42)
+    ref = OracleDriver(oracle_model, **kw)
+    xp_ref, st_ref = ref.run_mpc_fig8(np.zeros(12), fig, sim_dt=0.02, sim_time=0.4)
+    np.random.seed(42)
+    model, _, _ = pkg.load_robot_model()
+    drv = MPC_GATO_Batch_Sample(model, **kw)
+    best = []
+    orig = drv.find_best_trajectory_id_fig8
+    drv.find_best_trajectory_id_fig8 = lambda *a: best.append(orig(*a)) or best[-1]
+    xp, st = drv.run_mpc_fig8(np.zeros(12), fig, sim_dt=0.02, sim_time=0.4)
+    assert len(xp) == len(xp_ref) == 40
+    assert best == ref.best_ids and len(set(best)) > 2
+    assert rel(np.array(xp), np.array(xp_ref)) < 1e-6
+    assert np.allclose(st['goal_distances'], st_ref['goal_distances'], atol=2e-5)
