@@ -766,8 +766,13 @@ i7_status sim_forward_t(i7_handle* h, int batch, const void* x, const void* u, d
     i7_status rc;
     if ((rc = st.flush_in(s))) return rc;
     const auto& rob = get_rob<T>(h);
-    i7::sim_forward_kernel<T><<<(batch + 63) / 64, 64, 0, s>>>(rob, batch, dx, du, bcast,
-                                                               h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o);
+    // a warp per lane while that still fills the device only a few times over, a thread per lane beyond
+    if (batch <= 512)
+        i7::sim_forward_warp_kernel<T><<<batch, 32, 0, s>>>(rob, batch, dx, du, bcast,
+                                                           h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o);
+    else
+        i7::sim_forward_kernel<T><<<(batch + 63) / 64, 64, 0, s>>>(rob, batch, dx, du, bcast,
+                                                                   h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o);
     ++h->launches;
     I7_CUDA(h, cudaGetLastError());
     return st.flush_out(s);

@@ -110,6 +110,70 @@ __global__ void sim_forward_kernel(const __grid_constant__ Robot<T> rob, int n, 
     }
 }
 
+// Same plant step with ONE WARP per lane: the four forward-dynamics evaluations of rk4 are a dependent chain, so the
+// time of the thread-per-lane kernel above is pure latency (44 us whether 1 or 4096 lanes).  Here every evaluation is
+// spread over the lanes of a warp with the world-frame tasks of the solver's setup (i7_wf.cuh): cos/sin per joint,
+// the origin, one link record per lane, one mass-matrix column per lane, then the 6x6 solve; lane i < 6 owns
+// component i of the state through the rk4 stages.  Used for small and medium batches (i7_sim_forward).
+template <typename T>
+__global__ void __launch_bounds__(32) sim_forward_warp_kernel(const __grid_constant__ Robot<T> rob, int n, const T* x, const T* u,
+                                                              int bcast, const T* fext, T dt, T* x_next) {
+    __shared__ T s_cs[12], s_qd[6], s_pee[3], s_S[36], s_V[36], s_A[36], s_I[54], s_F[36], s_M[36], s_b[6], s_fx[6];
+    const int i = blockIdx.x, lane = threadIdx.x;
+    if (i >= n) return;
+    const T* xi = x + (bcast ? 0 : 12 * i);
+    const T* ui = u + (bcast ? 0 : 6 * i);
+    const int c = lane < 6 ? lane : 0;
+    const T q0 = xi[c], v0 = xi[6 + c];
+    T ur[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) ur[a] = ui[a];
+    if (lane < 6 && fext) s_fx[lane] = fext[6 * i + lane];
+    const T* f = fext ? s_fx : nullptr;
+    // forward dynamics at (qt, vt): every lane returns component c of qdd
+    auto fd = [&](T qt, T vt) -> T {
+        __syncwarp();
+        if (lane < 6) {
+            T sn, cs;
+            sincos_t<T>(qt, &sn, &cs);
+            s_cs[lane] = cs; s_cs[6 + lane] = sn; s_qd[lane] = vt;
+        }
+        __syncwarp();
+        if (lane == 0) { T pee[3]; wf_tip<T>(rob, s_cs, pee); s_pee[0] = pee[0]; s_pee[1] = pee[1]; s_pee[2] = pee[2]; }
+        __syncwarp();
+        if (lane < 6) wf_link<T>(rob, s_cs, s_qd, f, s_pee, lane, s_S + 6 * lane, s_V + 6 * lane, s_A + 6 * lane, s_I + 9 * lane, s_F + 6 * lane);
+        __syncwarp();
+        if (lane < 6) { T bj; wf_mass_column<T>(rob, s_S, s_I, s_F, lane, s_M, &bj); s_b[lane] = bj; }
+        __syncwarp();
+        T A[6][6], dinv[6], r[6];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            r[a] = ur[a] - s_b[a];
+#pragma unroll
+            for (int b2 = 0; b2 <= a; ++b2) A[a][b2] = s_M[6 * a + b2];
+        }
+        spd6_factor<T>(A, dinv);
+        spd6_solve_factored<T>(A, dinv, r);
+        T out = r[0];
+#pragma unroll
+        for (int a = 1; a < 6; ++a) if (c == a) out = r[a];
+        return out;
+    };
+    const T k1v = fd(q0, v0);
+    const T k2q = v0 + k1v * dt / T(2);
+    const T k2v = fd(q0 + v0 * dt / T(2), k2q);
+    const T k3q = v0 + k2v * dt / T(2);
+    const T k3v = fd(q0 + k2q * dt / T(2), k3q);
+    const T k4q = v0 + k3v * dt;
+    const T k4v = fd(q0 + k3q * dt, k4q);
+    if (lane < 6) {
+        const T vn = v0 + (dt / T(6)) * (k1v + T(2) * k2v + T(2) * k3v + k4v);
+        const T av = (v0 + T(2) * k2q + T(2) * k3q + k4q) / T(6);
+        x_next[12 * i + lane] = q0 + av * dt;
+        x_next[12 * i + 6 + lane] = vn;
+    }
+}
+
 // -----------------------------------------------------------------------------------------------------------
 // best-trajectory selection: one CTA; packed = [costs | best_cost, best_index, XU_best]
 template <typename T>
