@@ -9,7 +9,8 @@ Workload (BASELINE.json configs[3]): a batch of 4096 in
 problems — sampled start states around the simulator home pose, figure-8 end-effector references at per-lane
 offsets, per-lane external-wrench hypotheses — sharded across the ranks (strong scaling: the total batch is fixed).
 One "step" = one control tick: every lane runs one sqp() (fused sm_100a kernel), then the per-problem costs and
-the best trajectory are selected (i7_pack_best) and, for N > 1, gathered with ONE NCCL all-gather and reduced.
+the best trajectory are selected and, for N > 1, exchanged by ONE kernel over peer memory (i7_p2p_exchange: pack +
+NVLink stores + selection; I7_P2P=0: i7_pack_best, ONE NCCL all-gather, i7_reduce_best).
 Between ticks (untimed) the lanes advance like an MPC loop: x0 <- x_1 of the solution, trajectory shifted by one
 knot, goal window advanced by one sample — so every timed step is a realistic warm-started solve.
 
@@ -246,11 +247,26 @@ def run_b200(args):
         return nxt, out[:, 18:30].contiguous()
 
     gathered = torch.empty(world * (B + 2 + nz), dtype=tdt, device=dev) if world > 1 else None
+    # exchange of the per-rank records: ONE kernel over peer memory (NVLink stores + flags), fused with the packing and
+    # the selection; I7_P2P=0 selects the NCCL path (pack kernel, all_gather_into_tensor, reduce kernel)
+    use_p2p = world > 1 and os.environ.get("I7_P2P", "1") != "0"
+    if use_p2p:
+        i7d.connect_peers(eng, rank, world)
+
+    def exchange(st, out):
+        if use_p2p:
+            return eng.p2p_exchange(st, out, index_offset=rank * B)
+        packed = eng.pack_best(st, out, index_offset=rank * B)
+        return i7d.gather_best(packed, B, world, eng.reduce_best, gathered)[0]
 
     def tick(xu, x0, goals):
         out, st = eng.solve(xu, x0, goals)
-        packed = eng.pack_best(st, out, index_offset=rank * B)
-        best, _ = i7d.gather_best(packed, B, world, eng.reduce_best, gathered)
+        best = exchange(st, out)
+        if use_p2p:            # warm-up ticks double as a check against the NCCL path
+            packed = eng.pack_best(st, out, index_offset=rank * B)
+            ref = i7d.gather_best(packed, B, world, eng.reduce_best, gathered)[0]
+            if not torch.equal(best, ref):
+                raise RuntimeError("peer-memory exchange disagrees with the NCCL all-gather path")
         return out, st, best
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
@@ -279,13 +295,14 @@ def run_b200(args):
         kev[i][0].record()
         out, st = eng.solve(xu, x0, goals)               # dominant kernel timed on its own as well
         kev[i][1].record()
-        packed = eng.pack_best(st, out, index_offset=rank * B)
-        best, _ = i7d.gather_best(packed, B, world, eng.reduce_best, gathered)   # ONE all-gather (NCCL) when world > 1
+        best = exchange(st, out)                         # world > 1: ONE exchange per tick (peer memory, or NCCL all-gather)
         ev[i][1].record()
         xu, x0 = shift_dev(out)
         xu[:, :12] = x0
         last_st = st
     torch.cuda.synchronize()
+    if use_p2p:
+        eng.p2p_status()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -387,7 +404,8 @@ def run_b200(args):
         "dtype": "f64" if args.dtype == "fp64" else "f32", "data": "synthetic",
         "config": {"workload": f"batch {args.batch} sampled Indy7 SQP-MPC problems (BASELINE.json configs[3]), N={N}, "
                                f"dt=0.01, warm-started MPC ticks, per-lane wrench hypotheses, best-trajectory selection"
-                               + (" + one NCCL all-gather" if world > 1 else ""),
+                               + ((" + one peer-memory exchange kernel (NVLink stores, fused pack + gather + selection)"
+                                   if use_p2p else " + one NCCL all-gather") if world > 1 else ""),
                    "horizon": N, "batch_total": args.batch, "batch_per_gpu": B, "parallelism": f"batch-shard x{world}",
                    "l2": "flushed between timed steps (256 MB memset outside the events)",
                    "threads_per_cta": eng_threads(eng, B, args)},

@@ -151,6 +151,26 @@ i7_status i7_pack_best(i7_handle* h, int32_t batch, const void* stats, const voi
  * [best_cost, best_index, XU_best]; writes out = [best_cost, best_index, XU_best] of the winning rank. */
 i7_status i7_reduce_best(i7_handle* h, int32_t nranks, int32_t stride, const void* gathered, void* out, void* stream);
 
+/* Multi-GPU exchange over peer memory (one process per GPU on one node), the fused form of
+ * i7_pack_best -> all-gather -> i7_reduce_best (the reference analogue is the host loop find_best_trajectory_id,
+ * src/gato_mpc_batch_sample.py:254-300; the transport has no reference counterpart):
+ *   i7_p2p_create   allocates this rank's exchange buffer (sized for the handle's batch) and returns its 64-byte
+ *                   inter-process handle; the caller exchanges the handles of all ranks (any host-side all-gather);
+ *   i7_p2p_connect  maps every rank's buffer (handles = world x 64 bytes, in rank order);
+ *   i7_p2p_exchange ONE kernel: packs [local costs | best_cost, best_index, XU_best], stores it into every peer's
+ *                   buffer over NVLink, waits for all ranks and writes the overall winner [best_cost, global index,
+ *                   XU_best] to `out` (device pointer).  `batch` must be the same on every rank.  Every rank must call
+ *                   it once per tick; a rank missing for longer than the timeout raises I7_ERR_CUDA at i7_p2p_status.
+ *   i7_p2p_gathered device pointer to the world x (batch + 2 + nz) records of the latest exchange
+ *   i7_p2p_status   0, or an error once an exchange has timed out (synchronises the stream given). */
+#define I7_IPC_HANDLE_BYTES 64
+i7_status i7_p2p_create(i7_handle* h, int32_t world, int32_t rank, unsigned char* handle_out);
+i7_status i7_p2p_connect(i7_handle* h, const unsigned char* handles);
+i7_status i7_p2p_exchange(i7_handle* h, int32_t batch, const void* stats, const void* xu, int32_t index_offset, void* out,
+                          void* stream);
+i7_status i7_p2p_gathered(i7_handle* h, const void** gathered);
+i7_status i7_p2p_status(i7_handle* h, void* stream);
+
 /* Measurement utility for roofline denominators: sustained FMA throughput of the CUDA-core pipe of the
  * handle's dtype (dependent-chain-free FMA loop on every SM), in TFLOP/s. */
 i7_status i7_measure_fma_peak(i7_handle* h, double* tflops);

@@ -44,6 +44,11 @@ SYMBOLS = {
     "i7_kernel_form": (C.c_int, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "i7_pack_best": (_i32, [_vp, _i32, _vp, _vp, _i32, _vp, _vp]),
     "i7_reduce_best": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp]),
+    "i7_p2p_create": (_i32, [_vp, _i32, _i32, C.c_char_p]),
+    "i7_p2p_connect": (_i32, [_vp, C.c_char_p]),
+    "i7_p2p_exchange": (_i32, [_vp, _i32, _vp, _vp, _i32, _vp, _vp]),
+    "i7_p2p_gathered": (_i32, [_vp, C.POINTER(_vp)]),
+    "i7_p2p_status": (_i32, [_vp, _vp]),
     "i7_measure_fma_peak": (_i32, [_vp, C.POINTER(_dbl)]),
     "i7_profile_phases": (_i32, [_vp, _i32, C.POINTER(C.c_int64), _i32]),
     "i7_sim_forward": (_i32, [_vp, _i32, _vp, _vp, _dbl, _i32, _vp, _vp]),

@@ -48,6 +48,13 @@ struct i7_handle {
     cudaEvent_t pipe_fork = nullptr, pipe_join[kPipeStreams] = {nullptr, nullptr, nullptr};
     cudaEvent_t pipe_done[kPipeMaxChunks] = {};
     int pipe_chunk = 0;
+    // peer-memory exchange (i7_p2p_*): own buffer, the peers' mapped buffers, device copy of the pointer table
+    int p2p_world = 0, p2p_rank = 0;
+    void* p2p_mine = nullptr;
+    void* p2p_peer[16] = {};
+    unsigned char** p2p_table = nullptr;
+    int* p2p_err = nullptr;
+    unsigned long long p2p_seq = 0;
     int direct_max_batch = 0;    // host-buffer solves up to this batch use mapped host memory instead of copies
     bool timed = false;
     int64_t launches = 0;
@@ -391,6 +398,11 @@ void i7_destroy(i7_handle* h) {
     if (h->d_spill) cudaFree(h->d_spill);
     if (h->d_xbuf) cudaFree(h->d_xbuf);
     if (h->d_prof) cudaFree(h->d_prof);
+    for (int r = 0; r < h->p2p_world; ++r)
+        if (h->p2p_peer[r] && r != h->p2p_rank) cudaIpcCloseMemHandle(h->p2p_peer[r]);
+    if (h->p2p_mine) cudaFree(h->p2p_mine);
+    if (h->p2p_table) cudaFree(h->p2p_table);
+    if (h->p2p_err) cudaFree(h->p2p_err);
     for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
         if (h->pipe_stream[k]) cudaStreamDestroy(h->pipe_stream[k]);
         if (h->pipe_join[k]) cudaEventDestroy(h->pipe_join[k]);
@@ -639,6 +651,75 @@ i7_status i7_profile_phases(i7_handle* h, int32_t enable, int64_t* clocks16, int
         I7_CUDA(h, cudaMemcpy(clocks16, h->d_prof, (size_t)batch * 32 * sizeof(long long), cudaMemcpyDeviceToHost));
     }
     if (!enable && h->d_prof) { cudaFree(h->d_prof); h->d_prof = nullptr; }
+    return I7_OK;
+}
+
+i7_status i7_p2p_create(i7_handle* h, int32_t world, int32_t rank, unsigned char* handle_out) {
+    if (!h || !handle_out || world < 1 || world > 16 || rank < 0 || rank >= world) { if (h) h->err = "bad argument"; return I7_ERR_INVALID; }
+    if (h->p2p_mine) { h->err = "exchange buffer already created"; return I7_ERR_INVALID; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == I7_IPC_HANDLE_BYTES, "IPC handle size");
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    const int stride = h->cfg.batch + 2 + (int)h->nz;
+    const i7::P2PLayout L = i7::p2p_layout(world, stride, h->esize);
+    I7_CUDA(h, cudaMalloc(&h->p2p_mine, L.total));
+    I7_CUDA(h, cudaMemset(h->p2p_mine, 0, L.total));
+    I7_CUDA(h, cudaMalloc(&h->p2p_err, sizeof(int)));
+    I7_CUDA(h, cudaMemset(h->p2p_err, 0, sizeof(int)));
+    I7_CUDA(h, cudaDeviceSynchronize());
+    cudaIpcMemHandle_t ih;
+    I7_CUDA(h, cudaIpcGetMemHandle(&ih, h->p2p_mine));
+    std::memcpy(handle_out, &ih, sizeof(ih));
+    h->p2p_world = world; h->p2p_rank = rank;
+    return I7_OK;
+}
+
+i7_status i7_p2p_connect(i7_handle* h, const unsigned char* handles) {
+    if (!h || !handles || !h->p2p_mine) { if (h) h->err = "i7_p2p_create first"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    for (int r = 0; r < h->p2p_world; ++r) {
+        if (r == h->p2p_rank) { h->p2p_peer[r] = h->p2p_mine; continue; }
+        cudaIpcMemHandle_t ih;
+        std::memcpy(&ih, handles + (size_t)r * I7_IPC_HANDLE_BYTES, sizeof(ih));
+        I7_CUDA(h, cudaIpcOpenMemHandle(&h->p2p_peer[r], ih, cudaIpcMemLazyEnablePeerAccess));
+    }
+    I7_CUDA(h, cudaMalloc(&h->p2p_table, 16 * sizeof(unsigned char*)));
+    I7_CUDA(h, cudaMemcpy(h->p2p_table, h->p2p_peer, 16 * sizeof(unsigned char*), cudaMemcpyHostToDevice));
+    return I7_OK;
+}
+
+i7_status i7_p2p_exchange(i7_handle* h, int32_t batch, const void* stats, const void* xu, int32_t index_offset, void* out,
+                          void* stream) {
+    if (!h || !stats || !xu || !out || !h->p2p_table) { if (h) h->err = "i7_p2p_connect first"; return I7_ERR_INVALID; }
+    if (batch != h->cfg.batch) { h->err = "the exchange is laid out for the handle's batch on every rank"; return I7_ERR_INVALID; }
+    if (ptr_kind(stats) != 1 || ptr_kind(xu) != 1 || ptr_kind(out) != 1) { h->err = "i7_p2p_exchange takes device pointers"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned long long seq = ++h->p2p_seq;
+    const unsigned long long timeout_ns = 4000000000ull;
+    if (h->esize == 8)
+        i7::pack_exchange_reduce_kernel<double><<<1, 256, 0, s>>>(batch, (int)h->nz, (const double*)stats, I7_STATS_LEN, 8, (const double*)xu,
+                                                                 index_offset, h->p2p_rank, h->p2p_world, h->p2p_table, seq, timeout_ns, (double*)out, h->p2p_err);
+    else
+        i7::pack_exchange_reduce_kernel<float><<<1, 256, 0, s>>>(batch, (int)h->nz, (const float*)stats, I7_STATS_LEN, 8, (const float*)xu,
+                                                                index_offset, h->p2p_rank, h->p2p_world, h->p2p_table, seq, timeout_ns, (float*)out, h->p2p_err);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return I7_OK;
+}
+
+i7_status i7_p2p_gathered(i7_handle* h, const void** gathered) {
+    if (!h || !gathered || !h->p2p_mine || h->p2p_seq == 0) { if (h) h->err = "no exchange yet"; return I7_ERR_INVALID; }
+    const i7::P2PLayout L = i7::p2p_layout(h->p2p_world, h->cfg.batch + 2 + (int)h->nz, h->esize);
+    *gathered = (const char*)h->p2p_mine + (h->p2p_seq & 1) * L.data_bytes;
+    return I7_OK;
+}
+
+i7_status i7_p2p_status(i7_handle* h, void* stream) {
+    if (!h || !h->p2p_err) { if (h) h->err = "no exchange buffer"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaStreamSynchronize((cudaStream_t)stream));
+    int e = 0;
+    I7_CUDA(h, cudaMemcpy(&e, h->p2p_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (e) { h->err = "peer-memory exchange timed out waiting for a rank"; return I7_ERR_CUDA; }
     return I7_OK;
 }
 

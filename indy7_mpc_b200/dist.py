@@ -51,3 +51,16 @@ def all_costs(gathered, world, batch_local, nz):
     """Per-problem costs of the whole batch, in global problem order, from the gathered records."""
     stride = packed_len(batch_local, nz)
     return gathered.view(world, stride)[:, :batch_local].reshape(-1)
+
+
+def connect_peers(engine, rank, world, group=None):
+    """Sets up the peer-memory exchange of `engine` (i7_p2p_*): every rank allocates its exchange buffer, the 64-byte
+    inter-process handles travel once through the process group, every rank maps every buffer.  After this,
+    `engine.p2p_exchange(stats, xu, index_offset)` replaces pack_best + all_gather + reduce_best by ONE kernel that
+    stores the packed record straight into the peers' memory over NVLink."""
+    import torch.distributed as dist
+    mine = engine.p2p_create(world, rank)
+    handles = [None] * world
+    dist.all_gather_object(handles, mine, group=group)
+    engine.p2p_connect(handles)
+    dist.barrier(group=group)

@@ -235,6 +235,30 @@ class Engine:
         self._check(self.lib.i7_reduce_best(self._h, nranks, stride, p_in, p_out, self._stream(gathered)))
         return out
 
+    # ---- peer-memory exchange between the ranks of one node (i7_p2p_*) ----
+    def p2p_create(self, world, rank):
+        """Allocates this rank's exchange buffer; returns its 64-byte inter-process handle."""
+        buf = C.create_string_buffer(64)
+        self._check(self.lib.i7_p2p_create(self._h, int(world), int(rank), buf))
+        return buf.raw
+
+    def p2p_connect(self, handles):
+        """handles: the handles of all ranks in rank order (list of 64-byte strings)."""
+        self._check(self.lib.i7_p2p_connect(self._h, b"".join(handles)))
+
+    def p2p_exchange(self, stats, xu, index_offset=0):
+        """ONE kernel: pack the local record, store it into every peer's buffer over NVLink, wait for all ranks, pick
+        the winner.  Device tensors only; returns [best_cost, global index, XU_best] on the device."""
+        B = self._batch_of(xu)
+        keep = []
+        p_st, p_xu = self._in(stats, (B, _lib.I7_STATS_LEN), keep), self._in(xu, (B, self.nz), keep)
+        out, p_out = self._out((2 + self.nz,), xu, keep)
+        self._check(self.lib.i7_p2p_exchange(self._h, B, p_st, p_xu, int(index_offset), p_out, self._stream(xu)))
+        return out
+
+    def p2p_status(self, like=None):
+        self._check(self.lib.i7_p2p_status(self._h, self._stream(like) if like is not None else None))
+
     def measure_fma_peak(self):
         tf = C.c_double()
         self._check(self.lib.i7_measure_fma_peak(self._h, C.byref(tf)))

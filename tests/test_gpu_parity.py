@@ -587,3 +587,77 @@ def test_fig8_batch_sample_driver_matches_oracle(pkg, oracle_model):
     assert best == ref.best_ids and len(set(best)) > 2
     assert rel(np.array(xp), np.array(xp_ref)) < 1e-6
     assert np.allclose(st['goal_distances'], st_ref['goal_distances'], atol=2e-5)
+
+
+def test_peer_exchange_single_rank_matches_pack_reduce(pkg, oracle_model):
+    """i7_p2p_exchange with a world of one rank (the rank's own buffer is its only peer): the fused
+    pack + store + selection kernel returns bitwise what i7_pack_best + i7_reduce_best return, over several ticks
+    (the double-buffered sequence flags must not stall or go stale)."""
+    import torch
+    xu, x0, goals = make_cases(oracle_model, 24, N=32, seed=13)
+    e = pkg.Engine(N=32, batch=24, dtype="fp64", cluster=1)
+    h = e.p2p_create(1, 0)
+    assert len(h) == 64
+    e.p2p_connect([h])
+    dev = lambda a: torch.tensor(a, device="cuda")
+    xu_d, x0_d, g_d = dev(xu), dev(x0), dev(goals)
+    for tick in range(5):
+        out, st = e.solve(xu_d, x0_d, g_d)
+        ref = e.reduce_best(e.pack_best(st, out, index_offset=7).view(1, -1), 1)
+        got = e.p2p_exchange(st, out, index_offset=7)
+        assert torch.equal(got, ref)
+        xu_d = out
+    e.p2p_status(got)
+
+
+def _peer_rank(rank, world, port, q):
+    import os
+    import torch
+    import torch.distributed as dist
+    import indy7_mpc_b200 as pkg
+    from indy7_mpc_b200 import dist as i7d
+    from oracle.model import load_model
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        model = load_model()
+        xu, x0, goals = make_cases(model, 16 * world, N=32, seed=17)
+        lo, hi = i7d.shard_range(16 * world, rank, world)
+        e = pkg.Engine(N=32, batch=16, dtype="fp64", cluster=1, device=rank)
+        i7d.connect_peers(e, rank, world)
+        dev = lambda a: torch.tensor(a[lo:hi], device=f"cuda:{rank}")
+        xu_d, x0_d, g_d = dev(xu), dev(x0), dev(goals)
+        res = []
+        for tick in range(4):
+            out, st = e.solve(xu_d, x0_d, g_d)
+            packed = e.pack_best(st, out, index_offset=lo)
+            best = e.p2p_exchange(st, out, index_offset=lo)
+            parts = [torch.empty_like(packed).cpu() for _ in range(world)]
+            dist.all_gather(parts, packed.cpu())
+            ref = e.reduce_best(torch.stack(parts).to(best.device), world)
+            res.append(bool(torch.equal(best, ref)))
+            xu_d = out
+        e.p2p_status(best)
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_exchange_two_gpus(pkg):
+    """Two ranks, one per GPU: the peer-memory exchange kernel (stores over NVLink into cudaIpc-mapped buffers) selects
+    bitwise the same record as pack_best -> all-gather (gloo here) -> reduce_best on every rank, tick after tick."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_peer_rank, args=(r, 2, 29611, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    got = [q.get(timeout=240) for _ in ps]
+    for p in ps:
+        p.join(60)
+    assert sorted(r for r, _ in got) == [0, 1]
+    assert all(all(ok) for _, ok in got)
