@@ -140,6 +140,16 @@ i7_status i7_kernel_form(const i7_handle* h, int32_t* threads, int32_t* ctas_per
 i7_status i7_sim_forward(i7_handle* h, int32_t batch, const void* x, const void* u, double dt, int32_t bcast,
                          void* x_next, void* stream);
 
+/* Wrench-hypothesis selection of the batch drivers in ONE launch (gato_controller.py:109-118 find_best_idx;
+ * src/gato_mpc_batch_sample.py:254-300 find_best_trajectory_id after the wrench conversion): one rk4 plant step of
+ * length dt from the single row (x_last, u_last) per lane under that lane's external wrench, error_i =
+ * ||x_next_i - xs||_2, then the argmin in index order: tie_last != 0 compares with `<=` (last of equal minima,
+ * gato_controller.py:115), tie_last == 0 with `<` (first, gato_mpc_batch_sample.py:283); NaN errors never win.
+ * result: 2 numbers [best index (as a number; -1 when no lane qualified), its error].  x_next (batch x 12) and
+ * errors (batch) are optional outputs (NULL to skip).  Pointers host or device, handle dtype. */
+i7_status i7_find_best_idx(i7_handle* h, int32_t batch, const void* x_last, const void* u_last, const void* xs, double dt,
+                           int32_t tie_last, void* x_next, void* errors, void* result, void* stream);
+
 /* Best-trajectory selection over a batch (north_star: "a single NCCL gather of per-problem costs and best
  * trajectory"; reference analogue gato_controller.py:105-118 argmin over hypotheses).  Writes, on the device,
  * packed = [cost_0 .. cost_{batch-1} | best_cost, best_index (as a number), XU_best (18N-6)] where cost_b =

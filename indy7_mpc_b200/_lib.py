@@ -52,6 +52,7 @@ SYMBOLS = {
     "i7_measure_fma_peak": (_i32, [_vp, C.POINTER(_dbl)]),
     "i7_profile_phases": (_i32, [_vp, _i32, C.POINTER(C.c_int64), _i32]),
     "i7_sim_forward": (_i32, [_vp, _i32, _vp, _vp, _dbl, _i32, _vp, _vp]),
+    "i7_find_best_idx": (_i32, [_vp, _i32, _vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp]),
     "i7_solve_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp]),
     "i7_dump_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "i7_merit": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp]),

@@ -87,6 +87,14 @@ class _SQPSolverBase:
         u = np.asarray(u, float).reshape(-1)
         return np.asarray(eng.sim_forward(x[:12], u[:6], float(dt), batch=self.BATCH), float)
 
+    def find_best_idx(self, x_last, u_last, xs, dt, tie_last=True):
+        """Extension of the reference binding: ``BatchGATO.find_best_idx`` (gato_controller.py:109-118) — sim_forward
+        of all lanes, error against the measured state, `<=` argmin — as ONE launch that returns only the index."""
+        eng = self._engine or self._ensure(self._N or 32, self._dt or 0.01)
+        f = lambda a, n: np.asarray(a, float).reshape(-1)[:n]
+        return eng.find_best_idx(f(x_last, 12), f(u_last, 6), f(xs, 12), float(dt), batch=self.BATCH,
+                                 tie_last=tie_last)
+
 
 def _make(B):
     return type(f"SQPSolverfloat_{B}", (_SQPSolverBase,), {"BATCH": B, "__doc__": f"batch of {B} SQP problems"})

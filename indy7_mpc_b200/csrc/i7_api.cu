@@ -54,6 +54,8 @@ struct i7_handle {
     void* p2p_peer[16] = {};
     unsigned char** p2p_table = nullptr;
     int* p2p_err = nullptr;
+    unsigned* d_sel_counter = nullptr;   // i7_find_best_idx: ticket counter + error scratch (lazy)
+    void* d_sel_errs = nullptr;
     unsigned long long p2p_seq = 0;
     int direct_max_batch = 0;    // host-buffer solves up to this batch use mapped host memory instead of copies
     bool timed = false;
@@ -403,6 +405,8 @@ void i7_destroy(i7_handle* h) {
     if (h->p2p_mine) cudaFree(h->p2p_mine);
     if (h->p2p_table) cudaFree(h->p2p_table);
     if (h->p2p_err) cudaFree(h->p2p_err);
+    if (h->d_sel_counter) cudaFree(h->d_sel_counter);
+    if (h->d_sel_errs) cudaFree(h->d_sel_errs);
     for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
         if (h->pipe_stream[k]) cudaStreamDestroy(h->pipe_stream[k]);
         if (h->pipe_join[k]) cudaEventDestroy(h->pipe_join[k]);
@@ -850,7 +854,8 @@ i7_status sim_forward_t(i7_handle* h, int batch, const void* x, const void* u, d
     // a warp per lane while that still fills the device only a few times over, a thread per lane beyond
     if (batch <= 512)
         i7::sim_forward_warp_kernel<T><<<batch, 32, 0, s>>>(rob, batch, dx, du, bcast,
-                                                           h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o);
+                                                           h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o,
+                                                           i7::SelectArgs<T>{nullptr, nullptr, nullptr, nullptr, 0});
     else
         i7::sim_forward_kernel<T><<<(batch + 63) / 64, 64, 0, s>>>(rob, batch, dx, du, bcast,
                                                                    h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o);
@@ -858,9 +863,46 @@ i7_status sim_forward_t(i7_handle* h, int batch, const void* x, const void* u, d
     I7_CUDA(h, cudaGetLastError());
     return st.flush_out(s);
 }
+
+template <typename T>
+i7_status find_best_idx_t(i7_handle* h, int batch, const void* x_last, const void* u_last, const void* xs, double dt,
+                          int tie_last, void* x_next, void* errors, void* result, cudaStream_t s) {
+    const size_t es = sizeof(T);
+    if (!h->d_sel_counter) {
+        I7_CUDA(h, cudaMalloc((void**)&h->d_sel_counter, sizeof(unsigned)));
+        I7_CUDA(h, cudaMemset(h->d_sel_counter, 0, sizeof(unsigned)));
+        I7_CUDA(h, cudaMalloc(&h->d_sel_errs, (size_t)h->cfg.batch * es));
+    }
+    Stage st(h);
+    const T* dx = (const T*)st.in(x_last, 12 * es);
+    const T* du = (const T*)st.in(u_last, 6 * es);
+    const T* dxs = (const T*)st.in(xs, 12 * es);
+    T* o = x_next ? (T*)st.out(x_next, (size_t)batch * 12 * es) : nullptr;
+    T* de = errors ? (T*)st.out(errors, (size_t)batch * es) : (T*)h->d_sel_errs;
+    T* dr = (T*)st.out(result, 2 * es);
+    i7_status rc;
+    if ((rc = st.flush_in(s))) return rc;
+    i7::sim_forward_warp_kernel<T><<<batch, 32, 0, s>>>(get_rob<T>(h), batch, dx, du, 1,
+                                                       h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o,
+                                                       i7::SelectArgs<T>{dxs, de, dr, h->d_sel_counter, tie_last});
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
 }  // namespace
 
 extern "C" {
+
+i7_status i7_find_best_idx(i7_handle* h, int32_t batch, const void* x_last, const void* u_last, const void* xs, double dt,
+                           int32_t tie_last, void* x_next, void* errors, void* result, void* stream) {
+    if (!h || !x_last || !u_last || !xs || !result) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64
+               ? find_best_idx_t<double>(h, batch, x_last, u_last, xs, dt, tie_last, x_next, errors, result, s)
+               : find_best_idx_t<float>(h, batch, x_last, u_last, xs, dt, tie_last, x_next, errors, result, s);
+}
 
 i7_status i7_dynamics(i7_handle* h, int32_t n, const void* q, const void* v, const void* tau, const void* f_ext,
                       void* qdd, void* dqdd_dq, void* dqdd_dv, void* Minv, void* stream) {

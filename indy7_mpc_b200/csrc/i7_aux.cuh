@@ -1,6 +1,7 @@
 // i7_aux.cuh — sample-level kernels (one thread per sample) next to the fused solve: forward dynamics and its
 // derivatives, end-effector position / Jacobian, the rk4 plant step, best-trajectory selection, FMA-peak probe.
 #pragma once
+#include <math_constants.h>
 #include "i7_wf.cuh"
 
 namespace i7 {
@@ -115,9 +116,25 @@ __global__ void sim_forward_kernel(const __grid_constant__ Robot<T> rob, int n, 
 // spread over the lanes of a warp with the world-frame tasks of the solver's setup (i7_wf.cuh): cos/sin per joint,
 // the origin, one link record per lane, one mass-matrix column per lane, then the 6x6 solve; lane i < 6 owns
 // component i of the state through the rk4 stages.  Used for small and medium batches (i7_sim_forward).
+//
+// With sel.xs != nullptr the launch is also the hypothesis selection of the batch drivers (gato_controller.py:109-118
+// find_best_idx; src/gato_mpc_batch_sample.py:254-300): error_i = ||x_next_i - xs||_2 (squares summed in component
+// order), and the last CTA to finish picks the winner in index order — `<=` (last of equal minima) when tie_last,
+// `<` (first) otherwise; NaN errors never win, exactly like the Python comparisons.  result = [index, error], index
+// -1 when no lane qualified.
+template <typename T>
+struct SelectArgs {
+    const T* xs;          // 12 numbers, the measured state; nullptr = plain plant step
+    T* errs;              // n numbers (scratch or caller's buffer)
+    T* result;            // 2 numbers
+    unsigned* counter;    // zero before the launch; reset by the kernel
+    int tie_last;
+};
+
 template <typename T>
 __global__ void __launch_bounds__(32) sim_forward_warp_kernel(const __grid_constant__ Robot<T> rob, int n, const T* x, const T* u,
-                                                              int bcast, const T* fext, T dt, T* x_next) {
+                                                              int bcast, const T* fext, T dt, T* x_next,
+                                                              const SelectArgs<T> sel) {
     __shared__ T s_cs[12], s_qd[6], s_pee[3], s_S[36], s_V[36], s_A[36], s_I[54], s_F[36], s_M[36], s_b[6], s_fx[6];
     const int i = blockIdx.x, lane = threadIdx.x;
     if (i >= n) return;
@@ -166,11 +183,49 @@ __global__ void __launch_bounds__(32) sim_forward_warp_kernel(const __grid_const
     const T k3v = fd(q0 + k2q * dt / T(2), k3q);
     const T k4q = v0 + k3v * dt;
     const T k4v = fd(q0 + k3q * dt, k4q);
-    if (lane < 6) {
-        const T vn = v0 + (dt / T(6)) * (k1v + T(2) * k2v + T(2) * k3v + k4v);
-        const T av = (v0 + T(2) * k2q + T(2) * k3q + k4q) / T(6);
-        x_next[12 * i + lane] = q0 + av * dt;
+    const T vn = v0 + (dt / T(6)) * (k1v + T(2) * k2v + T(2) * k3v + k4v);
+    const T av = (v0 + T(2) * k2q + T(2) * k3q + k4q) / T(6);
+    const T qn = q0 + av * dt;
+    if (lane < 6 && x_next) {
+        x_next[12 * i + lane] = qn;
         x_next[12 * i + 6 + lane] = vn;
+    }
+    if (!sel.xs) return;
+    const T dq = qn - sel.xs[c], dv = vn - sel.xs[6 + c];
+    T ss = T(0);
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { const T d = __shfl_sync(0xffffffffu, dq, a); ss += d * d; }
+#pragma unroll
+    for (int a = 0; a < 6; ++a) { const T d = __shfl_sync(0xffffffffu, dv, a); ss += d * d; }
+    unsigned ticket = 0;
+    if (lane == 0) {
+        sel.errs[i] = sqrt(ss);
+        __threadfence();
+        ticket = atomicAdd(sel.counter, 1u);
+    }
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket != (unsigned)(n - 1)) return;
+    __threadfence();
+    // the last CTA: every error is visible; argmin in index order
+    T be = T(0);
+    int bi = -1;
+    for (int j = lane; j < n; j += 32) {
+        const T e = __ldcg(sel.errs + j);
+        if (e != e || (!sel.tie_last && !(e < T(CUDART_INF)))) continue;
+        if (bi < 0 || e < be || (sel.tie_last && e == be)) { be = e; bi = j; }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const T oe = __shfl_down_sync(0xffffffffu, be, off);
+        const int oi = __shfl_down_sync(0xffffffffu, bi, off);
+        if (oi < 0) continue;
+        const bool take = bi < 0 || oe < be || (oe == be && (sel.tie_last ? oi > bi : oi < bi));
+        if (take) { be = oe; bi = oi; }
+    }
+    if (lane == 0) {
+        sel.result[0] = T(bi);
+        sel.result[1] = bi < 0 ? T(CUDART_INF) : be;
+        *sel.counter = 0u;
     }
 }
 

@@ -215,9 +215,7 @@ class MPC_GATO_Batch_Sample:
         keeps the best wrench in lane 1 and the zero wrench in lane 0."""
         S = self.solver
         S.solver.set_external_wrench_batch(S.f_ext_batch)
-        x_next = np.asarray(S.solver.sim_forward(np.asarray(x_last, float), np.asarray(u_last, float), float(dt)), float)
-        err = np.linalg.norm(x_next - np.asarray(xcur, float)[None, :], axis=1)
-        best_id = int(len(err) - 1 - np.argmin(err[::-1]))
+        best_id = S.solver.find_best_idx(x_last, u_last, xcur, float(dt), tie_last=True)   # one launch, `<=` argmin
         if self.resample_f_ext and self.f_ext_resample_std != 0:
             f_best = S.f_ext_batch[best_id].copy()
             S.f_ext_batch = np.tile(f_best, (S.batch_size, 1)) + np.random.normal(0, self.f_ext_resample_std,
@@ -235,10 +233,9 @@ class MPC_GATO_Batch_Sample:
         S = self.solver
         local = self.model.world_wrench_to_last_joint(np.asarray(x_last, float)[:self.nq], S.f_ext_batch)
         self._hyp.set_external_wrench(local)
-        x_next = np.asarray(self._hyp.sim_forward(np.asarray(x_last, float), np.asarray(u_last, float), float(dt),
-                                                  batch=S.batch_size), float)
-        err = np.linalg.norm(x_next - np.asarray(xcur, float)[None, :], axis=1)
-        best_id = int(np.argmin(err))                 # first minimum, like the strict '<' of the reference loop
+        # plant step of every lane + error + first minimum (the strict '<' of the reference loop) in one launch
+        best_id = self._hyp.find_best_idx(np.asarray(x_last, float), np.asarray(u_last, float), np.asarray(xcur, float),
+                                          float(dt), batch=S.batch_size, tie_last=False)
         if self.resample_f_ext:
             f_best = S.f_ext_batch[best_id].copy()
             S.f_ext_batch = f_best + np.random.normal(0, self.f_ext_resample_std, S.f_ext_batch.shape)

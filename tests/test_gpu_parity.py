@@ -661,3 +661,51 @@ def test_peer_exchange_two_gpus(pkg):
         p.join(60)
     assert sorted(r for r, _ in got) == [0, 1]
     assert all(all(ok) for _, ok in got)
+
+
+@pytest.mark.parametrize("B", [1, 7, 64, 300])
+def test_find_best_idx_fused_selection(pkg, oracle_model, B):
+    """i7_find_best_idx (plant step of every lane + error + argmin in one launch) against the Python loops of
+    gato_controller.py:109-118 (`<=`: last of equal minima) and gato_mpc_batch_sample.py:279-285 (`<`: first):
+    errors to 1e-9, indices exact, duplicated hypotheses as exact ties, a NaN hypothesis never wins; device and
+    host buffers."""
+    import torch
+    rng = np.random.default_rng(40 + B)
+    e = pkg.Engine(N=8, batch=B, dtype="fp64")
+    x_last = np.concatenate([rng.uniform(-1, 1, 6), rng.uniform(-0.5, 0.5, 6)])
+    u_last = rng.uniform(-5, 5, 6)
+    f = np.zeros((B, 6)); f[:, :3] = rng.normal(0, 5, (B, 3))
+    k = B // 2
+    if B >= 7:
+        f[5] = f[2]                       # exact tie
+        f[3, 0] = np.nan                  # a poisoned lane
+        k = 2
+    step = lambda w: np.hstack(rbd.rk4(oracle_model, x_last[:6], x_last[6:], u_last, 0.002, w))
+    xs = step(f[k])
+    e.set_external_wrench(f)
+    ref_err = np.array([np.linalg.norm(step(f[i]) - xs) for i in range(B)])
+
+    def loop(le):
+        best, bi = np.inf, None
+        for i in range(B):
+            if (ref_err[i] <= best) if le else (ref_err[i] < best):
+                best, bi = ref_err[i], i
+        return bi
+    for tie_last in (True, False):
+        idx, errs = e.find_best_idx(x_last, u_last, xs, 0.002, batch=B, tie_last=tie_last, return_errors=True)
+        ok = ~np.isnan(ref_err)
+        assert np.array_equal(np.isnan(errs), ~ok)
+        assert np.abs(errs[ok] - ref_err[ok]).max() <= 1e-9
+        assert idx == loop(tie_last)
+        if B >= 7:
+            assert idx == (5 if tie_last else 2)
+        d = lambda a: torch.tensor(a, device="cuda")
+        assert e.find_best_idx(d(x_last), d(u_last), d(xs), 0.002, batch=B, tie_last=tie_last) == idx
+    # xs away from every prediction: a generic argmin; every lane NaN: no winner
+    xs2 = xs + rng.normal(0, 1e-3, 12)
+    ref_err = np.array([np.linalg.norm(step(f[i]) - xs2) for i in range(B)])
+    assert e.find_best_idx(x_last, u_last, xs2, 0.002, batch=B) == loop(True)
+    assert e.find_best_idx(x_last, u_last, np.full(12, np.nan), 0.002, batch=B) is None
+    e32 = pkg.Engine(N=8, batch=B, dtype="fp32")
+    e32.set_external_wrench(f)
+    assert e32.find_best_idx(x_last, u_last, xs2, 0.002, batch=B) == loop(True)
