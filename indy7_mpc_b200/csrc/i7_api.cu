@@ -679,6 +679,7 @@ i7_status i7_p2p_create(i7_handle* h, int32_t world, int32_t rank, unsigned char
 
 i7_status i7_p2p_connect(i7_handle* h, const unsigned char* handles) {
     if (!h || !handles || !h->p2p_mine) { if (h) h->err = "i7_p2p_create first"; return I7_ERR_INVALID; }
+    if (h->p2p_table) { h->err = "peers already connected"; return I7_ERR_INVALID; }
     I7_CUDA(h, cudaSetDevice(h->cfg.device));
     for (int r = 0; r < h->p2p_world; ++r) {
         if (r == h->p2p_rank) { h->p2p_peer[r] = h->p2p_mine; continue; }
