@@ -126,7 +126,9 @@ i7_status i7_reset_lambda(i7_handle* h);
 i7_status i7_solve(i7_handle* h, int32_t batch, const void* xu_in, const void* x0, const void* goals,
                    int32_t goal_stride, void* xu_out, void* stats, void* stream);
 
-/* Device-time of the latest i7_solve kernel in microseconds (CUDA events on the launch stream; blocks). */
+/* Device-time of the latest i7_solve kernel in microseconds (CUDA events on the launch stream; blocks).  With the
+ * environment variable I7_TIMING_EVENTS=0 at i7_create, small host-buffer solves (the mapped-memory path) are not
+ * timed (the two event records cost 3 us of host time per solve) and this call then returns I7_ERR_INVALID. */
 i7_status i7_last_solve_time_us(i7_handle* h, double* us);
 /* Number of kernel launches issued by this handle so far. */
 int64_t i7_launch_count(const i7_handle* h);

@@ -57,6 +57,7 @@ struct i7_handle {
     unsigned* d_sel_counter = nullptr;   // i7_find_best_idx: ticket counter + error scratch (lazy)
     void* d_sel_errs = nullptr;
     unsigned long long p2p_seq = 0;
+    int no_events = 0;           // I7_TIMING_EVENTS=0: no timing events around mapped-memory solves (3 us of host time each)
     int direct_max_batch = 0;    // host-buffer solves up to this batch use mapped host memory instead of copies
     bool timed = false;
     int64_t launches = 0;
@@ -267,10 +268,12 @@ i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     P.merits_out = (T*)st.out(c.merits, B * (c.mode == i7::MODE_MERIT ? 6 : 9) * es);
     i7_status rc = st.flush_in(s);
     if (rc) return rc;
-    if (c.mode == i7::MODE_SOLVE) I7_CUDA(h, cudaEventRecord(h->ev0, s));
+    const bool ev = c.mode == i7::MODE_SOLVE && !(h->no_events && st.direct);
+    if (ev) I7_CUDA(h, cudaEventRecord(h->ev0, s));
     rc = launch_sqp<T>(h, get_rob<T>(h), P, s);
     if (rc) return rc;
-    if (c.mode == i7::MODE_SOLVE) { I7_CUDA(h, cudaEventRecord(h->ev1, s)); h->timed = true; }
+    if (ev) { I7_CUDA(h, cudaEventRecord(h->ev1, s)); h->timed = true; }
+    else if (c.mode == i7::MODE_SOLVE) h->timed = false;
     return st.flush_out(s);
 }
 
@@ -526,6 +529,7 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
         int can_map = 0;
         cudaDeviceGetAttribute(&can_map, cudaDevAttrCanMapHostMemory, cfg->device);
         h->direct_max_batch = can_map ? (env ? std::atoi(env) : 8) : 0;
+        if (const char* e3 = std::getenv("I7_TIMING_EVENTS")) h->no_events = std::atoi(e3) == 0;
     }
     // chunked host pipeline for big batches (I7_PIPE_CHUNK problems per chunk; 0 disables)
     {

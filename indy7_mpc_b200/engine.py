@@ -21,6 +21,26 @@ def _is_torch(x):
     return torch is not None and isinstance(x, torch.Tensor)
 
 
+# the single-problem latency path counts microseconds of host time: ndarray.ctypes.data builds a helper object per
+# call (1.7 us) and np.prod of a shape tuple costs 3.5 us; these two do the same in ~0.4 us and ~0.05 us
+_from_buffer, _addressof = C.c_char.from_buffer, C.addressof
+
+
+def _addr(a):
+    try:
+        return _addressof(_from_buffer(a))
+    except (TypeError, ValueError, BufferError):          # read-only, empty or exotic arrays
+        return a.ctypes.data
+
+
+def _numel(x):
+    if isinstance(x, np.ndarray):
+        return x.size
+    if _is_torch(x):
+        return x.numel()
+    return int(np.prod(np.shape(x)))
+
+
 class Engine:
     def __init__(self, model=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
                  batch=1, dtype="fp64", device=0, max_qp=2, mu=10.0, step_tol=1e-3, threads=0, cluster=0):
@@ -86,16 +106,19 @@ class Engine:
             if t.is_cuda and t.device.index != self.device:
                 raise ValueError(f"tensor on {t.device}, engine on cuda:{self.device}")
             keep.append(t)
-            return C.c_void_p(t.data_ptr())
-        a = np.ascontiguousarray(np.asarray(x, dtype=self.np_dtype).reshape(shape))
+            return t.data_ptr()
+        if type(x) is np.ndarray and x.dtype == self.np_dtype and x.flags.c_contiguous and x.size == shape[0] * shape[1]:
+            a = x
+        else:
+            a = np.ascontiguousarray(np.asarray(x, dtype=self.np_dtype).reshape(shape))
         keep.append(a)
-        return C.c_void_p(a.ctypes.data)
+        return _addr(a)
 
     def _out(self, shape, like, keep, tag=""):
         if _is_torch(like) and like.is_cuda:
             t = torch.empty(shape, dtype=self._torch_dtype(), device=like.device)
             keep.append(t)
-            return t, C.c_void_p(t.data_ptr())
+            return t, t.data_ptr()
         if _is_torch(like) and like.is_pinned():
             # page-locked inputs get page-locked outputs (the C ABI then copies without staging); the buffers are
             # cached per call site and shape, so a result is valid until the next call of the same kind
@@ -105,10 +128,10 @@ class Engine:
                 t = torch.empty(shape, dtype=self._torch_dtype(), pin_memory=True)
                 self._pinned[key] = t
             keep.append(t)
-            return t, C.c_void_p(t.data_ptr())
+            return t, t.data_ptr()
         a = np.empty(shape, dtype=self.np_dtype)
         keep.append(a)
-        return a, C.c_void_p(a.ctypes.data)
+        return a, _addr(a)
 
     @staticmethod
     def _stream(like):
@@ -117,7 +140,7 @@ class Engine:
         return None
 
     def _goal_stride(self, goals, B):
-        n = int(np.prod(goals.shape)) // B
+        n = _numel(goals) // B
         if n == 3 * self.N:
             return 3
         if n == 6 * self.N:
@@ -125,7 +148,7 @@ class Engine:
         raise ValueError(f"goals must hold N*3 or N*6 numbers per problem, got {n} for N={self.N}")
 
     def _batch_of(self, xu):
-        n = int(np.prod(xu.shape))
+        n = _numel(xu)
         if n % self.nz:
             raise ValueError(f"trajectory length must be a multiple of 18N-6={self.nz}, got {n}")
         B = n // self.nz
