@@ -170,6 +170,7 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
         if (prof && tid == 0) prof[5 * qp + 2] = clock64();
         // ---- line search: candidates 0..7 (base, alpha = 1 .. 1/64) at the own knots — with 4 knots per CTA that is
         //      exactly one warp per task type; the last candidate (1/128) only if none of those is accepted ----
+#pragma unroll 1      // the body is 24 KB of code: unrolled by four it evicts itself from the instruction cache
         for (int c0 = 0; c0 < 8; c0 += M.merit_cap)
             merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, 8 - c0 < M.merit_cap ? 8 - c0 : M.merit_cap, mcomps, c0);
         cluster.sync();                                                             // barrier 3
