@@ -43,9 +43,10 @@ struct i7_handle {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // host-buffer calls on big batches run as a software pipeline of chunks over these streams (copy-in of chunk
     // i+1 and copy-out of chunk i-1 overlap the kernel of chunk i); pipe_chunk = problems per chunk, 0 = off
-    static constexpr int kPipeStreams = 3, kPipeMaxChunks = 64;
-    cudaStream_t pipe_stream[kPipeStreams] = {nullptr, nullptr, nullptr};
-    cudaEvent_t pipe_fork = nullptr, pipe_join[kPipeStreams] = {nullptr, nullptr, nullptr};
+    static constexpr int kPipeStreams = 6, kPipeMaxChunks = 64;    // streams in use: pipe_nstreams (I7_PIPE_STREAMS)
+    cudaStream_t pipe_stream[kPipeStreams] = {};
+    cudaEvent_t pipe_fork = nullptr, pipe_join[kPipeStreams] = {};
+    int pipe_nstreams = 3;
     cudaEvent_t pipe_done[kPipeMaxChunks] = {};
     int pipe_chunk = 0;
     // peer-memory exchange (i7_p2p_*): own buffer, the peers' mapped buffers, device copy of the pointer table
@@ -303,9 +304,9 @@ i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     const int nchunks = (int)((B + chunk - 1) / chunk);
     I7_CUDA(h, cudaEventRecord(h->ev0, s));
     I7_CUDA(h, cudaEventRecord(h->pipe_fork, s));
-    for (int k = 0; k < i7_handle::kPipeStreams; ++k) I7_CUDA(h, cudaStreamWaitEvent(h->pipe_stream[k], h->pipe_fork, 0));
+    for (int k = 0; k < h->pipe_nstreams; ++k) I7_CUDA(h, cudaStreamWaitEvent(h->pipe_stream[k], h->pipe_fork, 0));
     for (int i = 0; i < nchunks; ++i) {
-        cudaStream_t ps = h->pipe_stream[i % i7_handle::kPipeStreams];
+        cudaStream_t ps = h->pipe_stream[i % h->pipe_nstreams];
         const size_t b0 = (size_t)i * chunk, nb = B - b0 < chunk ? B - b0 : chunk;
         for (int a = 0; a < 3; ++a) {
             char* dev = (char*)h->in.dev + off_in[a] + b0 * per_in[a];
@@ -336,7 +337,7 @@ i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
         }
         I7_CUDA(h, cudaEventRecord(h->pipe_done[i], ps));
     }
-    for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
+    for (int k = 0; k < h->pipe_nstreams; ++k) {
         I7_CUDA(h, cudaEventRecord(h->pipe_join[k], h->pipe_stream[k]));
         I7_CUDA(h, cudaStreamWaitEvent(s, h->pipe_join[k], 0));
     }
@@ -535,6 +536,10 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
     {
         const char* env = std::getenv("I7_PIPE_CHUNK");
         h->pipe_chunk = env ? std::atoi(env) : 256;
+        if (const char* e4 = std::getenv("I7_PIPE_STREAMS")) {
+            const int n = std::atoi(e4);
+            h->pipe_nstreams = n < 1 ? 1 : (n > i7_handle::kPipeStreams ? i7_handle::kPipeStreams : n);
+        }
         if (h->pipe_chunk > 0 && cfg->batch >= 2 * h->pipe_chunk) {
             for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
                 I7_CUDA_C(cudaStreamCreateWithFlags(&h->pipe_stream[k], cudaStreamNonBlocking));
