@@ -251,7 +251,7 @@ def run_b200(args):
     # the selection; I7_P2P=0 selects the NCCL path (pack kernel, all_gather_into_tensor, reduce kernel)
     use_p2p = world > 1 and os.environ.get("I7_P2P", "1") != "0"
     if use_p2p:
-        i7d.connect_peers(eng, rank, world)
+        use_p2p = i7d.connect_peers(eng, rank, world)      # False (on every rank) -> the NCCL path
 
     def exchange(st, out):
         if use_p2p:

@@ -57,10 +57,34 @@ def connect_peers(engine, rank, world, group=None):
     """Sets up the peer-memory exchange of `engine` (i7_p2p_*): every rank allocates its exchange buffer, the 64-byte
     inter-process handles travel once through the process group, every rank maps every buffer.  After this,
     `engine.p2p_exchange(stats, xu, index_offset)` replaces pack_best + all_gather + reduce_best by ONE kernel that
-    stores the packed record straight into the peers' memory over NVLink."""
+    stores the packed record straight into the peers' memory over NVLink.
+
+    Returns True when EVERY rank is connected; False (on every rank alike) when any rank could not create or map a
+    buffer (no peer access between the devices, IPC handles not permitted, ...) — the caller then keeps the NCCL
+    path.  The collectives are issued by every rank whatever happened locally, so a failure cannot strand the others."""
+    import torch
     import torch.distributed as dist
-    mine = engine.p2p_create(world, rank)
+    ok, mine, why = 1, b"\0" * 64, ""
+    try:
+        mine = engine.p2p_create(world, rank)
+    except Exception as e:          # noqa: BLE001 - reported below, the decision is collective
+        ok, why = 0, str(e)
     handles = [None] * world
-    dist.all_gather_object(handles, mine, group=group)
-    engine.p2p_connect(handles)
+    dist.all_gather_object(handles, (ok, mine), group=group)
+    if all(o for o, _ in handles):
+        try:
+            engine.p2p_connect([h for _, h in handles])
+        except Exception as e:      # noqa: BLE001
+            ok, why = 0, str(e)
+    else:
+        ok = 0
+    oks = [None] * world
+    dist.all_gather_object(oks, ok, group=group)
+    if not all(oks):
+        if why:
+            import sys
+            print(f"[indy7_mpc_b200] rank {rank}: peer-memory exchange unavailable ({why}); using the NCCL path",
+                  file=sys.stderr)
+        return False
     dist.barrier(group=group)
+    return True

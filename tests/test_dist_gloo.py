@@ -96,3 +96,55 @@ def test_shard_range_and_world1():
     packed = torch.arange(4 + 2 + NZ, dtype=torch.float64)
     best, g = i7d.gather_best(packed, 4, 1, None)        # world 1: no collective, tail of the record
     assert best.numel() == 2 + NZ and best[0] == 4.0 and g is packed
+
+
+class _FakeEngine:
+    """Stands in for Engine.p2p_create / p2p_connect (CUDA IPC) in the collective set-up logic."""
+    def __init__(self, fail_create=False, fail_connect=False):
+        self.fail_create, self.fail_connect, self.connected = fail_create, fail_connect, None
+
+    def p2p_create(self, world, rank):
+        if self.fail_create:
+            raise RuntimeError("no peer access")
+        return bytes([rank]) * 64
+
+    def p2p_connect(self, handles):
+        if self.fail_connect:
+            raise RuntimeError("cannot map the peer buffer")
+        self.connected = list(handles)
+
+
+def _connect_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from indy7_mpc_b200 import dist as i7d
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        good = _FakeEngine()
+        r_ok = i7d.connect_peers(good, rank, world)
+        r_create = i7d.connect_peers(_FakeEngine(fail_create=(rank == 1)), rank, world)
+        r_connect = i7d.connect_peers(_FakeEngine(fail_connect=(rank == 0)), rank, world)
+        q.put((rank, r_ok, good.connected, r_create, r_connect))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+def test_connect_peers_is_a_collective_decision():
+    """dist.connect_peers: every rank gets every handle in rank order; a failure on ONE rank (creating or mapping a
+    buffer) makes EVERY rank return False (the caller keeps the NCCL path) and strands nobody."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_connect_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=150) for _ in procs]
+    for p in procs:
+        p.join(30)
+        assert p.exitcode == 0
+    for rank, r_ok, handles, r_create, r_connect in res:
+        assert r_ok is True and handles == [bytes([0]) * 64, bytes([1]) * 64]
+        assert r_create is False and r_connect is False

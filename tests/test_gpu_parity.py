@@ -625,7 +625,7 @@ def _peer_rank(rank, world, port, q):
         xu, x0, goals = make_cases(model, 16 * world, N=32, seed=17)
         lo, hi = i7d.shard_range(16 * world, rank, world)
         e = pkg.Engine(N=32, batch=16, dtype="fp64", cluster=1, device=rank)
-        i7d.connect_peers(e, rank, world)
+        assert i7d.connect_peers(e, rank, world)
         dev = lambda a: torch.tensor(a[lo:hi], device=f"cuda:{rank}")
         xu_d, x0_d, g_d = dev(xu), dev(x0), dev(goals)
         res = []
