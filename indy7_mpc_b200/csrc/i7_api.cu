@@ -48,6 +48,11 @@ struct i7_handle {
     cudaEvent_t pipe_fork = nullptr, pipe_join[kPipeStreams] = {};
     int pipe_nstreams = 3;
     cudaEvent_t pipe_done[kPipeMaxChunks] = {};
+    // mode 2 (default): all copies-in on ONE stream back to back, kernels round-robin on the compute streams (each
+    // waits for its chunk's inputs), all copies-out on ONE stream — a compute stream never waits for a copy-out
+    cudaStream_t pipe_in = nullptr, pipe_out = nullptr;
+    cudaEvent_t pipe_in_done[kPipeMaxChunks] = {}, pipe_k_done[kPipeMaxChunks] = {};
+    int pipe_mode = 2;
     int pipe_chunk = 0;
     // peer-memory exchange (i7_p2p_*): own buffer, the peers' mapped buffers, device copy of the pointer table
     int p2p_world = 0, p2p_rank = 0;
@@ -58,6 +63,7 @@ struct i7_handle {
     unsigned* d_sel_counter = nullptr;   // i7_find_best_idx: ticket counter + error scratch (lazy)
     void* d_sel_errs = nullptr;
     unsigned long long p2p_seq = 0;
+    int zero_copy = 1;           // I7_ZERO_COPY=0: page-locked user buffers go through copies / the chunked pipeline
     int no_events = 0;           // I7_TIMING_EVENTS=0: no timing events around mapped-memory solves (3 us of host time each)
     int direct_max_batch = 0;    // host-buffer solves up to this batch use mapped host memory instead of copies
     bool timed = false;
@@ -127,7 +133,17 @@ struct Stage {
     // memory, same address on the device under unified addressing) — no copy operations in the stream.  For a handful
     // of problems the two copies cost more stream latency (~10 us) than the few KB cost over PCIe inside the kernel.
     bool direct = false;
+    // zero_copy: page-locked USER buffers are handed to the kernel as they are (cudaHostAlloc / registered memory is
+    // device-accessible under unified addressing): every CTA pulls its problem over PCIe when it starts and pushes its
+    // result when it ends, so the transfers of a big batch are spread over the whole launch with no copy operation,
+    // no staging and a single launch.
+    bool zero_copy = false, zc_pending = false;
     explicit Stage(i7_handle* h_, bool direct_ = false) : h(h_), direct(direct_) {}
+    static void* mapped(const void* p) {
+        void* d = nullptr;
+        if (cudaHostGetDevicePointer(&d, const_cast<void*>(p), 0) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        return d;
+    }
     struct Xfer { void* user; size_t off; size_t bytes; bool pinned; };
     Xfer ins[8], outs[10];
     int nin = 0, nout = 0;
@@ -135,6 +151,8 @@ struct Stage {
         if (!p) return nullptr;
         const int kind = ptr_kind(p);
         if (kind == 1) return p;
+        if (kind == 2 && zero_copy)
+            if (const void* d = mapped(p)) return d;
         if (kind == 0 || direct) std::memcpy((char*)h->in.host + in_off, p, bytes);
         if (!direct) ins[nin++] = Xfer{const_cast<void*>(p), in_off, bytes, kind == 2};
         const void* d = (char*)(direct ? h->in.host : h->in.dev) + in_off;
@@ -145,6 +163,8 @@ struct Stage {
         if (!p) return nullptr;
         const int kind = ptr_kind(p);
         if (kind == 1) return p;
+        if (kind == 2 && zero_copy)
+            if (void* d = mapped(p)) { zc_pending = true; return d; }
         outs[nout++] = Xfer{p, out_off, bytes, kind == 2 && !direct};
         void* d = (char*)(direct ? h->out.host : h->out.dev) + out_off;
         out_off += (bytes + 15) & ~size_t(15);
@@ -169,6 +189,7 @@ struct Stage {
         return I7_OK;
     }
     i7_status flush_out(cudaStream_t s) {
+        if (!nout && zc_pending) I7_CUDA(h, cudaStreamSynchronize(s));      // results land in the caller's memory
         if (!nout) return I7_OK;
         for (int i = 0; i < nout && !direct;) {
             if (outs[i].pinned) {
@@ -247,11 +268,12 @@ struct SqpCall {
 };
 
 template <typename T>
-i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s) {
+i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s, bool zero_copy = false) {
     const int N = h->cfg.N;
     const size_t nz = h->nz, B = c.batch, es = sizeof(T);
     I7_CUDA(h, cudaSetDevice(h->cfg.device));
     Stage st(h, c.mode == i7::MODE_SOLVE && c.batch <= h->direct_max_batch);
+    st.zero_copy = zero_copy;
     i7::SolveParams<T> P;
     base_params<T>(h, P, c.batch, c.goal_stride, c.mode);
     P.xu_in = (const T*)st.in(c.xu, B * nz * es);
@@ -284,6 +306,10 @@ i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s) {
 // tail wave of one chunk's kernel overlaps the head of the next.  Pageable buffers pass through the pinned mirror of
 // the arena chunk by chunk (the host memcpy of chunk i+1 overlaps the GPU work on chunk i).  Synchronous, like every
 // host-buffer call.
+// problems per chunk.  Smaller chunks for smaller batches were measured and lose: every chunk costs ~25 us of host
+// time to issue (copies, launch, events), which for 64-problem chunks is more than the exposed copies they save.
+int pipe_chunk_for(const i7_handle* h, int /*batch*/) { return h->pipe_chunk; }
+
 template <typename T>
 i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     const int N = h->cfg.N;
@@ -300,13 +326,19 @@ i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     bool pin_in[3], pin_out[2];
     for (int a = 0; a < 3; ++a) pin_in[a] = ptr_kind(uin[a]) == 2;
     for (int a = 0; a < 2; ++a) pin_out[a] = uout[a] && ptr_kind(uout[a]) == 2;
-    const size_t chunk = (size_t)h->pipe_chunk;
+    const size_t chunk = (size_t)pipe_chunk_for(h, c.batch);
+    const bool m2 = h->pipe_mode == 2;
     const int nchunks = (int)((B + chunk - 1) / chunk);
     I7_CUDA(h, cudaEventRecord(h->ev0, s));
     I7_CUDA(h, cudaEventRecord(h->pipe_fork, s));
     for (int k = 0; k < h->pipe_nstreams; ++k) I7_CUDA(h, cudaStreamWaitEvent(h->pipe_stream[k], h->pipe_fork, 0));
+    if (m2) {
+        I7_CUDA(h, cudaStreamWaitEvent(h->pipe_in, h->pipe_fork, 0));
+        I7_CUDA(h, cudaStreamWaitEvent(h->pipe_out, h->pipe_fork, 0));
+    }
     for (int i = 0; i < nchunks; ++i) {
         cudaStream_t ps = h->pipe_stream[i % h->pipe_nstreams];
+        cudaStream_t s_in = m2 ? h->pipe_in : ps, s_out = m2 ? h->pipe_out : ps;
         const size_t b0 = (size_t)i * chunk, nb = B - b0 < chunk ? B - b0 : chunk;
         for (int a = 0; a < 3; ++a) {
             char* dev = (char*)h->in.dev + off_in[a] + b0 * per_in[a];
@@ -316,7 +348,11 @@ i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
                 std::memcpy(mir, src, nb * per_in[a]);
                 src = mir;
             }
-            I7_CUDA(h, cudaMemcpyAsync(dev, src, nb * per_in[a], cudaMemcpyHostToDevice, ps));
+            I7_CUDA(h, cudaMemcpyAsync(dev, src, nb * per_in[a], cudaMemcpyHostToDevice, s_in));
+        }
+        if (m2) {
+            I7_CUDA(h, cudaEventRecord(h->pipe_in_done[i], s_in));
+            I7_CUDA(h, cudaStreamWaitEvent(ps, h->pipe_in_done[i], 0));
         }
         i7::SolveParams<T> P;
         base_params<T>(h, P, (int)nb, c.goal_stride, c.mode);
@@ -329,17 +365,24 @@ i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
         P.stats = uout[1] ? (T*)((char*)h->out.dev + off_out[1] + b0 * per_out[1]) : nullptr;
         i7_status rc = launch_sqp<T>(h, get_rob<T>(h), P, ps, b0);
         if (rc) return rc;
+        if (m2) {
+            I7_CUDA(h, cudaEventRecord(h->pipe_k_done[i], ps));
+            I7_CUDA(h, cudaStreamWaitEvent(s_out, h->pipe_k_done[i], 0));
+        }
         for (int a = 0; a < 2; ++a) {
             if (!uout[a]) continue;
             const char* dev = (const char*)h->out.dev + off_out[a] + b0 * per_out[a];
             char* dst = pin_out[a] ? (char*)uout[a] + b0 * per_out[a] : (char*)h->out.host + off_out[a] + b0 * per_out[a];
-            I7_CUDA(h, cudaMemcpyAsync(dst, dev, nb * per_out[a], cudaMemcpyDeviceToHost, ps));
+            I7_CUDA(h, cudaMemcpyAsync(dst, dev, nb * per_out[a], cudaMemcpyDeviceToHost, s_out));
         }
-        I7_CUDA(h, cudaEventRecord(h->pipe_done[i], ps));
+        I7_CUDA(h, cudaEventRecord(h->pipe_done[i], s_out));
     }
     for (int k = 0; k < h->pipe_nstreams; ++k) {
         I7_CUDA(h, cudaEventRecord(h->pipe_join[k], h->pipe_stream[k]));
         I7_CUDA(h, cudaStreamWaitEvent(s, h->pipe_join[k], 0));
+    }
+    if (m2) {       // every kernel is awaited by the copy-out stream; the copy-in stream by the kernels
+        I7_CUDA(h, cudaStreamWaitEvent(s, h->pipe_done[nchunks - 1], 0));
     }
     I7_CUDA(h, cudaEventRecord(h->ev1, s));
     h->timed = true;
@@ -360,7 +403,8 @@ i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
 
 bool pipeline_eligible(const i7_handle* h, const SqpCall& c) {
     if (c.mode != i7::MODE_SOLVE || h->pipe_chunk <= 0 || h->use_cluster) return false;
-    if (c.batch < 2 * h->pipe_chunk || (c.batch + h->pipe_chunk - 1) / h->pipe_chunk > i7_handle::kPipeMaxChunks) return false;
+    const int chunk = pipe_chunk_for(h, c.batch);
+    if (c.batch < 2 * chunk || (c.batch + chunk - 1) / chunk > i7_handle::kPipeMaxChunks) return false;
     if (c.xu_full || c.z_out || c.Adata || c.Pdata || c.g || c.l || c.alpha || c.merits) return false;
     const void* ptrs[5] = {c.xu, c.x0, c.goals, c.xu_out, c.stats};
     for (int a = 0; a < 5; ++a)
@@ -372,6 +416,13 @@ i7_status run_sqp(i7_handle* h, const SqpCall& c, void* stream) {
     i7_status rc = check_batch(h, c.batch, c.goal_stride);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
+    if (h->zero_copy && c.mode == i7::MODE_SOLVE && c.batch > h->direct_max_batch) {
+        // every host buffer of the call page-locked: one launch straight on the caller's memory
+        const void* ptrs[5] = {c.xu, c.x0, c.goals, c.xu_out, c.stats};
+        bool all = true;
+        for (int a = 0; a < 5; ++a) all = all && (!ptrs[a] || ptr_kind(ptrs[a]) == 2);
+        if (all) return h->cfg.dtype == I7_F64 ? run_sqp_t<double>(h, c, s, true) : run_sqp_t<float>(h, c, s, true);
+    }
     if (pipeline_eligible(h, c))
         return h->cfg.dtype == I7_F64 ? run_solve_pipelined<double>(h, c, s) : run_solve_pipelined<float>(h, c, s);
     return h->cfg.dtype == I7_F64 ? run_sqp_t<double>(h, c, s) : run_sqp_t<float>(h, c, s);
@@ -417,6 +468,12 @@ void i7_destroy(i7_handle* h) {
     }
     for (int k = 0; k < i7_handle::kPipeMaxChunks; ++k) if (h->pipe_done[k]) cudaEventDestroy(h->pipe_done[k]);
     if (h->pipe_fork) cudaEventDestroy(h->pipe_fork);
+    if (h->pipe_in) cudaStreamDestroy(h->pipe_in);
+    if (h->pipe_out) cudaStreamDestroy(h->pipe_out);
+    for (int k = 0; k < i7_handle::kPipeMaxChunks; ++k) {
+        if (h->pipe_in_done[k]) cudaEventDestroy(h->pipe_in_done[k]);
+        if (h->pipe_k_done[k]) cudaEventDestroy(h->pipe_k_done[k]);
+    }
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     delete h;
@@ -531,16 +588,25 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
         cudaDeviceGetAttribute(&can_map, cudaDevAttrCanMapHostMemory, cfg->device);
         h->direct_max_batch = can_map ? (env ? std::atoi(env) : 8) : 0;
         if (const char* e3 = std::getenv("I7_TIMING_EVENTS")) h->no_events = std::atoi(e3) == 0;
+        if (const char* e6 = std::getenv("I7_ZERO_COPY")) h->zero_copy = std::atoi(e6) != 0;
+        if (!can_map) h->zero_copy = 0;
     }
     // chunked host pipeline for big batches (I7_PIPE_CHUNK problems per chunk; 0 disables)
     {
         const char* env = std::getenv("I7_PIPE_CHUNK");
         h->pipe_chunk = env ? std::atoi(env) : 256;
+        if (const char* e5 = std::getenv("I7_PIPE_MODE")) h->pipe_mode = std::atoi(e5) == 1 ? 1 : 2;
         if (const char* e4 = std::getenv("I7_PIPE_STREAMS")) {
             const int n = std::atoi(e4);
             h->pipe_nstreams = n < 1 ? 1 : (n > i7_handle::kPipeStreams ? i7_handle::kPipeStreams : n);
         }
         if (h->pipe_chunk > 0 && cfg->batch >= 2 * h->pipe_chunk) {
+            I7_CUDA_C(cudaStreamCreateWithFlags(&h->pipe_in, cudaStreamNonBlocking));
+            I7_CUDA_C(cudaStreamCreateWithFlags(&h->pipe_out, cudaStreamNonBlocking));
+            for (int k = 0; k < i7_handle::kPipeMaxChunks; ++k) {
+                I7_CUDA_C(cudaEventCreateWithFlags(&h->pipe_in_done[k], cudaEventDisableTiming));
+                I7_CUDA_C(cudaEventCreateWithFlags(&h->pipe_k_done[k], cudaEventDisableTiming));
+            }
             for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
                 I7_CUDA_C(cudaStreamCreateWithFlags(&h->pipe_stream[k], cudaStreamNonBlocking));
                 I7_CUDA_C(cudaEventCreateWithFlags(&h->pipe_join[k], cudaEventDisableTiming));

@@ -420,8 +420,9 @@ def test_sharded_batch_is_bitwise_identical(pkg, oracle_model):
 
 
 def test_host_pipeline_is_bitwise_identical(pkg, oracle_model, monkeypatch):
-    """Host-buffer solves of big batches run as a chunked copy/compute pipeline (i7_api.cu: run_solve_pipelined):
-    pageable numpy and page-locked torch buffers, a ragged last chunk, per-lane wrenches — all bitwise equal to the
+    """Host-buffer solves of big batches: pageable buffers run as a chunked copy/compute pipeline (i7_api.cu:
+    run_solve_pipelined; a ragged last chunk, per-lane wrenches), page-locked buffers are read and written by the
+    kernel itself in one launch (zero-copy) or, with I7_ZERO_COPY=0, through the pipeline — all bitwise equal to the
     single-launch device-resident solve."""
     import torch
     xu1, x01, g1 = make_cases(oracle_model, 40, N=16, seed=21)
@@ -444,8 +445,22 @@ def test_host_pipeline_is_bitwise_identical(pkg, oracle_model, monkeypatch):
     assert piped.launch_count() - n0 == 8
     assert np.array_equal(np.asarray(out), ref) and np.array_equal(np.asarray(st), ref_st)
     pin = lambda a: torch.tensor(a).pin_memory()
-    out2, st2 = piped.solve(pin(xu), pin(x0), pin(goals))              # page-locked host buffers
+    n0 = piped.launch_count()
+    out2, st2 = piped.solve(pin(xu), pin(x0), pin(goals))              # page-locked host buffers: zero-copy, ONE launch
+    assert piped.launch_count() - n0 == 1
     assert np.array_equal(out2.numpy(), ref) and np.array_equal(st2.numpy(), ref_st)
+    monkeypatch.setenv("I7_ZERO_COPY", "0")                            # page-locked buffers through the chunked pipeline
+    piped2 = pkg.Engine(N=16, batch=900, dtype="fp64")
+    piped2.set_external_wrench(fext)
+    n0 = piped2.launch_count()
+    out4, st4 = piped2.solve(pin(xu), pin(x0), pin(goals))
+    assert piped2.launch_count() - n0 == 8
+    assert np.array_equal(out4.numpy(), ref) and np.array_equal(st4.numpy(), ref_st)
+    monkeypatch.setenv("I7_PIPE_MODE", "1")                            # the one-stream-per-chunk form of the pipeline
+    piped3 = pkg.Engine(N=16, batch=900, dtype="fp64")
+    piped3.set_external_wrench(fext)
+    out5, st5 = piped3.solve(xu, x0, goals)
+    assert np.array_equal(np.asarray(out5), ref) and np.array_equal(np.asarray(st5), ref_st)
     out3, _ = plain.solve(xu, x0, goals)                               # pipeline off: one launch
     assert np.array_equal(np.asarray(out3), ref)
 
