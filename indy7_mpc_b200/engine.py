@@ -157,13 +157,19 @@ class Engine:
         return B
 
     # ---- C-ABI calls ------------------------------------------------------------------------------------
-    def solve(self, xu, x0, goals, want_stats=True):
+    def solve(self, xu, x0, goals, want_stats=True, device_out=False):
+        """sqp() of every problem.  Outputs live where the inputs live; with device_out=True and host inputs the
+        results stay on the GPU (for a selection kernel to follow) and the call returns without waiting for the
+        stream — page-locked inputs must then stay untouched until the stream is synchronised."""
         B = self._batch_of(xu)
         gs = self._goal_stride(goals, B)
         keep = []
         p_xu, p_x0, p_g = self._in(xu, (B, self.nz), keep), self._in(x0, (B, 12), keep), self._in(goals, (B, gs * self.N), keep)
-        out, p_out = self._out((B, self.nz), xu, keep, "solve.xu")
-        stats, p_st = self._out((B, _lib.I7_STATS_LEN), xu, keep, "solve.st") if want_stats else (None, None)
+        like = xu
+        if device_out and not (_is_torch(xu) and xu.is_cuda):
+            like = torch.empty(0, dtype=self._torch_dtype(), device=f"cuda:{self.device}")
+        out, p_out = self._out((B, self.nz), like, keep, "solve.xu")
+        stats, p_st = self._out((B, _lib.I7_STATS_LEN), like, keep, "solve.st") if want_stats else (None, None)
         self._check(self.lib.i7_solve(self._h, B, p_xu, p_x0, p_g, gs, p_out, p_st, self._stream(xu)))
         return out, stats
 
