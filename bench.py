@@ -14,6 +14,11 @@ NVLink stores + selection; I7_P2P=0: i7_pack_best, ONE NCCL all-gather, i7_reduc
 Between ticks (untimed) the lanes advance like an MPC loop: x0 <- x_1 of the solution, trajectory shifted by one
 knot, goal window advanced by one sample — so every timed step is a realistic warm-started solve.
 
+End-to-end arm ("e2e"): the same closed loop from page-locked HOST buffers through the public API — every tick the
+kernel reads XU / x0 / goals of all lanes from host memory (zero-copy), the selection (N > 1: the exchange kernel) runs
+on the GPU and the result record is read back, all inside the wall-clock-timed call; "all_trajectories_to_host" is the
+variant that writes every trajectory back and selects on the host.
+
 Timing: CUDA events around every step on the launch stream, L2 flushed (256 MB memset) between steps outside the
 events, sum over the K timed steps, MAX over ranks; barrier + synchronize on both sides of the timed loop.
 """

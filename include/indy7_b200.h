@@ -122,7 +122,12 @@ i7_status i7_reset_lambda(i7_handle* h);
 
 /* One SQP solve per problem (src/osqp_sqp.py:76-93): xu_out[b] = sqp(x0[b], goals[b], xu_in[b]).
  * xu_in/xu_out: batch x (18N-6); x0: batch x 12; goals: batch x (N*goal_stride); stats: batch x I7_STATS_LEN
- * (may be NULL).  xu_out may alias xu_in. */
+ * (may be NULL).  xu_out may alias xu_in.
+ * Host buffers: the call returns when the results are in the caller's memory.  Page-locked host buffers
+ * (cudaHostAlloc / cudaHostRegister) are read and written by the kernel itself (zero-copy; I7_ZERO_COPY=0 at
+ * i7_create selects copy operations instead); pageable ones pass through the handle's page-locked mirror, chunk by
+ * chunk for 512 problems and more.  Host inputs with DEVICE outputs: the call is asynchronous on `stream`, and
+ * page-locked inputs must stay untouched until the stream is synchronised. */
 i7_status i7_solve(i7_handle* h, int32_t batch, const void* xu_in, const void* x0, const void* goals,
                    int32_t goal_stride, void* xu_out, void* stats, void* stream);
 
