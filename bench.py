@@ -2,25 +2,27 @@
 """Benchmark of the SQP-MPC hot path (BASELINE.json metric: batched SQP-MPC solves/s + p50 single-solve latency).
 
   python bench.py --gpus N --steps K --warmup W            the B200 arm (one rank per GPU under torchrun for N > 1)
-  python bench.py --impl reference --gpus N --steps K ...  the reference arm: the CPU restatement of osqp_sqp
-                                                            (oracle/c, OSQP-style ADMM) on the host cores
+  python bench.py --impl reference --gpus N --steps K ...  the reference arm: the reference's CPU loop on the host cores
+                                                            (the real src/osqp_sqp.py when pinocchio + osqp import,
+                                                            else its C restatement oracle/c with OSQP-style ADMM)
 
-Workload (BASELINE.json configs[3]): a batch of 4096 independent Indy7 N=32 SQP-MPC
-problems — sampled start states around the simulator home pose, figure-8 end-effector references at per-lane
+Workload of both arms (BASELINE.json configs[3]): a batch of 4096 independent Indy7 N=32
+SQP-MPC problems — sampled start states around the simulator home pose, figure-8 end-effector references at per-lane
 offsets, per-lane external-wrench hypotheses — sharded across the ranks (strong scaling: the total batch is fixed).
-One "step" = one control tick: every lane runs one sqp() (fused sm_100a kernel), then the per-problem costs and
-the best trajectory are selected and, for N > 1, exchanged by ONE kernel over peer memory (i7_p2p_exchange: pack +
-NVLink stores + selection; I7_P2P=0: i7_pack_best, ONE NCCL all-gather, i7_reduce_best).
-Between ticks (untimed) the lanes advance like an MPC loop: x0 <- x_1 of the solution, trajectory shifted by one
-knot, goal window advanced by one sample — so every timed step is a realistic warm-started solve.
+One "step" = one control tick of ALL lanes: every lane runs one sqp() warm-started from its shifted previous solution,
+then the per-problem costs and the best trajectory are selected (N > 1: exchanged between the ranks once per tick).
+Between ticks the lanes advance like an MPC loop (i7_shift / i7_goal_window on the device): x0 <- x_1 of the solution,
+trajectory moved one knot on, goal window advanced by one sample.
 
-End-to-end arm ("e2e"): the same closed loop from page-locked HOST buffers through the public API — every tick the
-kernel reads XU / x0 / goals of all lanes from host memory (zero-copy), the selection (N > 1: the exchange kernel) runs
-on the GPU and the result record is read back, all inside the wall-clock-timed call; "all_trajectories_to_host" is the
-variant that writes every trajectory back and selects on the host.
-
-Timing: CUDA events around every step on the launch stream, L2 flushed (256 MB memset) between steps outside the
-events, sum over the K timed steps, MAX over ranks; barrier + synchronize on both sides of the timed loop.
+B200 arm, three measurements in one JSON line:
+  value   device-resident tick (inputs in HBM when the timed region starts): CUDA events around solve + selection /
+          exchange on the launch stream, L2 flushed (256 MB memset) between ticks outside the events, max over ranks
+  e2e     the same tick through the public call Indy7SQP.step(x0, xref) with page-locked HOST inputs, wall clock: the
+          tick's inputs (measured states, goal windows) are read from host memory, the result (costs, best trajectory,
+          the state every lane predicts) is written back to host memory; the warm start stays on the GPU on both
+          sides.  'all_trajectories_to_host' = Indy7SQP.solve(x0, xref, xu_init) with every trajectory in and out.
+  latency BASELINE.json configs[1]: one problem, fig-8 tracking, closed loop with the rk4 plant
+plus 'configs': configs[2] (batch 16/32/64) and configs[4] (N=128, batch 512, fp64 and fp32) with their own CPU figures.
 """
 import argparse
 import json
@@ -141,67 +143,122 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_baseline(N, wl, tick_goals, seconds, sample_cap, nthreads=0):
-    """The plain-C restatement of osqp_sqp (OSQP-style ADMM) on the host cores, OpenMP across problems."""
-    from oracle.cport import COracle
-    from oracle.model import load_model
-    model = load_model()
+def workload_config(args):
+    """The `config` object of the JSON line — the same in both arms (the reference arm runs this very workload)."""
+    return {"workload": f"batch {args.batch} sampled Indy7 SQP-MPC problems (BASELINE.json configs[3]), N={args.horizon}, dt=0.01, "
+                        f"fp64 reference arithmetic, warm-started closed-loop MPC ticks of all lanes, per-lane wrench hypotheses, "
+                        f"per-problem costs + best-trajectory selection every tick",
+            "horizon": args.horizon, "batch_total": args.batch, "lanes_per_step": args.batch,
+            "parallelism": "batch sharded over the ranks (GPU arm) / OpenMP over lanes (CPU arm)",
+            "l2": "GPU arm: flushed between timed steps (256 MB memset outside the events)"}
+
+
+def probe_reference():
+    """can the real reference path run on this box?  It needs pinocchio + osqp (absent from
+    the image) and the reference's own sources (never shipped to the GPU box)."""
+    out = {}
+    for mod in ("pinocchio", "osqp"):
+        try:
+            m = __import__(mod)
+            out[mod] = getattr(m, "__version__", "present")
+        except Exception:
+            out[mod] = "absent"
+    src = os.environ.get("I7_REFERENCE_SRC", "")
+    out["reference_src"] = src if (src and os.path.exists(os.path.join(src, "osqp_sqp.py"))) else "absent"
+    out["runnable"] = all(v != "absent" for v in out.values())
+    return out
+
+
+class CpuLoop:
+    """The closed loop of the workload on the host cores: sqp() of every lane per tick, warm-started, then the shift.
+    kind 'port' = oracle/c (plain-C restatement of src/osqp_sqp.py + src/osqp_solver.py, OSQP-style ADMM at the
+    reference's tolerances, warm-started per lane, OpenMP over lanes); kind 'reference' = the unmodified reference
+    classes, one solver object per lane, when pinocchio + osqp + the reference sources are importable."""
+
+    def __init__(self, wl, lanes, N, nthreads, probe=None):
+        self.wl, self.lanes, self.N, self.nthreads = wl, lanes, N, nthreads
+        self.xu, self.x0 = wl["xu"][lanes].copy(), wl["x0"][lanes].copy()
+        self.tick = 0
+        self.kind = "port"
+        if probe and probe.get("runnable"):
+            self._init_reference(probe["reference_src"])
+        else:
+            from oracle.cport import COracle
+            from oracle.model import load_model
+            self.orc = COracle(load_model(), N=N, backend="admm", batch=len(lanes))
+
+    def _init_reference(self, src):            # pragma: no cover - needs pinocchio + osqp
+        sys.path.insert(0, src)
+        import pinocchio as pin
+        from osqp_solver import OSQPSolver
+        from osqp_sqp import SQP_OSQP
+        urdf = os.path.join(ROOT, "indy7_mpc_b200", "description", "indy7.urdf")
+        model = pin.buildModelFromUrdf(urdf)
+        model.gravity.linear = np.array([0.0, 0.0, -9.81])
+        self.ref = [SQP_OSQP(OSQPSolver(model, N=self.N)) for _ in self.lanes]
+        self.kind = "reference"
+
+    def step(self):
+        goals = goals_at(self.wl["fig"], self.wl["offsets"][self.lanes], self.tick, self.N)
+        t0 = time.perf_counter()
+        if self.kind == "port":
+            out, _, _ = self.orc.sqp(self.x0, goals, self.xu, f_ext=self.wl["f_ext"][self.lanes], nthreads=self.nthreads)
+        else:                                  # pragma: no cover
+            out = np.stack([r.sqp(self.x0[i], goals[i], self.xu[i]) for i, r in enumerate(self.ref)])
+        dt = time.perf_counter() - t0
+        self.xu, self.x0 = shift_host(out, self.N)
+        self.xu[:, :12] = self.x0
+        self.tick += 1
+        return dt
+
+
+def cpu_baseline(wl, N, seconds, lanes=None, max_ticks=50, warm=2):
+    """Bounded sample of the SAME workload on the host cores: `warm` untimed ticks (cold -> warm start), then
+    warm-started ticks of the given lanes (default: all of them) until `seconds` have been timed."""
     cores = host_cores()
-    nthreads = nthreads or cores      # explicit: torchrun exports OMP_NUM_THREADS=1 to every rank
-    chunk = max(8, min(sample_cap, 8 * cores))
-    orc = COracle(model, N=N, backend="admm", batch=chunk)
-    done, t0 = 0, time.perf_counter()
-    lo = 0
-    B = wl["x0"].shape[0]
-    while True:
-        idx = (lo + np.arange(chunk)) % B
-        orc.reset()
-        orc.sqp(wl["x0"][idx], tick_goals[idx], wl["xu"][idx], f_ext=wl["f_ext"][idx], nthreads=nthreads)
-        done += chunk; lo += chunk
-        el = time.perf_counter() - t0
-        if el >= seconds or done >= sample_cap:
-            break
-    return {"value": done / el, "unit": UNIT, "cores": nthreads, "kind": "port",
-            "sample": f"{done} cold-start problems of the same workload (tick 0) in {el:.1f} s, C restatement of "
-                      f"osqp_sqp with OSQP-style ADMM (oracle/c), OpenMP over problems"}
+    lanes = np.arange(wl["x0"].shape[0]) if lanes is None else lanes
+    probe = probe_reference()
+    loop = CpuLoop(wl, lanes, N, cores, probe)
+    for _ in range(warm):
+        loop.step()
+    times = []
+    while sum(times) < seconds and len(times) < max_ticks:
+        times.append(loop.step())
+    el = float(np.sum(times))
+    what = ("the unmodified reference classes (pinocchio + osqp)" if loop.kind == "reference" else
+            "C restatement of osqp_sqp with OSQP-style ADMM (oracle/c), OpenMP over lanes")
+    return {"value": len(lanes) * len(times) / el, "unit": UNIT, "cores": cores if loop.kind == "port" else 1, "kind": loop.kind,
+            "sample": f"{len(times)} warm-started ticks x {len(lanes)} lanes of the same workload in {el:.1f} s after "
+                      f"{warm} untimed ticks; {what}",
+            "probe": {k: probe[k] for k in ("pinocchio", "osqp", "reference_src")}}
 
 
 def run_reference(args):
-    """Reference arm: CPU restatement of the reference path on the host cores (Pinocchio / OSQP are not installable
-    here, so oracle/_ref does not exist; kind = 'port')."""
+    """Reference arm: the reference's CPU loop on the host cores, on the B200 arm's workload and config — ALL lanes of
+    the batch per step.  Pinocchio / OSQP are probed at start; without them (this image) the C restatement runs."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle.cport import COracle
-    from oracle.model import load_model
     N = args.horizon
     wl = make_workload(args.batch, N)
-    model = load_model()
     cores = host_cores()
-    per_step = max(8, min(args.batch, 4 * cores))
-    orc = COracle(model, N=N, backend="admm", batch=per_step)
-    idx = np.arange(per_step)
-    xu, x0 = wl["xu"][idx].copy(), wl["x0"][idx].copy()
+    probe = probe_reference()
+    loop = CpuLoop(wl, np.arange(args.batch), N, cores, probe)
     times = []
     for t in range(args.warmup + args.steps):
-        goals = goals_at(wl["fig"], wl["offsets"][idx], t, N)
-        t0 = time.perf_counter()
-        out, st, _ = orc.sqp(x0, goals, xu, f_ext=wl["f_ext"][idx], nthreads=cores)
-        dt = time.perf_counter() - t0
+        dt = loop.step()
         if t >= args.warmup:
             times.append(dt)
-        xu, x0 = shift_host(out, N)
-        xu[:, :12] = x0
     total = float(np.sum(times))
-    value = per_step * len(times) / total
-    sample = f"{per_step} lanes of the {args.batch}-lane workload per step, warm-started MPC ticks"
+    value = args.batch * len(times) / total
+    sample = f"all {args.batch} lanes per step, {len(times)} warm-started closed-loop ticks after {args.warmup} warm-up ticks"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"batch {args.batch} sampled Indy7 SQP-MPC problems, N={N} (bounded sample on CPU)",
-                   "horizon": N, "batch_total": args.batch, "sample_per_step": per_step},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": workload_config(args),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores if loop.kind == "port" else 1, "kind": loop.kind,
+                         "sample": sample, "probe": {k: probe[k] for k in ("pinocchio", "osqp", "reference_src")}},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -209,11 +266,92 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------- B200 arm
+def device_loop(eng, wl, N, W, K, dtype, dev, exchange=None, flush=None, check=None):
+    """W + K device-resident closed-loop ticks (solve -> selection/exchange -> shift -> goal window, all library
+    kernels on torch's current stream).  Returns per-tick (step_ms, kernel_ms) of the K timed ticks, the last stats."""
+    import torch
+    tdt = torch.float64 if dtype == "fp64" else torch.float32
+    B = wl["x0"].shape[0]
+    fig_d = torch.tensor(wl["fig"], dtype=tdt, device=dev)
+    off_d = torch.tensor(wl["offsets"], dtype=torch.int32, device=dev)
+    xu = torch.tensor(wl["xu"], dtype=tdt, device=dev)
+    x0 = torch.tensor(wl["x0"], dtype=tdt, device=dev)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    st = None
+    for t in range(W + K):
+        goals = eng.goal_window(fig_d, off_d, tick=t, wrap=True, batch=B)
+        i = t - W
+        if i >= 0:
+            if flush is not None:
+                flush.zero_()                            # L2 flush, outside the timed events
+            ev[i][0].record()
+        out, st = eng.solve(xu, x0, goals)
+        if i >= 0:
+            ev[i][1].record()                            # the dominant kernel on its own
+        best = exchange(st, out) if exchange is not None else eng.pack_best(st, out)
+        if i >= 0:
+            ev[i][2].record()
+        elif check is not None:
+            check(st, out, best)
+        xu, x0 = eng.shift(out, steps=1, tail="repeat")
+    torch.cuda.synchronize()
+    step_ms = np.array([e[0].elapsed_time(e[2]) for e in ev])
+    kern_ms = np.array([e[0].elapsed_time(e[1]) for e in ev])
+    return step_ms, kern_ms, st
+
+
+def fp_roofline(eng, st_host, N, B, kern_ms, dtype, fma_peak):
+    """Roofline of the solve kernel against the FP64 / FP32 FMA pipe (arithmetic intensity
+    ~215 flop/B, the bound is the CUDA-core FMA pipe): algorithmic flops of the measured (n_qp, n_try) per lane."""
+    flops = algorithmic_flops(st_host, N)
+    ach = flops * B / (kern_ms * 1e-3) / 1e12
+    return {"achieved": ach, "peak": fma_peak, "unit": "TFLOP/s", "frac": ach / fma_peak if fma_peak else None,
+            "algorithmic_flops_per_solve": flops}
+
+
+def extra_configs(args, local, fma_peaks):
+    """BASELINE.json configs[2] (batch 16/32/64, N=32) and configs[4] (N=128, batch 512, fp64 vs fp32) on one GPU:
+    device-resident closed-loop ticks, L2 flushed, with the FMA-pipe fraction and the CPU figure of the same lanes."""
+    import torch
+    from indy7_mpc_b200 import Engine
+    dev = torch.device("cuda", local)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    cases = [("configs[2]", 16, 32, "fp64"), ("configs[2]", 32, 32, "fp64"), ("configs[2]", 64, 32, "fp64"),
+             ("configs[4]", 512, 128, "fp64"), ("configs[4]", 512, 128, "fp32")]
+    out, cpu_cache, first = [], {}, {}
+    for name, B, N, dtype in cases:
+        wl = make_workload(B, N)
+        eng = Engine(N=N, batch=B, dtype=dtype, device=local)
+        eng.set_external_wrench(wl["f_ext"])
+        step_ms, kern_ms, st = device_loop(eng, wl, N, 5, args.config_ticks, dtype, dev, flush=flush)
+        sth = st.double().cpu().numpy()
+        if dtype not in fma_peaks:
+            fma_peaks[dtype] = eng.measure_fma_peak()
+        thr, ctas, smem = eng.kernel_form()
+        rec = {"config": name, "batch": B, "horizon": N, "dtype": "f64" if dtype == "fp64" else "f32",
+               "ms_per_tick": float(np.median(step_ms)), "solves_per_s": float(B / np.mean(step_ms) * 1e3),
+               "kernel": f"{thr} threads x {ctas} CTA(s) per problem, {smem} B shared memory",
+               "fp_pipe": fp_roofline(eng, sth, N, B, float(kern_ms.mean()), dtype, fma_peaks[dtype]),
+               "mean_qp_iters": float(sth[:, 0].mean())}
+        if N == 128:                         # fp32 against fp64 on identical inputs (north_star: 1e-4)
+            o, _ = eng.solve(torch.tensor(wl["xu"], dtype=st.dtype, device=dev), torch.tensor(wl["x0"], dtype=st.dtype, device=dev),
+                             torch.tensor(goals_at(wl["fig"], wl["offsets"], 0, N), dtype=st.dtype, device=dev))
+            first[dtype] = o.double().cpu().numpy()
+            if "fp64" in first and dtype == "fp32":
+                rec["fp32_vs_fp64_rel"] = float(np.abs(first["fp32"] - first["fp64"]).max() / np.abs(first["fp64"]).max())
+        if not args.no_cpu_baseline:
+            if (B, N) not in cpu_cache:
+                cpu_cache[(B, N)] = cpu_baseline(wl, N, args.config_cpu_seconds, max_ticks=20)
+            rec["cpu_baseline"] = cpu_cache[(B, N)]
+        out.append(rec)
+        del eng
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from indy7_mpc_b200 import Engine, Indy7SQP
-    from indy7_mpc_b200 import _lib
     from indy7_mpc_b200 import dist as i7d
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -239,17 +377,6 @@ def run_b200(args):
     wl = {k: (v[sl] if k != "fig" else v) for k, v in wl_all.items()}
     eng = Engine(N=N, batch=B, dtype=args.dtype, device=local, threads=args.threads)
     eng.set_external_wrench(wl["f_ext"])
-    fig_d = torch.tensor(wl["fig"], dtype=tdt, device=dev)
-    off_d = torch.tensor(wl["offsets"], device=dev)
-    ar_d = torch.arange(N, device=dev)
-
-    def goals_dev(t):
-        idx = (off_d[:, None] + t + ar_d[None, :]) % fig_d.shape[0]
-        return fig_d[idx].reshape(B, 3 * N).contiguous()
-
-    def shift_dev(out):
-        nxt = torch.cat([out[:, 18:], out[:, -18:]], dim=1).contiguous()
-        return nxt, out[:, 18:30].contiguous()
 
     gathered = torch.empty(world * (B + 2 + nz), dtype=tdt, device=dev) if world > 1 else None
     # exchange of the per-rank records: ONE kernel over peer memory (NVLink stores + flags), fused with the packing and
@@ -258,33 +385,28 @@ def run_b200(args):
     if use_p2p:
         use_p2p = i7d.connect_peers(eng, rank, world)      # False (on every rank) -> the NCCL path
 
-    def exchange(st, out):
-        if use_p2p:
-            return eng.p2p_exchange(st, out, index_offset=rank * B)
-        packed = eng.pack_best(st, out, index_offset=rank * B)
-        return i7d.gather_best(packed, B, world, eng.reduce_best, gathered)[0]
+    def nccl_exchange(e):
+        def f(st, out):
+            packed = e.pack_best(st, out, index_offset=rank * B)
+            return i7d.gather_best(packed, B, world, e.reduce_best, gathered)[0]
+        return f
 
-    def tick(xu, x0, goals):
-        out, st = eng.solve(xu, x0, goals)
-        best = exchange(st, out)
-        if use_p2p:            # warm-up ticks double as a check against the NCCL path
-            packed = eng.pack_best(st, out, index_offset=rank * B)
-            ref = i7d.gather_best(packed, B, world, eng.reduce_best, gathered)[0]
+    def make_exchange(e, p2p):
+        if world == 1:
+            return None
+        if p2p:
+            return lambda st, out: e.p2p_exchange(st, out, index_offset=rank * B)
+        return nccl_exchange(e)
+
+    def check(st, out, best):          # warm-up ticks double as a check of the peer-memory exchange against NCCL
+        if use_p2p:
+            ref = nccl_exchange(eng)(st, out)
             if not torch.equal(best, ref):
                 raise RuntimeError("peer-memory exchange disagrees with the NCCL all-gather path")
-        return out, st, best
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
-    xu = torch.tensor(wl["xu"], dtype=tdt, device=dev)
-    x0 = torch.tensor(wl["x0"], dtype=tdt, device=dev)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
 
     # ---- device-resident arm: W warm-up ticks, then K timed ticks ----
-    for t in range(W):
-        out, st, best = tick(xu, x0, goals_dev(t))
-        xu, x0 = shift_dev(out)
-        xu[:, :12] = x0
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -292,20 +414,7 @@ def run_b200(args):
     clocks = ClockSampler(local) if rank == 0 else None
     launches0 = eng.launch_count()
     t_wall0 = time.time()
-    last_st = None
-    for i in range(K):
-        goals = goals_dev(W + i)
-        flush.zero_()                                    # L2 flush, outside the timed events
-        ev[i][0].record()
-        kev[i][0].record()
-        out, st = eng.solve(xu, x0, goals)               # dominant kernel timed on its own as well
-        kev[i][1].record()
-        best = exchange(st, out)                         # world > 1: ONE exchange per tick (peer memory, or NCCL all-gather)
-        ev[i][1].record()
-        xu, x0 = shift_dev(out)
-        xu[:, :12] = x0
-        last_st = st
-    torch.cuda.synchronize()
+    step_ms, kern_ms, last_st = device_loop(eng, wl, N, W, K, args.dtype, dev, make_exchange(eng, use_p2p), flush, check)
     if use_p2p:
         eng.p2p_status()
     if world > 1:
@@ -313,47 +422,48 @@ def run_b200(args):
     torch.cuda.synchronize()
     t_wall1 = time.time()
     launches = eng.launch_count() - launches0
-    step_ms = np.array([a.elapsed_time(b) for a, b in ev])
-    kern_ms = np.array([a.elapsed_time(b) for a, b in kev])
     total_ms = torch.tensor([step_ms.sum()], dtype=torch.float64, device=dev)
+    per_rank = torch.tensor([kern_ms.mean(), (step_ms - kern_ms).mean()], dtype=torch.float64, device=dev)
+    per_rank_all = [torch.zeros_like(per_rank) for _ in range(world)]
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+        dist.all_gather(per_rank_all, per_rank)
+    else:
+        per_rank_all = [per_rank]
     total_ms = float(total_ms.item())
-    st_host = last_st.cpu().numpy()
+    st_host = last_st.double().cpu().numpy()
 
     # ---- end-to-end arm through the public API with HOST buffers (H2D + D2H inside the timed region) ----
     solver = Indy7SQP(N=N, batch=B, dtype=args.dtype, device=f"cuda:{local}", threads=args.threads)
     solver.set_external_wrench(wl["f_ext"])
-    hxu, hx0 = wl["xu"].copy(), wl["x0"].copy()
     npdt = np.float64 if args.dtype == "fp64" else np.float32
-    # the caller's buffers are page-locked host memory (the C ABI then transfers without a staging copy)
-    pin = lambda shape: torch.empty(shape, dtype=tdt, pin_memory=True)
+    pin = lambda shape: torch.empty(shape, dtype=tdt).pin_memory()
     p_xu, p_x0, p_goals = pin((B, nz)), pin((B, 12)), pin((B, 3 * N))
-    def e2e_loop(select_on_device):
-        """W + K closed-loop ticks from HOST buffers; returns the sum of the K timed ticks (max over ranks).
-        select_on_device: the trajectories stay on the GPU, the selection (+ exchange for N > 1) runs there and only
-        its result comes back; otherwise every trajectory and stats row comes back and the selection runs on the host."""
+    e2e_p2p = use_p2p and i7d.connect_peers(solver.engine, rank, world)
+    e2e_exchange = make_exchange(solver.engine, e2e_p2p)
+
+    def e2e_loop(full):
+        """W + K closed-loop ticks from HOST buffers, wall clock per tick (max over ranks of the sum).
+        full = False: Indy7SQP.step — inputs x0 + goal windows from page-locked host memory, results (costs, best
+        trajectory, next states) to host memory, warm start resident on the GPU.
+        full = True: Indy7SQP.solve(x0, xref, xu_init) — every warm start in, every trajectory out, selection on the host."""
+        solver.reset()
         hxu, hx0 = wl["xu"].copy(), wl["x0"].copy()
-        times = []
+        times, h2d, d2h = [], 0, 0
         for t in range(W + K):
             p_goals.copy_(torch.from_numpy(goals_at(wl["fig"], wl["offsets"], t, N).astype(npdt)))
-            p_xu.copy_(torch.from_numpy(hxu.astype(npdt)))
             p_x0.copy_(torch.from_numpy(hx0.astype(npdt)))
+            if full:
+                p_xu.copy_(torch.from_numpy(hxu.astype(npdt)))
             if world > 1:
                 dist.barrier()
             torch.cuda.synchronize()
             t0 = time.perf_counter()
-            if select_on_device:
-                out_d, st_d = solver.engine.solve(p_xu, p_x0, p_goals, device_out=True)
-                if world > 1 and use_p2p:
-                    res_d = solver.engine.p2p_exchange(st_d, out_d, index_offset=rank * B)
-                else:
-                    res_d = solver.engine.pack_best(st_d, out_d, index_offset=rank * B)
-                    if world > 1:
-                        res_d = i7d.gather_best(res_d, B, world, solver.engine.reduce_best, gathered)[0]
-                rec = res_d.cpu().numpy()                      # the step's result: [costs |] best_cost, index, XU_best
+            if not full:
+                res = solver.step(p_x0, p_goals, exchange=e2e_exchange, index_offset=rank * B)
                 dt_ = time.perf_counter() - t0
-                full = out_d.cpu().numpy().astype(float)       # untimed: the host keeps the warm start of every lane
+                hx0 = res["x_next"].astype(float)
+                h2d, d2h = res["h2d_bytes"], res["d2h_bytes"]
             else:
                 x_traj, u_traj, stats = solver.solve(p_x0, p_goals, xu_init=p_xu)
                 cost = np.asarray(stats["cost"], float)        # best-trajectory selection on the host result
@@ -365,20 +475,20 @@ def run_b200(args):
                     gh = g.cpu().numpy().reshape(world, -1)
                     rec = gh[int(np.argmin(gh[:, 0]))]
                 dt_ = time.perf_counter() - t0
-                full = stats["xu"].numpy().astype(float)
+                hxu, hx0 = shift_host(stats["xu"].numpy().astype(float), N)
+                hxu[:, :12] = hx0
+                h2d, d2h = int(B * (nz + 12 + 3 * N) * esize), int(B * (nz + 12) * esize)
             if t >= W:
                 times.append(dt_)
-            hxu, hx0 = shift_host(full, N)
-            hxu[:, :12] = hx0
         total = torch.tensor([float(np.sum(times))], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(total, op=dist.ReduceOp.MAX)
-        return float(total.item()), int(rec.size)
+        return float(total.item()), h2d, d2h
 
-    if world > 1 and use_p2p:
-        use_p2p = i7d.connect_peers(solver.engine, rank, world)
-    e2e_total, res_numbers = e2e_loop(True)
-    e2e_full_total, _ = e2e_loop(False)
+    e2e_total, e2e_h2d, e2e_d2h = e2e_loop(False)
+    e2e_full_total, full_h2d, full_d2h = e2e_loop(True)
+    if e2e_p2p:
+        solver.engine.p2p_status()
     clk = clocks.stop(t_wall0, time.time()) if clocks else None
 
     if rank != 0:
@@ -389,7 +499,7 @@ def run_b200(args):
     # ---- single-problem latency (BASELINE.json configs[1]): fig-8 tracking, B = 1, warm-started closed loop ----
     lat = single_problem_latency(args, local)
 
-    # ---- roofline of the dominant kernel (sqp_kernel) ----
+    # ---- roofline of the dominant kernel: the FMA pipe of the arithmetic type ----
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -399,60 +509,67 @@ def run_b200(args):
     peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
     kern_avg_s = float(kern_ms.mean()) * 1e-3
     bytes_launch = algorithmic_bytes(N, esize) * B
-    flops_solve = algorithmic_flops(st_host, N)
-    fma_peak = eng.measure_fma_peak()
-    traffic = None
+    fma_peaks = {args.dtype: eng.measure_fma_peak()}
+    traffic, traffic_src = None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = tj.get(f"sqp_kernel_B{B}_N{N}_{args.dtype}")
-        if traffic is None and f"sqp_kernel_B4096_N{N}_{args.dtype}" in tj:      # per-launch, scaled by problems
-            traffic = tj[f"sqp_kernel_B4096_N{N}_{args.dtype}"] * B // 4096
+        key = f"sqp_kernel_B{B}_N{N}_{args.dtype}"
+        if key in tj:
+            traffic, traffic_src = tj[key], tj.get("source", "profiles/traffic.json")
+        elif f"sqp_kernel_B4096_N{N}_{args.dtype}" in tj:      # per-launch, scaled by problems
+            traffic, traffic_src = tj[f"sqp_kernel_B4096_N{N}_{args.dtype}"] * B // 4096, tj.get("source", "profiles/traffic.json") + " (scaled by problems)"
     except Exception:
         pass
+    thr, ctas, smem = eng.kernel_form()
+    fp = fp_roofline(eng, st_host, N, B, float(kern_ms.mean()), args.dtype, fma_peaks[args.dtype])
     roofline = {
-        "bound": "hbm", "achieved": bytes_launch / kern_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-        "frac": bytes_launch / kern_avg_s / 1e9 / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-        "kernel": f"sqp_kernel<{args.dtype},{eng_threads(eng, B, args)}>", "kernel_ms": float(kern_ms.mean()),
-        "algorithmic_bytes_per_solve": algorithmic_bytes(N, esize),
-        "note": "the path is FP-pipe / dependency-latency bound, not HBM bound (SURVEY.md §8d); see 'fp_pipe'",
-        "fp_pipe": {"achieved_tflops": flops_solve * B / kern_avg_s / 1e12, "peak_tflops": fma_peak,
-                    "frac": flops_solve * B / kern_avg_s / 1e12 / fma_peak if fma_peak else None,
-                    "algorithmic_flops_per_solve": flops_solve,
-                    "peak_source": "i7_measure_fma_peak (FMA microbenchmark on this GPU, this run)"},
+        "bound": "fp64_fma" if args.dtype == "fp64" else "fp32_fma", "achieved": fp["achieved"], "peak": fp["peak"],
+        "unit": "TFLOP/s", "frac": fp["frac"], "traffic": traffic, "traffic_source": traffic_src,
+        "peak_source": "i7_measure_fma_peak: dependent-chain-free FMA loop on every SM of this GPU, this run "
+                       "(MEASURED_PEAKS.json holds no FP64 / FP32 CUDA-core figure)",
+        "kernel": f"sqp_kernel<{args.dtype}>: {thr} threads x {ctas} CTA(s) per problem, {smem} B shared memory",
+        "kernel_ms": float(kern_ms.mean()), "algorithmic_flops_per_solve": fp["algorithmic_flops_per_solve"],
+        "why": "arithmetic intensity ~215 flop/B (SURVEY.md section 8d): the FMA pipe of the CUDA cores bounds the kernel, "
+               "neither HBM nor the tensor cores (6x6 / 12x12 fp64 blocks with data-dependent structure)",
+        "hbm": {"achieved": bytes_launch / kern_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                "frac": bytes_launch / kern_avg_s / 1e9 / hbm_peak, "peak_source": peak_src,
+                "algorithmic_bytes_per_solve": algorithmic_bytes(N, esize)},
     }
 
     cpu = None
     if not args.no_cpu_baseline:
-        cpu = cpu_baseline(N, wl_all, goals_at(wl_all["fig"], wl_all["offsets"], 0, N), args.cpu_seconds, args.cpu_sample)
+        cpu = cpu_baseline(wl_all, N, args.cpu_seconds)
+    configs = extra_configs(args, local, fma_peaks) if (world == 1 and args.config_ticks > 0) else None
 
     value = args.batch * K / (total_ms * 1e-3)
+    run_cfg = {"batch_per_gpu": B, "parallelism": f"batch-shard x{world}",
+               "exchange": ("none (one GPU)" if world == 1 else
+                            ("one peer-memory exchange kernel per tick (NVLink stores, fused pack + gather + selection)"
+                             if use_p2p else "pack kernel + one NCCL all-gather + reduce kernel per tick"))}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64" if args.dtype == "fp64" else "f32", "data": "synthetic",
-        "config": {"workload": f"batch {args.batch} sampled Indy7 SQP-MPC problems (BASELINE.json configs[3]), N={N}, "
-                               f"dt=0.01, warm-started MPC ticks, per-lane wrench hypotheses, best-trajectory selection"
-                               + ((" + one peer-memory exchange kernel (NVLink stores, fused pack + gather + selection)"
-                                   if use_p2p else " + one NCCL all-gather") if world > 1 else ""),
-                   "horizon": N, "batch_total": args.batch, "batch_per_gpu": B, "parallelism": f"batch-shard x{world}",
-                   "l2": "flushed between timed steps (256 MB memset outside the events)",
-                   "threads_per_cta": eng_threads(eng, B, args)},
+        "config": workload_config(args), "run_config": run_cfg,
         "e2e": {"value": args.batch * K / e2e_total, "unit": UNIT,
-                "h2d_bytes_per_step": int(B * (nz + 12 + 3 * N) * esize), "d2h_bytes_per_step": int(res_numbers * esize),
+                "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
                 "ms_per_step": 1e3 * e2e_total / K,
-                "api": "Engine.solve(XU, x0, xref: page-locked host tensors, device_out=True) -> selection on the GPU "
-                       "(pack_best; N > 1: the exchange kernel) -> .cpu() of the result [costs | best_cost, best_index, XU_best]; "
-                       "the kernel reads the host buffers itself (zero-copy), the result read is inside the timed call",
+                "api": "Indy7SQP.step(x0, xref) per tick, wall clock: x0 and the goal windows of all lanes are read from "
+                       "page-locked host memory by the kernels (zero-copy), shift + solve + selection (N > 1: exchange) on "
+                       "the GPU, [costs | best_cost, best_index, XU_best] and the next state of every lane written back to "
+                       "host memory inside the timed call; the warm start of every lane stays on the GPU on both sides",
                 "all_trajectories_to_host": {
                     "value": args.batch * K / e2e_full_total, "ms_per_step": 1e3 * e2e_full_total / K,
-                    "d2h_bytes_per_step": int(B * (nz + 12) * esize),
-                    "api": "Indy7SQP.solve(x0, xref, xu_init) with page-locked host tensors: every trajectory and stats "
-                           "row written back to host memory, selection on the host (N > 1: + NCCL all-gather of the records)"}},
+                    "h2d_bytes_per_step": full_h2d, "d2h_bytes_per_step": full_d2h,
+                    "api": "Indy7SQP.solve(x0, xref, xu_init) with page-locked host tensors: every warm start read from and every "
+                           "trajectory + stats row written to host memory, selection on the host (N > 1: + NCCL all-gather of the records)"}},
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": roofline,
         "cpu_baseline": cpu,
         "latency": lat,
+        "configs": configs,
+        "per_rank": {"kernel_ms": [float(p[0]) for p in per_rank_all], "selection_exchange_ms": [float(p[1]) for p in per_rank_all]},
         "wall_s_timed_loop": t_wall1 - t_wall0,
         "stats_last_tick": {"mean_qp_iters": float(st_host[:, 0].mean()), "linesearch_fail_frac": float((st_host[:, 3] == 1).mean()),
                             "nonfinite": int((st_host[:, 3] == 2).sum())},
@@ -460,10 +577,6 @@ def run_b200(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
-
-
-def eng_threads(eng, B, args):
-    return eng.kernel_form()[0]
 
 
 def single_problem_latency(args, local):
@@ -504,14 +617,13 @@ def single_problem_latency(args, local):
     xud = torch.zeros(1, 18 * N - 6, dtype=tdt, device=dev); xud[0, :12] = xd[0]
     figd = torch.tensor(fig, dtype=tdt, device=dev)
     res_us = []
-    for t in range(n_ticks + 20):
-        goals = figd[(t + torch.arange(N, device=dev)) % figd.shape[0]].reshape(1, -1).contiguous()
+    for t in range(n_ticks + 20):        # every step of the tick is a library kernel: window, solve, plant, shift
+        goals = eng.goal_window(figd, None, tick=t, wrap=True, batch=1)
         out, st = eng.solve(xud, xd, goals)
         if t >= 20:
             res_us.append(eng.last_solve_time_us())
         xd = eng.sim_forward(xd, out[:, 12:18].contiguous(), 0.01)
-        xud = torch.cat([out[:, 18:], out[:, -18:]], dim=1).contiguous()
-        xud[0, :12] = xd[0]
+        xud, _ = eng.shift(out, steps=1, tail="repeat", x_cur=xd, want_x0=False)
     res = {"config": f"fig-8 tracking, N={N}, 1 problem, closed loop with rk4 plant, {n_ticks} warm ticks",
            "device_us": {"p50": p(res_us, 50), "p99": p(res_us, 99), "mean": float(np.mean(res_us)),
                          "what": "solve kernel, buffers resident in HBM (CUDA events)"},
@@ -560,7 +672,8 @@ def main():
     ap.add_argument("--dtype", default="fp64", choices=["fp64", "fp32"])
     ap.add_argument("--threads", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
-    ap.add_argument("--cpu-sample", type=int, default=4096)
+    ap.add_argument("--config-ticks", type=int, default=20, help="timed ticks per extra config (0: skip configs[2], configs[4])")
+    ap.add_argument("--config-cpu-seconds", type=float, default=3.0)
     ap.add_argument("--latency-ticks", type=int, default=500)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -24,8 +24,10 @@
  *     re-entrant.  Distinct handles may be used from distinct threads / streams.
  *   - every data pointer may be HOST or DEVICE memory (queried with cudaPointerGetAttributes).  Element
  *     type = the handle's dtype (double for I7_F64, float for I7_F32), C-contiguous, row = one problem.
- *     With device pointers a call is asynchronous on `stream`; with host pointers the library stages through
- *     its own pinned buffers and returns after the results are in the caller's memory.
+ *     With device pointers a call is asynchronous on `stream`.  With host pointers the call returns after the
+ *     results are in the caller's memory: page-locked buffers (cudaHostAlloc / cudaHostRegister) are read and
+ *     written by the kernels themselves (zero-copy), pageable ones pass through the handle's page-locked mirror
+ *     (details at i7_solve).
  *   - trajectory layout (src/osqp_solver.py:22,88-91): XU = [x_0 u_0 x_1 u_1 ... x_{N-1}], x = [q(6) v(6)],
  *     length 18N-6.  Goals: N knots of `goal_stride` numbers (3 = [x y z]; 6 = GATO format [x y z 0 0 0],
  *     src/gato_mpc_batch.py:80-88), only the first three of each knot are read.
@@ -147,6 +149,24 @@ i7_status i7_kernel_form(const i7_handle* h, int32_t* threads, int32_t* ctas_per
 i7_status i7_sim_forward(i7_handle* h, int32_t batch, const void* x, const void* u, double dt, int32_t bcast,
                          void* x_next, void* stream);
 
+/* MPC tick plumbing on the device (reference: src/osqp_mpc.py:65-70; device precedent just_shift<T>,
+ * indy7-sdk/src/trajopt/include/trajopt_solver.cuh:153-172): the warm start of the next tick = the new solution moved
+ * `steps` knots towards the present.  xu_out[b] = xu_new[b][18 steps:], the last `steps` knots filled per `tail`:
+ *   0  the reference loop: they keep the values of the previous warm start xu_prev, and the last state becomes
+ *      [1 x 6, 0 x 6] (src/osqp_mpc.py:66,70);  1  trajopt_solver.cuh: x_{N-1} repeated, controls zeroed;
+ *   2  the last [u, x] pair repeated (batch drivers, bench.py).
+ * x_cur (batch x 12, may be NULL) overwrites x_0 (src/osqp_mpc.py:69); NULL: x_0 = x_steps of the solution.
+ * x0_out (batch x 12, may be NULL) receives the new x_0.  xu_prev may be NULL unless tail == 0.  Not in place. */
+i7_status i7_shift(i7_handle* h, int32_t batch, int32_t steps, int32_t tail, const void* xu_new, const void* xu_prev,
+                   const void* x_cur, void* xu_out, void* x0_out, void* stream);
+/* Goal window of every lane from ONE reference trajectory (gato_controller.py:210-218 slices
+ * ref_traj[offset : offset + 6N] of the padded figure-8; trajopt_solver.cuh:97-146 keeps the same window on the
+ * device): goals[b][k] = traj[offsets[b] + tick + k] (first three numbers of each sample of `traj_stride`), the index
+ * wrapped (wrap != 0) or clamped to the last sample.  offsets: batch int32 (host or device; NULL = 0).  out_stride 3, or
+ * 6 for the GATO format [x y z 0 0 0]. */
+i7_status i7_goal_window(i7_handle* h, int32_t batch, const void* traj, int32_t traj_len, int32_t traj_stride,
+                         const int32_t* offsets, int32_t tick, int32_t wrap, int32_t out_stride, void* goals, void* stream);
+
 /* Wrench-hypothesis selection of the batch drivers in ONE launch (gato_controller.py:109-118 find_best_idx;
  * src/gato_mpc_batch_sample.py:254-300 find_best_trajectory_id after the wrench conversion): one rk4 plant step of
  * length dt from the single row (x_last, u_last) per lane under that lane's external wrench, error_i =
@@ -179,7 +199,10 @@ i7_status i7_reduce_best(i7_handle* h, int32_t nranks, int32_t stride, const voi
  *                   XU_best] to `out` (device pointer).  `batch` must be the same on every rank.  Every rank must call
  *                   it once per tick; a rank missing for longer than the timeout raises I7_ERR_CUDA at i7_p2p_status.
  *   i7_p2p_gathered device pointer to the world x (batch + 2 + nz) records of the latest exchange
- *   i7_p2p_status   0, or an error once an exchange has timed out (synchronises the stream given). */
+ *   i7_p2p_status   0, or an error once an exchange has timed out (synchronises the stream given).  A timed-out
+ *                   exchange writes [NaN, -1, 0...] to `out`, never a stale winner.
+ *   i7_p2p_reset    clears the time-out state, the arrival flags and the tick counter of this rank.  COLLECTIVE: every
+ *                   rank calls it, with a host-side barrier before and after (no exchange may be in flight). */
 #define I7_IPC_HANDLE_BYTES 64
 i7_status i7_p2p_create(i7_handle* h, int32_t world, int32_t rank, unsigned char* handle_out);
 i7_status i7_p2p_connect(i7_handle* h, const unsigned char* handles);
@@ -187,6 +210,7 @@ i7_status i7_p2p_exchange(i7_handle* h, int32_t batch, const void* stats, const 
                           void* stream);
 i7_status i7_p2p_gathered(i7_handle* h, const void** gathered);
 i7_status i7_p2p_status(i7_handle* h, void* stream);
+i7_status i7_p2p_reset(i7_handle* h);
 
 /* Measurement utility for roofline denominators: sustained FMA throughput of the CUDA-core pipe of the
  * handle's dtype (dependent-chain-free FMA loop on every SM), in TFLOP/s. */
@@ -200,9 +224,12 @@ i7_status i7_measure_fma_peak(i7_handle* h, double* tflops);
 i7_status i7_profile_phases(i7_handle* h, int32_t enable, int64_t* clocks32, int32_t batch);
 
 /* ---- stage-level entry points (parity tests and debugging; same device code as i7_solve) ---- */
-/* The full-step QP solution `setup_and_solve_qp(xu, x0, goals).x` (src/osqp_solver.py:137-143). */
+/* The full-step QP solution of `setup_and_solve_qp(xu, x0, goals)` (src/osqp_solver.py:137-143): z_out = `.x`
+ * (batch x (18N-6)); y_out (batch x 12N, may be NULL) = `.y`, the duals of the equality rows in the row order of the
+ * reference's A (block 0: -x_0 = -xs; block k+1: A_k x_k + B_k u_k - x_{k+1} = -c_k), sign convention of OSQP
+ * (P z + g + A'y = 0). */
 i7_status i7_solve_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,
-                      int32_t goal_stride, void* z_out, void* stream);
+                      int32_t goal_stride, void* z_out, void* y_out, void* stream);
 /* The QP data in the reference's CSC value order, per problem:
  * Adata: 360(N-1)+144, Pdata: 33N-6... (N*27 + (N-1)*6), g: 18N-6, l: 12N.  Any pointer may be NULL. */
 i7_status i7_dump_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,

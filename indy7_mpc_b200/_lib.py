@@ -49,11 +49,14 @@ SYMBOLS = {
     "i7_p2p_exchange": (_i32, [_vp, _i32, _vp, _vp, _i32, _vp, _vp]),
     "i7_p2p_gathered": (_i32, [_vp, C.POINTER(_vp)]),
     "i7_p2p_status": (_i32, [_vp, _vp]),
+    "i7_p2p_reset": (_i32, [_vp]),
     "i7_measure_fma_peak": (_i32, [_vp, C.POINTER(_dbl)]),
     "i7_profile_phases": (_i32, [_vp, _i32, C.POINTER(C.c_int64), _i32]),
     "i7_sim_forward": (_i32, [_vp, _i32, _vp, _vp, _dbl, _i32, _vp, _vp]),
+    "i7_shift": (_i32, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "i7_goal_window": (_i32, [_vp, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp]),
     "i7_find_best_idx": (_i32, [_vp, _i32, _vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp]),
-    "i7_solve_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp]),
+    "i7_solve_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "i7_dump_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "i7_merit": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp]),
     "i7_linesearch": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
@@ -73,6 +76,14 @@ def load():
         raise RuntimeError(
             f"{LIB_PATH} not found: build it with `python -m indy7_mpc_b200.build` (nvcc, sm_100a). "
             "indy7_mpc_b200 has no CPU fallback.")
+    try:        # a library older than the sources next to it is a silent source of wrong conclusions: say so
+        from . import build as _build
+        if _build.needs_build():
+            import warnings
+            warnings.warn(f"{LIB_PATH} is older than the sources under csrc/ (build stamp mismatch): "
+                          "rebuild with `python -m indy7_mpc_b200.build`", RuntimeWarning, stacklevel=2)
+    except OSError:
+        pass
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SYMBOLS.items():
         fn = getattr(lib, name)          # AttributeError if a declared symbol is not exported

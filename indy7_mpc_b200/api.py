@@ -33,10 +33,57 @@ class Indy7SQP:
                              regularize=regularize, eps=eps, batch=batch, dtype=dtype, device=device, threads=threads,
                              cluster=cluster)
         self._warm = None
+        self._tick_prev = None          # step(): previous solution of every lane, device-resident
+        self._tick_bufs = None
 
     def reset(self):
         self._warm = None
+        self._tick_prev = None
         self.engine.reset()
+
+    def step(self, x0, xref, exchange=None, index_offset=0):
+        """One closed-loop MPC tick of a batch of sampled problems (BASELINE.json configs[3]; the tick of
+        gato_controller.py:201-256 with the batch as wrench / start-state hypotheses):
+
+            warm start = previous solution of every lane moved one knot on, x_0 <- x0      (i7_shift; kept on the GPU)
+            sqp() of every lane                                                           (i7_solve, one launch)
+            per-lane costs + best trajectory                                              (i7_pack_best | `exchange`)
+
+        x0 (B,12) and xref (B,3N | B,6N) are the tick's inputs — host (page-locked tensors are read by the kernels
+        themselves) or device; the warm start never leaves the device.  Returns a dict of HOST arrays: 'costs' (B,),
+        'best_cost', 'best_index', 'x_traj' (N,12) / 'u_traj' (N-1,6) of the best lane, and 'x_next' (B,12) = the
+        state every lane predicts for the next tick.  `exchange(stats, xu) -> device record` replaces the local
+        selection (multi-GPU: Engine.p2p_exchange or pack_best + all-gather + reduce_best)."""
+        eng = self.engine
+        B = self.batch
+        tdt = eng._torch_dtype()
+        dev = torch.device("cuda", eng.device)
+        if not _is_torch(x0):
+            x0 = torch.as_tensor(np.ascontiguousarray(np.asarray(x0, dtype=eng.np_dtype).reshape(B, 12)))
+        if not _is_torch(xref):
+            xref = torch.as_tensor(np.ascontiguousarray(np.asarray(xref, dtype=eng.np_dtype).reshape(B, -1)))
+        if self._tick_bufs is None:
+            self._tick_bufs = (torch.empty(B + 2 + self.nz, dtype=tdt).pin_memory(), torch.empty(B, 12, dtype=tdt).pin_memory())
+        rec_h, x1_h = self._tick_bufs
+        if self._tick_prev is None:
+            xu = torch.zeros(B, self.nz, dtype=tdt, device=dev)
+            xu[:, :12] = x0.to(dev, non_blocking=True)
+        else:
+            xu, _ = eng.shift(self._tick_prev, steps=1, tail="repeat", x_cur=x0, want_x0=False)
+        out, st = eng.solve(xu, x0, xref, device_out=True)
+        rec = exchange(st, out) if exchange is not None else eng.pack_best(st, out, index_offset=index_offset)
+        n = rec.numel()
+        rec_h[:n].copy_(rec, non_blocking=True)
+        x1_h.copy_(out[:, 18:30], non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        self._tick_prev = out
+        r = rec_h[:n].numpy()
+        best = r[n - self.nz:]
+        full = np.concatenate([best, np.zeros(6, best.dtype)]).reshape(self.N, 18)
+        return {'costs': r[:n - 2 - self.nz], 'best_cost': float(r[n - 2 - self.nz]), 'best_index': int(r[n - 1 - self.nz]),
+                'x_traj': full[:, :12], 'u_traj': full[:-1, 12:], 'x_next': x1_h.numpy(),
+                'h2d_bytes': int((x0.numel() + xref.numel()) * x0.element_size()) if not x0.is_cuda else 0,
+                'd2h_bytes': int((n + x1_h.numel()) * rec_h.element_size())}
 
     def set_external_wrench(self, f_ext):
         self.engine.set_external_wrench(f_ext)

@@ -12,7 +12,6 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libindy7_b200.so")
-HEADERS = ["i7_rbd.cuh", "i7_sqp.cuh", "i7_cluster.cuh", "i7_aux.cuh", "i7_launch.h", os.path.join("..", "..", "include", "indy7_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 
 # (object name, source, extra defines)
@@ -37,8 +36,10 @@ def nvcc_path():
 
 
 def _sources():
-    srcs = sorted({u[1] for u in UNITS})
-    return [os.path.join(CSRC, s) for s in srcs + HEADERS] + [os.path.abspath(__file__)]
+    """Everything the library is built from: every file under csrc/, the public header, this script."""
+    srcs = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h")))
+    return [os.path.join(CSRC, s) for s in srcs] + [os.path.join(HERE, "..", "include", "indy7_b200.h"),
+                                                     os.path.abspath(__file__)]
 
 
 def _stamp():

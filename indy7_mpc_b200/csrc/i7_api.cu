@@ -41,6 +41,10 @@ struct i7_handle {
     int cluster_smem_bytes = 0;
     void* d_xbuf = nullptr;      // exchange buffer of the cluster kernel (batch x cluster_xbuf_len(N))
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // the pinned input mirror (in.host) is read asynchronously by a copy / by the kernel itself when a call with host
+    // inputs and device outputs returns without waiting: the next call that stages through it waits for this event
+    cudaEvent_t mirror_ev = nullptr;
+    bool mirror_pending = false;
     // host-buffer calls on big batches run as a software pipeline of chunks over these streams (copy-in of chunk
     // i+1 and copy-out of chunk i-1 overlap the kernel of chunk i); pipe_chunk = problems per chunk, 0 = off
     static constexpr int kPipeStreams = 6, kPipeMaxChunks = 64;    // streams in use: pipe_nstreams (I7_PIPE_STREAMS)
@@ -114,6 +118,7 @@ bool is_device_ptr(const void* p) { return ptr_kind(p) == 1; }
 
 i7_status arena_reserve(i7_handle* h, Arena& a, size_t bytes) {
     if (bytes <= a.bytes) return I7_OK;
+    if (h->mirror_pending) { cudaEventSynchronize(h->mirror_ev); h->mirror_pending = false; }
     if (a.dev) cudaFree(a.dev);
     if (a.host) cudaFreeHost(a.host);
     a.dev = a.host = nullptr; a.bytes = 0;
@@ -145,15 +150,20 @@ struct Stage {
         return d;
     }
     struct Xfer { void* user; size_t off; size_t bytes; bool pinned; };
-    Xfer ins[8], outs[10];
+    Xfer ins[8], outs[12];
     int nin = 0, nout = 0;
+    bool used_mirror = false;
     const void* in(const void* p, size_t bytes) {
         if (!p) return nullptr;
         const int kind = ptr_kind(p);
         if (kind == 1) return p;
         if (kind == 2 && zero_copy)
             if (const void* d = mapped(p)) return d;
-        if (kind == 0 || direct) std::memcpy((char*)h->in.host + in_off, p, bytes);
+        if (kind == 0 || direct) {
+            if (h->mirror_pending) { cudaEventSynchronize(h->mirror_ev); h->mirror_pending = false; }
+            std::memcpy((char*)h->in.host + in_off, p, bytes);
+            used_mirror = true;
+        }
         if (!direct) ins[nin++] = Xfer{const_cast<void*>(p), in_off, bytes, kind == 2};
         const void* d = (char*)(direct ? h->in.host : h->in.dev) + in_off;
         in_off += (bytes + 15) & ~size_t(15);
@@ -190,6 +200,10 @@ struct Stage {
     }
     i7_status flush_out(cudaStream_t s) {
         if (!nout && zc_pending) I7_CUDA(h, cudaStreamSynchronize(s));      // results land in the caller's memory
+        else if (!nout && used_mirror) {                                      // asynchronous return: the mirror stays in use
+            I7_CUDA(h, cudaEventRecord(h->mirror_ev, s));
+            h->mirror_pending = true;
+        }
         if (!nout) return I7_OK;
         for (int i = 0; i < nout && !direct;) {
             if (outs[i].pinned) {
@@ -264,7 +278,7 @@ i7_status check_batch(i7_handle* h, int batch, int goal_stride) {
 struct SqpCall {
     int mode, batch, goal_stride;
     const void *xu, *x0, *goals, *xu_full;
-    void *xu_out, *stats, *z_out, *Adata, *Pdata, *g, *l, *alpha, *merits;
+    void *xu_out, *stats, *z_out, *y_out, *Adata, *Pdata, *g, *l, *alpha, *merits;
 };
 
 template <typename T>
@@ -283,6 +297,7 @@ i7_status run_sqp_t(i7_handle* h, const SqpCall& c, cudaStream_t s, bool zero_co
     P.xu_out = (T*)st.out(c.xu_out, B * nz * es);
     P.stats = (T*)st.out(c.stats, B * I7_STATS_LEN * es);
     P.z_out = (T*)st.out(c.z_out, B * nz * es);
+    P.y_out = (T*)st.out(c.y_out, B * 12 * N * es);
     P.Adata = (T*)st.out(c.Adata, B * (360 * (N - 1) + 144) * es);
     P.Pdata = (T*)st.out(c.Pdata, B * (27 * N + 6 * (N - 1)) * es);
     P.g = (T*)st.out(c.g, B * nz * es);
@@ -328,6 +343,7 @@ i7_status run_solve_pipelined(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     for (int a = 0; a < 2; ++a) pin_out[a] = uout[a] && ptr_kind(uout[a]) == 2;
     const size_t chunk = (size_t)pipe_chunk_for(h, c.batch);
     const bool m2 = h->pipe_mode == 2;
+    if (h->mirror_pending) { I7_CUDA(h, cudaEventSynchronize(h->mirror_ev)); h->mirror_pending = false; }
     const int nchunks = (int)((B + chunk - 1) / chunk);
     I7_CUDA(h, cudaEventRecord(h->ev0, s));
     I7_CUDA(h, cudaEventRecord(h->pipe_fork, s));
@@ -405,7 +421,7 @@ bool pipeline_eligible(const i7_handle* h, const SqpCall& c) {
     if (c.mode != i7::MODE_SOLVE || h->pipe_chunk <= 0 || h->use_cluster) return false;
     const int chunk = pipe_chunk_for(h, c.batch);
     if (c.batch < 2 * chunk || (c.batch + chunk - 1) / chunk > i7_handle::kPipeMaxChunks) return false;
-    if (c.xu_full || c.z_out || c.Adata || c.Pdata || c.g || c.l || c.alpha || c.merits) return false;
+    if (c.xu_full || c.z_out || c.y_out || c.Adata || c.Pdata || c.g || c.l || c.alpha || c.merits) return false;
     const void* ptrs[5] = {c.xu, c.x0, c.goals, c.xu_out, c.stats};
     for (int a = 0; a < 5; ++a)
         if (ptrs[a] && ptr_kind(ptrs[a]) == 1) return false;      // device-resident buffers: one launch, no copies
@@ -480,6 +496,7 @@ void i7_destroy(i7_handle* h) {
     }
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->mirror_ev) cudaEventDestroy(h->mirror_ev);
     delete h;
 }
 
@@ -586,6 +603,7 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
     I7_CUDA_C(cudaMemset(h->d_fext, 0, B * 6 * es));
     I7_CUDA_C(cudaEventCreate(&h->ev0));
     I7_CUDA_C(cudaEventCreate(&h->ev1));
+    I7_CUDA_C(cudaEventCreateWithFlags(&h->mirror_ev, cudaEventDisableTiming));
     {
         const char* env = std::getenv("I7_DIRECT_MAX_BATCH");
         int can_map = 0;
@@ -807,6 +825,18 @@ i7_status i7_p2p_status(i7_handle* h, void* stream) {
     return I7_OK;
 }
 
+i7_status i7_p2p_reset(i7_handle* h) {
+    if (!h || !h->p2p_mine) { if (h) h->err = "no exchange buffer"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    I7_CUDA(h, cudaDeviceSynchronize());
+    const i7::P2PLayout L = i7::p2p_layout(h->p2p_world, h->cfg.batch + 2 + (int)h->nz, h->esize);
+    I7_CUDA(h, cudaMemset((char*)h->p2p_mine + L.flags_off, 0, L.total - L.flags_off));
+    I7_CUDA(h, cudaMemset(h->p2p_err, 0, sizeof(int)));
+    I7_CUDA(h, cudaDeviceSynchronize());
+    h->p2p_seq = 0;
+    return I7_OK;
+}
+
 i7_status i7_measure_fma_peak(i7_handle* h, double* tflops) {
     if (!h || !tflops) return I7_ERR_INVALID;
     I7_CUDA(h, cudaSetDevice(h->cfg.device));
@@ -838,11 +868,11 @@ i7_status i7_measure_fma_peak(i7_handle* h, double* tflops) {
 }
 
 i7_status i7_solve_qp(i7_handle* h, int32_t batch, const void* xu, const void* x0, const void* goals,
-                      int32_t goal_stride, void* z_out, void* stream) {
+                      int32_t goal_stride, void* z_out, void* y_out, void* stream) {
     if (!h || !xu || !x0 || !goals || !z_out) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
     SqpCall c{};
     c.mode = i7::MODE_QP; c.batch = batch; c.goal_stride = goal_stride;
-    c.xu = xu; c.x0 = x0; c.goals = goals; c.z_out = z_out;
+    c.xu = xu; c.x0 = x0; c.goals = goals; c.z_out = z_out; c.y_out = y_out;
     return run_sqp(h, c, stream);
 }
 
@@ -969,9 +999,73 @@ i7_status find_best_idx_t(i7_handle* h, int batch, const void* x_last, const voi
     I7_CUDA(h, cudaGetLastError());
     return st.flush_out(s);
 }
+template <typename T>
+i7_status shift_t(i7_handle* h, int batch, int steps, int tail, const void* xu_new, const void* xu_prev, const void* x_cur,
+                  void* xu_out, void* x0_out, cudaStream_t s) {
+    const size_t es = sizeof(T), nz = h->nz;
+    Stage st(h);
+    st.zero_copy = h->zero_copy != 0;       // page-locked buffers (the measured states of a tick) are read in place
+    const T* d_new = (const T*)st.in(xu_new, (size_t)batch * nz * es);
+    const T* d_prev = (const T*)st.in(xu_prev, (size_t)batch * nz * es);
+    const T* d_cur = (const T*)st.in(x_cur, (size_t)batch * 12 * es);
+    T* d_out = (T*)st.out(xu_out, (size_t)batch * nz * es);
+    T* d_x0 = (T*)st.out(x0_out, (size_t)batch * 12 * es);
+    i7_status rc;
+    if ((rc = st.flush_in(s))) return rc;
+    const size_t total = (size_t)batch * nz;
+    const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
+    i7::shift_kernel<T><<<blocks, 256, 0, s>>>(batch, h->cfg.N, steps, tail, d_new, d_prev, d_cur, d_out, d_x0);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
+
+template <typename T>
+i7_status goal_window_t(i7_handle* h, int batch, const void* traj, int traj_len, int traj_stride, const int32_t* offsets,
+                        int tick, int wrap, int out_stride, void* goals, cudaStream_t s) {
+    const size_t es = sizeof(T);
+    i7_status rc;
+    const size_t need = (size_t)traj_len * traj_stride * es + (size_t)batch * sizeof(int32_t) + 256;
+    if (ptr_kind(traj) != 1 && (rc = arena_reserve(h, h->in, need))) return rc;
+    Stage st(h);
+    const T* d_traj = (const T*)st.in(traj, (size_t)traj_len * traj_stride * es);
+    const int* d_off = (const int*)st.in(offsets, (size_t)batch * sizeof(int32_t));
+    T* d_goals = (T*)st.out(goals, (size_t)batch * h->cfg.N * out_stride * es);
+    if ((rc = st.flush_in(s))) return rc;
+    const size_t total = (size_t)batch * h->cfg.N * out_stride;
+    const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
+    i7::goal_window_kernel<T><<<blocks, 256, 0, s>>>(batch, h->cfg.N, d_traj, traj_len, traj_stride, d_off, tick, wrap, out_stride, d_goals);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
 }  // namespace
 
 extern "C" {
+
+i7_status i7_shift(i7_handle* h, int32_t batch, int32_t steps, int32_t tail, const void* xu_new, const void* xu_prev,
+                   const void* x_cur, void* xu_out, void* x0_out, void* stream) {
+    if (!h || !xu_new || !xu_out) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    if (steps < 0 || steps >= h->cfg.N || tail < 0 || tail > 2) { h->err = "steps must be in [0, N), tail in {0, 1, 2}"; return I7_ERR_INVALID; }
+    if (tail == 0 && !xu_prev) { h->err = "tail 0 (src/osqp_mpc.py:65-70) keeps the end of the previous warm start: xu_prev required"; return I7_ERR_INVALID; }
+    if (xu_out == xu_new && steps > 0) { h->err = "i7_shift cannot run in place"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64 ? shift_t<double>(h, batch, steps, tail, xu_new, xu_prev, x_cur, xu_out, x0_out, s)
+                                  : shift_t<float>(h, batch, steps, tail, xu_new, xu_prev, x_cur, xu_out, x0_out, s);
+}
+
+i7_status i7_goal_window(i7_handle* h, int32_t batch, const void* traj, int32_t traj_len, int32_t traj_stride,
+                         const int32_t* offsets, int32_t tick, int32_t wrap, int32_t out_stride, void* goals, void* stream) {
+    if (!h || !traj || !goals) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    if (traj_len < 1 || traj_stride < 3 || (out_stride != 3 && out_stride != 6)) { h->err = "traj_len >= 1, traj_stride >= 3, out_stride 3 or 6"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64 ? goal_window_t<double>(h, batch, traj, traj_len, traj_stride, offsets, tick, wrap, out_stride, goals, s)
+                                  : goal_window_t<float>(h, batch, traj, traj_len, traj_stride, offsets, tick, wrap, out_stride, goals, s);
+}
 
 i7_status i7_find_best_idx(i7_handle* h, int32_t batch, const void* x_last, const void* u_last, const void* xs, double dt,
                            int32_t tie_last, void* x_next, void* errors, void* result, void* stream) {

@@ -323,8 +323,9 @@ __global__ void __launch_bounds__(256) pack_exchange_reduce_kernel(int batch, in
                                                                    unsigned long long timeout_ns, T* out, int* err) {
     __shared__ T s_val[32];
     __shared__ int s_idx[32];
-    __shared__ int s_win;
+    __shared__ int s_win, s_timed_out;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_timed_out = 0;
     const int stride = batch + 2 + nz;
     const P2PLayout L = p2p_layout(world, stride, (int)sizeof(T));
     const int par = (int)(seq & 1);
@@ -377,12 +378,18 @@ __global__ void __launch_bounds__(256) pack_exchange_reduce_kernel(int batch, in
         const unsigned long long* f = reinterpret_cast<const unsigned long long*>(mine + L.flags_off) + (size_t)par * world + tid;
         const unsigned long long t0 = global_ns();
         while (ld_acquire_sys(f) < seq) {
-            if (global_ns() - t0 > timeout_ns) { *err = 1; break; }
+            if (global_ns() - t0 > timeout_ns) { *err = 1; s_timed_out = 1; break; }
             __nanosleep(200);
         }
     }
     __threadfence_system();
     __syncthreads();
+    if (s_timed_out) {
+        // a rank did not arrive: no winner can be named.  The caller gets a record that cannot be mistaken for one
+        // (cost NaN, index -1, zero trajectory) and i7_p2p_status reports the time-out until i7_p2p_reset
+        for (int t = tid; t < 2 + nz; t += blockDim.x) out[t] = t == 0 ? T(CUDART_NAN) : (t == 1 ? T(-1) : T(0));
+        return;
+    }
     // ---- winner over the ranks (same rule as reduce_best_kernel: lowest cost, lowest rank on ties) ----
     const T* gathered = reinterpret_cast<const T*>(mine + par * L.data_bytes);
     if (tid == 0) {
@@ -397,6 +404,61 @@ __global__ void __launch_bounds__(256) pack_exchange_reduce_kernel(int batch, in
     __syncthreads();
     const T* tl = gathered + (size_t)s_win * stride + batch;
     for (int t = tid; t < 2 + nz; t += blockDim.x) out[t] = __ldcg(tl + t);
+}
+
+// -----------------------------------------------------------------------------------------------------------
+// MPC tick plumbing between two solves, one thread per trajectory element (grid-stride over batch x nz):
+// the warm start of the next tick is the new solution moved `steps` knots towards the present.
+//   tail 0  reference loop src/osqp_mpc.py:65-70: XU[:-18 s] = xu_new[18 s:], the last s knots keep the values of the
+//           PREVIOUS warm start, then the last state becomes [1 x 6, 0 x 6] (the reference's terminal quirk)
+//   tail 1  device precedent trajopt_solver.cuh:153-172 (just_shift): per shifted knot x_{N-1} is repeated and the
+//           control in front of it zeroed
+//   tail 2  the batch drivers / the benchmark: the last [u, x] pair is repeated
+// x_cur (batch x 12, measured state) overwrites x_0; when absent x_0 is the solution's own x_s.  x0_out (batch x 12,
+// optional) receives the new x_0 — the `xs` argument of the next solve.
+template <typename T>
+__global__ void shift_kernel(int batch, int N, int steps, int tail, const T* __restrict__ xu_new, const T* __restrict__ xu_prev,
+                             const T* __restrict__ x_cur, T* __restrict__ xu_out, T* __restrict__ x0_out) {
+    const int nz = 18 * N - 6;
+    const size_t total = (size_t)batch * nz;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int b = (int)(e / nz), t = (int)(e - (size_t)b * nz);
+        const T* src = xu_new + (size_t)b * nz;
+        T v;
+        if (t < 12) {
+            v = x_cur ? x_cur[(size_t)b * 12 + t] : src[(18 * steps + t < nz) ? 18 * steps + t : nz - 12 + t];
+            if (x0_out) x0_out[(size_t)b * 12 + t] = v;
+        } else if (t + 18 * steps < nz) {
+            v = src[t + 18 * steps];
+        } else if (tail == 0) {
+            v = xu_prev[(size_t)b * nz + t];
+        } else if (tail == 1) {
+            const int r = (nz - 1 - t) % 18;          // 0..11: inside a state block, 12..17: inside a control block
+            v = r < 12 ? src[nz - 1 - r] : T(0);
+        } else {
+            const int r = (nz - 1 - t) % 18;
+            v = src[nz - 1 - r];
+        }
+        if (tail == 0 && t >= nz - 12) v = (t - (nz - 12)) < 6 ? T(1) : T(0);
+        xu_out[e] = v;
+    }
+}
+
+// Goal window of every lane out of ONE reference trajectory (traj_len samples of `traj_stride` numbers, the first three
+// are read): goals[b][k] = traj[offset_b + tick + k], index wrapped (wrap != 0: periodic figure-8) or clamped to the
+// last sample (the padded tail of gato_controller.py:316-323).  out_stride 3 or 6 (GATO format, zeros appended).
+template <typename T>
+__global__ void goal_window_kernel(int batch, int N, const T* __restrict__ traj, int traj_len, int traj_stride,
+                                   const int* __restrict__ offsets, int tick, int wrap, int out_stride, T* __restrict__ goals) {
+    const size_t total = (size_t)batch * N * out_stride;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int per = N * out_stride;
+        const int b = (int)(e / per), r = (int)(e - (size_t)b * per), k = r / out_stride, a = r - k * out_stride;
+        long long idx = (long long)(offsets ? offsets[b] : 0) + tick + k;
+        if (wrap) { idx %= traj_len; if (idx < 0) idx += traj_len; }
+        else idx = idx < 0 ? 0 : (idx >= traj_len ? traj_len - 1 : idx);
+        goals[e] = a < 3 ? traj[(size_t)idx * traj_stride + a] : T(0);
+    }
 }
 
 // FMA-pipe peak: 8 independent chains per thread, 2 flop per FMA

@@ -37,6 +37,7 @@ struct SolveParams {
     T* xu_out;            // batch x (18N-6)
     T* stats;             // batch x 12 or nullptr
     T* z_out;             // MODE_QP
+    T* y_out;             // MODE_QP, optional: duals of the 12N equality rows
     T* Adata; T* Pdata; T* g; T* l;   // MODE_DUMP (each may be nullptr)
     T* alpha_out; T* merits_out;      // MODE_LINESEARCH (9 per problem) / MODE_MERIT (6 per problem)
     long long* prof;      // optional: per problem 32 clock64() stamps (phase boundaries), debugging aid
@@ -870,6 +871,44 @@ __device__ __noinline__ void phase_controls(const SolveParams<T>& P, int o_z, in
     __syncthreads();
 }
 
+// Duals of the equality rows at the QP solution z, in the row order of the reference's A (src/osqp_solver.py:83-101:
+// block 0 = -x_0, block k+1 = A_k x_k + B_k u_k - x_{k+1}).  Stationarity in x_j reads
+// P_j x_j + g_j - y_j + A_j' y_{j+1} = 0, so y_j = P_j z_j + g_j + A_j' y_{j+1} (y_N = 0): the co-states of the backward
+// sweep, recovered here by one more pass over the knots (warp 0, lane c = component of y_j; debugging / parity entry).
+template <typename T>
+__device__ void qp_duals(const SolveParams<T>& P, const T* z, const T* xu, const T* cost, const T* krb, int kstride, int oGQ,
+                         int oGV, T* y_out) {
+    if (threadIdx.x >= 32) return;
+    const int lane = threadIdx.x, c = lane < 12 ? lane : 0, N = P.N;
+    const int ca = c < 6 ? c : c - 6;
+    T y = T(0);
+    for (int j = N - 1; j >= 0; --j) {
+        const T* ck = cost + COST_STRIDE * j;
+        const T* zj = z + 18 * j;
+        T own;
+        if (c < 6) {
+            T jz = T(1);
+            for (int i = 0; i < 6; ++i) jz += ck[i] * zj[i];
+            own = ck[6] * ck[c] * jz;                       // Q_k j (j'z) + Q_k j
+        } else {
+            own = ck[7] * (zj[c] + xu[18 * j + c]);         // dQ_k z_v + dQ_k v_bar
+        }
+        T acc = T(0);
+        const T yq = __shfl_sync(0xffffffffu, y, ca);       // y_{j+1}, q part, component ca
+        if (j < N - 1) {
+            const T* G = krb + (size_t)kstride * j + (c < 6 ? oGQ : oGV);
+            acc = c < 6 ? yq : P.dt * yq;
+#pragma unroll
+            for (int r = 0; r < 6; ++r) acc += G[6 * r + ca] * __shfl_sync(0xffffffffu, y, 6 + r);
+        } else {
+#pragma unroll
+            for (int r = 0; r < 6; ++r) (void)__shfl_sync(0xffffffffu, y, 6 + r);
+        }
+        y = own + acc;
+        if (lane < 12) y_out[12 * j + lane] = y;
+    }
+}
+
 // -----------------------------------------------------------------------------------------------------------
 // fixed-order reduction helper: sum of vals[0..n) by one warp (lane-strided partial sums + xor tree)
 template <typename T> I7_DEV T warp_sum_strided(const T* vals, int n, int lane) {
@@ -1130,6 +1169,7 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 2] = clock64();
                 if (P.mode == MODE_QP) {
                     for (int t = tid; t < nz; t += NT) P.z_out[(size_t)b * nz + t] = M.z[t];
+                    if (P.y_out) qp_duals<T>(P, M.z, M.xu, M.cost, M.kr, KR_STRIDE, KR_GQ, KR_GV, P.y_out + (size_t)b * 12 * N);
                     break;
                 }
             }

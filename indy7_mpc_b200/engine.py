@@ -120,13 +120,16 @@ class Engine:
             keep.append(t)
             return t, t.data_ptr()
         if _is_torch(like) and like.is_pinned():
-            # page-locked inputs get page-locked outputs (the C ABI then copies without staging); the buffers are
-            # cached per call site and shape, so a result is valid until the next call of the same kind
+            # page-locked inputs get page-locked outputs (the kernel then writes them itself, zero-copy).  Page-locking
+            # costs milliseconds, so the buffers are owned by the engine: a ring of TWO per call site and shape — a
+            # result stays valid until the second-next call of the same kind (long enough to be the warm start of the
+            # next one), then it is overwritten.  Callers that keep results longer clone them.
             key = (tag, tuple(shape))
-            t = self._pinned.get(key)
-            if t is None:
-                t = torch.empty(shape, dtype=self._torch_dtype(), pin_memory=True)
-                self._pinned[key] = t
+            ring = self._pinned.get(key)
+            if ring is None:
+                ring = self._pinned[key] = [[torch.empty(shape, dtype=self._torch_dtype(), pin_memory=True) for _ in range(2)], 0]
+            t = ring[0][ring[1]]
+            ring[1] ^= 1
             keep.append(t)
             return t, t.data_ptr()
         a = np.empty(shape, dtype=self.np_dtype)
@@ -173,14 +176,16 @@ class Engine:
         self._check(self.lib.i7_solve(self._h, B, p_xu, p_x0, p_g, gs, p_out, p_st, self._stream(xu)))
         return out, stats
 
-    def solve_qp(self, xu, x0, goals):
+    def solve_qp(self, xu, x0, goals, want_duals=False):
+        """z = setup_and_solve_qp(xu, x0, goals).x; with want_duals also y (B x 12N, duals of the equality rows)."""
         B = self._batch_of(xu)
         gs = self._goal_stride(goals, B)
         keep = []
         p_xu, p_x0, p_g = self._in(xu, (B, self.nz), keep), self._in(x0, (B, 12), keep), self._in(goals, (B, gs * self.N), keep)
         out, p_out = self._out((B, self.nz), xu, keep)
-        self._check(self.lib.i7_solve_qp(self._h, B, p_xu, p_x0, p_g, gs, p_out, self._stream(xu)))
-        return out
+        y, p_y = self._out((B, 12 * self.N), xu, keep) if want_duals else (None, None)
+        self._check(self.lib.i7_solve_qp(self._h, B, p_xu, p_x0, p_g, gs, p_out, p_y, self._stream(xu)))
+        return (out, y) if want_duals else out
 
     def dump_qp(self, xu, x0, goals):
         B = self._batch_of(xu)
@@ -246,6 +251,41 @@ class Engine:
         self._check(self.lib.i7_sim_forward(self._h, B, px, pu, float(dt), bcast, po, self._stream(x)))
         return out
 
+    TAILS = {"osqp_mpc": 0, "hold": 1, "repeat": 2}
+
+    def shift(self, xu_new, steps=1, tail="repeat", xu_prev=None, x_cur=None, want_x0=True):
+        """Warm start of the next tick (i7_shift): the solution moved `steps` knots towards the present.  tail:
+        'osqp_mpc' (src/osqp_mpc.py:65-70, needs xu_prev), 'hold' (trajopt_solver.cuh:153-172), 'repeat' (batch drivers).
+        Returns (xu_next, x0_next)."""
+        B = self._batch_of(xu_new)
+        keep = []
+        p_new = self._in(xu_new, (B, self.nz), keep)
+        p_prev = self._in(xu_prev, (B, self.nz), keep)
+        p_cur = self._in(x_cur, (B, 12), keep)
+        out, p_out = self._out((B, self.nz), xu_new, keep, "shift.xu")
+        x0, p_x0 = self._out((B, 12), xu_new, keep, "shift.x0") if want_x0 else (None, None)
+        self._check(self.lib.i7_shift(self._h, B, int(steps), self.TAILS[tail], p_new, p_prev, p_cur, p_out, p_x0,
+                                      self._stream(xu_new)))
+        return out, x0
+
+    def goal_window(self, traj, offsets=None, tick=0, wrap=True, out_stride=3, batch=None):
+        """Goal windows of `batch` lanes out of one reference trajectory (T x 3 or T x 6), i7_goal_window."""
+        B = int(batch) if batch is not None else self.batch
+        tlen = int(traj.shape[0])
+        tstride = _numel(traj) // tlen
+        keep = []
+        p_traj = self._in(traj, (tlen, tstride), keep)
+        p_off = None
+        if offsets is not None:
+            if _is_torch(offsets):
+                o = offsets.to(torch.int32).contiguous(); keep.append(o); p_off = o.data_ptr()
+            else:
+                o = np.ascontiguousarray(np.asarray(offsets, dtype=np.int32)); keep.append(o); p_off = o.ctypes.data
+        goals, p_g = self._out((B, self.N * out_stride), traj, keep, "goals")
+        self._check(self.lib.i7_goal_window(self._h, B, p_traj, tlen, tstride, p_off, int(tick), int(bool(wrap)), int(out_stride),
+                                            p_g, self._stream(traj)))
+        return goals
+
     def find_best_idx(self, x_last, u_last, xs, dt, batch=None, tie_last=True, return_errors=False):
         """ONE launch: plant step of every lane under its wrench hypothesis from (x_last, u_last), error against the
         measured state xs, argmin (i7_find_best_idx).  Returns the index (None when no lane qualified), or
@@ -302,6 +342,10 @@ class Engine:
 
     def p2p_status(self, like=None):
         self._check(self.lib.i7_p2p_status(self._h, self._stream(like) if like is not None else None))
+
+    def p2p_reset(self):
+        """Collective (every rank, barrier before and after): clears the time-out state, flags and tick counter."""
+        self._check(self.lib.i7_p2p_reset(self._h))
 
     def measure_fma_peak(self):
         tf = C.c_double()

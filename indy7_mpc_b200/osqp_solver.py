@@ -11,10 +11,10 @@ from .model import RobotModel
 
 
 class QPResult:
-    def __init__(self, x):
+    def __init__(self, x, y=None, iters=1):
         self.x = x
-        self.y = None
-        self.info = type("info", (), dict(status="solved", iter=1))()
+        self.y = y
+        self.info = type("info", (), dict(status="solved", iter=iters))()
 
 
 class OSQPSolver:
@@ -63,7 +63,8 @@ class OSQPSolver:
     def setup_and_solve_qp(self, xu, xs, eepos_g):
         xu, xs, eepos_g = self._check(xu, xs, eepos_g)
         self._sync_weights()
-        return QPResult(np.asarray(self.engine.solve_qp(xu, xs, eepos_g)[0], float))
+        z, y = self.engine.solve_qp(xu, xs, eepos_g, want_duals=True)
+        return QPResult(np.asarray(z[0], float), np.asarray(y[0], float))
 
     def eepos(self, q):
         return np.asarray(self.engine.eepos(np.asarray(q, float).reshape(1, 6))[0], float)

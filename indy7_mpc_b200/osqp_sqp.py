@@ -43,8 +43,9 @@ class SQP_OSQP:
         self.stats['linesearch_alphas']['values'].extend(float(a) for a in rec[4:4 + n_ls])
         self.stats['sqp_stepsizes']['values'].extend(float(a) for a in rec[6:6 + n_steps])
         self.stats['qp_iters']['values'].append(int(rec[0]))
-        if int(rec[3]) == 2:
-            raise FloatingPointError("non-finite value met in the SQP solve")
+        # status 2 = a non-finite merit was met: every comparison of the line search is then false, alpha = 0 and XU
+        # comes back unchanged — what the reference loop does as well (src/osqp_sqp.py:66-72,81-82); the status stays
+        # readable in `last_record[3]`
         return np.asarray(out[0], float)
 
     def get_stats(self):
