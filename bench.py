@@ -421,7 +421,7 @@ def run_b200(args):
         dist.barrier()
     torch.cuda.synchronize()
     t_wall1 = time.time()
-    launches = eng.launch_count() - launches0
+    launches = (eng.launch_count() - launches0) * K // (W + K)      # the timed ticks' share (every tick launches alike)
     total_ms = torch.tensor([step_ms.sum()], dtype=torch.float64, device=dev)
     per_rank = torch.tensor([kern_ms.mean(), (step_ms - kern_ms).mean()], dtype=torch.float64, device=dev)
     per_rank_all = [torch.zeros_like(per_rank) for _ in range(world)]
