@@ -45,6 +45,14 @@ typedef struct {
     int backend;       /* 0: refined KKT solve (exact), 1: OSQP-style ADMM */
     double mu, step_tol;
     int max_qp;
+    /* extension: box limits of description/indy7.urdf:203-238 as inequality rows
+     * lo <= z_i <= hi on every q_k, v_k (k >= 1) and u_k; ADMM back-end only.  rho of the state rows = rho_x (0.1, OSQP's
+     * rho for inequality rows; equality rows carry 1e3 x 0.1), of the effort rows rho_u (1e-3: without OSQP's Ruiz
+     * scaling a rho far above the 1e-5 curvature of the control cost stalls the iteration). max_iter: 0 = 4000. */
+    int limits;
+    double qmin[NJ], qmax[NJ], vmax[NJ], umax[NJ];
+    double rho_x, rho_u;
+    int max_iter;
 } orc_cfg;
 
 /* ---------------------------------------------------------------- spatial algebra ---------------------- */
@@ -280,6 +288,8 @@ typedef struct {
     double *j, *Qk, *dQk, *Rk;     /* N x 6, N, N, N */
     /* ADMM state (warm start across calls, like the OSQP object held by the reference solver) */
     double *x, *y;
+    double *yl, *zl;               /* duals / auxiliary variables of the n - 12 limit rows (z index 12 + i) */
+    double rp, rd;                 /* residuals at the last termination check */
     int n, mrows;
     /* banded workspace */
     double *band, *rhs, *sol, *perm_work;
@@ -399,16 +409,17 @@ static inline void band_add(double* band, int i, int j, double v) {   /* lower b
     if (i < j) { int t = i; i = j; j = t; }
     band[(size_t)i * (BW + 1) + (i - j)] += v;
 }
-static void kkt_build(const orc_work* w, double dt, double sigma, double delta, double* band) {
+static void kkt_build(const orc_work* w, double dt, double sigma, double delta, double rho_x, double rho_u, double* band) {
     const int N = w->N, nk = 30 * N - 6;
     memset(band, 0, sizeof(double) * (size_t)nk * (BW + 1));
     for (int k = 0; k < N; ++k) {
         const double* jk = w->j + 6 * k;
         for (int a = 0; a < 6; ++a) {
             for (int b = 0; b <= a; ++b) band_add(band, pos_x(k) + a, pos_x(k) + b, w->Qk[k] * jk[a] * jk[b]);
-            band_add(band, pos_x(k) + a, pos_x(k) + a, sigma);
-            band_add(band, pos_x(k) + 6 + a, pos_x(k) + 6 + a, w->dQk[k] + sigma);
-            if (k < N - 1) band_add(band, pos_u(k) + a, pos_u(k) + a, w->Rk[k] + sigma);
+            /* limit rows are identity rows: eliminating their multipliers adds rho_lim to the diagonal (x_0 has none) */
+            band_add(band, pos_x(k) + a, pos_x(k) + a, sigma + (k > 0 ? rho_x : 0.0));
+            band_add(band, pos_x(k) + 6 + a, pos_x(k) + 6 + a, w->dQk[k] + sigma + (k > 0 ? rho_x : 0.0));
+            if (k < N - 1) band_add(band, pos_u(k) + a, pos_u(k) + a, w->Rk[k] + sigma + rho_u);
         }
         for (int a = 0; a < NX; ++a) band_add(band, pos_lam(k) + a, pos_lam(k) + a, -delta);
     }
@@ -486,7 +497,7 @@ static int solve_qp(const orc_cfg* c, orc_work* w, const double* xu, const doubl
     if (c->backend == 0) {
         /* [[P + d I, A'], [A, -d I]] with d = 1e-8, iterative refinement on the true KKT residual */
         const double d = 1e-8;
-        kkt_build(w, c->dt, d, d, w->band);
+        kkt_build(w, c->dt, d, d, 0.0, 0.0, w->band);
         band_factor(w->band, nk);
         memset(zt, 0, sizeof(double) * n); memset(nu, 0, sizeof(double) * mr);
         for (iters = 0; iters < 30; ++iters) {
@@ -504,14 +515,21 @@ static int solve_qp(const orc_cfg* c, orc_work* w, const double* xu, const doubl
         memcpy(zout, zt, sizeof(double) * n);
     } else {
         const double rho = 0.1 * 1e3, sigma = 1e-6, alpha = 1.6, eps_abs = 1e-3, eps_rel = 1e-3;
+        const int lim = c->limits, nl = lim ? n - NX : 0;
+        const double rho_x = lim ? c->rho_x : 0.0, rho_u = lim ? c->rho_u : 0.0;
+        const int max_iter = c->max_iter > 0 ? c->max_iter : 4000;
         /* osqp.update(Px) and osqp.update(Ax) each refactorise (src/osqp_solver.py:140-141) */
-        kkt_build(w, c->dt, sigma, 1.0 / rho, w->band); band_factor(w->band, nk);
-        kkt_build(w, c->dt, sigma, 1.0 / rho, w->band); band_factor(w->band, nk);
-        double *x = w->x, *y = w->y;
+        kkt_build(w, c->dt, sigma, 1.0 / rho, rho_x, rho_u, w->band); band_factor(w->band, nk);
+        kkt_build(w, c->dt, sigma, 1.0 / rho, rho_x, rho_u, w->band); band_factor(w->band, nk);
+        double *x = w->x, *y = w->y, *yl = w->yl, *zl = w->zl;
         double* z = r2;                     /* z = projection onto {l} = l after the first iteration */
         A_mul(w, c->dt, x, z);              /* OSQP warm start: z = A x */
-        for (iters = 1; iters <= 4000; ++iters) {
+        for (int i = 0; i < nl; ++i) zl[i] = x[NX + i];
+        w->rp = w->rd = 0;
+        for (iters = 1; iters <= max_iter; ++iters) {
             for (int i = 0; i < n; ++i) t1[i] = sigma * x[i] - g[i];
+            /* the limit rows [I; -1/rho_l] are eliminated by hand: nu_l = rho_l (x~ - z_l) + y_l */
+            for (int i = 0; i < nl; ++i) t1[NX + i] += ((NX + i) % NXU < NX ? rho_x : rho_u) * zl[i] - yl[i];
             for (int i = 0; i < mr; ++i) r1[i] = z[i] - y[i] / rho;
             to_perm(N, t1, r1, b);
             band_solve(w->band, nk, b);
@@ -523,19 +541,38 @@ static int solve_qp(const orc_cfg* c, orc_work* w, const double* xu, const doubl
                 y[i] += rho * (zr - l[i]);
                 z[i] = l[i];
             }
+            for (int i = 0; i < nl; ++i) {
+                const int e = (NX + i) % NXU;
+                const double rho_l = e < NX ? rho_x : rho_u;
+                const double lo = e < 6 ? c->qmin[e] : (e < 12 ? -c->vmax[e - 6] : -c->umax[e - 12]);
+                const double hi = e < 6 ? c->qmax[e] : (e < 12 ? c->vmax[e - 6] : c->umax[e - 12]);
+                double zr = alpha * zt[NX + i] + (1 - alpha) * zl[i];          /* z~_l = x~_l */
+                double zn = zr + yl[i] / rho_l;
+                zn = zn < lo ? lo : (zn > hi ? hi : zn);
+                yl[i] += rho_l * (zr - zn);
+                zl[i] = zn;
+            }
             if (iters % 25 == 0) {
                 A_mul(w, c->dt, x, Ax); P_mul(w, x, t1); At_mul(w, c->dt, y, t2);
-                double rp = 0, rd = 0;
+                for (int i = 0; i < nl; ++i) t2[NX + i] += yl[i];
+                double rp = 0, rd = 0, nAx = inf_norm(Ax, mr), nz = inf_norm(l, mr);
                 for (int i = 0; i < mr; ++i) { double v = fabs(Ax[i] - l[i]); if (v > rp) rp = v; }
+                for (int i = 0; i < nl; ++i) {
+                    double v = fabs(x[NX + i] - zl[i]); if (v > rp) rp = v;
+                    v = fabs(x[NX + i]); if (v > nAx) nAx = v;
+                    v = fabs(zl[i]); if (v > nz) nz = v;
+                }
                 for (int i = 0; i < n; ++i) { double v = fabs(t1[i] + g[i] + t2[i]); if (v > rd) rd = v; }
-                double ep = eps_abs + eps_rel * fmax(inf_norm(Ax, mr), inf_norm(l, mr));
+                double ep = eps_abs + eps_rel * fmax(nAx, nz);
                 double ed = eps_abs + eps_rel * fmax(fmax(inf_norm(t1, n), inf_norm(t2, n)), inf_norm(g, n));
+                w->rp = rp; w->rd = rd;
                 if (rp <= ep && rd <= ed) break;
             }
         }
         memcpy(zout, x, sizeof(double) * n);
     }
     free(g);
+    if (c->backend == 1 && iters > (c->max_iter > 0 ? c->max_iter : 4000)) iters = c->max_iter > 0 ? c->max_iter : 4000;
     return iters;
 }
 
@@ -589,15 +626,26 @@ orc_work* orc_work_new(int N) {
     w->j = (double*)calloc((size_t)6 * N, sizeof(double)); w->Qk = (double*)calloc(N, sizeof(double));
     w->dQk = (double*)calloc(N, sizeof(double)); w->Rk = (double*)calloc(N, sizeof(double));
     w->x = (double*)calloc(w->n, sizeof(double)); w->y = (double*)calloc(w->mrows, sizeof(double));
+    w->yl = (double*)calloc(w->n, sizeof(double)); w->zl = (double*)calloc(w->n, sizeof(double));
     w->band = (double*)calloc((size_t)w->nk * (BW + 1), sizeof(double));
     return w;
 }
 void orc_work_free(orc_work* w) {
     if (!w) return;
     free(w->Gq); free(w->Gv); free(w->H); free(w->cv); free(w->j); free(w->Qk); free(w->dQk); free(w->Rk);
-    free(w->x); free(w->y); free(w->band); free(w);
+    free(w->x); free(w->y); free(w->yl); free(w->zl); free(w->band); free(w);
 }
-void orc_work_reset(orc_work* w) { memset(w->x, 0, sizeof(double) * w->n); memset(w->y, 0, sizeof(double) * w->mrows); }
+void orc_work_reset(orc_work* w) {
+    memset(w->x, 0, sizeof(double) * w->n); memset(w->y, 0, sizeof(double) * w->mrows);
+    memset(w->yl, 0, sizeof(double) * w->n); memset(w->zl, 0, sizeof(double) * w->n);
+}
+/* ADMM state of a work area (parity tests): x (n), y (12N equality rows), yl (n - 12 limit rows), residuals of the last check */
+void orc_work_state(const orc_work* w, double* x, double* y, double* yl, double* res2) {
+    if (x) memcpy(x, w->x, sizeof(double) * w->n);
+    if (y) memcpy(y, w->y, sizeof(double) * w->mrows);
+    if (yl) memcpy(yl, w->yl, sizeof(double) * (w->n - NX));
+    if (res2) { res2[0] = w->rp; res2[1] = w->rd; }
+}
 
 static void pin_to_featherstone(const double* f, double* o) { for (int a = 0; a < 3; ++a) { o[a] = f[3 + a]; o[3 + a] = f[a]; } }
 
@@ -614,7 +662,8 @@ int orc_solve_qp(const orc_model* m, const orc_cfg* c, orc_work* w, const double
     return it;
 }
 
-/* xu_out = sqp(xs, goals, xu_in); stats[8] laid out like the product's record; returns total QP iterations */
+/* xu_out = sqp(xs, goals, xu_in); stats[12] laid out like the product's record ([8], [9]: QP-solver iterations of the
+ * two passes, [10] their sum); returns total QP iterations */
 int orc_sqp(const orc_model* m, const orc_cfg* c, orc_work* w, const double* xs, const double* goals, const double* xu_in,
             const double* fext_pin, double* xu_out, double* stats) {
     const int N = c->N, n = NXU * N - 6;
@@ -625,10 +674,12 @@ int orc_sqp(const orc_model* m, const orc_cfg* c, orc_work* w, const double* xs,
     double *z = xu + NXU * N, *tmp = z + NXU * N;
     memcpy(xu, xu_in, sizeof(double) * n);
     int qp, n_ls = 0, n_steps = 0, status = 0, total_it = 0;
-    double alphas[2] = {0, 0}, steps[2] = {0, 0};
+    double alphas[2] = {0, 0}, steps[2] = {0, 0}, its[2] = {0, 0};
     for (qp = 0; qp < c->max_qp; ++qp) {
         assemble(m, c, xu, goals, fext, w);
-        total_it += solve_qp(c, w, xu, xs, z);
+        const int it = solve_qp(c, w, xu, xs, z);
+        if (qp < 2) its[qp] = it;
+        total_it += it;
         double alpha = linesearch(m, c, xu, z, goals, fext, tmp);
         if (n_ls < 2) alphas[n_ls] = alpha;
         ++n_ls;
@@ -644,6 +695,7 @@ int orc_sqp(const orc_model* m, const orc_cfg* c, orc_work* w, const double* xs,
     if (stats) {
         stats[0] = qp; stats[1] = n_ls; stats[2] = n_steps; stats[3] = status;
         stats[4] = alphas[0]; stats[5] = alphas[1]; stats[6] = steps[0]; stats[7] = steps[1];
+        stats[8] = its[0]; stats[9] = its[1]; stats[10] = total_it; stats[11] = 0;
     }
     free(xu);
     return total_it;
@@ -660,7 +712,7 @@ int orc_sqp_batch(const orc_model* m, const orc_cfg* c, orc_work** works, int ba
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : total)
     for (int b = 0; b < batch; ++b)
         total += orc_sqp(m, c, works[b], xs + (size_t)NX * b, goals + (size_t)3 * c->N * b, xu_in + (size_t)n * b,
-                         fext_pin ? fext_pin + 6 * (size_t)b : NULL, xu_out + (size_t)n * b, stats ? stats + 8 * (size_t)b : NULL);
+                         fext_pin ? fext_pin + 6 * (size_t)b : NULL, xu_out + (size_t)n * b, stats ? stats + 12 * (size_t)b : NULL);
     return (int)total;
 }
 

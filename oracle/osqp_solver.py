@@ -11,7 +11,14 @@ Same constructor, attributes and methods as the reference class.  Pinocchio call
           equality rows), sigma=1e-6, alpha=1.6, eps_abs=eps_rel=1e-3, max_iter=4000,
           check_termination=25, Ruiz scaling (10 passes), warm start across calls, no polish.
           OSQP's wall-clock-driven adaptive-rho schedule is not reproducible and is left out
-          ("QP-iteration parity unpinned").
+          ("QP-iteration parity unpinned").  ``scaling=0`` gives the unscaled iteration
+          that oracle/c/oracle.c and the product's "osqp" QP mode run.
+
+Extension (not reference behaviour: src/osqp_solver.py:41 passes l == u): with
+``limits=(qmin, qmax, vmax, umax)`` (description/indy7.urdf:203-238) the QP gets the box rows
+lo <= z_i <= hi on every q_k, v_k (k >= 1) and u_k (identity rows below the 12N dynamics rows; rho = rho_x on the
+state rows, rho_u on the effort rows — see oracle/c/oracle.c);
+ADMM back-end only.
 
 The CSC value orders of ``Adata`` / ``Pdata`` follow the reference exactly so the
 product's debug dump (``i7_dump_qp``) can be compared entry by entry.
@@ -31,7 +38,7 @@ class QPResult:
 
 class OSQPSolver:
     def __init__(self, model, dt=0.01, N=32, dQ_cost=0.01, R_cost=1e-5, QN_cost=100, regularize=True, eps=1,
-                 qp_backend='kkt', f_ext=None):
+                 qp_backend='kkt', f_ext=None, limits=None, admm_scaling=10, rho_x=0.1, rho_u=1e-3, max_iter=4000):
         self.model = model
         self.data = model.createData()
         self.N, self.dt = N, dt
@@ -44,6 +51,10 @@ class OSQPSolver:
         self.regularize, self.eps = regularize, eps
         self.qp_backend = qp_backend
         self.f_ext = f_ext                                    # extension: local wrench on the last link
+        self.limits = None if limits is None else tuple(np.asarray(v, float) for v in limits)
+        if self.limits is not None and qp_backend != 'admm':
+            raise ValueError("limits need qp_backend='admm' (the exact KKT back-end is equality-only)")
+        self.admm_scaling, self.rho_x, self.rho_u, self.max_iter = admm_scaling, rho_x, rho_u, max_iter
         self.A = self.initialize_A()
         self.P = self.initialize_P()
         self.l = np.zeros(N * self.nx)
@@ -142,9 +153,20 @@ class OSQPSolver:
         P = Pu + triu(Pu, 1).T
         if self.qp_backend == 'kkt':
             return solve_kkt(P, self.g, A, self.l)
+        lo = hi = self.l
+        if self.limits is not None:                          # box rows on z[12:]
+            qmin, qmax, vmax, umax = self.limits
+            blo = np.tile(np.concatenate([qmin, -vmax, -umax]), self.N)[:self.traj_len][self.nx:]
+            bhi = np.tile(np.concatenate([qmax, vmax, umax]), self.N)[:self.traj_len][self.nx:]
+            sel = speye(self.traj_len, format='csc')[self.nx:, :]
+            A = bmat([[A], [sel]], format='csc')
+            lo, hi = np.concatenate([self.l, blo]), np.concatenate([self.l, bhi])
+            rho_rows = np.tile(np.concatenate([np.full(self.nx, self.rho_x), np.full(self.nu, self.rho_u)]), self.N)[:self.traj_len][self.nx:]
+        else:
+            rho_rows = np.zeros(0)
         if self._admm is None:
-            self._admm = OSQPADMM(self.traj_len, self.N * self.nx)
-        return self._admm.solve(P, self.g, A, self.l)
+            self._admm = OSQPADMM(self.traj_len, A.shape[0], scaling=self.admm_scaling, max_iter=self.max_iter)
+        return self._admm.solve(P, self.g, A, lo, hi, rho_ineq=rho_rows)
 
     # ---- end effector (src/osqp_solver.py:146-155) -------------------------------------------------------
     def eepos(self, q):
@@ -165,12 +187,13 @@ def solve_kkt(P, g, A, l):
 
 
 class OSQPADMM:
-    """OSQP's ADMM for an equality-only QP (l == u), default settings, warm-started between calls."""
+    """OSQP's ADMM for l <= Ax <= u, default settings, warm-started between calls.  rho per row: rho on inequality
+    rows, rho x 1e3 on equality rows (l == u), as OSQP sets it."""
 
     def __init__(self, n, m, rho=0.1, sigma=1e-6, alpha=1.6, eps_abs=1e-3, eps_rel=1e-3, max_iter=4000,
                  check_termination=25, scaling=10, rho_eq_factor=1e3):
         self.n, self.m = n, m
-        self.rho = rho * rho_eq_factor          # every row is an equality: RHO_EQ_OVER_RHO_INEQ = 1e3
+        self.rho, self.rho_eq_factor = rho, rho_eq_factor     # RHO_EQ_OVER_RHO_INEQ = 1e3
         self.sigma, self.alpha = sigma, alpha
         self.eps_abs, self.eps_rel = eps_abs, eps_rel
         self.max_iter, self.check = max_iter, check_termination
@@ -197,20 +220,24 @@ class OSQPADMM:
             c = 1.0 / cost  # OSQP accumulates c across passes on the already-scaled data; one-shot here
         return D, E, c
 
-    def solve(self, P, q, A, l):
+    def solve(self, P, q, A, l, u=None, rho_ineq=None):
         n, m = self.n, self.m
+        u = l if u is None else u
         if self.scaling:
             D, E, c = self._ruiz(P, A, q)
         else:
             D, E, c = np.ones(n), np.ones(m), 1.0
         Ps = (diags(D) @ P @ diags(D) * c).tocsc()
         As = (diags(E) @ A @ diags(D)).tocsc()
-        qs, ls = c * D * q, E * l
-        K = bmat([[Ps + self.sigma * speye(n), As.T], [As, -speye(m) / self.rho]], format='csc')
+        qs, ls, us = c * D * q, E * l, E * u
+        rho = np.where(l == u, self.rho * self.rho_eq_factor, self.rho)
+        if rho_ineq is not None and len(rho_ineq):               # per-row rho of the trailing inequality rows
+            rho[-len(rho_ineq):] = rho_ineq
+        K = bmat([[Ps + self.sigma * speye(n), As.T], [As, -diags(1.0 / rho)]], format='csc')
         lu = splu(K)
         x, y = self.x / D, self.y * c / E      # warm start in scaled variables
-        z = ls.copy()
-        rho, al = self.rho, self.alpha
+        z = As @ x                              # OSQP warm start: z = A x
+        al = self.alpha
         it, status = 0, 'maximum iterations reached'
         rp = rd = np.inf
         while it < self.max_iter:
@@ -220,15 +247,15 @@ class OSQPADMM:
             zt = z + (nu - y) / rho
             x = al * xt + (1 - al) * x
             zr = al * zt + (1 - al) * z
-            znew = ls                                  # projection onto {l}
+            znew = np.clip(zr + y / rho, ls, us)       # projection onto [l, u]
             y = y + rho * (zr - znew)
             z = znew
             if it % self.check == 0:
-                xu_, yu_ = D * x, E * y / c
+                xu_, yu_, zu_ = D * x, E * y / c, z / E
                 Ax, Px, Aty = A @ xu_, P @ xu_, A.T @ yu_
-                rp = np.abs(Ax - l).max()
+                rp = np.abs(Ax - zu_).max()
                 rd = np.abs(Px + q + Aty).max()
-                ep = self.eps_abs + self.eps_rel * max(np.abs(Ax).max(), np.abs(l).max())
+                ep = self.eps_abs + self.eps_rel * max(np.abs(Ax).max(), np.abs(zu_).max())
                 ed = self.eps_abs + self.eps_rel * max(np.abs(Px).max(), np.abs(Aty).max(), np.abs(q).max())
                 if rp <= ep and rd <= ed:
                     status = 'solved'

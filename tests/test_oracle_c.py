@@ -1,5 +1,6 @@
 """The plain-C oracle port (timed CPU baseline) must agree with the numpy oracle."""
 import numpy as np
+import pytest
 
 from oracle import rbd
 from oracle.cport import COracle
@@ -49,3 +50,44 @@ def test_c_admm_meets_osqp_tolerances(oracle_model):
         ref = OSQPSolver(oracle_model, qp_backend="kkt").setup_and_solve_qp(xu[b], x0[b], goals[b]).x
         assert it % 25 == 0 and it <= 200
         assert rel(z, ref) < 1e-3
+
+
+URDF_LIMITS = (np.full(6, -3.0543261909900767), np.full(6, 3.0543261909900767), np.array([2.6179938779914944] * 3 + [3.141592653589793] * 3),
+               np.array([431.97, 431.97, 197.23, 79.79, 79.79, 79.79]))        # description/indy7.urdf:203-238
+TIGHT_LIMITS = (np.full(6, -2.0), np.full(6, 2.0), np.full(6, 0.8), np.array([60.0, 60.0, 30.0, 8.0, 8.0, 8.0]))
+
+
+@pytest.mark.parametrize("limits", [None, URDF_LIMITS, TIGHT_LIMITS])
+def test_c_admm_equals_numpy_admm_unscaled(oracle_model, limits):
+    """The two restatements of the ADMM iteration (C: banded LDL' with the limit rows eliminated by hand; numpy: sparse LU
+    of the full quasi-definite KKT with the limit rows in A) run the same algorithm: same iteration count, same iterate —
+    without limits (the reference's l == u QP) and with the box rows of SURVEY.md section 8 f-4."""
+    xu, x0, goals = make_cases(oracle_model, 4, seed=11)
+    for b in (0, 1, 3):                                       # problem 2 of this seed is infeasible under the limits
+        ca = COracle(oracle_model, backend="admm", limits=limits)
+        ns = OSQPSolver(oracle_model, qp_backend="admm", admm_scaling=0, limits=limits)
+        for rep in range(2):                                  # second call: warm-started
+            z, it = ca.solve_qp(xu[b], x0[b], goals[b])
+            r = ns.setup_and_solve_qp(xu[b], x0[b], goals[b])
+            assert it == r.info.iter and r.info.status == "solved"
+            assert rel(z, r.x) < 1e-8
+            x, y, yl, res = ca.admm_state()
+            assert rel(y, r.y[:12 * 32]) < 1e-6
+            if limits is not None:
+                assert rel(yl, r.y[12 * 32:]) < 1e-6 or np.abs(yl - r.y[12 * 32:]).max() < 1e-9
+                lo = np.tile(np.concatenate([limits[0], -limits[2], -limits[3]]), 32)[:z.size][12:]
+                hi = np.tile(np.concatenate([limits[1], limits[2], limits[3]]), 32)[:z.size][12:]
+                viol = np.maximum(lo - z[12:], z[12:] - hi).max()
+                assert viol <= 1e-3 * (1.0 + np.abs(z).max())        # OSQP's eps_prim = eps_abs + eps_rel max(|Ax|, |z|)
+
+
+def test_c_admm_limits_bind(oracle_model):
+    """With tight limits the solution differs from the equality-only one and the bounds are active."""
+    xu, x0, goals = make_cases(oracle_model, 1, seed=11)
+    free, _ = COracle(oracle_model, backend="admm").solve_qp(xu[0], x0[0], goals[0])
+    lim, _ = COracle(oracle_model, backend="admm", limits=TIGHT_LIMITS).solve_qp(xu[0], x0[0], goals[0])
+    u_free = np.concatenate([free, np.zeros(6)]).reshape(32, 18)[:, 12:]
+    u_lim = np.concatenate([lim, np.zeros(6)]).reshape(32, 18)[:, 12:]
+    assert np.abs(u_free).max(axis=0)[3] > 8.0 * 1.05          # the free solution violates the tight effort limit ...
+    assert np.abs(u_lim).max() <= 60.0 * (1 + 1e-3) and np.abs(u_lim[:, 3:]).max() <= 8.0 * (1 + 2e-3)
+    assert np.abs(u_lim[:, 3:]).max() > 8.0 * 0.99             # ... the limited one sits on it
