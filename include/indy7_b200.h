@@ -68,7 +68,20 @@ typedef struct {
     double com[I7_NJ][3];   /* centre of mass in the link frame */
     double Ic[I7_NJ][9];    /* rotational inertia about the COM, link frame, row-major */
     double gravity[3];      /* world gravity, default (0, 0, -9.81) */
+    /* joint limits (description/indy7.urdf:203-238 <limit lower upper effort velocity>); read only when
+     * i7_config.limits != 0.  The reference QP has no inequality rows (src/osqp_solver.py:41 passes l == u). */
+    double q_min[I7_NJ], q_max[I7_NJ], v_max[I7_NJ], u_max[I7_NJ];
 } i7_model;
+
+/* How the QP of an SQP pass is solved (src/osqp_solver.py:137-143):
+ *   I7_QP_EXACT  block recursion over the knots: the exact KKT point OSQP converges to; no warm-start state; one
+ *                launch per i7_solve (default — the throughput / latency path)
+ *   I7_QP_OSQP   the reference's own regime: OSQP's ADMM (rho = 0.1, x 1e3 on equality rows; sigma = 1e-6; alpha = 1.6;
+ *                eps_abs = eps_rel = 1e-3 checked every 25 iterations; no Ruiz scaling, no adaptive rho), warm-started
+ *                per problem from the previous call on the same handle slot — (x, y) live in the handle like the OSQP
+ *                object lives in the reference solver (src/osqp_solver.py:39-41).  f64 only; three launches per SQP pass
+ *                (linearise, ADMM, line search + update).  Required for `limits`. */
+typedef enum { I7_QP_EXACT = 0, I7_QP_OSQP = 1 } i7_qp_mode;
 
 typedef struct {
     int32_t N;              /* knot points (32 in the drivers, 64 in gato_controller.py:314, 128 in trajopt_node.cu:178) */
@@ -88,6 +101,17 @@ typedef struct {
     int32_t cluster;        /* i7_solve kernel form: 0 = auto (the largest cluster of 8, 4 or 2 CTAs per problem for which
                                the whole batch is co-resident, else one CTA per problem), 1 = always one CTA per
                                problem, 2 | 4 | 8 = always that cluster form */
+    int32_t qp_mode;        /* i7_qp_mode; default I7_QP_EXACT */
+    int32_t limits;         /* != 0: box rows q_min <= q_k <= q_max, |v_k| <= v_max (k >= 1), |u_k| <= u_max in every QP
+                               (needs I7_QP_OSQP) */
+    double admm_rho;        /* 0.1   rho of inequality rows on states; equality rows carry 1e3 x admm_rho */
+    double admm_rho_u;      /* 1e-3  rho of the effort-limit rows (unscaled ADMM: 0.1 stalls against R_cost = 1e-5) */
+    double admm_sigma;      /* 1e-6 */
+    double admm_alpha;      /* 1.6  */
+    double admm_eps_abs;    /* 1e-3 */
+    double admm_eps_rel;    /* 1e-3 */
+    int32_t admm_max_iter;  /* 4000 */
+    int32_t admm_check;     /* 25   */
     i7_model model;
 } i7_config;
 
@@ -102,7 +126,7 @@ typedef struct {
  *   [8] merit of the returned trajectory as evaluated by the last line search (the accepted candidate, or the
  *       base merit when that line search failed) — the per-problem cost used for best-trajectory selection
  *   [9] base merit of the first line search (merit of the input trajectory)
- *   [10],[11] reserved (0)                                                                            */
+ *   [10],[11] I7_QP_OSQP: ADMM iterations of QP 0 / QP 1 (what OSQP reports as info.iter); I7_QP_EXACT: 0      */
 
 typedef struct i7_handle i7_handle;
 
@@ -116,8 +140,10 @@ i7_status i7_set_weights(i7_handle* h, double dQ_cost, double R_cost, double QN_
 /* f_ext: batch x 6 DOUBLES on the host, Pinocchio order [fx fy fz tx ty tz], expressed in the local frame of
  * the last joint (src/gato_mpc_batch_sample.py:97-101,158); NULL clears. */
 i7_status i7_set_external_wrench(i7_handle* h, const double* f_ext, int32_t batch);
-/* Kept for bindings.batch_sqp compatibility.  The direct QP solve carries no warm-start state, so these only
- * clear the statistics counters. */
+/* bindings.batch_sqp compatibility (reset / resetRho / resetLambda, gato_controller.py:70-78).  I7_QP_OSQP: i7_reset
+ * clears the whole warm start (x and y of every problem slot), i7_reset_lambda the duals only, i7_reset_rho restores
+ * the configured rho (rho is never adapted, so it has nothing to undo).  I7_QP_EXACT carries no solver state: the
+ * three calls only clear the timing state. */
 i7_status i7_reset(i7_handle* h);
 i7_status i7_reset_rho(i7_handle* h);
 i7_status i7_reset_lambda(i7_handle* h);
@@ -224,6 +250,12 @@ i7_status i7_measure_fma_peak(i7_handle* h, double* tflops);
 i7_status i7_profile_phases(i7_handle* h, int32_t enable, int64_t* clocks32, int32_t batch);
 
 /* ---- stage-level entry points (parity tests and debugging; same device code as i7_solve) ---- */
+/* State of the I7_QP_OSQP solver after the latest i7_solve / i7_solve_qp (host or device pointers, any may be NULL):
+ * x: batch x (18N-6) primal iterate; y: batch x 12N duals of the equality rows; y_lim: batch x (18N-18) duals of the
+ * limit rows (z order from x_1 on; zeros without limits); info: batch x 4 = [iterations, primal residual, dual
+ * residual, status (0 solved, 1 iteration limit)] of the latest QP. */
+i7_status i7_qp_state(i7_handle* h, int32_t batch, void* x, void* y, void* y_lim, void* info, void* stream);
+
 /* The full-step QP solution of `setup_and_solve_qp(xu, x0, goals)` (src/osqp_solver.py:137-143): z_out = `.x`
  * (batch x (18N-6)); y_out (batch x 12N, may be NULL) = `.y`, the duals of the equality rows in the row order of the
  * reference's A (block 0: -x_0 = -xs; block k+1: A_k x_k + B_k u_k - x_{k+1} = -c_k), sign convention of OSQP

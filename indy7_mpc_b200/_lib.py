@@ -11,18 +11,24 @@ LIB_PATH = os.path.join(HERE, "libindy7_b200.so")
 
 I7_NJ, I7_STATS_LEN = 6, 12
 I7_F64, I7_F32 = 0, 1
+I7_QP_EXACT, I7_QP_OSQP = 0, 1
 
 
 class I7Model(C.Structure):
     _fields_ = [("R", C.c_double * 9 * I7_NJ), ("p", C.c_double * 3 * I7_NJ), ("mass", C.c_double * I7_NJ),
-                ("com", C.c_double * 3 * I7_NJ), ("Ic", C.c_double * 9 * I7_NJ), ("gravity", C.c_double * 3)]
+                ("com", C.c_double * 3 * I7_NJ), ("Ic", C.c_double * 9 * I7_NJ), ("gravity", C.c_double * 3),
+                ("q_min", C.c_double * I7_NJ), ("q_max", C.c_double * I7_NJ), ("v_max", C.c_double * I7_NJ),
+                ("u_max", C.c_double * I7_NJ)]
 
 
 class I7Config(C.Structure):
     _fields_ = [("N", C.c_int32), ("batch", C.c_int32), ("dtype", C.c_int32), ("device", C.c_int32),
                 ("dt", C.c_double), ("dQ_cost", C.c_double), ("R_cost", C.c_double), ("QN_cost", C.c_double),
                 ("eps", C.c_double), ("regularize", C.c_int32), ("max_qp", C.c_int32), ("mu", C.c_double),
-                ("step_tol", C.c_double), ("threads", C.c_int32), ("cluster", C.c_int32), ("model", I7Model)]
+                ("step_tol", C.c_double), ("threads", C.c_int32), ("cluster", C.c_int32), ("qp_mode", C.c_int32),
+                ("limits", C.c_int32), ("admm_rho", C.c_double), ("admm_rho_u", C.c_double), ("admm_sigma", C.c_double),
+                ("admm_alpha", C.c_double), ("admm_eps_abs", C.c_double), ("admm_eps_rel", C.c_double),
+                ("admm_max_iter", C.c_int32), ("admm_check", C.c_int32), ("model", I7Model)]
 
 
 # every symbol include/indy7_b200.h declares: name -> (restype, argtypes)
@@ -56,6 +62,7 @@ SYMBOLS = {
     "i7_shift": (_i32, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp]),
     "i7_goal_window": (_i32, [_vp, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp]),
     "i7_find_best_idx": (_i32, [_vp, _i32, _vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp]),
+    "i7_qp_state": (_i32, [_vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "i7_solve_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "i7_dump_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "i7_merit": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp]),

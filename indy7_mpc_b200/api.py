@@ -18,7 +18,7 @@ except Exception:  # pragma: no cover
 
 class Indy7SQP:
     def __init__(self, urdf=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
-                 dtype="fp64", device="cuda", batch=1, threads=0, cluster=0):
+                 dtype="fp64", device="cuda", batch=1, threads=0, cluster=0, qp_mode="exact", limits=False, admm=None):
         if isinstance(urdf, RobotModel):
             self.model = urdf
         else:
@@ -31,7 +31,7 @@ class Indy7SQP:
         self.nz = 18 * self.N - 6
         self.engine = Engine(self.model, N=N, dt=dt, dQ_cost=dQ_cost, R_cost=R_cost, QN_cost=QN_cost,
                              regularize=regularize, eps=eps, batch=batch, dtype=dtype, device=device, threads=threads,
-                             cluster=cluster)
+                             cluster=cluster, qp_mode=qp_mode, limits=limits, admm=admm)
         self._warm = None
         self._tick_prev = None          # step(): previous solution of every lane, device-resident
         self._tick_bufs = None
@@ -39,7 +39,7 @@ class Indy7SQP:
     def reset(self):
         self._warm = None
         self._tick_prev = None
-        self.engine.reset()
+        self.engine.reset()             # qp_mode 'osqp': also clears the ADMM warm start of every problem slot
 
     def step(self, x0, xref, exchange=None, index_offset=0):
         """One closed-loop MPC tick of a batch of sampled problems (BASELINE.json configs[3]; the tick of

@@ -15,7 +15,7 @@ LIB = os.path.join(HERE, "libindy7_b200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 
 # (object name, source, extra defines)
-UNITS = [("i7_api", "i7_api.cu", [])]
+UNITS = [("i7_api", "i7_api.cu", []), ("i7_admm", "i7_admm_inst.cu", [])]
 for tname, t in (("f64", "double"), ("f32", "float")):
     for nt in (128, 256, 384):
         for sp in ("false", "true"):

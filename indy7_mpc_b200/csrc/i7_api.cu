@@ -3,6 +3,7 @@
 #undef I7_NJ
 #include "i7_launch.h"
 #include "i7_aux.cuh"
+#include "i7_admm.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -67,6 +68,13 @@ struct i7_handle {
     unsigned* d_sel_counter = nullptr;   // i7_find_best_idx: ticket counter + error scratch (lazy)
     void* d_sel_errs = nullptr;
     unsigned long long p2p_seq = 0;
+    // qp_mode "osqp": per-problem ADMM warm start (x, y, y of the limit rows), QP blocks, factor workspace, QP solution,
+    // QP record, "SQP loop ended" flags, statistics scratch
+    void *d_wx = nullptr, *d_wy = nullptr, *d_wyl = nullptr, *d_blk = nullptr, *d_fac = nullptr, *d_zbuf = nullptr,
+         *d_qpinfo = nullptr, *d_stats = nullptr;
+    int* d_done = nullptr;
+    int admm_smem_bytes = 0;
+    i7::AdmmSettings admm{};
     int zero_copy = 1;           // I7_ZERO_COPY=0: page-locked user buffers go through copies / the chunked pipeline
     int no_events = 0;           // I7_TIMING_EVENTS=0: no timing events around mapped-memory solves (3 us of host time each)
     int direct_max_batch = 0;    // host-buffer solves up to this batch use mapped host memory instead of copies
@@ -428,10 +436,66 @@ bool pipeline_eligible(const i7_handle* h, const SqpCall& c) {
     return true;
 }
 
+// qp_mode "osqp": an SQP pass is three launches — linearise + export the QP blocks (MODE_EXPORT of the fused kernel),
+// ADMM (i7_admm.cuh), line search + update (MODE_STEP) — all on the caller's stream, the per-problem "loop ended" flags
+// stay on the device.  Host buffers go through the arena copies.
+i7_status run_osqp(i7_handle* h, const SqpCall& c, cudaStream_t s) {
+    using T = double;
+    const int N = h->cfg.N;
+    const size_t nz = h->nz, B = c.batch, es = sizeof(T);
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    Stage st(h);
+    const T* d_xu = (const T*)st.in(c.xu, B * nz * es);
+    const T* d_x0 = (const T*)st.in(c.x0, B * 12 * es);
+    const T* d_goals = (const T*)st.in(c.goals, B * N * c.goal_stride * es);
+    T* d_out = (T*)st.out(c.xu_out, B * nz * es);
+    T* d_stats = (T*)st.out(c.stats, B * I7_STATS_LEN * es);
+    T* d_z = (T*)st.out(c.z_out, B * nz * es);
+    T* d_y = (T*)st.out(c.y_out, B * 12 * N * es);
+    i7_status rc = st.flush_in(s);
+    if (rc) return rc;
+    auto admm = [&](const T* xu_lin, T* z_out, T* y_out, const int* done) -> i7_status {
+        i7::AdmmParams<T> A;
+        std::memset(&A, 0, sizeof(A));
+        A.blk = (const T*)h->d_blk; A.xu = xu_lin; A.x0 = d_x0;
+        A.wx = (T*)h->d_wx; A.wy = (T*)h->d_wy; A.wyl = (T*)h->d_wyl;
+        A.z_out = z_out; A.y_out = y_out; A.info = (T*)h->d_qpinfo; A.fac = (T*)h->d_fac; A.done = done;
+        A.N = N; A.batch = c.batch; A.dt = h->cfg.dt; A.S = h->admm;
+        I7_CUDA(h, i7::launch_admm(A, h->admm_smem_bytes, s));
+        ++h->launches;
+        return I7_OK;
+    };
+    auto fused = [&](int mode, const T* xu_in, const T* xu_full, T* xu_out, T* stats, int* done, int qp_index) -> i7_status {
+        i7::SolveParams<T> P;
+        base_params<T>(h, P, c.batch, c.goal_stride, mode);
+        P.xu_in = xu_in; P.x0 = d_x0; P.goals = d_goals; P.xu_full = xu_full; P.xu_out = xu_out; P.stats = stats;
+        P.blk_out = (T*)h->d_blk; P.qp_info = (const T*)h->d_qpinfo; P.done = done; P.qp_index = qp_index;
+        return launch_sqp<T>(h, get_rob<T>(h), P, s);
+    };
+    if (c.mode == i7::MODE_QP) {
+        if ((rc = fused(i7::MODE_EXPORT, d_xu, nullptr, nullptr, nullptr, nullptr, 0))) return rc;
+        if ((rc = admm(d_xu, d_z, d_y, nullptr))) return rc;
+        return st.flush_out(s);
+    }
+    T* stats = d_stats ? d_stats : (T*)h->d_stats;
+    I7_CUDA(h, cudaEventRecord(h->ev0, s));
+    if (d_out != d_xu) I7_CUDA(h, cudaMemcpyAsync(d_out, d_xu, B * nz * es, cudaMemcpyDeviceToDevice, s));
+    I7_CUDA(h, cudaMemsetAsync(h->d_done, 0, B * sizeof(int), s));
+    for (int qp = 0; qp < h->cfg.max_qp; ++qp) {
+        if ((rc = fused(i7::MODE_EXPORT, d_out, nullptr, nullptr, nullptr, h->d_done, qp))) return rc;
+        if ((rc = admm(d_out, (T*)h->d_zbuf, nullptr, h->d_done))) return rc;
+        if ((rc = fused(i7::MODE_STEP, d_out, (const T*)h->d_zbuf, d_out, stats, h->d_done, qp))) return rc;
+    }
+    I7_CUDA(h, cudaEventRecord(h->ev1, s));
+    h->timed = true;
+    return st.flush_out(s);
+}
+
 i7_status run_sqp(i7_handle* h, const SqpCall& c, void* stream) {
     i7_status rc = check_batch(h, c.batch, c.goal_stride);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
+    if (h->cfg.qp_mode == I7_QP_OSQP && (c.mode == i7::MODE_SOLVE || c.mode == i7::MODE_QP)) return run_osqp(h, c, s);
     if (h->zero_copy && c.mode == i7::MODE_SOLVE && c.batch > h->direct_max_batch) {
         // every host buffer of the call page-locked: one launch straight on the caller's memory
         const void* ptrs[5] = {c.xu, c.x0, c.goals, c.xu_out, c.stats};
@@ -459,7 +523,11 @@ void i7_default_config(i7_config* cfg) {
     cfg->N = 32; cfg->batch = 1; cfg->dtype = I7_F64; cfg->device = 0;
     cfg->dt = 0.01; cfg->dQ_cost = 0.01; cfg->R_cost = 1e-5; cfg->QN_cost = 100.0; cfg->eps = 1.0;
     cfg->regularize = 1; cfg->max_qp = 2; cfg->mu = 10.0; cfg->step_tol = 1e-3; cfg->threads = 0;
+    cfg->qp_mode = I7_QP_EXACT; cfg->limits = 0;
+    cfg->admm_rho = 0.1; cfg->admm_rho_u = 1e-3; cfg->admm_sigma = 1e-6; cfg->admm_alpha = 1.6;
+    cfg->admm_eps_abs = 1e-3; cfg->admm_eps_rel = 1e-3; cfg->admm_max_iter = 4000; cfg->admm_check = 25;
     cfg->model.gravity[2] = -9.81;
+    for (int i = 0; i < I7_NJ; ++i) { cfg->model.q_min[i] = -1e30; cfg->model.q_max[i] = 1e30; cfg->model.v_max[i] = 1e30; cfg->model.u_max[i] = 1e30; }
 }
 
 const char* i7_last_error(const i7_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
@@ -475,6 +543,8 @@ void i7_destroy(i7_handle* h) {
     if (h->d_spill) cudaFree(h->d_spill);
     if (h->d_xbuf) cudaFree(h->d_xbuf);
     if (h->d_prof) cudaFree(h->d_prof);
+    for (void* p : {h->d_wx, h->d_wy, h->d_wyl, h->d_blk, h->d_fac, h->d_zbuf, h->d_qpinfo, h->d_stats, (void*)h->d_done})
+        if (p) cudaFree(p);
     for (int r = 0; r < h->p2p_world; ++r)
         if (h->p2p_peer[r] && r != h->p2p_rank) cudaIpcCloseMemHandle(h->p2p_peer[r]);
     if (h->p2p_mine) cudaFree(h->p2p_mine);
@@ -507,6 +577,18 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
         cfg->max_qp < 1 || cfg->max_qp > I7_MAX_QP || !(cfg->dt > 0)) {
         g_create_error = "invalid configuration (N in [2,512], batch >= 1, dtype f64|f32, max_qp in [1,2], dt > 0)";
         return I7_ERR_INVALID;
+    }
+    if ((cfg->qp_mode != I7_QP_EXACT && cfg->qp_mode != I7_QP_OSQP) || (cfg->limits && cfg->qp_mode != I7_QP_OSQP)) {
+        g_create_error = "qp_mode must be I7_QP_EXACT or I7_QP_OSQP; limits need I7_QP_OSQP (the exact solve is equality-only)";
+        return I7_ERR_INVALID;
+    }
+    if (cfg->qp_mode == I7_QP_OSQP) {
+        if (cfg->dtype != I7_F64) { g_create_error = "I7_QP_OSQP runs in f64 only (sigma = 1e-6 against rho = 100)"; return I7_ERR_UNSUPPORTED; }
+        if (!(cfg->admm_rho > 0) || !(cfg->admm_rho_u > 0) || !(cfg->admm_sigma > 0) || !(cfg->admm_alpha > 0 && cfg->admm_alpha < 2) ||
+            cfg->admm_max_iter < 1 || cfg->admm_check < 1) {
+            g_create_error = "invalid ADMM settings (rho, rho_u, sigma > 0; 0 < alpha < 2; max_iter, check >= 1)";
+            return I7_ERR_INVALID;
+        }
     }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -569,7 +651,7 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
         }
         const bool f64 = cfg->dtype == I7_F64;
         const int sizes[3] = {8, 4, 2};
-        for (int si = 0; si < 3 && !h->use_cluster && cfg->cluster != 1; ++si) {
+        for (int si = 0; si < 3 && !h->use_cluster && cfg->cluster != 1 && cfg->qp_mode == I7_QP_EXACT; ++si) {
             const int cl = sizes[si];
             if (cfg->cluster != 0 && cfg->cluster != cl) continue;
             int ccap = 0, nact = 0;
@@ -592,6 +674,31 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
             h->use_cluster = true; h->cluster_size = cl; h->cluster_smem_bytes = bytes;
         }
         if (h->use_cluster) I7_CUDA_C(cudaMalloc(&h->d_xbuf, (size_t)cfg->batch * i7::cluster_xbuf_len(cfg->N) * h->esize));
+    }
+    if (cfg->qp_mode == I7_QP_OSQP) {
+        const size_t B = cfg->batch, N = cfg->N;
+        int acap = 0;
+        I7_CUDA_C(i7::smem_cap_admm(h->max_smem_optin, &acap));
+        h->admm_smem_bytes = i7::admm_smem_elems(cfg->N) * (int)sizeof(double);
+        if (h->admm_smem_bytes > acap) { h->err = "horizon too long for the ADMM kernel's shared-memory vectors"; return fail(I7_ERR_UNSUPPORTED); }
+        i7::AdmmSettings& S = h->admm;
+        S.rho_eq = 1e3 * cfg->admm_rho; S.rho_x = cfg->admm_rho; S.rho_u = cfg->admm_rho_u; S.sigma = cfg->admm_sigma;
+        S.alpha = cfg->admm_alpha; S.eps_abs = cfg->admm_eps_abs; S.eps_rel = cfg->admm_eps_rel;
+        S.max_iter = cfg->admm_max_iter; S.check = cfg->admm_check; S.limits = cfg->limits ? 1 : 0;
+        for (int i = 0; i < 6; ++i) { S.qmin[i] = cfg->model.q_min[i]; S.qmax[i] = cfg->model.q_max[i]; S.vmax[i] = cfg->model.v_max[i]; S.umax[i] = cfg->model.u_max[i]; }
+        I7_CUDA_C(cudaMalloc(&h->d_wx, B * 18 * N * 8));
+        I7_CUDA_C(cudaMalloc(&h->d_wy, B * 12 * N * 8));
+        I7_CUDA_C(cudaMalloc(&h->d_wyl, B * 18 * N * 8));
+        I7_CUDA_C(cudaMemset(h->d_wx, 0, B * 18 * N * 8));
+        I7_CUDA_C(cudaMemset(h->d_wy, 0, B * 12 * N * 8));
+        I7_CUDA_C(cudaMemset(h->d_wyl, 0, B * 18 * N * 8));
+        I7_CUDA_C(cudaMalloc(&h->d_blk, B * N * i7::QB_STRIDE * 8));
+        I7_CUDA_C(cudaMalloc(&h->d_fac, B * N * (size_t)i7::admm_fac_stride() * 8));
+        I7_CUDA_C(cudaMalloc(&h->d_zbuf, B * h->nz * 8));
+        I7_CUDA_C(cudaMalloc(&h->d_qpinfo, B * 4 * 8));
+        I7_CUDA_C(cudaMemset(h->d_qpinfo, 0, B * 4 * 8));
+        I7_CUDA_C(cudaMalloc(&h->d_stats, B * I7_STATS_LEN * 8));
+        I7_CUDA_C(cudaMalloc((void**)&h->d_done, B * sizeof(int)));
     }
     const size_t B = cfg->batch, N = cfg->N, es = h->esize;
     // worst case over all entry points: inputs xu, x0, goals(6), xu_full; outputs of the dump mode
@@ -670,9 +777,35 @@ i7_status i7_set_external_wrench(i7_handle* h, const double* f_ext, int32_t batc
     return I7_OK;
 }
 
-i7_status i7_reset(i7_handle* h) { if (!h) return I7_ERR_INVALID; h->timed = false; return I7_OK; }
-i7_status i7_reset_rho(i7_handle* h) { return h ? I7_OK : I7_ERR_INVALID; }
-i7_status i7_reset_lambda(i7_handle* h) { return h ? I7_OK : I7_ERR_INVALID; }
+i7_status i7_reset(i7_handle* h) {
+    if (!h) return I7_ERR_INVALID;
+    h->timed = false;
+    if (h->cfg.qp_mode == I7_QP_OSQP) {      // OSQP object re-created: primal and dual warm start gone
+        const size_t B = h->cfg.batch, N = h->cfg.N;
+        I7_CUDA(h, cudaSetDevice(h->cfg.device));
+        I7_CUDA(h, cudaDeviceSynchronize());
+        I7_CUDA(h, cudaMemset(h->d_wx, 0, B * 18 * N * 8));
+        I7_CUDA(h, cudaMemset(h->d_wy, 0, B * 12 * N * 8));
+        I7_CUDA(h, cudaMemset(h->d_wyl, 0, B * 18 * N * 8));
+    }
+    return I7_OK;
+}
+i7_status i7_reset_rho(i7_handle* h) {
+    if (!h) return I7_ERR_INVALID;
+    if (h->cfg.qp_mode == I7_QP_OSQP) { h->admm.rho_eq = 1e3 * h->cfg.admm_rho; h->admm.rho_x = h->cfg.admm_rho; h->admm.rho_u = h->cfg.admm_rho_u; }
+    return I7_OK;
+}
+i7_status i7_reset_lambda(i7_handle* h) {
+    if (!h) return I7_ERR_INVALID;
+    if (h->cfg.qp_mode == I7_QP_OSQP) {
+        const size_t B = h->cfg.batch, N = h->cfg.N;
+        I7_CUDA(h, cudaSetDevice(h->cfg.device));
+        I7_CUDA(h, cudaDeviceSynchronize());
+        I7_CUDA(h, cudaMemset(h->d_wy, 0, B * 12 * N * 8));
+        I7_CUDA(h, cudaMemset(h->d_wyl, 0, B * 18 * N * 8));
+    }
+    return I7_OK;
+}
 
 i7_status i7_solve(i7_handle* h, int32_t batch, const void* xu_in, const void* x0, const void* goals,
                    int32_t goal_stride, void* xu_out, void* stats, void* stream) {
@@ -864,6 +997,22 @@ i7_status i7_measure_fma_peak(i7_handle* h, double* tflops) {
     cudaFree(sink);
     I7_CUDA(h, cudaGetLastError());
     *tflops = best;
+    return I7_OK;
+}
+
+i7_status i7_qp_state(i7_handle* h, int32_t batch, void* x, void* y, void* y_lim, void* info, void* stream) {
+    if (!h) return I7_ERR_INVALID;
+    if (h->cfg.qp_mode != I7_QP_OSQP) { h->err = "i7_qp_state: the exact QP solve keeps no state (qp_mode I7_QP_OSQP only)"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t N = h->cfg.N, nz = h->nz;
+    // the warm start is kept padded to 18 numbers per knot; rows of the caller's arrays are 18N-6 / 18N-18 long
+    if (x) I7_CUDA(h, cudaMemcpy2DAsync(x, nz * 8, h->d_wx, 18 * N * 8, nz * 8, batch, cudaMemcpyDefault, s));
+    if (y) I7_CUDA(h, cudaMemcpyAsync(y, h->d_wy, (size_t)batch * 12 * N * 8, cudaMemcpyDefault, s));
+    if (y_lim) I7_CUDA(h, cudaMemcpy2DAsync(y_lim, (nz - 12) * 8, (char*)h->d_wyl + 12 * 8, 18 * N * 8, (nz - 12) * 8, batch, cudaMemcpyDefault, s));
+    if (info) I7_CUDA(h, cudaMemcpyAsync(info, h->d_qpinfo, (size_t)batch * 4 * 8, cudaMemcpyDefault, s));
+    I7_CUDA(h, cudaStreamSynchronize(s));
     return I7_OK;
 }
 

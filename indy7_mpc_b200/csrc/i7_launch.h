@@ -23,4 +23,13 @@ int cluster_xbuf_len(int N);     // exchange-buffer elements per problem
 constexpr int kClusterSize = 8;
 constexpr int kClusterThreads = 384;     // = CL_NT of i7_cluster.cuh (checked in i7_cluster_inst.cu)
 
+
+// ADMM QP kernel of qp_mode "osqp" (i7_admm.cuh; fp64): grid = batch
+struct AdmmSettings;
+template <typename T> struct AdmmParams;
+cudaError_t launch_admm(const AdmmParams<double>& P, int smem_bytes, cudaStream_t s);
+cudaError_t smem_cap_admm(int optin_bytes, int* cap);
+int admm_smem_elems(int N);
+int admm_fac_stride();
+
 }  // namespace i7

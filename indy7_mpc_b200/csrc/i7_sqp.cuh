@@ -24,8 +24,13 @@ enum Mode : int {
     MODE_QP = 1,          // z = setup_and_solve_qp(xu).x
     MODE_DUMP = 2,        // reference-ordered Adata / Pdata / g / l
     MODE_LINESEARCH = 3,  // alpha + nine merits for given (xu, xu_full)
-    MODE_MERIT = 4        // merit terms of xu against xu_ref (passed as xu_full)
+    MODE_MERIT = 4,       // merit terms of xu against xu_ref (passed as xu_full)
+    // the two halves of an SQP pass around an external QP solver (qp_mode "osqp": i7_admm.cuh):
+    MODE_EXPORT = 5,      // linearisation + cost terms of the pass, as compact per-knot blocks (QB_*)
+    MODE_STEP = 6         // line search on (xu, xu_full = QP solution), update, statistics of pass `qp_index`
 };
+// per-knot block of MODE_EXPORT: A_k = [[I, dt I], [Gq, Gv]], B_k = [0; Hm], c_k = [0; cv]; cost = j[6], Q_k, dQ_k, R_k
+constexpr int QB_GQ = 0, QB_GV = 36, QB_CV = 72, QB_HM = 78, QB_COST = 114, QB_STRIDE = 124;
 
 template <typename T>
 struct SolveParams {
@@ -42,6 +47,10 @@ struct SolveParams {
     T* alpha_out; T* merits_out;      // MODE_LINESEARCH (9 per problem) / MODE_MERIT (6 per problem)
     long long* prof;      // optional: per problem 32 clock64() stamps (phase boundaries), debugging aid
     T* spill_ws;          // gridDim.x x Layout::reg_size workspace when the knot records live in global memory
+    T* blk_out;           // MODE_EXPORT: batch x N x QB_STRIDE
+    const T* qp_info;     // MODE_STEP, optional: batch x 4 record of the QP solver ([0] = its iterations)
+    int* done;            // MODE_EXPORT / MODE_STEP, optional: per problem 1 = the SQP loop has ended (skipped; set by MODE_STEP)
+    int qp_index;         // MODE_STEP: index of the pass (0 .. max_qp-1)
     int N, batch, goal_stride, mode, max_qp, regularize;
     T dt, dQ, R, QN, eps, mu, step_tol;
 };
@@ -1115,6 +1124,7 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
     const Win W{0, N - 1, N};
 
     for (int b = blockIdx.x; b < P.batch; b += gridDim.x) {
+        if (P.done && P.done[b]) continue;                           // multi-launch SQP loop: this problem has converged
         // ---- load inputs ----
         for (int t = tid; t < nz; t += NT) M.xu[t] = P.xu_in[(size_t)b * nz + t];
         if (tid < 6) M.xu[nz + tid] = T(0);                          // padded u_{N-1}
@@ -1124,7 +1134,7 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
         }
         if (tid < 12) M.x0[tid] = P.x0 ? P.x0[(size_t)b * 12 + tid] : T(0);
         if (tid < 6) s_fext[tid] = P.fext ? P.fext[(size_t)b * 6 + tid] : T(0);
-        if (P.mode == MODE_LINESEARCH || P.mode == MODE_MERIT) {
+        if (P.mode == MODE_LINESEARCH || P.mode == MODE_MERIT || P.mode == MODE_STEP) {
             for (int t = tid; t < nz; t += NT) M.z[t] = P.xu_full[(size_t)b * nz + t];
             if (tid < 6) M.z[nz + tid] = T(0);
         }
@@ -1150,14 +1160,34 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
 
         int qp_iters = 0, n_ls = 0, n_steps = 0, status = 0;
         T alphas[2] = {T(0), T(0)}, steps[2] = {T(0), T(0)};
-        T merit_final = T(0), merit_first = T(0);
-        for (int qp = 0; qp < P.max_qp; ++qp) {
-            qp_iters = qp + 1;
+        T merit_final = T(0), merit_first = T(0), qp_its[2] = {T(0), T(0)};
+        const bool step_mode = (P.mode == MODE_STEP);
+        const int qoff = step_mode ? P.qp_index : 0;                 // MODE_STEP runs ONE pass: number qp_index
+        if (step_mode && qoff > 0 && P.stats) {                      // the record so far (written by the previous pass)
+            const T* st = P.stats + (size_t)b * 12;
+            n_ls = (int)st[1]; n_steps = (int)st[2]; status = (int)st[3];
+            alphas[0] = st[4]; steps[0] = st[6]; steps[1] = st[7]; merit_first = st[9]; qp_its[0] = st[10];
+        }
+        if (step_mode && P.qp_info && qoff < 2) qp_its[qoff] = P.qp_info[(size_t)b * 4];
+        for (int qp = 0; qp < (step_mode ? 1 : P.max_qp); ++qp) {
+            qp_iters = qp + qoff + 1;
             if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 0] = clock64();
-            if (P.mode != MODE_LINESEARCH) {
-                phase_setup<T, NT>(rob, P, M, W, fext, P.mode == MODE_DUMP, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
+            if (P.mode != MODE_LINESEARCH && !step_mode) {
+                phase_setup<T, NT>(rob, P, M, W, fext, P.mode == MODE_DUMP || P.mode == MODE_EXPORT, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 1] = clock64();
                 if (P.mode == MODE_DUMP) { dump_qp<T, BlockRecLayout>(P, M, b); break; }
+                if (P.mode == MODE_EXPORT) {
+                    T* o = P.blk_out + (size_t)b * N * QB_STRIDE;
+                    for (int t = tid; t < N * QB_STRIDE; t += NT) {
+                        const int k = t / QB_STRIDE, e = t - QB_STRIDE * k;
+                        const T* kr = M.kr + (size_t)KR_STRIDE * k;
+                        T v = T(0);
+                        if (e >= QB_COST) { if (e < QB_COST + COST_STRIDE) v = M.cost[COST_STRIDE * k + e - QB_COST]; }
+                        else if (k < N - 1) v = e < QB_GV ? kr[KR_GQ + e] : (e < QB_CV ? kr[KR_GV + e - QB_GV] : (e < QB_HM ? kr[KR_CV + e - QB_CV] : kr[KR_S + e - QB_HM]));
+                        o[t] = v;
+                    }
+                    break;
+                }
                 {
                     long long* pr = (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr;
                     long long tc = 0;
@@ -1198,9 +1228,9 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
             if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 3] = clock64();
             const T alpha = s_alpha;
             merit_final = s_merit_acc;
-            if (qp == 0) merit_first = s_merits[0];
+            if (qp + qoff == 0) merit_first = s_merits[0];
             if (s_flag) status = 2;
-            if (qp < 2) alphas[qp] = alpha;
+            if (qp + qoff < 2) alphas[qp + qoff] = alpha;
             ++n_ls;
             if (P.mode == MODE_LINESEARCH) {
                 if (tid == 0) P.alpha_out[b] = alpha;
@@ -1210,8 +1240,10 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
             if (alpha == T(0)) {
                 // src/osqp_sqp.py:81-82 `continue`: the next pass would re-solve the identical QP and, with an
                 // exact QP solve, reach the same alpha = 0; the remaining passes are skipped but still counted.
+                // (MODE_STEP: the QP solver is iterative and warm-started, the next pass really re-solves, as the reference does)
                 if (status == 0) status = 1;
-                for (int q2 = qp + 1; q2 < P.max_qp; ++q2) { if (q2 < 2) alphas[q2] = T(0); ++n_ls; qp_iters = q2 + 1; }
+                if (!step_mode)
+                    for (int q2 = qp + 1; q2 < P.max_qp; ++q2) { if (q2 < 2) alphas[q2] = T(0); ++n_ls; qp_iters = q2 + 1; }
                 break;
             }
             __syncthreads();
@@ -1235,15 +1267,18 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
             if (n_steps < 2) steps[n_steps] = stepsize;
             ++n_steps;
             __syncthreads();
-            if (stepsize < P.step_tol) break;
+            if (stepsize < P.step_tol) {
+                if (step_mode && P.done && tid == 0) P.done[b] = 1;
+                break;
+            }
         }
-        if (P.mode == MODE_SOLVE) {
+        if (P.mode == MODE_SOLVE || step_mode) {
             for (int t = tid; t < nz; t += NT) P.xu_out[(size_t)b * nz + t] = M.xu[t];
             if (P.stats && tid == 0) {
                 T* st = P.stats + (size_t)b * 12;
                 st[0] = T(qp_iters); st[1] = T(n_ls); st[2] = T(n_steps); st[3] = T(status);
                 st[4] = alphas[0]; st[5] = alphas[1]; st[6] = steps[0]; st[7] = steps[1];
-                st[8] = merit_final; st[9] = merit_first; st[10] = T(0); st[11] = T(0);
+                st[8] = merit_final; st[9] = merit_first; st[10] = qp_its[0]; st[11] = qp_its[1];
             }
         }
         __syncthreads();

@@ -43,7 +43,12 @@ def _numel(x):
 
 class Engine:
     def __init__(self, model=None, N=32, dt=0.01, dQ_cost=0.01, R_cost=1e-5, QN_cost=100.0, regularize=True, eps=1.0,
-                 batch=1, dtype="fp64", device=0, max_qp=2, mu=10.0, step_tol=1e-3, threads=0, cluster=0):
+                 batch=1, dtype="fp64", device=0, max_qp=2, mu=10.0, step_tol=1e-3, threads=0, cluster=0,
+                 qp_mode="exact", limits=False, admm=None):
+        """qp_mode: 'exact' (block recursion, default) or 'osqp' (the reference's regime: warm-started ADMM at eps 1e-3,
+        include/indy7_b200.h: i7_qp_mode).  limits=True adds the URDF position / velocity / effort limits of `model` as
+        inequality rows of every QP (needs qp_mode='osqp').  admm: optional dict overriding rho, rho_u, sigma, alpha,
+        eps_abs, eps_rel, max_iter, check."""
         self.lib = _lib.load()
         self._pinned = {}
         if model is None:
@@ -52,6 +57,9 @@ class Engine:
             raise TypeError("model must be an indy7_mpc_b200.model.RobotModel (use load_robot_model)")
         if dtype not in ("fp64", "fp32"):
             raise ValueError("dtype must be 'fp64' or 'fp32'")
+        if qp_mode not in ("exact", "osqp"):
+            raise ValueError("qp_mode must be 'exact' or 'osqp'")
+        self.qp_mode, self.limits = qp_mode, bool(limits)
         self.model = model
         self.N, self.batch, self.dtype = int(N), int(batch), dtype
         self.np_dtype = np.float64 if dtype == "fp64" else np.float32
@@ -65,13 +73,18 @@ class Engine:
         cfg.dt, cfg.dQ_cost, cfg.R_cost, cfg.QN_cost, cfg.eps = float(dt), float(dQ_cost), float(R_cost), float(QN_cost), float(eps)
         cfg.regularize, cfg.max_qp, cfg.mu, cfg.step_tol, cfg.threads = int(bool(regularize)), int(max_qp), float(mu), float(step_tol), int(threads)
         cfg.cluster = int(cluster)      # 0 auto, 1 one CTA per problem, 2|4|8 cluster of that many CTAs per problem (latency forms)
+        cfg.qp_mode, cfg.limits = (_lib.I7_QP_OSQP if qp_mode == "osqp" else _lib.I7_QP_EXACT), int(bool(limits))
+        for k, v in (admm or {}).items():
+            if k not in ("rho", "rho_u", "sigma", "alpha", "eps_abs", "eps_rel", "max_iter", "check"):
+                raise ValueError(f"unknown ADMM setting {k!r}")
+            setattr(cfg, "admm_" + k, int(v) if k in ("max_iter", "check") else float(v))
         cfg.model = model.to_c()
         self._h = C.c_void_p()
         rc = self.lib.i7_create(C.byref(cfg), C.byref(self._h))
         if rc != 0:
             msg = self.lib.i7_last_error(None).decode()
             self._h = None
-            if rc == 1:
+            if rc in (1, 4):
                 raise ValueError(f"i7_create: {msg}")
             raise RuntimeError(f"i7_create failed (status {rc}): {msg}")
 
@@ -186,6 +199,14 @@ class Engine:
         y, p_y = self._out((B, 12 * self.N), xu, keep) if want_duals else (None, None)
         self._check(self.lib.i7_solve_qp(self._h, B, p_xu, p_x0, p_g, gs, p_out, p_y, self._stream(xu)))
         return (out, y) if want_duals else out
+
+    def qp_state(self, batch=None):
+        """qp_mode 'osqp': (x (B, 18N-6), y (B, 12N), y_lim (B, 18N-18), info (B, 4) = [iterations, r_prim, r_dual,
+        status]) of the ADMM solver after the latest solve / solve_qp (i7_qp_state)."""
+        B = int(batch) if batch is not None else self.batch
+        x = np.empty((B, self.nz)); y = np.empty((B, 12 * self.N)); yl = np.empty((B, self.nz - 12)); info = np.empty((B, 4))
+        self._check(self.lib.i7_qp_state(self._h, B, _addr(x), _addr(y), _addr(yl), _addr(info), None))
+        return x, y, yl, info
 
     def dump_qp(self, xu, x0, goals):
         B = self._batch_of(xu)

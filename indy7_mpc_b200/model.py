@@ -87,6 +87,12 @@ class RobotModel:
             m.mass[i] = float(self.mass[i])
         for a in range(3):
             m.gravity[a] = float(g[a])
+        big = 1e30                                   # "no limit" (URDF joints without a <limit> element)
+        for i in range(6):
+            m.q_min[i] = float(max(self.lowerPositionLimit[i], -big))
+            m.q_max[i] = float(min(self.upperPositionLimit[i], big))
+            m.v_max[i] = float(min(self.velocityLimit[i], big))
+            m.u_max[i] = float(min(self.effortLimit[i], big))
         return m
 
 

@@ -1,8 +1,11 @@
 """``OSQPSolver`` with the reference's constructor, attributes and methods (src/osqp_solver.py:6-155), backed by
 the sm_100a kernels through the C ABI.  No Pinocchio, no OSQP, no CPU fallback.
 
-The QP of one SQP iteration is solved exactly on the GPU (block recursion over the knots), so the object returned
-by ``setup_and_solve_qp`` carries the solution OSQP converges to; ``.info.status`` is always 'solved'.
+By default (``qp_mode='exact'``) the QP of one SQP iteration is solved exactly on the GPU (block recursion over the
+knots), so the object returned by ``setup_and_solve_qp`` carries the solution OSQP converges to and ``.info.status`` is
+always 'solved'.  ``qp_mode='osqp'`` runs the reference's own regime instead — OSQP's ADMM at eps_abs = eps_rel = 1e-3,
+warm-started between calls like the OSQP object of src/osqp_solver.py:39-41 — and is what ``limits=True`` (URDF joint
+position / velocity / effort limits as inequality rows; not in the reference QP) needs.
 """
 import numpy as np
 
@@ -11,15 +14,15 @@ from .model import RobotModel
 
 
 class QPResult:
-    def __init__(self, x, y=None, iters=1):
+    def __init__(self, x, y=None, iters=1, status="solved", pri_res=0.0, dua_res=0.0):
         self.x = x
         self.y = y
-        self.info = type("info", (), dict(status="solved", iter=iters))()
+        self.info = type("info", (), dict(status=status, iter=iters, pri_res=pri_res, dua_res=dua_res))()
 
 
 class OSQPSolver:
     def __init__(self, model, dt=0.01, N=32, dQ_cost=0.01, R_cost=1e-5, QN_cost=100, regularize=True, eps=1,
-                 dtype="fp64", device=0):
+                 dtype="fp64", device=0, qp_mode="exact", limits=False, admm=None):
         if not isinstance(model, RobotModel):
             raise TypeError("model must come from indy7_mpc_b200.load_robot_model")
         self.model = model
@@ -33,7 +36,9 @@ class OSQPSolver:
         self.dQ_cost, self.R_cost, self.QN_cost = dQ_cost, R_cost, QN_cost
         self.regularize, self.eps = regularize, eps
         self.engine = Engine(model, N=N, dt=dt, dQ_cost=dQ_cost, R_cost=R_cost, QN_cost=QN_cost,
-                             regularize=regularize, eps=eps, batch=1, dtype=dtype, device=device)
+                             regularize=regularize, eps=eps, batch=1, dtype=dtype, device=device, qp_mode=qp_mode,
+                             limits=limits, admm=admm)
+        self.qp_mode, self.limits = qp_mode, bool(limits)
         self.l = np.zeros(self.N * self.nx)
         self.g = np.zeros(self.traj_len)
         self.Pdata = np.zeros(27 * N + 6 * (N - 1))
@@ -64,6 +69,11 @@ class OSQPSolver:
         xu, xs, eepos_g = self._check(xu, xs, eepos_g)
         self._sync_weights()
         z, y = self.engine.solve_qp(xu, xs, eepos_g, want_duals=True)
+        if self.qp_mode == "osqp":
+            _, _, yl, info = self.engine.qp_state(1)
+            yy = np.concatenate([np.asarray(y[0], float), yl[0]]) if self.limits else np.asarray(y[0], float)
+            return QPResult(np.asarray(z[0], float), yy, int(info[0, 0]),
+                            "solved" if info[0, 3] == 0 else "maximum iterations reached", float(info[0, 1]), float(info[0, 2]))
         return QPResult(np.asarray(z[0], float), np.asarray(y[0], float))
 
     def eepos(self, q):

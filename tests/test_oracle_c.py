@@ -52,7 +52,7 @@ def test_c_admm_meets_osqp_tolerances(oracle_model):
         assert rel(z, ref) < 1e-3
 
 
-URDF_LIMITS = (np.full(6, -3.0543261909900767), np.full(6, 3.0543261909900767), np.array([2.6179938779914944] * 3 + [3.141592653589793] * 3),
+URDF_LIMITS = (np.array([-3.0543261909900767] * 5 + [-3.7524578917878086]), np.array([3.0543261909900767] * 5 + [3.7524578917878086]), np.array([2.6179938779914944] * 3 + [3.141592653589793] * 3),
                np.array([431.97, 431.97, 197.23, 79.79, 79.79, 79.79]))        # description/indy7.urdf:203-238
 TIGHT_LIMITS = (np.full(6, -2.0), np.full(6, 2.0), np.full(6, 0.8), np.array([60.0, 60.0, 30.0, 8.0, 8.0, 8.0]))
 
