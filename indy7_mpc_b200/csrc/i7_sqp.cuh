@@ -72,8 +72,13 @@ constexpr int MP_STRIDE = WP_STRIDE;      // 97: axes S, world inertias, bias (i
 // Riccati work area (first in the layouts: 16-byte aligned)
 constexpr int WK_SIZE = 296;   // two sweep-state blocks (SB_*), see riccati_sweep
 
+// SPILL form (long horizons: the records of all knots do not fit an SM): the records live in a global workspace, but
+// they are BUILT in a shared-memory tile of TILE_K knots at a time (the setup makes ~10 passes over a record and uses it
+// as scratch: from L2 that costs 3.6x per knot) and copied out once; the same tile is the scratch of the line-search
+// points (MP_STRIDE numbers each), evaluated TILE_PTS at a time.
+constexpr int TILE_K = 20;      // 6380 numbers: 65 line-search points, two windows of a 128-knot horizon
 struct Layout {
-    int xu, z, goals, x0, cost, work, ls, reg, reg_size, total;
+    int xu, z, goals, x0, cost, work, ls, reg, reg_size, tile, total;
 };
 __host__ __device__ inline Layout make_layout(int N, bool spill) {
     Layout L;
@@ -84,10 +89,14 @@ __host__ __device__ inline Layout make_layout(int N, bool spill) {
     L.x0 = o; o += 12;
     L.cost = o; o += COST_STRIDE * N;
     L.z = o; o += 18 * N;            // z and ls are adjacent: during setup (both dead) they hold the aux side array
-    L.ls = o; o += (4 * 5 * N > 400 ? 4 * 5 * N : 400) + 16;
+    // line-search terms of up to 5 candidates per wave; SPILL form: one candidate at a time (its waves are serial anyway:
+    // the points of ONE candidate already exceed the scratch tile), so only the 6N of phase_controls / 4N terms remain
+    L.ls = o; o += (spill ? (6 * N > 400 ? 6 * N : 400) : (4 * 5 * N > 400 ? 4 * 5 * N : 400)) + 16;
     L.reg = o;
     L.reg_size = KR_STRIDE * N;
+    L.tile = o;
     if (!spill) o += L.reg_size;
+    else o += TILE_K * KR_STRIDE;
     L.total = o;
     return L;
 }
@@ -543,6 +552,8 @@ template <typename T, bool SPILL> struct RicLocal {
     I7_DEV const T* ck(int k) const { return smem_base<T>() + o_cost + COST_STRIDE * k; }
     I7_DEV T* gain(int k) const { return (SPILL ? krg : smem_base<T>() + o_kr) + KR_STRIDE * k + KR_SG; }
     static I7_DEV T ld(const T* p) { return *p; }
+    static constexpr bool kStageGains = SPILL;
+    int o_stage, stage_len;      // SPILL: shared-memory region the gains are staged through for the roll-out
 };
 template <typename T> struct RicGlobal {
     const T* ric; int o_gains;
@@ -551,6 +562,7 @@ template <typename T> struct RicGlobal {
     I7_DEV const T* ck(int k) const { return ric + RIC_STRIDE * k + RIC_COST; }
     I7_DEV T* gain(int k) const { return smem_base<T>() + o_gains + GAIN_STRIDE * k; }
     static I7_DEV T ld(const T* p) { return __ldcg(p); }
+    static constexpr bool kStageGains = false;
 };
 static_assert(KR_D == KR_SG + 72, "the gains (Kw | kw) must be contiguous in the record");
 
@@ -797,46 +809,69 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, int o_work, 
     // registers, replicated in every lane; lane r (mod 6) evaluates row r of the gain and the six results are
     // exchanged with shuffles, so the serial chain per stage is 3 FMAs + 2 adds + one shuffle (no shared-memory
     // round trip); the gain row of the next stage is fetched while the current one is applied.
-    if (tid < 32) {
+    {
         const int row = tid % 6;
-        T x[12], g[12], ff, my_q = x0[row], my_v = x0[6 + row];
+        T x[12], my_q = x0[row], my_v = x0[6 + row];
 #pragma unroll
         for (int i = 0; i < 12; ++i) x[i] = x0[i];
         if (tid < 12) z[tid] = x0[tid];
-        {
-            const T* G = src.gain(0);
-#pragma unroll
-            for (int i = 0; i < 12; ++i) g[i] = G[6 * i + row];
-            ff = G[72 + row];
-        }
-        for (int k = 0; k < N - 1; ++k) {
-            T gn[12], ffn;
+        // stages [ka, kb) by warp 0; gp(k) = gains of stage k; the gain row of the next stage is fetched while the
+        // current one is applied
+        auto roll = [&](int ka, int kb, auto gp) {
+            T g[12], ff;
             {
-                const T* G = src.gain(k + 1 < N - 1 ? k + 1 : k);
+                const T* G = gp(ka);
 #pragma unroll
-                for (int i = 0; i < 12; ++i) gn[i] = G[6 * i + row];
-                ffn = G[72 + row];
+                for (int i = 0; i < 12; ++i) g[i] = G[6 * i + row];
+                ff = G[72 + row];
             }
-            T a0 = ff, a1 = T(0), a2 = T(0), a3 = T(0);
+            for (int k = ka; k < kb; ++k) {
+                T gn[12], ffn;
+                {
+                    const T* G = gp(k + 1 < kb ? k + 1 : k);
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                a0 += g[i] * x[i];
-                a1 += g[3 + i] * x[3 + i];
-                a2 += g[6 + i] * x[6 + i];
-                a3 += g[9 + i] * x[9 + i];
+                    for (int i = 0; i < 12; ++i) gn[i] = G[6 * i + row];
+                    ffn = G[72 + row];
+                }
+                T a0 = ff, a1 = T(0), a2 = T(0), a3 = T(0);
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    a0 += g[i] * x[i];
+                    a1 += g[3 + i] * x[3 + i];
+                    a2 += g[6 + i] * x[6 + i];
+                    a3 += g[9 + i] * x[9 + i];
+                }
+                const T vn = (a0 + a1) + (a2 + a3);
+                my_q = my_q + dt * my_v;
+                my_v = vn;
+                if (tid < 6) { z[18 * (k + 1) + row] = my_q; z[18 * (k + 1) + 6 + row] = vn; }
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    x[i] = x[i] + dt * x[6 + i];
+                    x[6 + i] = __shfl_sync(0xffffffffu, vn, i);
+                }
+#pragma unroll
+                for (int i = 0; i < 12; ++i) g[i] = gn[i];
+                ff = ffn;
             }
-            const T vn = (a0 + a1) + (a2 + a3);
-            my_q = my_q + dt * my_v;
-            my_v = vn;
-            if (tid < 6) { z[18 * (k + 1) + row] = my_q; z[18 * (k + 1) + 6 + row] = vn; }
-#pragma unroll
-            for (int i = 0; i < 6; ++i) {
-                x[i] = x[i] + dt * x[6 + i];
-                x[6 + i] = __shfl_sync(0xffffffffu, vn, i);
+        };
+        if constexpr (Src::kStageGains) {
+            // the gains sit in the global workspace: an L2 round trip per stage would dominate this serial chain, so all
+            // threads copy them into the (idle) shared-memory tile, a chunk of stages at a time, and the chain runs there
+            T* ring = sm + src.o_stage;
+            const int cap = src.stage_len / GAIN_LEN;
+            for (int c0 = 0; c0 < N - 1; c0 += cap) {
+                const int nst = N - 1 - c0 < cap ? N - 1 - c0 : cap;
+                __syncthreads();
+                for (int t = tid; t < nst * GAIN_LEN; t += NT) {
+                    const int k = t / GAIN_LEN, e = t - GAIN_LEN * k;
+                    ring[t] = src.gain(c0 + k)[e];
+                }
+                __syncthreads();
+                if (tid < 32) roll(c0, c0 + nst, [&](int k) { return (const T*)(ring + GAIN_LEN * (k - c0)); });
             }
-#pragma unroll
-            for (int i = 0; i < 12; ++i) g[i] = gn[i];
-            ff = ffn;
+        } else {
+            if (tid < 32) roll(0, N - 1, [&](int k) { return (const T*)src.gain(k); });
         }
     }
     __syncthreads();
@@ -1114,7 +1149,7 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
     M.aux = M.z; M.pair = nullptr;
     {
         int cap = L.reg_size / (MP_STRIDE * N);
-        M.merit_cap = cap > 5 ? 5 : (cap < 1 ? 1 : cap);
+        M.merit_cap = SPILL ? 1 : (cap > 5 ? 5 : (cap < 1 ? 1 : cap));
     }
     __shared__ T s_merits[9];
     __shared__ T s_alpha;
@@ -1144,6 +1179,13 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
         if (P.mode == MODE_MERIT) {
             // merit terms of xu; the initial-state term is taken against the reference iterate z
             T* comps = M.ls;
+            if constexpr (SPILL) {
+                constexpr int TILE_PTS = (TILE_K * KR_STRIDE) / MP_STRIDE;
+                for (int k0 = 0; k0 < N; k0 += TILE_PTS) {
+                    const Win Wm{k0, N - 1 - k0 < TILE_PTS ? N - 1 - k0 : TILE_PTS, N - k0 < TILE_PTS ? N - k0 : TILE_PTS};
+                    merit_points<T, NT>(rob, P, M, Wm, sm + L.tile, M.xu, M.xu, fext, 0, 1, comps, 0);
+                }
+            } else
             merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.xu, fext, 0, 1, comps, 0);
             merit_reduce<T, NT, false>(P, M.xu, M.xu, 0, 1, comps, 0, s_merits, M.work);
             if (tid == 0) {
@@ -1173,7 +1215,20 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
             qp_iters = qp + qoff + 1;
             if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 0] = clock64();
             if (P.mode != MODE_LINESEARCH && !step_mode) {
-                phase_setup<T, NT>(rob, P, M, W, fext, P.mode == MODE_DUMP || P.mode == MODE_EXPORT, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
+                if constexpr (SPILL) {
+                    for (int k0 = 0; k0 < N; k0 += TILE_K) {
+                        const Win Wt{k0, N - 1 - k0 < TILE_K ? N - 1 - k0 : TILE_K, N - k0 < TILE_K ? N - k0 : TILE_K};
+                        Ptrs<T> Mt = M;
+                        Mt.kr = sm + L.tile; Mt.cost = M.cost + COST_STRIDE * k0;
+                        phase_setup<T, NT>(rob, P, Mt, Wt, fext, P.mode == MODE_DUMP || P.mode == MODE_EXPORT,
+                                           (P.prof && qp == 0 && k0 == 0) ? P.prof + (size_t)b * 32 : nullptr);
+                        T* dst = krg + (size_t)KR_STRIDE * k0;
+                        for (int t = tid; t < Wt.nc * KR_STRIDE; t += NT) dst[t] = Mt.kr[t];
+                        __syncthreads();
+                    }
+                } else {
+                    phase_setup<T, NT>(rob, P, M, W, fext, P.mode == MODE_DUMP || P.mode == MODE_EXPORT, (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr);
+                }
                 if (P.prof && tid == 0) P.prof[(size_t)b * 32 + 5 * qp + 1] = clock64();
                 if (P.mode == MODE_DUMP) { dump_qp<T, BlockRecLayout>(P, M, b); break; }
                 if (P.mode == MODE_EXPORT) {
@@ -1191,7 +1246,7 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
                 {
                     long long* pr = (P.prof && qp == 0) ? P.prof + (size_t)b * 32 : nullptr;
                     long long tc = 0;
-                    riccati_sweep<T, NT, RicLocal<T, SPILL>>(P, L.work, L.z, L.x0, L.xu, RicLocal<T, SPILL>{L.reg, L.cost, krg}, pr);
+                    riccati_sweep<T, NT, RicLocal<T, SPILL>>(P, L.work, L.z, L.x0, L.xu, RicLocal<T, SPILL>{L.reg, L.cost, krg, L.tile, TILE_K * KR_STRIDE}, pr);
                     if (pr && tid == 0) tc = clock64();
                     phase_controls<T, NT, SPILL>(P, L.z, L.ls, L.reg, krg, W, nullptr);
                     if (pr && tid == 0) pr[13] = clock64() - tc;
@@ -1211,7 +1266,17 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
                 if (tid == 0) { s_alpha = T(0); s_flag = 0; }
                 while (c0 < 9) {
                     int nc = 9 - c0 < M.merit_cap ? 9 - c0 : M.merit_cap;
-                    merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, nc, M.ls, 0);
+                    if constexpr (SPILL) {
+                        constexpr int TILE_PTS = (TILE_K * KR_STRIDE) / MP_STRIDE;
+                        const int nwin = (N + TILE_PTS - 1) / TILE_PTS, wlen = (N + nwin - 1) / nwin;    // equal windows
+                        for (int ci = 0; ci < nc; ++ci)
+                            for (int k0 = 0; k0 < N; k0 += wlen) {
+                                const Win Wm{k0, N - 1 - k0 < wlen ? N - 1 - k0 : wlen, N - k0 < wlen ? N - k0 : wlen};
+                                merit_points<T, NT>(rob, P, M, Wm, sm + L.tile, M.xu, M.z, fext, c0 + ci, 1, M.ls, ci);
+                            }
+                    } else {
+                        merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, nc, M.ls, 0);
+                    }
                     merit_reduce<T, NT, false>(P, M.xu, M.z, c0, nc, M.ls, 0, s_merits, nullptr);
                     if (tid == 0 && s_alpha == T(0)) {
                         if (!(s_merits[0] == s_merits[0])) s_flag = 1;
