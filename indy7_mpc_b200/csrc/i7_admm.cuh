@@ -42,14 +42,18 @@ struct AdmmParams {
     T* info;          // batch x 4: iterations, primal residual, dual residual, status (0 solved, 1 max_iter)
     T* fac;           // workspace: batch x N x FAC_STRIDE
     const int* done;  // optional skip flags
+    long long* prof;  // optional: per problem 32 cycle counters (debugging aid): [0] factorisation, [1] vectors, [2..10] steps 1-9 summed over the iterations
     int N, batch;
     T dt;
     AdmmSettings S;
 };
 
-constexpr int ADMM_NT = 256;
+constexpr int ADMM_NT = 128;     // two CTAs per SM (registers: the in-register 18 x 18 factorisation), three where shared memory allows
 constexpr int FAC_LINV = 0, FAC_MT = 324, FAC_FT = 648, FAC_STRIDE = 864;
-__host__ __device__ inline int admm_smem_len(int N) { return 156 * N + 2 * 324 + 2 * 216 + 108 + 16 + 64; }
+// shared memory: the vectors (156 N), the stage scratch of the factorisation, and — while it fits — the QP blocks
+// (QB_STRIDE N), which every iteration reads twice (A x~ and A' t)
+__host__ __device__ inline int admm_smem_len(int N, bool blocks) { return 156 * N + 2 * 324 + 2 * 216 + 108 + 16 + 64 + (blocks ? QB_STRIDE * N : 0); }
+constexpr int ADMM_BLOCKS_IN_SMEM_MAX_N = 64;
 
 // element (r, c) of G^ = [Gq Gv Hm] (6 x 18) in a QB block
 template <typename T> I7_DEV T ghat(const T* blk, int r, int c) {
@@ -57,7 +61,7 @@ template <typename T> I7_DEV T ghat(const T* blk, int r, int c) {
 }
 
 template <typename T>
-__global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ AdmmParams<T> P) {
+__global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant__ AdmmParams<T> P) {
     constexpr int NT = ADMM_NT;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* sm = reinterpret_cast<T*>(smem_raw);
@@ -83,11 +87,18 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
     T* s_Gh = s_Gn + 216;        // 108  G^_k (6 x 18)
     T* s_ck = s_Gh + 108;        // 16   cost terms of the knot
     T* s_red = s_ck + 16;        // 64   reduction scratch
+    T* s_blk = s_red + 64;       // QB_STRIDE N  the QP blocks (short horizons only)
+    const bool blk_smem = N <= ADMM_BLOCKS_IN_SMEM_MAX_N;
     __shared__ int s_stop;
 
     for (int b = blockIdx.x; b < P.batch; b += gridDim.x) {
         if (P.done && P.done[b]) continue;
         const T* blk = P.blk + (size_t)b * N * QB_STRIDE;
+        if (blk_smem) {
+            for (int t = tid; t < N * QB_STRIDE; t += NT) s_blk[t] = blk[t];
+            blk = s_blk;
+            __syncthreads();
+        }
         T* fac = P.fac + (size_t)b * N * FAC_STRIDE;
         const T* xu = P.xu + (size_t)b * nz;
         const bool lim = S.limits != 0;
@@ -95,11 +106,15 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
         auto lo_of = [&](int e) { return e < 6 ? T(S.qmin[e]) : (e < 12 ? T(-S.vmax[e - 6]) : T(-S.umax[e - 12])); };
         auto hi_of = [&](int e) { return e < 6 ? T(S.qmax[e]) : (e < 12 ? T(S.vmax[e - 6]) : T(S.umax[e - 12])); };
 
+        long long* prof = P.prof ? P.prof + (size_t)b * 32 : nullptr;
+        long long pacc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, ptt = prof ? clock64() : 0;
+// every thread keeps the counters (a branch on tid == 0 here would leave warp 0 diverged in front of its shuffle chains)
+#define I7_ACC(i) do { if (prof) { const long long n_ = clock64(); pacc[i] += n_ - ptt; ptt = n_; } } while (0)
         // ---------------------------------------------------------------- factorisation ----------------
         for (int k = 0; k < N; ++k) {
             const T* bk = blk + (size_t)k * QB_STRIDE;
             if (tid < 108) s_Gh[tid] = k < N - 1 ? ghat<T>(bk, tid / 18, tid % 18) : T(0);
-            if (tid >= 128 && tid < 128 + 9) s_ck[tid - 128] = bk[QB_COST + tid - 128];
+            if (tid >= 112 && tid < 112 + 9) s_ck[tid - 112] = bk[QB_COST + tid - 112];
             __syncthreads();
             // pivot block D = H_kk - G_{k-1}' G_{k-1} (x x part), lower triangle
             for (int e = tid; e < 324; e += NT) {
@@ -129,6 +144,7 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
             __syncthreads();
             // Cholesky D = L L' and X = L^-1 by warp 0, in registers: lane i owns row i of L and column i of X
             if (warp == 0) {
+                __syncwarp();
                 T A[18], X[18], rr[18];
 #pragma unroll
                 for (int c = 0; c < 18; ++c) A[c] = (lane < 18 && c <= lane) ? s_D[18 * lane + c] : T(0);
@@ -198,6 +214,7 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
             __syncthreads();
         }
 
+        I7_ACC(0);
         // ---------------------------------------------------------------- vectors ----------------------
         for (int i = tid; i < nv; i += NT) {
             const int k = i / 18, e = i - 18 * k;
@@ -252,6 +269,7 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
         for (int i = tid; i < nv; i += NT) s_zl[i] = s_x[i];
         __syncthreads();
 
+        I7_ACC(1);
         int it = 0, status = 1;
         T rp = T(0), rd = T(0);
         while (it < S.max_iter) {
@@ -259,6 +277,7 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
             // (1) t = rho z - y
             for (int r = tid; r < nr; r += NT) s_t[r] = rho * s_z[r] - s_y[r];
             __syncthreads();
+            I7_ACC(2);
             // (2) right-hand side
             for (int i = tid; i < nv; i += NT) {
                 const int k = i / 18, e = i - 18 * k;
@@ -270,35 +289,39 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
                 s_b1[i] = v;
             }
             __syncthreads();
+            I7_ACC(3);
             // (3) a = L^-1 r
             for (int i = tid; i < nv; i += NT) {
                 const int k = i / 18, e = i - 18 * k;
+                // full 18-term rows (the stored factor has explicit zeros above the diagonal): 18 independent loads in
+                // flight instead of a dependent load-FMA chain of data-dependent length
                 const T* Li = fac + (size_t)k * FAC_STRIDE + FAC_LINV + 18 * e;
                 const T* rk = s_b1 + 18 * k;
-                T a0 = T(0), a1 = T(0);
-                for (int c = 0; c + 1 <= e; c += 2) { a0 += Li[c] * rk[c]; a1 += Li[c + 1] * rk[c + 1]; }
-                if (!(e & 1)) a0 += Li[e] * rk[e];
-                s_b2[i] = a0 + a1;
+                T lv[18];
+#pragma unroll
+                for (int c = 0; c < 18; ++c) lv[c] = Li[c];
+                T a0 = T(0), a1 = T(0), a2 = T(0);
+#pragma unroll
+                for (int c = 0; c < 18; c += 3) { a0 += lv[c] * rk[c]; a1 += lv[c + 1] * rk[c + 1]; a2 += lv[c + 2] * rk[c + 2]; }
+                s_b2[i] = a0 + (a1 + a2);
             }
             __syncthreads();
-            // (4) forward chain  w_k = a_k - M_k w_{k-1}   (warp 0; lane i = component i)
+            I7_ACC(4);
+            // (4) forward chain  w_k = a_k - M_k w_{k-1}   (warp 0; lane i = component i).  The stage matrices are held
+            //     in three register buffers used in rotation (static renaming, no moves): the one consumed two stages from
+            //     now is being fetched while the current one is applied (an L2 round trip is ~2.5 stages of this chain)
             if (warp == 0) {
                 const int li = lane < 18 ? lane : 0;
-                T m[18], mn[18];
+                T mA[18], mB[18], mC[18];
                 T w = s_b2[li];
-                if (N > 1) {
-                    const T* Mk = fac + (size_t)1 * FAC_STRIDE + FAC_MT;
+                auto load = [&](T (&m)[18], int k) {
+                    const T* Mk = fac + (size_t)(k < N ? k : N - 1) * FAC_STRIDE + FAC_MT + li;
 #pragma unroll
-                    for (int j = 0; j < 18; ++j) m[j] = Mk[18 * j + li];
-                }
-                for (int k = 1; k < N; ++k) {
-                    const T ak = s_b2[18 * k + li];
-                    if (k + 1 < N) {
-                        const T* Mk = fac + (size_t)(k + 1) * FAC_STRIDE + FAC_MT;
-#pragma unroll
-                        for (int j = 0; j < 18; ++j) mn[j] = Mk[18 * j + li];
-                    }
-                    T a0 = ak, a1 = T(0), a2 = T(0);
+                    for (int j = 0; j < 18; ++j) m[j] = Mk[18 * j];
+                };
+                auto stage = [&](const T (&m)[18], int k) {
+                    __syncwarp();
+                    T a0 = s_b2[18 * k + li], a1 = T(0), a2 = T(0);
 #pragma unroll
                     for (int j = 0; j < 18; j += 3) {
                         a0 -= m[j] * __shfl_sync(0xffffffffu, w, j);
@@ -307,41 +330,46 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
                     }
                     w = a0 + (a1 + a2);
                     if (lane < 18) s_b2[18 * k + lane] = w;
-#pragma unroll
-                    for (int j = 0; j < 18; ++j) m[j] = mn[j];
+                };
+                load(mA, 1); load(mB, 2);
+                for (int k = 1; k < N; k += 3) {
+                    load(mC, k + 2); stage(mA, k);
+                    if (k + 1 >= N) break;
+                    load(mA, k + 3); stage(mB, k + 1);
+                    if (k + 2 >= N) break;
+                    load(mB, k + 4); stage(mC, k + 2);
                 }
             }
             __syncthreads();
+            I7_ACC(5);
             // (5) c = L^-T w
             for (int i = tid; i < nv; i += NT) {
                 const int k = i / 18, e = i - 18 * k;
-                const T* Lk = fac + (size_t)k * FAC_STRIDE + FAC_LINV;
+                const T* Lk = fac + (size_t)k * FAC_STRIDE + FAC_LINV + e;
                 const T* wk = s_b2 + 18 * k;
-                T a0 = T(0), a1 = T(0);
-                int r = e;
-                for (; r + 1 < 18; r += 2) { a0 += Lk[18 * r + e] * wk[r]; a1 += Lk[18 * (r + 1) + e] * wk[r + 1]; }
-                if (r < 18) a0 += Lk[18 * r + e] * wk[r];
-                s_b1[i] = a0 + a1;
+                T lv[18];
+#pragma unroll
+                for (int r = 0; r < 18; ++r) lv[r] = Lk[18 * r];
+                T a0 = T(0), a1 = T(0), a2 = T(0);
+#pragma unroll
+                for (int r = 0; r < 18; r += 3) { a0 += lv[r] * wk[r]; a1 += lv[r + 1] * wk[r + 1]; a2 += lv[r + 2] * wk[r + 2]; }
+                s_b1[i] = a0 + (a1 + a2);
             }
             __syncthreads();
-            // (6) backward chain  x_k = c_k - F_k x_{k+1}[:12]   (warp 0)
+            I7_ACC(6);
+            // (6) backward chain  x_k = c_k - F_k x_{k+1}[:12]   (warp 0), same rotation of three register buffers
             if (warp == 0) {
                 const int li = lane < 18 ? lane : 0;
-                T f[12], fn[12];
+                T fA[12], fB[12], fC[12];
                 T xv = s_b1[18 * (N - 1) + li];
-                if (N > 1) {
-                    const T* Fk = fac + (size_t)(N - 2) * FAC_STRIDE + FAC_FT;
+                auto load = [&](T (&f)[12], int k) {
+                    const T* Fk = fac + (size_t)(k > 0 ? k : 0) * FAC_STRIDE + FAC_FT + li;
 #pragma unroll
-                    for (int j = 0; j < 12; ++j) f[j] = Fk[18 * j + li];
-                }
-                for (int k = N - 2; k >= 0; --k) {
-                    const T ck = s_b1[18 * k + li];
-                    if (k > 0) {
-                        const T* Fk = fac + (size_t)(k - 1) * FAC_STRIDE + FAC_FT;
-#pragma unroll
-                        for (int j = 0; j < 12; ++j) fn[j] = Fk[18 * j + li];
-                    }
-                    T a0 = ck, a1 = T(0), a2 = T(0);
+                    for (int j = 0; j < 12; ++j) f[j] = Fk[18 * j];
+                };
+                auto stage = [&](const T (&f)[12], int k) {
+                    __syncwarp();
+                    T a0 = s_b1[18 * k + li], a1 = T(0), a2 = T(0);
 #pragma unroll
                     for (int j = 0; j < 12; j += 3) {
                         a0 -= f[j] * __shfl_sync(0xffffffffu, xv, j);
@@ -350,11 +378,18 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
                     }
                     xv = a0 + (a1 + a2);
                     if (lane < 18) s_b1[18 * k + lane] = xv;
-#pragma unroll
-                    for (int j = 0; j < 12; ++j) f[j] = fn[j];
+                };
+                load(fA, N - 2); load(fB, N - 3);
+                for (int k = N - 2; k >= 0; k -= 3) {
+                    load(fC, k - 2); stage(fA, k);
+                    if (k - 1 < 0) break;
+                    load(fA, k - 3); stage(fB, k - 1);
+                    if (k - 2 < 0) break;
+                    load(fB, k - 4); stage(fC, k - 2);
                 }
             }
             __syncthreads();
+            I7_ACC(7);
             // (7) z~ = A x~ and the updates of the equality rows; (8) x and the limit rows
             for (int r = tid; r < nr; r += NT) {
                 const T zt = a_row(s_b1, r);
@@ -378,6 +413,7 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
                 s_x[i] = al * xt + (T(1) - al) * s_x[i];
             }
             __syncthreads();
+            I7_ACC(8);
             // (9) termination check (OSQP: every `check` iterations)
             if (it % S.check == 0) {
                 T m_rp = T(0), m_ax = T(0), m_z = T(0), m_rd = T(0), m_px = T(0), m_aty = T(0), m_q = T(0);
@@ -424,9 +460,12 @@ __global__ void __launch_bounds__(ADMM_NT) admm_kernel(const __grid_constant__ A
                 rp = s_red[56]; rd = s_red[57];
                 const int stop = s_stop;
                 __syncthreads();
+                I7_ACC(9);
                 if (stop) { status = 0; break; }
             }
         }
+        if (prof && tid == 0) for (int i = 0; i < 12; ++i) prof[i] = pacc[i];
+#undef I7_ACC
         // ---------------------------------------------------------------- results ----------------------
         for (int i = tid; i < nv; i += NT) {
             P.wx[(size_t)b * nv + i] = s_x[i];

@@ -17,7 +17,7 @@ cudaError_t smem_cap_admm(int optin_bytes, int* cap) {
     return cudaFuncSetAttribute(admm_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, *cap);
 }
 
-int admm_smem_elems(int N) { return admm_smem_len(N); }
+int admm_smem_elems(int N) { return admm_smem_len(N, N <= ADMM_BLOCKS_IN_SMEM_MAX_N); }
 int admm_fac_stride() { return FAC_STRIDE; }
 
 }  // namespace i7

@@ -460,7 +460,7 @@ i7_status run_osqp(i7_handle* h, const SqpCall& c, cudaStream_t s) {
         A.blk = (const T*)h->d_blk; A.xu = xu_lin; A.x0 = d_x0;
         A.wx = (T*)h->d_wx; A.wy = (T*)h->d_wy; A.wyl = (T*)h->d_wyl;
         A.z_out = z_out; A.y_out = y_out; A.info = (T*)h->d_qpinfo; A.fac = (T*)h->d_fac; A.done = done;
-        A.N = N; A.batch = c.batch; A.dt = h->cfg.dt; A.S = h->admm;
+        A.N = N; A.batch = c.batch; A.dt = h->cfg.dt; A.S = h->admm; A.prof = h->d_prof;
         I7_CUDA(h, i7::launch_admm(A, h->admm_smem_bytes, s));
         ++h->launches;
         return I7_OK;

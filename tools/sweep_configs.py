@@ -16,6 +16,8 @@ ap.add_argument("--warmup", type=int, default=5)
 ap.add_argument("--cases", default="1x32,16x32,32x32,64x32,148x32,512x32,1024x32,2048x32,4096x32,512x128")
 ap.add_argument("--dtypes", default="fp64,fp32")
 ap.add_argument("--threads", type=int, default=0)
+ap.add_argument("--qp-mode", default="exact", help="exact | osqp (the reference regime: warm-started ADMM at eps 1e-3)")
+ap.add_argument("--limits", action="store_true", help="URDF joint limits as inequality rows (osqp mode)")
 ap.add_argument("--cluster", type=int, default=0, help="kernel form: 0 auto, 1 CTA per problem, 2|4|8 clusters (multi-wave when the batch is not co-resident)")
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
@@ -25,7 +27,7 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 def run(B, N, dtype):
     tdt = torch.float64 if dtype == "fp64" else torch.float32
     wl = bench.make_workload(B, N)
-    eng = Engine(N=N, batch=B, dtype=dtype, threads=a.threads, cluster=a.cluster)
+    eng = Engine(N=N, batch=B, dtype=dtype, threads=a.threads, cluster=a.cluster, qp_mode=a.qp_mode, limits=a.limits)
     eng.set_external_wrench(wl["f_ext"])
     fig = torch.tensor(wl["fig"], dtype=tdt, device=dev)
     off = torch.tensor(wl["offsets"], device=dev)
@@ -50,7 +52,7 @@ def run(B, N, dtype):
         xu[:, :12] = x0
     ms = np.array(ms)
     sth = st.cpu().numpy()
-    return dict(batch=B, horizon=N, dtype=dtype, threads=a.threads, cluster=a.cluster, form=list(eng.kernel_form()), ms_p50=float(np.median(ms)), ms_mean=float(ms.mean()),
+    return dict(batch=B, horizon=N, dtype=dtype, qp_mode=a.qp_mode, limits=bool(a.limits), admm_iters_mean=float(sth[:, 10:12].sum(axis=1).mean()), threads=a.threads, cluster=a.cluster, form=list(eng.kernel_form()), ms_p50=float(np.median(ms)), ms_mean=float(ms.mean()),
                 ms_p99=float(np.percentile(ms, 99)), solves_per_s=float(B / ms.mean() * 1e3),
                 mean_qp_iters=float(sth[:, 0].mean()), nonfinite=int((~np.isfinite(sth)).sum())), first
 
