@@ -175,17 +175,17 @@ class CpuLoop:
     reference's tolerances, warm-started per lane, OpenMP over lanes); kind 'reference' = the unmodified reference
     classes, one solver object per lane, when pinocchio + osqp + the reference sources are importable."""
 
-    def __init__(self, wl, lanes, N, nthreads, probe=None):
+    def __init__(self, wl, lanes, N, nthreads, probe=None, limits=None):
         self.wl, self.lanes, self.N, self.nthreads = wl, lanes, N, nthreads
         self.xu, self.x0 = wl["xu"][lanes].copy(), wl["x0"][lanes].copy()
         self.tick = 0
         self.kind = "port"
-        if probe and probe.get("runnable"):
+        if probe and probe.get("runnable") and limits is None:
             self._init_reference(probe["reference_src"])
         else:
             from oracle.cport import COracle
             from oracle.model import load_model
-            self.orc = COracle(load_model(), N=N, backend="admm", batch=len(lanes))
+            self.orc = COracle(load_model(), N=N, backend="admm", batch=len(lanes), limits=limits)
 
     def _init_reference(self, src):            # pragma: no cover - needs pinocchio + osqp
         sys.path.insert(0, src)
@@ -212,13 +212,13 @@ class CpuLoop:
         return dt
 
 
-def cpu_baseline(wl, N, seconds, lanes=None, max_ticks=50, warm=2):
+def cpu_baseline(wl, N, seconds, lanes=None, max_ticks=50, warm=2, limits=None):
     """Bounded sample of the SAME workload on the host cores: `warm` untimed ticks (cold -> warm start), then
     warm-started ticks of the given lanes (default: all of them) until `seconds` have been timed."""
     cores = host_cores()
     lanes = np.arange(wl["x0"].shape[0]) if lanes is None else lanes
     probe = probe_reference()
-    loop = CpuLoop(wl, lanes, N, cores, probe)
+    loop = CpuLoop(wl, lanes, N, cores, probe, limits)
     for _ in range(warm):
         loop.step()
     times = []
@@ -266,7 +266,7 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------- B200 arm
-def device_loop(eng, wl, N, W, K, dtype, dev, exchange=None, flush=None, check=None):
+def device_loop(eng, wl, N, W, K, dtype, dev, exchange=None, flush=None, check=None, fused_offset=None):
     """W + K device-resident closed-loop ticks (solve -> selection/exchange -> shift -> goal window, all library
     kernels on torch's current stream).  Returns per-tick (step_ms, kernel_ms) of the K timed ticks, the last stats."""
     import torch
@@ -285,10 +285,14 @@ def device_loop(eng, wl, N, W, K, dtype, dev, exchange=None, flush=None, check=N
             if flush is not None:
                 flush.zero_()                            # L2 flush, outside the timed events
             ev[i][0].record()
-        out, st = eng.solve(xu, x0, goals)
+        if fused_offset is not None:                     # solve + selection + exchange: ONE launch (i7_solve_select)
+            out, st, best = eng.solve_select(xu, x0, goals, index_offset=fused_offset)
+        else:
+            out, st = eng.solve(xu, x0, goals)
         if i >= 0:
-            ev[i][1].record()                            # the dominant kernel on its own
-        best = exchange(st, out) if exchange is not None else eng.pack_best(st, out)
+            ev[i][1].record()                            # the dominant kernel on its own (fused: incl. its epilogue)
+        if fused_offset is None:
+            best = exchange(st, out) if exchange is not None else eng.pack_best(st, out)
         if i >= 0:
             ev[i][2].record()
         elif check is not None:
@@ -316,12 +320,17 @@ def extra_configs(args, local, fma_peaks):
     from indy7_mpc_b200 import Engine
     dev = torch.device("cuda", local)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
-    cases = [("configs[2]", 16, 32, "fp64"), ("configs[2]", 32, 32, "fp64"), ("configs[2]", 64, 32, "fp64"),
-             ("configs[4]", 512, 128, "fp64"), ("configs[4]", 512, 128, "fp32")]
+    # the last two run the QP of every pass the way the reference does (qp_mode 'osqp': warm-started ADMM at eps 1e-3),
+    # i.e. the SAME algorithm as the CPU port beside them; the very last adds the URDF joint limits as inequality rows
+    cases = [("configs[2]", 16, 32, "fp64", "exact", False), ("configs[2]", 32, 32, "fp64", "exact", False),
+             ("configs[2]", 64, 32, "fp64", "exact", False),
+             ("configs[4]", 512, 128, "fp64", "exact", False), ("configs[4]", 512, 128, "fp32", "exact", False),
+             ("configs[3] (per-GPU share at 8 GPUs) in the reference's QP regime", 512, 32, "fp64", "osqp", False),
+             ("configs[3] (per-GPU share at 8 GPUs) in the reference's QP regime + joint limits (SURVEY 8 f-4)", 512, 32, "fp64", "osqp", True)]
     out, cpu_cache, first = [], {}, {}
-    for name, B, N, dtype in cases:
+    for name, B, N, dtype, qp_mode, limits in cases:
         wl = make_workload(B, N)
-        eng = Engine(N=N, batch=B, dtype=dtype, device=local)
+        eng = Engine(N=N, batch=B, dtype=dtype, device=local, qp_mode=qp_mode, limits=limits)
         eng.set_external_wrench(wl["f_ext"])
         step_ms, kern_ms, st = device_loop(eng, wl, N, 5, args.config_ticks, dtype, dev, flush=flush)
         sth = st.double().cpu().numpy()
@@ -333,16 +342,25 @@ def extra_configs(args, local, fma_peaks):
                "kernel": f"{thr} threads x {ctas} CTA(s) per problem, {smem} B shared memory",
                "fp_pipe": fp_roofline(eng, sth, N, B, float(kern_ms.mean()), dtype, fma_peaks[dtype]),
                "mean_qp_iters": float(sth[:, 0].mean())}
-        if N == 128:                         # fp32 against fp64 on identical inputs (north_star: 1e-4)
+        if qp_mode == "osqp":
+            rec["qp_mode"] = "osqp: OSQP-style ADMM, eps_abs = eps_rel = 1e-3, warm-started per lane" + (", joint position / velocity / effort limits as inequality rows" if limits else "")
+            rec["mean_admm_iters_per_solve"] = float(sth[:, 10:12].sum(axis=1).mean())
+            rec["fp_pipe"]["note"] = "the flop model counts the direct-method floor of the QP; ADMM iterations are overhead by the survey's definition"
+        if N == 128 and qp_mode == "exact":                         # fp32 against fp64 on identical inputs (north_star: 1e-4)
             o, _ = eng.solve(torch.tensor(wl["xu"], dtype=st.dtype, device=dev), torch.tensor(wl["x0"], dtype=st.dtype, device=dev),
                              torch.tensor(goals_at(wl["fig"], wl["offsets"], 0, N), dtype=st.dtype, device=dev))
             first[dtype] = o.double().cpu().numpy()
             if "fp64" in first and dtype == "fp32":
                 rec["fp32_vs_fp64_rel"] = float(np.abs(first["fp32"] - first["fp64"]).max() / np.abs(first["fp64"]).max())
         if not args.no_cpu_baseline:
-            if (B, N) not in cpu_cache:
-                cpu_cache[(B, N)] = cpu_baseline(wl, N, args.config_cpu_seconds, max_ticks=20)
-            rec["cpu_baseline"] = cpu_cache[(B, N)]
+            key = (B, N, limits)
+            if key not in cpu_cache:
+                lim = None
+                if limits:
+                    m = eng.model
+                    lim = (m.lowerPositionLimit, m.upperPositionLimit, m.velocityLimit, m.effortLimit)
+                cpu_cache[key] = cpu_baseline(wl, N, args.config_cpu_seconds, max_ticks=20, limits=lim)
+            rec["cpu_baseline"] = cpu_cache[key]
         out.append(rec)
         del eng
     return out
@@ -398,7 +416,19 @@ def run_b200(args):
             return lambda st, out: e.p2p_exchange(st, out, index_offset=rank * B)
         return nccl_exchange(e)
 
+    # selection (+ exchange) as the epilogue of the solve kernel — one launch per tick instead of two — whenever the
+    # one-CTA-per-problem form runs and the peer buffers are mapped (a single GPU maps its own); I7_FUSED=0: two launches
+    # OFF by default: measured on the same box it loses — the selection scan + fences become a serial tail of the big kernel
+    # (1 GPU, 4096 problems: 1.975 vs 1.954 ms per tick; 2 GPUs: 1.038 vs 1.030 ms); I7_FUSED=1 selects it
+    fused_env = os.environ.get("I7_FUSED", "0")
+    fused = fused_env != "0" and eng.kernel_form()[1] == 1 and (use_p2p or world == 1)
+    if fused and world == 1:
+        eng.p2p_connect([eng.p2p_create(1, 0)])
+
     def check(st, out, best):          # warm-up ticks double as a check of the peer-memory exchange against NCCL
+        if world == 1 and fused:
+            if not torch.equal(best, eng.pack_best(st, out)[B:]):
+                raise RuntimeError("fused selection disagrees with i7_pack_best")
         if use_p2p:
             ref = nccl_exchange(eng)(st, out)
             if not torch.equal(best, ref):
@@ -414,8 +444,12 @@ def run_b200(args):
     clocks = ClockSampler(local) if rank == 0 else None
     launches0 = eng.launch_count()
     t_wall0 = time.time()
-    step_ms, kern_ms, last_st = device_loop(eng, wl, N, W, K, args.dtype, dev, make_exchange(eng, use_p2p), flush, check)
-    if use_p2p:
+    if fused:
+        eng.exchange_wait_ns(reset=True)
+    step_ms, kern_ms, last_st = device_loop(eng, wl, N, W, K, args.dtype, dev, make_exchange(eng, use_p2p), flush, check,
+                                            fused_offset=rank * B if fused else None)
+    wait_ms = eng.exchange_wait_ns() / 1e6 / (W + K) if fused else 0.0      # per tick, inside the fused kernel
+    if use_p2p or fused:
         eng.p2p_status()
     if world > 1:
         dist.barrier()
@@ -423,7 +457,7 @@ def run_b200(args):
     t_wall1 = time.time()
     launches = (eng.launch_count() - launches0) * K // (W + K)      # the timed ticks' share (every tick launches alike)
     total_ms = torch.tensor([step_ms.sum()], dtype=torch.float64, device=dev)
-    per_rank = torch.tensor([kern_ms.mean(), (step_ms - kern_ms).mean()], dtype=torch.float64, device=dev)
+    per_rank = torch.tensor([kern_ms.mean(), (step_ms - kern_ms).mean(), wait_ms], dtype=torch.float64, device=dev)
     per_rank_all = [torch.zeros_like(per_rank) for _ in range(world)]
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
@@ -543,9 +577,11 @@ def run_b200(args):
 
     value = args.batch * K / (total_ms * 1e-3)
     run_cfg = {"batch_per_gpu": B, "parallelism": f"batch-shard x{world}",
-               "exchange": ("none (one GPU)" if world == 1 else
-                            ("one peer-memory exchange kernel per tick (NVLink stores, fused pack + gather + selection)"
-                             if use_p2p else "pack kernel + one NCCL all-gather + reduce kernel per tick"))}
+               "exchange": (("none (one GPU); selection in the epilogue of the solve kernel" if fused else "none (one GPU)") if world == 1 else
+                            ("epilogue of the solve kernel: the CTA that finishes the last problem packs, stores the record into "
+                             "every peer over NVLink, waits for the ranks and selects (no second launch)" if fused else
+                             ("one peer-memory exchange kernel per tick (NVLink stores, fused pack + gather + selection)"
+                              if use_p2p else "pack kernel + one NCCL all-gather + reduce kernel per tick")))}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -569,7 +605,11 @@ def run_b200(args):
         "cpu_baseline": cpu,
         "latency": lat,
         "configs": configs,
-        "per_rank": {"kernel_ms": [float(p[0]) for p in per_rank_all], "selection_exchange_ms": [float(p[1]) for p in per_rank_all]},
+        "per_rank": {"kernel_ms": [float(p[0]) for p in per_rank_all], "selection_exchange_ms": [float(p[1]) for p in per_rank_all],
+                     "exchange_wait_ms": [float(p[2]) for p in per_rank_all],
+                     "what": ("fused: kernel_ms = solve + selection + exchange in one launch, exchange_wait_ms = the part of it its "
+                              "epilogue spent waiting for the other ranks" if fused else
+                              "kernel_ms = solve kernel, selection_exchange_ms = the launch(es) after it")},
         "wall_s_timed_loop": t_wall1 - t_wall0,
         "stats_last_tick": {"mean_qp_iters": float(st_host[:, 0].mean()), "linesearch_fail_frac": float((st_host[:, 3] == 1).mean()),
                             "nonfinite": int((st_host[:, 3] == 2).sum())},

@@ -235,6 +235,16 @@ i7_status i7_p2p_connect(i7_handle* h, const unsigned char* handles);
 i7_status i7_p2p_exchange(i7_handle* h, int32_t batch, const void* stats, const void* xu, int32_t index_offset, void* out,
                           void* stream);
 i7_status i7_p2p_gathered(i7_handle* h, const void** gathered);
+/* i7_solve and i7_p2p_exchange in ONE launch: the CTA that finishes the last problem of the batch runs the selection
+ * and the exchange as the kernel's epilogue (ranks that finish early post their record while the others still compute;
+ * no second launch).  Same results as the two calls, bit for bit.  Device pointers only; needs i7_p2p_connect (a world
+ * of one rank gives the single-GPU selection), the one-CTA-per-problem kernel form (i7_config.cluster = 1 or a batch
+ * beyond the latency forms) and I7_QP_EXACT.  best_out: [best_cost, global index, XU_best] (2 + 18N-6 numbers). */
+i7_status i7_solve_select(i7_handle* h, int32_t batch, const void* xu_in, const void* x0, const void* goals, int32_t goal_stride,
+                          void* xu_out, void* stats, int32_t index_offset, void* best_out, void* stream);
+/* Time the epilogues of i7_solve_select have spent waiting for the other ranks, in nanoseconds, summed since the last
+ * reset (synchronises the device). */
+i7_status i7_exchange_wait_ns(i7_handle* h, int64_t* total_ns, int32_t reset);
 i7_status i7_p2p_status(i7_handle* h, void* stream);
 i7_status i7_p2p_reset(i7_handle* h);
 

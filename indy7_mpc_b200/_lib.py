@@ -54,6 +54,8 @@ SYMBOLS = {
     "i7_p2p_connect": (_i32, [_vp, C.c_char_p]),
     "i7_p2p_exchange": (_i32, [_vp, _i32, _vp, _vp, _i32, _vp, _vp]),
     "i7_p2p_gathered": (_i32, [_vp, C.POINTER(_vp)]),
+    "i7_solve_select": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp, _vp]),
+    "i7_exchange_wait_ns": (_i32, [_vp, C.POINTER(C.c_int64), _i32]),
     "i7_p2p_status": (_i32, [_vp, _vp]),
     "i7_p2p_reset": (_i32, [_vp]),
     "i7_measure_fma_peak": (_i32, [_vp, C.POINTER(_dbl)]),

@@ -68,6 +68,8 @@ struct i7_handle {
     unsigned* d_sel_counter = nullptr;   // i7_find_best_idx: ticket counter + error scratch (lazy)
     void* d_sel_errs = nullptr;
     unsigned long long p2p_seq = 0;
+    unsigned* d_xchg_ticket = nullptr;   // i7_solve_select: problems finished in the current launch
+    long long* d_xchg_wait = nullptr;    // ... and the time its epilogue spent waiting for the peers (ns, summed)
     // qp_mode "osqp": per-problem ADMM warm start (x, y, y of the limit rows), QP blocks, factor workspace, QP solution,
     // QP record, "SQP loop ended" flags, statistics scratch
     void *d_wx = nullptr, *d_wy = nullptr, *d_wyl = nullptr, *d_blk = nullptr, *d_fac = nullptr, *d_zbuf = nullptr,
@@ -550,6 +552,8 @@ void i7_destroy(i7_handle* h) {
     if (h->p2p_mine) cudaFree(h->p2p_mine);
     if (h->p2p_table) cudaFree(h->p2p_table);
     if (h->p2p_err) cudaFree(h->p2p_err);
+    if (h->d_xchg_ticket) cudaFree(h->d_xchg_ticket);
+    if (h->d_xchg_wait) cudaFree(h->d_xchg_wait);
     if (h->d_sel_counter) cudaFree(h->d_sel_counter);
     if (h->d_sel_errs) cudaFree(h->d_sel_errs);
     for (int k = 0; k < i7_handle::kPipeStreams; ++k) {
@@ -939,6 +943,61 @@ i7_status i7_p2p_exchange(i7_handle* h, int32_t batch, const void* stats, const 
                                                                 index_offset, h->p2p_rank, h->p2p_world, h->p2p_table, seq, timeout_ns, (float*)out, h->p2p_err);
     ++h->launches;
     I7_CUDA(h, cudaGetLastError());
+    return I7_OK;
+}
+
+i7_status i7_solve_select(i7_handle* h, int32_t batch, const void* xu_in, const void* x0, const void* goals, int32_t goal_stride,
+                          void* xu_out, void* stats, int32_t index_offset, void* best_out, void* stream) {
+    if (!h || !xu_in || !x0 || !goals || !xu_out || !stats || !best_out) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (!h->p2p_table) { h->err = "i7_p2p_connect first (a world of one rank is fine)"; return I7_ERR_INVALID; }
+    if (batch != h->cfg.batch) { h->err = "the exchange is laid out for the handle's batch on every rank"; return I7_ERR_INVALID; }
+    if (h->use_cluster || h->cfg.qp_mode != I7_QP_EXACT) { h->err = "i7_solve_select needs the one-CTA-per-problem form (cluster = 1) of the exact QP mode"; return I7_ERR_UNSUPPORTED; }
+    const void* ptrs[6] = {xu_in, x0, goals, xu_out, stats, best_out};
+    for (const void* p : ptrs) if (ptr_kind(p) != 1) { h->err = "i7_solve_select takes device pointers"; return I7_ERR_INVALID; }
+    i7_status rc = check_batch(h, batch, goal_stride);
+    if (rc) return rc;
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!h->d_xchg_ticket) {
+        I7_CUDA(h, cudaMalloc((void**)&h->d_xchg_ticket, sizeof(unsigned)));
+        I7_CUDA(h, cudaMemset(h->d_xchg_ticket, 0, sizeof(unsigned)));
+        I7_CUDA(h, cudaMalloc((void**)&h->d_xchg_wait, sizeof(long long)));
+        I7_CUDA(h, cudaMemset(h->d_xchg_wait, 0, sizeof(long long)));
+    }
+    i7::XchgArgs X{};
+    X.peers = h->p2p_table; X.seq = ++h->p2p_seq; X.timeout_ns = 4000000000ull; X.out = best_out; X.err = h->p2p_err;
+    X.ticket = h->d_xchg_ticket; X.wait_ns = h->d_xchg_wait; X.rank = h->p2p_rank; X.world = h->p2p_world;
+    X.index_offset = index_offset; X.enabled = 1;
+    I7_CUDA(h, cudaEventRecord(h->ev0, s));
+    if (h->cfg.dtype == I7_F64) {
+        i7::SolveParams<double> P;
+        base_params<double>(h, P, batch, goal_stride, i7::MODE_SOLVE);
+        P.xu_in = (const double*)xu_in; P.x0 = (const double*)x0; P.goals = (const double*)goals; P.xu_out = (double*)xu_out;
+        P.stats = (double*)stats; P.xchg = X;
+        rc = launch_sqp<double>(h, h->rob64, P, s);
+    } else {
+        i7::SolveParams<float> P;
+        base_params<float>(h, P, batch, goal_stride, i7::MODE_SOLVE);
+        P.xu_in = (const float*)xu_in; P.x0 = (const float*)x0; P.goals = (const float*)goals; P.xu_out = (float*)xu_out;
+        P.stats = (float*)stats; P.xchg = X;
+        rc = launch_sqp<float>(h, h->rob32, P, s);
+    }
+    if (rc) return rc;
+    I7_CUDA(h, cudaEventRecord(h->ev1, s));
+    h->timed = true;
+    return I7_OK;
+}
+
+i7_status i7_exchange_wait_ns(i7_handle* h, int64_t* total_ns, int32_t reset) {
+    if (!h || !total_ns) return I7_ERR_INVALID;
+    *total_ns = 0;
+    if (!h->d_xchg_wait) return I7_OK;
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    I7_CUDA(h, cudaDeviceSynchronize());
+    long long v = 0;
+    I7_CUDA(h, cudaMemcpy(&v, h->d_xchg_wait, sizeof(v), cudaMemcpyDeviceToHost));
+    *total_ns = v;
+    if (reset) I7_CUDA(h, cudaMemset(h->d_xchg_wait, 0, sizeof(long long)));
     return I7_OK;
 }
 

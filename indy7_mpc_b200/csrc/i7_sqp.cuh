@@ -16,6 +16,7 @@
 //   update    first-accept alpha selection, XU += alpha (z - XU), statistics              (src/osqp_sqp.py:80-92)
 #pragma once
 #include "i7_wf.cuh"
+#include "i7_xchg.cuh"
 
 namespace i7 {
 
@@ -31,6 +32,19 @@ enum Mode : int {
 };
 // per-knot block of MODE_EXPORT: A_k = [[I, dt I], [Gq, Gv]], B_k = [0; Hm], c_k = [0; cv]; cost = j[6], Q_k, dQ_k, R_k
 constexpr int QB_GQ = 0, QB_GV = 36, QB_CV = 72, QB_HM = 78, QB_COST = 114, QB_STRIDE = 124;
+
+// Epilogue of MODE_SOLVE (optional): the CTA that finishes the LAST problem of the launch packs [costs | best_cost,
+// best_index, XU_best], stores it into every peer's exchange buffer over NVLink, waits for the other ranks and writes
+// the overall winner — selection and multi-GPU exchange without a second launch (i7_solve_select).
+struct XchgArgs {
+    unsigned char* const* peers;       // exchange buffers of all ranks (device copy of the pointer table)
+    unsigned long long seq, timeout_ns;
+    void* out;                         // [best_cost, global index, XU_best]
+    int* err;
+    unsigned* ticket;                  // problems finished so far in this launch (reset by the last one)
+    long long* wait_ns;                // optional: time spent waiting for the peers, summed over the launches
+    int rank, world, index_offset, enabled;
+};
 
 template <typename T>
 struct SolveParams {
@@ -51,6 +65,7 @@ struct SolveParams {
     const T* qp_info;     // MODE_STEP, optional: batch x 4 record of the QP solver ([0] = its iterations)
     int* done;            // MODE_EXPORT / MODE_STEP, optional: per problem 1 = the SQP loop has ended (skipped; set by MODE_STEP)
     int qp_index;         // MODE_STEP: index of the pass (0 .. max_qp-1)
+    XchgArgs xchg;        // MODE_SOLVE epilogue (enabled != 0)
     int N, batch, goal_stride, mode, max_qp, regularize;
     T dt, dQ, R, QN, eps, mu, step_tol;
 };
@@ -1347,6 +1362,22 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
             }
         }
         __syncthreads();
+        if (P.mode == MODE_SOLVE && P.xchg.enabled) {
+            // last-problem-done: every CTA publishes its results (fence), takes a ticket; the holder of the last ticket
+            // sees all of them (fence after the atomic) and runs the selection + exchange
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) s_flag = (atomicAdd(P.xchg.ticket, 1u) == (unsigned)P.batch - 1u) ? 1 : 0;
+            __syncthreads();
+            if (s_flag) {
+                if (tid == 0) *P.xchg.ticket = 0u;
+                __threadfence();
+                pack_exchange_reduce<T>(P.batch, nz, P.stats, 12, 8, P.xu_out, P.xchg.index_offset, P.xchg.rank, P.xchg.world,
+                                        P.xchg.peers, P.xchg.seq, P.xchg.timeout_ns, static_cast<T*>(P.xchg.out), P.xchg.err,
+                                        P.xchg.wait_ns);
+            }
+            __syncthreads();
+        }
     }
 }
 

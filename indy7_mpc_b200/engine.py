@@ -361,6 +361,25 @@ class Engine:
         self._check(self.lib.i7_p2p_exchange(self._h, B, p_st, p_xu, int(index_offset), p_out, self._stream(xu)))
         return out
 
+    def solve_select(self, xu, x0, goals, index_offset=0):
+        """sqp() of every problem AND the best-trajectory selection / multi-GPU exchange in ONE launch (i7_solve_select):
+        returns (xu_out, stats, best = [best_cost, global index, XU_best]) on the device.  Device tensors only."""
+        B = self._batch_of(xu)
+        gs = self._goal_stride(goals, B)
+        keep = []
+        p_xu, p_x0, p_g = self._in(xu, (B, self.nz), keep), self._in(x0, (B, 12), keep), self._in(goals, (B, gs * self.N), keep)
+        out, p_out = self._out((B, self.nz), xu, keep)
+        stats, p_st = self._out((B, _lib.I7_STATS_LEN), xu, keep)
+        best, p_best = self._out((2 + self.nz,), xu, keep)
+        self._check(self.lib.i7_solve_select(self._h, B, p_xu, p_x0, p_g, gs, p_out, p_st, int(index_offset), p_best, self._stream(xu)))
+        return out, stats, best
+
+    def exchange_wait_ns(self, reset=True):
+        """Nanoseconds the epilogues of solve_select have waited for the other ranks since the last reset."""
+        v = C.c_int64()
+        self._check(self.lib.i7_exchange_wait_ns(self._h, C.byref(v), int(bool(reset))))
+        return int(v.value)
+
     def p2p_status(self, like=None):
         self._check(self.lib.i7_p2p_status(self._h, self._stream(like) if like is not None else None))
 

@@ -137,3 +137,20 @@ def test_osqp_mode_long_horizon_and_classes(oracle_model):
     got = sq.sqp(x0[0], goals[0], xu[0])
     want, rst, _ = o2.sqp(x0[0], goals[0], xu[0])
     assert rel(got, want[0]) < 1e-6 and sq.stats["linesearch_alphas"]["values"] == list(rst[0, 4:4 + int(rst[0, 1])])
+
+
+def test_osqp_mode_closed_loop_golden_prefix(golden):
+    """The reference's stored closed-loop series (notebooks/pin_mpc_indy7.ipynb:98-597) was produced BY OSQP at eps 1e-3;
+    MPC_OSQP.run_mpc over the 'osqp' QP mode (same regime: warm-started ADMM, same tolerances; no Ruiz scaling / adaptive
+    rho) reproduces its first 12 values to 5e-6, as the CPU restatement does (tests/test_oracle_golden.py)."""
+    import indy7_mpc_b200 as pkg
+    g = golden["closed_loop"]
+    model, _, _ = pkg.load_robot_model()
+    solver = pkg.OSQPSolver(model, qp_mode="osqp")
+    sqp = pkg.SQP_OSQP(solver)
+    mpc = pkg.MPC_OSQP(model, sqp, solver)
+    endpoints = np.array([solver.eepos(np.array(q)) for q in g["endpoint_qs"]])
+    mpc.run_mpc(np.array(g["xstart"]), endpoints, num_steps=12)
+    got, ref = np.array(mpc.goal_distances), np.array(g["goal_distances"][:12])
+    assert (np.abs(got - ref) / ref).max() < 5e-6
+    assert all(v == 2 for v in sqp.stats["qp_iters"]["values"])

@@ -621,8 +621,19 @@ def test_peer_exchange_single_rank_matches_pack_reduce(pkg, oracle_model):
         ref = e.reduce_best(e.pack_best(st, out, index_offset=7).view(1, -1), 1)
         got = e.p2p_exchange(st, out, index_offset=7)
         assert torch.equal(got, ref)
+        # ... and as the epilogue of the solve kernel itself (i7_solve_select): one launch, same bits
+        out2, st2, got2 = e.solve_select(xu_d, x0_d, g_d, index_offset=7)
+        assert torch.equal(out2, out) and torch.equal(st2, st) and torch.equal(got2, ref)
         xu_d = out
     e.p2p_status(got)
+    assert e.exchange_wait_ns() >= 0
+    big = pkg.Engine(N=32, batch=600, dtype="fp64")          # several waves of CTAs: the last ticket still sees every result
+    big.p2p_connect([big.p2p_create(1, 0)])
+    xb, x0b, gb = (dev(np.tile(a, (25, 1))) for a in (xu, x0, goals))
+    o, s_, b_ = big.solve_select(xb, x0b, gb)
+    assert torch.equal(b_, big.reduce_best(big.pack_best(s_, o).view(1, -1), 1))
+    o1, s1 = big.solve(xb, x0b, gb)
+    assert torch.equal(o, o1) and torch.equal(s_, s1)
 
 
 def _peer_rank(rank, world, port, q):
@@ -652,6 +663,9 @@ def _peer_rank(rank, world, port, q):
             dist.all_gather(parts, packed.cpu())
             ref = e.reduce_best(torch.stack(parts).to(best.device), world)
             res.append(bool(torch.equal(best, ref)))
+            # the same tick with selection + exchange as the epilogue of the solve kernel (ONE launch)
+            out2, st2, best2 = e.solve_select(xu_d, x0_d, g_d, index_offset=lo)
+            res.append(bool(torch.equal(out2, out) and torch.equal(st2, st) and torch.equal(best2, ref)))
             xu_d = out
         e.p2p_status(best)
         q.put((rank, res))

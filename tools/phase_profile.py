@@ -32,7 +32,9 @@ for i in range(2):
     print(f"  qp {i}: " + ", ".join(f"{n} {np.median(d[:, j]):.0f}" for j, n in enumerate(names)) + f"   total {np.median(c[:, 5*i+4]-c[:, 5*i]):.0f}")
 print(f"  first QP: 6x6 solves {np.median(c[:,10]):.0f}, value update {np.median(c[:,11]):.0f}, roll-out {np.median(c[:,12]):.0f}, controls {np.median(c[:,13]):.0f}")
 print("  first setup waves W0..W9: " + ", ".join(f"{v:.0f}" for v in np.median(np.diff(c[:, 16:27], axis=1), axis=0)))
-print(f"  whole solve (first stamp -> last): median {np.median(c[:, 9] - c[:, 0]):.0f} cycles; alphas {st[0,4:6]}")
+tot = c[:, 9] - c[:, 0]
+print(f"  whole solve (first stamp -> last): median {np.median(tot):.0f} cycles; alphas {st[0,4:6]}")
+print("  whole solve percentiles 1/10/50/90/99/max: " + ", ".join(f"{np.percentile(tot, q):.0f}" for q in (1, 10, 50, 90, 99, 100)))
 if np.any(c[:, 27] > 0):       # cluster kernel: finer stamps of the first QP phase (lead CTA)
     m = lambda a: float(np.median(a))
     print(f"  first QP (cluster): barrier1->init done {m(c[:,14]-c[:,1]):.0f}, sweep loop+roll-out {m(c[:,27]-c[:,14]):.0f}, "
