@@ -614,6 +614,7 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
 #define I7_CUDA_C(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(I7_ERR_CUDA); } } while (0)
     I7_CUDA_C(cudaSetDevice(cfg->device));
     I7_CUDA_C(cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
+    bool want_spill = false;
     // threads per CTA of the throughput form: 384 while every problem has an SM to itself; for bigger batches 128 when
     // shared memory lets two or more CTAs share an SM (more independent problems per SM beats wider CTAs: measured
     // 1.60 -> 1.27 ms for 4096 fp32 problems, four CTAs per SM), 256 when only one fits (long horizons)
@@ -621,9 +622,16 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
         const size_t per_sm = (size_t)h->max_smem_optin + 1024;
-        size_t need = (size_t)i7::make_layout(cfg->N, false).total * h->esize + 1024;
-        if (need > per_sm) need = (size_t)i7::make_layout(cfg->N, true).total * h->esize + 1024;
-        const int fit = (int)(per_sm / need);
+        const size_t need_n = (size_t)i7::make_layout(cfg->N, false).total * h->esize + 1024;
+        const size_t need_s = (size_t)i7::make_layout(cfg->N, true).total * h->esize + 1024;
+        const int fit_n = (int)(per_sm / need_n), fit_s = (int)(per_sm / need_s);
+        // records in shared memory (fit_n CTAs per SM) or in the global workspace with the shared-memory tile (fit_s):
+        // the tile form when the records do not fit at all, and for throughput batches when the resident form would leave
+        // ONE CTA per SM while the tile form runs three or more (fp32 N=128, four per SM: 1.30 -> 0.90 ms for 512 problems;
+        // with only two — fp64 N=64 — the resident 256-thread form stays ahead: 0.81 vs 0.85 ms)
+        want_spill = fit_n == 0 || (cfg->batch > sms && fit_n < 2 && fit_s >= 3);
+        if (const char* e7 = std::getenv("I7_FORCE_SPILL")) want_spill = (std::atoi(e7) != 0 || fit_n == 0) && fit_s >= 1;
+        const int fit = want_spill ? fit_s : fit_n;
         h->threads = cfg->threads ? cfg->threads : (cfg->batch <= sms ? 384 : (fit >= 2 ? 128 : 256));
     }
     if (h->threads != 128 && h->threads != 256 && h->threads != 384) { h->err = "threads must be 0, 128, 256 or 384"; return fail(I7_ERR_INVALID); }
@@ -636,7 +644,7 @@ i7_status i7_create(const i7_config* cfg, i7_handle** out) {
     }
     i7::Layout L = i7::make_layout(cfg->N, false);
     h->spill = false;
-    if ((size_t)L.total * h->esize > (size_t)cap) {
+    if (want_spill || (size_t)L.total * h->esize > (size_t)cap) {
         L = i7::make_layout(cfg->N, true);
         h->spill = true;
         if ((size_t)L.total * h->esize > (size_t)cap) {

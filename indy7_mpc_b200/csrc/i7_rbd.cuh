@@ -151,10 +151,6 @@ I7_DEV void fk_ee(const Robot<T>& rob, const T* cs, T* pee, T* zs /*18*/, T* ps 
     pee[0] = p[0]; pee[1] = p[1]; pee[2] = p[2];
 }
 
-template <typename T> I7_DEV void fk_ee_only(const Robot<T>& rob, const T* cs, T* pee) {
-    fk_ee<T>(rob, cs, pee, nullptr, nullptr);
-}
-
 // 3x6 translational Jacobian (row-major) from the per-joint axes / origins
 template <typename T> I7_DEV void ee_jacobian(const T* pee, const T* zs, const T* ps, T* J) {
 #pragma unroll
