@@ -25,13 +25,25 @@ namespace i7 {
 constexpr int CL_NT = 384;     // threads per CTA
 
 __host__ __device__ inline int cluster_merit_cap(int chunk) { return chunk <= 8 ? 8 : (chunk <= 16 ? 4 : 2); }
-struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, aux, pair, gains, total, chunk; };
+// Line-search points of the latency forms: instead of one thread per point walking the whole chain (a 20 k-cycle
+// dependency chain), the dynamics of a point are split into the task waves of the setup — (point, joint) sin / cos,
+// (point) tip, (point, link) link records, (point, column) mass-matrix column + bias, (point) 6x6 solve + merit terms —
+// about half the latency; needs PR_STRIDE numbers of scratch per point instead of MP_STRIDE.
+constexpr int PR_CS = 0, PR_PEE = 12, PR_QD = 15, PR_U = 21, PR_S = 27, PR_F = 63, PR_I = 99, PR_M = 153, PR_B = 189, PR_STRIDE = 197;
+struct CLayout { int xu, z, goals, x0, cost, work, ls, kr, aux, pair, gains, total, chunk, par_merit; };
 __host__ __device__ inline CLayout make_clayout(int N, int CL) {
     CLayout L;
     L.chunk = (N + CL - 1) / CL;
     // knot records, later the merit scratch (as many line-search candidates per wave as fit: 8 up to N = 32)
     const int mcap = cluster_merit_cap(L.chunk);
-    const int recw = KR_STRIDE > mcap * MP_STRIDE ? KR_STRIDE : mcap * MP_STRIDE;
+    // task-parallel line-search points while a wave of them (candidates x knots of the window, 6 tasks each) fits the
+    // CTA's threads and its scratch stays moderate
+    // (and the whole layout stays within an SM's shared memory: long horizons keep the one-thread-per-point form)
+    const int fixed = WK_SIZE + 36 * N + 3 * N + 16 + COST_STRIDE * L.chunk + CL_NT + 16 + AUX_STRIDE * L.chunk +
+                      (L.chunk <= 8 ? 432 * L.chunk : 0) + GAIN_STRIDE * N + 8;
+    L.par_merit = (6 * mcap * L.chunk <= CL_NT && fixed + mcap * L.chunk * PR_STRIDE <= 27500) ? 1 : 0;
+    const int mw = L.par_merit ? mcap * PR_STRIDE : mcap * MP_STRIDE;
+    const int recw = KR_STRIDE > mw ? KR_STRIDE : mw;
     int o = 0;
     L.work = o; o += WK_SIZE;
     L.xu = o; o += 18 * N;
@@ -54,6 +66,104 @@ __host__ __device__ inline int xbuf_zx(int N) { return RIC_STRIDE * N; }
 __host__ __device__ inline int xbuf_zu(int N) { return RIC_STRIDE * N + 12 * N; }
 __host__ __device__ inline int xbuf_mc(int N) { return RIC_STRIDE * N + 18 * N; }
 __host__ __device__ inline int xbuf_size(int N) { return RIC_STRIDE * N + 18 * N + 36 * N; }
+
+// Merit terms of candidates c0 .. c0+nc-1 at the knots of window W, task-parallel form (same outputs as merit_points).
+template <typename T, int NT>
+__device__ void merit_points_par(const Robot<T>& rob, const SolveParams<T>& P, const Ptrs<T>& M, const Win W, T* scr,
+                                 const T* xa_, const T* xb_, const T* fext, int c0, int nc, T* comps, int cbase) {
+    const int tid = threadIdx.x, N = P.N, nk = W.nd, nw = W.nc;
+    const int npts = nc * nw;
+    const T* xa = xa_ + 18 * W.k0;
+    const T* xb = xb_ + 18 * W.k0;
+    // P0: per (point, i): interpolated q_i -> cos / sin; qd_i, u_i (u = 0 at the last knot of the horizon)
+    for (int t = tid; t < 6 * npts; t += NT) {
+        const int i = t / npts, p = t - i * npts;
+        const int ci = p / nw, k = p - ci * nw;
+        const T alpha = T(c_alphas[c0 + ci]);
+        const T* a = xa + 18 * k;
+        const T* b = xb + 18 * k;
+        T sn, cs;
+        sincos_t<T>(a[i] + alpha * (b[i] - a[i]), &sn, &cs);
+        T* pr = scr + PR_STRIDE * p;
+        pr[PR_CS + i] = cs; pr[PR_CS + 6 + i] = sn;
+        pr[PR_QD + i] = a[6 + i] + alpha * (b[6 + i] - a[6 + i]);
+        pr[PR_U + i] = (W.k0 + k < N - 1) ? a[12 + i] + alpha * (b[12 + i] - a[12 + i]) : T(0);
+    }
+    __syncthreads();
+    // P1: per point: position of the last joint (spatial origin of the point; eepos of the cost)
+    for (int p = tid; p < npts; p += NT) {
+        T* pr = scr + PR_STRIDE * p;
+        T pee[3];
+        wf_tip<T>(rob, pr + PR_CS, pee);
+        pr[PR_PEE] = pee[0]; pr[PR_PEE + 1] = pee[1]; pr[PR_PEE + 2] = pee[2];
+    }
+    __syncthreads();
+    // P2: per (point, link): axis, world inertia, force at qdd = 0 (velocity / acceleration stay in registers)
+    for (int t = tid; t < 6 * npts; t += NT) {
+        const int l = t / npts, p = t - l * npts;
+        const int k = p % nw;
+        if (k >= nk) continue;
+        T* pr = scr + PR_STRIDE * p;
+        T v[6], a[6];
+        wf_link<T>(rob, pr + PR_CS, pr + PR_QD, fext, pr + PR_PEE, l, pr + PR_S + 6 * l, v, a, pr + PR_I + 9 * l, pr + PR_F + 6 * l);
+    }
+    __syncthreads();
+    // P3: per (point, j): column j of M and the bias torque b_j
+    for (int t = tid; t < 6 * npts; t += NT) {
+        const int j = t / npts, p = t - j * npts;
+        const int k = p % nw;
+        if (k >= nk) continue;
+        T* pr = scr + PR_STRIDE * p;
+        T bj;
+        wf_mass_column<T>(rob, pr + PR_S, pr + PR_I, pr + PR_F, j, pr + PR_M, &bj);
+        pr[PR_B + j] = bj;
+    }
+    __syncthreads();
+    // P4: per point: qdd = M^-1 (u - b), merit terms (src/osqp_sqp.py:13-47)
+    for (int p = tid; p < npts; p += NT) {
+        const int ci = p / nw, k = p - ci * nw;
+        const int kg = W.k0 + k;
+        const T alpha = T(c_alphas[c0 + ci]);
+        const T* pr = scr + PR_STRIDE * p;
+        const T* goal = M.goals + 3 * kg;
+        const T e[3] = {pr[PR_PEE] - goal[0], pr[PR_PEE + 1] - goal[1], pr[PR_PEE + 2] - goal[2]};
+        const T Qk = (kg == N - 1) ? P.QN : T(1);
+        T* out = comps + 4 * ((cbase + ci) * N + kg);
+        out[0] = Qk * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]);
+        T vv = T(0), uu = T(0);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { vv += pr[PR_QD + i] * pr[PR_QD + i]; uu += pr[PR_U + i] * pr[PR_U + i]; }
+        out[1] = P.dQ * vv;
+        out[2] = P.R * uu;
+        T ie = T(0);
+        if (k < nk) {
+            T A[6][6], dinv[6], qdd[6];
+#pragma unroll
+            for (int r = 0; r < 6; ++r)
+#pragma unroll
+                for (int q = 0; q <= r; ++q) A[r][q] = pr[PR_M + 6 * r + q];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) qdd[r] = pr[PR_U + r] - pr[PR_B + r];
+            spd6_factor<T>(A, dinv);
+            spd6_solve_factored<T>(A, dinv, qdd);
+            const T* a = xa + 18 * k;
+            const T* b = xb + 18 * k;
+            T qe = T(0), ve = T(0);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const T q = a[i] + alpha * (b[i] - a[i]);
+                const T xnq = a[18 + i] + alpha * (b[18 + i] - a[18 + i]);
+                const T xnv = a[24 + i] + alpha * (b[24 + i] - a[24 + i]);
+                const T dq = q + pr[PR_QD + i] * P.dt - xnq;
+                const T dv = pr[PR_QD + i] + qdd[i] * P.dt - xnv;
+                qe += dq * dq; ve += dv * dv;
+            }
+            ie = sqrt_t<T>(qe) + sqrt_t<T>(ve);
+        }
+        out[3] = ie;
+    }
+    __syncthreads();
+}
 
 template <typename T, int CL>
 __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(CL_NT)
@@ -171,8 +281,11 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
         // ---- line search: candidates 0..7 (base, alpha = 1 .. 1/64) at the own knots — with 4 knots per CTA that is
         //      exactly one warp per task type; the last candidate (1/128) only if none of those is accepted ----
 #pragma unroll 1      // the body is 24 KB of code: unrolled by four it evicts itself from the instruction cache
-        for (int c0 = 0; c0 < 8; c0 += M.merit_cap)
-            merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, 8 - c0 < M.merit_cap ? 8 - c0 : M.merit_cap, mcomps, c0);
+        for (int c0 = 0; c0 < 8; c0 += M.merit_cap) {
+            const int ncw = 8 - c0 < M.merit_cap ? 8 - c0 : M.merit_cap;
+            if (L.par_merit) merit_points_par<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, ncw, mcomps, c0);
+            else merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, c0, ncw, mcomps, c0);
+        }
         cluster.sync();                                                             // barrier 3
         for (int t = tid; t < 6 * (N - 1); t += NT) {
             const int k = t / 6, i = t - 6 * k;
@@ -188,7 +301,8 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
         }
         __syncthreads();
         if (s_alpha == T(0)) {          // identical decision in every CTA of the cluster (same data, same arithmetic)
-            merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, 8, 1, mcomps, 8);
+            if (L.par_merit) merit_points_par<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, 8, 1, mcomps, 8);
+            else merit_points<T, NT>(rob, P, M, W, M.kr, M.xu, M.z, fext, 8, 1, mcomps, 8);
             cluster.sync();                                                         // barrier 3b (rare)
             merit_reduce<T, NT, true>(P, M.xu, M.z, 8, 1, mcomps, 8, s_merits, nullptr);
             if (tid == 0 && s_merits[8] <= s_merits[0]) { s_alpha = T(c_alphas[8]); s_merit_acc = s_merits[8]; }
