@@ -266,38 +266,57 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------- B200 arm
-def device_loop(eng, wl, N, W, K, dtype, dev, exchange=None, flush=None, check=None, fused_offset=None):
-    """W + K device-resident closed-loop ticks (solve -> selection/exchange -> shift -> goal window, all library
-    kernels on torch's current stream).  Returns per-tick (step_ms, kernel_ms) of the K timed ticks, the last stats."""
+def device_loop(eng, wl, N, W, K, dtype, dev, exchange=None, flush=None, check=None, mode=None, index_offset=0):
+    """W + K device-resident closed-loop ticks (goal window -> solve -> selection/exchange -> shift, all library kernels on
+    torch's current stream).  mode 'local' | 'p2p' | 'fused': the bound-buffer runner `DeviceTick` (one C-ABI call per
+    stage, ~50 us of host time per tick); mode None: the generic Engine calls with `exchange(stats, out)` (NCCL path).
+    Returns per-tick (step_ms, kernel_ms) of the K timed ticks, the last stats."""
     import torch
+    from indy7_mpc_b200 import DeviceTick
     tdt = torch.float64 if dtype == "fp64" else torch.float32
     B = wl["x0"].shape[0]
-    fig_d = torch.tensor(wl["fig"], dtype=tdt, device=dev)
-    off_d = torch.tensor(wl["offsets"], dtype=torch.int32, device=dev)
-    xu = torch.tensor(wl["xu"], dtype=tdt, device=dev)
-    x0 = torch.tensor(wl["x0"], dtype=tdt, device=dev)
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
-    st = None
-    for t in range(W + K):
-        goals = eng.goal_window(fig_d, off_d, tick=t, wrap=True, batch=B)
-        i = t - W
-        if i >= 0:
-            if flush is not None:
-                flush.zero_()                            # L2 flush, outside the timed events
-            ev[i][0].record()
-        if fused_offset is not None:                     # solve + selection + exchange: ONE launch (i7_solve_select)
-            out, st, best = eng.solve_select(xu, x0, goals, index_offset=fused_offset)
-        else:
+    if mode is not None:
+        tk = DeviceTick(eng, wl["fig"], wl["offsets"], wl["xu"], wl["x0"], mode=mode, index_offset=index_offset)
+        for t in range(W + K):
+            tk.goal(t)
+            i = t - W
+            if i >= 0:
+                if flush is not None:
+                    flush.zero_()                        # L2 flush, outside the timed events
+                ev[i][0].record()
+            tk.solve()
+            if i >= 0:
+                ev[i][1].record()                        # the dominant kernel on its own (fused: incl. its epilogue)
+            tk.select()
+            if i >= 0:
+                ev[i][2].record()
+            elif check is not None:
+                check(tk.stats, tk.out, tk.best)
+            tk.shift()
+        st = tk.stats
+    else:
+        fig_d = torch.tensor(wl["fig"], dtype=tdt, device=dev)
+        off_d = torch.tensor(wl["offsets"], dtype=torch.int32, device=dev)
+        xu = torch.tensor(wl["xu"], dtype=tdt, device=dev)
+        x0 = torch.tensor(wl["x0"], dtype=tdt, device=dev)
+        st = None
+        for t in range(W + K):
+            goals = eng.goal_window(fig_d, off_d, tick=t, wrap=True, batch=B)
+            i = t - W
+            if i >= 0:
+                if flush is not None:
+                    flush.zero_()
+                ev[i][0].record()
             out, st = eng.solve(xu, x0, goals)
-        if i >= 0:
-            ev[i][1].record()                            # the dominant kernel on its own (fused: incl. its epilogue)
-        if fused_offset is None:
+            if i >= 0:
+                ev[i][1].record()
             best = exchange(st, out) if exchange is not None else eng.pack_best(st, out)
-        if i >= 0:
-            ev[i][2].record()
-        elif check is not None:
-            check(st, out, best)
-        xu, x0 = eng.shift(out, steps=1, tail="repeat")
+            if i >= 0:
+                ev[i][2].record()
+            elif check is not None:
+                check(st, out, best)
+            xu, x0 = eng.shift(out, steps=1, tail="repeat")
     torch.cuda.synchronize()
     step_ms = np.array([e[0].elapsed_time(e[2]) for e in ev])
     kern_ms = np.array([e[0].elapsed_time(e[1]) for e in ev])
@@ -332,7 +351,7 @@ def extra_configs(args, local, fma_peaks):
         wl = make_workload(B, N)
         eng = Engine(N=N, batch=B, dtype=dtype, device=local, qp_mode=qp_mode, limits=limits)
         eng.set_external_wrench(wl["f_ext"])
-        step_ms, kern_ms, st = device_loop(eng, wl, N, 5, args.config_ticks, dtype, dev, flush=flush)
+        step_ms, kern_ms, st = device_loop(eng, wl, N, 5, args.config_ticks, dtype, dev, flush=flush, mode="local")
         sth = st.double().cpu().numpy()
         if dtype not in fma_peaks:
             fma_peaks[dtype] = eng.measure_fma_peak()
@@ -427,7 +446,7 @@ def run_b200(args):
 
     def check(st, out, best):          # warm-up ticks double as a check of the peer-memory exchange against NCCL
         if world == 1 and fused:
-            if not torch.equal(best, eng.pack_best(st, out)[B:]):
+            if not torch.equal(best, eng.pack_best(st, out, index_offset=rank * B)[B:]):
                 raise RuntimeError("fused selection disagrees with i7_pack_best")
         if use_p2p:
             ref = nccl_exchange(eng)(st, out)
@@ -446,8 +465,9 @@ def run_b200(args):
     t_wall0 = time.time()
     if fused:
         eng.exchange_wait_ns(reset=True)
+    loop_mode = "fused" if fused else ("p2p" if use_p2p else ("local" if world == 1 else None))
     step_ms, kern_ms, last_st = device_loop(eng, wl, N, W, K, args.dtype, dev, make_exchange(eng, use_p2p), flush, check,
-                                            fused_offset=rank * B if fused else None)
+                                            mode=loop_mode, index_offset=rank * B)
     wait_ms = eng.exchange_wait_ns() / 1e6 / (W + K) if fused else 0.0      # per tick, inside the fused kernel
     if use_p2p or fused:
         eng.p2p_status()

@@ -242,3 +242,29 @@ def test_nonfinite_input_returns_trajectory_unchanged(pkg):
     out = sqp.sqp(np.zeros(12), np.zeros(96), xu)
     assert np.array_equal(np.isnan(out), np.isnan(xu)) and np.array_equal(out[~np.isnan(xu)], xu[~np.isnan(xu)])
     assert int(sqp.last_record[3]) == 2 and sqp.stats['linesearch_alphas']['values'] == [0.0, 0.0]
+
+
+def test_device_tick_equals_generic_calls(pkg):
+    """DeviceTick (buffers bound once, one C-ABI call per stage) runs the same closed loop as the generic Engine calls —
+    goal window, solve, selection, shift — bit for bit, in the local and in the fused-epilogue mode."""
+    import torch
+    import bench
+    B, N = 48, 32
+    wl = bench.make_workload(B, N)
+    dev = torch.device("cuda", 0)
+    for mode in ("local", "fused"):
+        e = pkg.Engine(N=N, batch=B, cluster=1)
+        e.set_external_wrench(wl["f_ext"])
+        if mode == "fused":
+            e.p2p_connect([e.p2p_create(1, 0)])
+        tk = pkg.DeviceTick(e, wl["fig"], wl["offsets"], wl["xu"], wl["x0"], mode=mode, index_offset=5)
+        fig_d, off_d = torch.tensor(wl["fig"], device=dev), torch.tensor(wl["offsets"], dtype=torch.int32, device=dev)
+        xu, x0 = torch.tensor(wl["xu"], device=dev), torch.tensor(wl["x0"], device=dev)
+        for t in range(4):
+            tk.run(t)
+            goals = e.goal_window(fig_d, off_d, tick=t, wrap=True, batch=B)
+            out, st = e.solve(xu, x0, goals)
+            pk = e.pack_best(st, out, index_offset=5)
+            xu, x0 = e.shift(out, steps=1, tail="repeat")
+            assert torch.equal(out, tk.out) and torch.equal(st, tk.stats) and torch.equal(pk[B:], tk.best)
+            assert torch.equal(xu, tk.xu) and torch.equal(x0, tk.x0)
