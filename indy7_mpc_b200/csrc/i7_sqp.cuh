@@ -287,7 +287,10 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
         // a column of joint j costs ~ (6 - j) link terms and a warp owns whole columns (slots w, w + NT/32, ...):
         // the order below gives every warp of a 256-thread CTA at most 6 units of work (10 in natural order)
         const int slot = t / np, k = t - slot * np;
-        const int col = (int)((0xB9A471605382ull >> (4 * slot)) & 15);       // q2 v2 q3 q5 q0 v0 q1 v1 q4 v4 v3 v5
+        // (128-thread CTA, four warps: q0 q3 q5 | v0 v3 v5 | q1 q2 q4 | v1 v2 v4 — 10, 10, 11, 11 units against 12 with
+        // the 256-thread order)
+        const int col = NT == 128 ? (int)((0xA4B582937160ull >> (4 * slot)) & 15)       // q0 v0 q1 v1 q3 v3 q2 v2 q5 v5 q4 v4
+                                  : (int)((0xB9A471605382ull >> (4 * slot)) & 15);      // q2 v2 q3 q5 q0 v0 q1 v1 q4 v4 v3 v5
         if (k >= nk) continue;
         T* kr = M.kr + KR_STRIDE * k;
         // the raw columns land in the GQ / GV slots, which hold cos / sin and the origin until here: every column
