@@ -157,7 +157,7 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
     // task index = major * np + knot.  With a whole horizon per CTA the knots are padded to whole warps so that the
     // lanes of a warp share the major index (link | column: uniform trip counts and predicates); with a few knots
     // per CTA (cluster form) the tasks are packed densely instead — idle lanes would only waste FP64 issue slots
-    const int np = nk > 16 ? (nk + 31) & ~31 : nk;
+    const int np = nk > 24 ? (nk + 31) & ~31 : nk;       // (a 20-knot tile padded to 32 would idle 3 lanes in 8)
     // W0: cos / sin of every joint angle
     for (int t = tid; t < 6 * nc; t += NT) {
         const int i = t / nc, k = t - i * nc;
@@ -283,10 +283,12 @@ __device__ void phase_setup(const Robot<T>& rob, const SolveParams<T>& P, const 
             else kr[KR_GV + 6 * i + j] = wf_dgather<T, false>(kr + WS_S, kr + WS_F, pr, j, i);
         }
     } else {
-    for (int t = tid; t < 12 * np; t += NT) {
+    // (whole warps per column here even for a 17..24-knot tile: with mixed columns in a warp the longest one sets the pace)
+    const int np5 = nk > 16 ? (nk + 31) & ~31 : nk;
+    for (int t = tid; t < 12 * np5; t += NT) {
         // a column of joint j costs ~ (6 - j) link terms and a warp owns whole columns (slots w, w + NT/32, ...):
         // the order below gives every warp of a 256-thread CTA at most 6 units of work (10 in natural order)
-        const int slot = t / np, k = t - slot * np;
+        const int slot = t / np5, k = t - slot * np5;
         // (128-thread CTA, four warps: q0 q3 q5 | v0 v3 v5 | q1 q2 q4 | v1 v2 v4 — 10, 10, 11, 11 units against 12 with
         // the 256-thread order)
         const int col = NT == 128 ? (int)((0xA4B582937160ull >> (4 * slot)) & 15)       // q0 v0 q1 v1 q3 v3 q2 v2 q5 v5 q4 v4
@@ -836,6 +838,9 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, int o_work, 
         // stages [ka, kb) by warp 0; gp(k) = gains of stage k; the gain row of the next stage is fetched while the
         // current one is applied
         auto roll = [&](int ka, int kb, auto gp) {
+            // the warp may arrive here still split by the loops in front of it (lanes with different trip counts): without
+            // re-convergence every shuffle below takes the divergent slow path (measured: 600 instead of 225 cycles / stage)
+            __syncwarp();
             T g[12], ff;
             {
                 const T* G = gp(ka);
@@ -863,6 +868,7 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, int o_work, 
                 my_q = my_q + dt * my_v;
                 my_v = vn;
                 if (tid < 6) { z[18 * (k + 1) + row] = my_q; z[18 * (k + 1) + 6 + row] = vn; }
+                __syncwarp();
 #pragma unroll
                 for (int i = 0; i < 6; ++i) {
                     x[i] = x[i] + dt * x[6 + i];
@@ -881,9 +887,17 @@ __device__ __noinline__ void riccati_sweep(const SolveParams<T>& P, int o_work, 
             for (int c0 = 0; c0 < N - 1; c0 += cap) {
                 const int nst = N - 1 - c0 < cap ? N - 1 - c0 : cap;
                 __syncthreads();
-                for (int t = tid; t < nst * GAIN_LEN; t += NT) {
-                    const int k = t / GAIN_LEN, e = t - GAIN_LEN * k;
-                    ring[t] = src.gain(c0 + k)[e];
+                // a warp per stage, three independent loads per lane, four stages in flight: the copy is bound by the
+                // L2 round trip, so what matters is how many loads are outstanding (one element per thread per iteration
+                // with a division in the address left them serialised: 34 k cycles for the two chunks of N = 128)
+#pragma unroll 4
+                for (int k = tid >> 5; k < nst; k += NT / 32) {
+                    const T* gk = src.gain(c0 + k);
+                    const int l0 = tid & 31;
+                    const T v0 = gk[l0], v1 = gk[l0 + 32], v2 = l0 + 64 < GAIN_LEN ? gk[l0 + 64] : T(0);
+                    T* rk = ring + GAIN_LEN * k;
+                    rk[l0] = v0; rk[l0 + 32] = v1;
+                    if (l0 + 64 < GAIN_LEN) rk[l0 + 64] = v2;
                 }
                 __syncthreads();
                 if (tid < 32) roll(c0, c0 + nst, [&](int k) { return (const T*)(ring + GAIN_LEN * (k - c0)); });
