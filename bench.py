@@ -494,7 +494,7 @@ def run_b200(args):
     pin = lambda shape: torch.empty(shape, dtype=tdt).pin_memory()
     p_xu, p_x0, p_goals = pin((B, nz)), pin((B, 12)), pin((B, 3 * N))
     e2e_p2p = use_p2p and i7d.connect_peers(solver.engine, rank, world)
-    e2e_exchange = make_exchange(solver.engine, e2e_p2p)
+    e2e_exchange = "p2p" if e2e_p2p else make_exchange(solver.engine, e2e_p2p)     # "p2p": the bound fast path of step()
 
     def e2e_loop(full):
         """W + K closed-loop ticks from HOST buffers, wall clock per tick (max over ranks of the sum).

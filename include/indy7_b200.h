@@ -137,6 +137,12 @@ void i7_destroy(i7_handle* h);
 const char* i7_last_error(const i7_handle* h);  /* h may be NULL: last create error */
 
 i7_status i7_set_weights(i7_handle* h, double dQ_cost, double R_cost, double QN_cost, int32_t regularize, double eps);
+/* Run-time switches of a handle.
+ *   I7_OPT_X0_INTO_WARM_START (default 0): i7_solve / i7_solve_select overwrite the first state of every warm start with x0
+ *   while loading it — the `XU[:12] = xcur` of the reference loop (src/osqp_mpc.py:69) done inside the solve, so the
+ *   shift of a tick (i7_shift with x_cur == NULL) can run at the END of the previous tick, off the critical path. */
+#define I7_OPT_X0_INTO_WARM_START 1
+i7_status i7_set_option(i7_handle* h, int32_t option, int32_t value);
 /* f_ext: batch x 6 DOUBLES on the host, Pinocchio order [fx fy fz tx ty tz], expressed in the local frame of
  * the last joint (src/gato_mpc_batch_sample.py:97-101,158); NULL clears. */
 i7_status i7_set_external_wrench(i7_handle* h, const double* f_ext, int32_t batch);

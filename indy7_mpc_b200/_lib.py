@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(HERE, "libindy7_b200.so")
 I7_NJ, I7_STATS_LEN = 6, 12
 I7_F64, I7_F32 = 0, 1
 I7_QP_EXACT, I7_QP_OSQP = 0, 1
+I7_OPT_X0_INTO_WARM_START = 1
 
 
 class I7Model(C.Structure):
@@ -40,6 +41,7 @@ SYMBOLS = {
     "i7_destroy": (None, [_vp]),
     "i7_last_error": (C.c_char_p, [_vp]),
     "i7_set_weights": (_i32, [_vp, _dbl, _dbl, _dbl, _i32, _dbl]),
+    "i7_set_option": (_i32, [_vp, _i32, _i32]),
     "i7_set_external_wrench": (_i32, [_vp, C.POINTER(_dbl), _i32]),
     "i7_reset": (_i32, [_vp]),
     "i7_reset_rho": (_i32, [_vp]),

@@ -7,6 +7,11 @@ xcur_batch, eepos_goals_batch) -> dict``, ``reset()``, ``resetRho()``, ``resetLa
 ``set_external_wrench_batch(f_ext)``, ``sim_forward(x, u, dt) -> (B, 12)``.  The horizon N is taken from the shape
 of the first ``XU_batch`` (it is compiled into the reference binding).  Outputs are float32 like the reference
 binding; the arithmetic type is ``COMPUTE_DTYPE`` ('fp32' mirrors SQPSolverfloat; 'fp64' is the accurate mode).
+
+Environment (read at import): ``INDY7_B200_BATCH_DTYPE=fp64|fp32``; ``INDY7_B200_QP_MODE=exact|osqp`` — 'osqp' solves
+every QP by the warm-started ADMM of the reference's own solver (then ``reset`` / ``resetRho`` / ``resetLambda`` act on
+its state, as they do on the GATO solver's rho and lambda, gato_controller.py:134-138) and fills ``pcg_stats`` with its
+iteration counts; ``INDY7_B200_LIMITS=1`` adds the URDF joint limits as inequality rows (osqp mode, fp64).
 """
 import os
 
@@ -16,6 +21,8 @@ from .engine import Engine
 from .model import build_model_from_urdf
 
 COMPUTE_DTYPE = os.environ.get("INDY7_B200_BATCH_DTYPE", "fp64")
+QP_MODE = os.environ.get("INDY7_B200_QP_MODE", "exact")
+LIMITS = os.environ.get("INDY7_B200_LIMITS", "0") not in ("0", "", "false", "False")
 SUPPORTED_BATCH = (1, 2, 4, 8, 16, 32, 64, 128, 256)
 
 
@@ -34,7 +41,7 @@ class _SQPSolverBase:
         if self._engine is None or N != self._N or abs(dt - self._dt) > 0:
             if self._engine is not None:
                 self._engine.close()
-            self._engine = Engine(self._model, N=N, dt=dt, batch=self.BATCH, dtype=COMPUTE_DTYPE)
+            self._engine = Engine(self._model, N=N, dt=dt, batch=self.BATCH, dtype=COMPUTE_DTYPE, qp_mode=QP_MODE, limits=LIMITS)
             self._N, self._dt = N, dt
             self._engine.set_external_wrench(self._f_ext)
         return self._engine
@@ -56,8 +63,8 @@ class _SQPSolverBase:
             "xu_trajectory": np.asarray(out, np.float32),
             "solve_time_us": float(eng.last_solve_time_us()),
             "sqp_iterations": st[:, 0].astype(np.int32),
-            # the QP is solved directly (no PCG); one entry per QP solve, zero iterations each
-            "pcg_stats": [{"pcg_iterations": np.zeros(self.BATCH, np.int32)} for _ in range(nqp)],
+            # one entry per QP solve: exact mode — solved directly, zero iterations; osqp mode — the ADMM iterations
+            "pcg_stats": [{"pcg_iterations": st[:, 10 + i].astype(np.int32)} for i in range(nqp)],
             "line_search_stats": [{"step_size": [float(a) for a in st[:, 4 + i]]} for i in range(nqp)],
         }
 

@@ -77,6 +77,7 @@ struct i7_handle {
     int* d_done = nullptr;
     int admm_smem_bytes = 0;
     i7::AdmmSettings admm{};
+    int opt_x0_into_xu = 0;      // i7_set_option(I7_OPT_X0_INTO_WARM_START)
     int zero_copy = 1;           // I7_ZERO_COPY=0: page-locked user buffers go through copies / the chunked pipeline
     int no_events = 0;           // I7_TIMING_EVENTS=0: no timing events around mapped-memory solves (3 us of host time each)
     int direct_max_batch = 0;    // host-buffer solves up to this batch use mapped host memory instead of copies
@@ -275,6 +276,7 @@ void base_params(const i7_handle* h, i7::SolveParams<T>& P, int batch, int goal_
     P.mu = T(c.mu); P.step_tol = T(c.step_tol);
     P.fext = h->has_fext ? (const T*)h->d_fext : nullptr;
     P.prof = (mode == i7::MODE_SOLVE) ? h->d_prof : nullptr;
+    P.x0_into_xu = (mode == i7::MODE_SOLVE) ? h->opt_x0_into_xu : 0;
 }
 
 i7_status check_batch(i7_handle* h, int batch, int goal_stride) {
@@ -482,6 +484,8 @@ i7_status run_osqp(i7_handle* h, const SqpCall& c, cudaStream_t s) {
     T* stats = d_stats ? d_stats : (T*)h->d_stats;
     I7_CUDA(h, cudaEventRecord(h->ev0, s));
     if (d_out != d_xu) I7_CUDA(h, cudaMemcpyAsync(d_out, d_xu, B * nz * es, cudaMemcpyDeviceToDevice, s));
+    if (h->opt_x0_into_xu)       // I7_OPT_X0_INTO_WARM_START: XU[:12] = xcur (src/osqp_mpc.py:69)
+        I7_CUDA(h, cudaMemcpy2DAsync(d_out, nz * es, d_x0, 12 * es, 12 * es, B, cudaMemcpyDeviceToDevice, s));
     I7_CUDA(h, cudaMemsetAsync(h->d_done, 0, B * sizeof(int), s));
     for (int qp = 0; qp < h->cfg.max_qp; ++qp) {
         if ((rc = fused(i7::MODE_EXPORT, d_out, nullptr, nullptr, nullptr, h->d_done, qp))) return rc;
@@ -769,6 +773,14 @@ i7_status i7_set_weights(i7_handle* h, double dQ_cost, double R_cost, double QN_
     h->cfg.dQ_cost = dQ_cost; h->cfg.R_cost = R_cost; h->cfg.QN_cost = QN_cost;
     h->cfg.regularize = regularize; h->cfg.eps = eps;
     return I7_OK;
+}
+
+i7_status i7_set_option(i7_handle* h, int32_t option, int32_t value) {
+    if (!h) return I7_ERR_INVALID;
+    switch (option) {
+        case I7_OPT_X0_INTO_WARM_START: h->opt_x0_into_xu = value != 0; return I7_OK;
+        default: h->err = "unknown option"; return I7_ERR_INVALID;
+    }
 }
 
 i7_status i7_set_external_wrench(i7_handle* h, const double* f_ext, int32_t batch) {

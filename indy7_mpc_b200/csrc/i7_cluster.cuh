@@ -225,6 +225,7 @@ sqp_cluster_kernel(const __grid_constant__ Robot<T> rob, const __grid_constant__
             M.goals[t] = gin[k * P.goal_stride + (t - 3 * k)];
         }
         if (tid < 12) M.x0[tid] = rx;
+        if (P.x0_into_xu && tid < 12) M.xu[tid] = rx;               // same thread as the store of xu[tid] above
         if (tid < 6) s_fext[tid] = rf;
         if (tid < 6) M.xu[nz + tid] = T(0);                          // padded u_{N-1}
         for (int t = tid; t < 18 * N; t += NT) M.z[t] = T(0);

@@ -66,6 +66,8 @@ struct SolveParams {
     int* done;            // MODE_EXPORT / MODE_STEP, optional: per problem 1 = the SQP loop has ended (skipped; set by MODE_STEP)
     int qp_index;         // MODE_STEP: index of the pass (0 .. max_qp-1)
     XchgArgs xchg;        // MODE_SOLVE epilogue (enabled != 0)
+    int x0_into_xu;       // != 0: the warm start's x_0 is overwritten by x0 when the inputs are loaded (XU[:12] = xcur,
+                          // src/osqp_mpc.py:69, done here instead of by the caller / i7_shift)
     int N, batch, goal_stride, mode, max_qp, regularize;
     T dt, dQ, R, QN, eps, mu, step_tol;
 };
@@ -1200,6 +1202,7 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
             M.goals[t] = P.goals[(size_t)b * N * P.goal_stride + k * P.goal_stride + a];
         }
         if (tid < 12) M.x0[tid] = P.x0 ? P.x0[(size_t)b * 12 + tid] : T(0);
+        if (P.x0_into_xu && P.x0 && tid < 12) M.xu[tid] = P.x0[(size_t)b * 12 + tid];      // same thread as the load of xu[tid] above
         if (tid < 6) s_fext[tid] = P.fext ? P.fext[(size_t)b * 6 + tid] : T(0);
         if (P.mode == MODE_LINESEARCH || P.mode == MODE_MERIT || P.mode == MODE_STEP) {
             for (int t = tid; t < nz; t += NT) M.z[t] = P.xu_full[(size_t)b * nz + t];

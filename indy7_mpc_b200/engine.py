@@ -408,6 +408,10 @@ class Engine:
         f = np.ascontiguousarray(np.asarray(f_ext, dtype=np.float64).reshape(-1, 6))
         self._check(self.lib.i7_set_external_wrench(self._h, f.ctypes.data_as(C.POINTER(C.c_double)), f.shape[0]))
 
+    def set_option(self, option, value):
+        """i7_set_option; option: an I7_OPT_* constant of indy7_mpc_b200._lib."""
+        self._check(self.lib.i7_set_option(self._h, int(option), int(value)))
+
     def set_weights(self, dQ_cost, R_cost, QN_cost, regularize, eps):
         self._check(self.lib.i7_set_weights(self._h, float(dQ_cost), float(R_cost), float(QN_cost), int(bool(regularize)), float(eps)))
 

@@ -154,3 +154,26 @@ def test_osqp_mode_closed_loop_golden_prefix(golden):
     got, ref = np.array(mpc.goal_distances), np.array(g["goal_distances"][:12])
     assert (np.abs(got - ref) / ref).max() < 5e-6
     assert all(v == 2 for v in sqp.stats["qp_iters"]["values"])
+
+
+def test_osqp_mode_step_tick(oracle_model):
+    """Indy7SQP.step (bound buffers, x_0 of the warm start replaced inside the solve) in the osqp mode equals the generic
+    path tick after tick."""
+    import torch
+    import bench
+    import indy7_mpc_b200 as pkg
+    B, N = 6, 32
+    wl = bench.make_workload(B, N)
+    fast = pkg.Indy7SQP(N=N, batch=B, qp_mode="osqp", admm=dict(max_iter=200))
+    slow = pkg.Indy7SQP(N=N, batch=B, qp_mode="osqp", admm=dict(max_iter=200))
+    p_x0 = torch.empty(B, 12, dtype=torch.float64).pin_memory()
+    p_g = torch.empty(B, 3 * N, dtype=torch.float64).pin_memory()
+    x0 = wl["x0"].copy()
+    for t in range(3):
+        goals = bench.goals_at(wl["fig"], wl["offsets"], t, N)
+        p_x0.copy_(torch.from_numpy(x0)); p_g.copy_(torch.from_numpy(goals))
+        a = fast.step(p_x0, p_g)
+        b = slow.step(x0, goals)
+        assert np.array_equal(a["costs"], b["costs"]) and a["best_index"] == b["best_index"]
+        assert np.array_equal(a["x_next"], b["x_next"]) and np.array_equal(a["x_traj"], b["x_traj"])
+        x0 = a["x_next"].copy()

@@ -268,3 +268,46 @@ def test_device_tick_equals_generic_calls(pkg):
             xu, x0 = e.shift(out, steps=1, tail="repeat")
             assert torch.equal(out, tk.out) and torch.equal(st, tk.stats) and torch.equal(pk[B:], tk.best)
             assert torch.equal(xu, tk.xu) and torch.equal(x0, tk.x0)
+
+
+def test_indy7sqp_step_bound_path_equals_generic(pkg):
+    """Indy7SQP.step — the closed-loop tick of the end-to-end arm — on buffers bound once (page-locked torch inputs)
+    returns what the generic path (numpy inputs) returns, tick after tick, and both equal the explicit sequence
+    shift -> solve -> pack_best of Engine calls."""
+    import torch
+    import bench
+    B, N = 40, 32
+    wl = bench.make_workload(B, N)
+    fast = pkg.Indy7SQP(N=N, batch=B, cluster=1)
+    slow = pkg.Indy7SQP(N=N, batch=B, cluster=1)
+    eng = pkg.Engine(N=N, batch=B, cluster=1)
+    for s in (fast, slow):
+        s.set_external_wrench(wl["f_ext"])
+    eng.set_external_wrench(wl["f_ext"])
+    p_x0 = torch.empty(B, 12, dtype=torch.float64).pin_memory()
+    p_g = torch.empty(B, 3 * N, dtype=torch.float64).pin_memory()
+    x0 = wl["x0"].copy()
+    prev = None
+    for t in range(4):
+        goals = bench.goals_at(wl["fig"], wl["offsets"], t, N)
+        p_x0.copy_(torch.from_numpy(x0)); p_g.copy_(torch.from_numpy(goals))
+        a = fast.step(p_x0, p_g, index_offset=3)
+        b = slow.step(x0, goals, index_offset=3)
+        if prev is None:
+            xu = np.zeros((B, 18 * N - 6)); xu[:, :12] = x0
+        else:
+            xu, _ = eng.shift(prev, steps=1, tail="repeat", x_cur=x0, want_x0=False)
+        out, st = eng.solve(np.asarray(xu), x0, goals)
+        pk = np.asarray(eng.pack_best(st, out, index_offset=3))
+        prev = np.asarray(out)
+        for r in (a, b):
+            assert np.array_equal(r["costs"], pk[:B]) and r["best_cost"] == pk[B] and r["best_index"] == int(pk[B + 1])
+            assert np.array_equal(r["x_next"], prev[:, 18:30])
+            assert np.array_equal(np.concatenate([r["x_traj"], np.vstack([r["u_traj"], np.zeros((1, 6))])], axis=1).reshape(-1)[:18 * N - 6], pk[B + 2:])
+        x0 = a["x_next"].copy()
+    fast.reset()
+    p_x0.copy_(torch.from_numpy(wl["x0"])); p_g.copy_(torch.from_numpy(bench.goals_at(wl["fig"], wl["offsets"], 0, N)))
+    again = fast.step(p_x0, p_g, index_offset=3)           # after reset: the cold first tick again
+    cold = pkg.Indy7SQP(N=N, batch=B, cluster=1); cold.set_external_wrench(wl["f_ext"])
+    ref = cold.step(wl["x0"], bench.goals_at(wl["fig"], wl["offsets"], 0, N), index_offset=3)
+    assert np.array_equal(again["costs"], ref["costs"])
