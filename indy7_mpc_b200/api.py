@@ -124,17 +124,24 @@ class Indy7SQP:
                 "started": False, "nrec": nrec,
             }
             tb["p"] = {k: tb[k].data_ptr() for k in ("xu", "out", "stats", "buf")}
-            eng.set_option(_lib.I7_OPT_X0_INTO_WARM_START, 1)
         p = tb["p"]
         stream = torch.cuda.current_stream(dev).cuda_stream
         p_x0, p_ref = x0.data_ptr(), xref.data_ptr()
         gs = xref.numel() // (B * self.N)
         if gs not in (3, 6):
             raise ValueError(f"xref must hold N*3 or N*6 numbers per problem, got {xref.numel() // B} for N={self.N}")
+        if self._tick_prev is not None and self._tick_prev is not tb["out"]:
+            # the previous tick went through the generic path (other kinds of inputs): take its solution over
+            xu_prev, _ = eng.shift(self._tick_prev, steps=1, tail="repeat", want_x0=False)
+            tb["xu"].copy_(xu_prev)
+            tb["started"] = True
         if not tb["started"]:
             tb["xu"].zero_()
             tb["started"] = True
-        eng._check(lib.i7_solve(eng._h, B, p["xu"], p_x0, p_ref, gs, p["out"], p["stats"], stream))
+        lib.i7_set_option(eng._h, _lib.I7_OPT_X0_INTO_WARM_START, 1)        # for this launch only: solve() keeps the
+        rc = lib.i7_solve(eng._h, B, p["xu"], p_x0, p_ref, gs, p["out"], p["stats"], stream)     # reference's semantics
+        lib.i7_set_option(eng._h, _lib.I7_OPT_X0_INTO_WARM_START, 0)
+        eng._check(rc)
         n = 2 + nz if exchange == "p2p" else tb["nrec"]
         es = tb["buf"].element_size()
         if exchange == "p2p":

@@ -305,6 +305,18 @@ def test_indy7sqp_step_bound_path_equals_generic(pkg):
             assert np.array_equal(r["x_next"], prev[:, 18:30])
             assert np.array_equal(np.concatenate([r["x_traj"], np.vstack([r["u_traj"], np.zeros((1, 6))])], axis=1).reshape(-1)[:18 * N - 6], pk[B + 2:])
         x0 = a["x_next"].copy()
+    # alternating the two paths on ONE solver keeps the closed loop intact (the bound path takes over the generic path's
+    # last solution and vice versa)
+    mixed = pkg.Indy7SQP(N=N, batch=B, cluster=1); mixed.set_external_wrench(wl["f_ext"])
+    pure = pkg.Indy7SQP(N=N, batch=B, cluster=1); pure.set_external_wrench(wl["f_ext"])
+    x0m = wl["x0"].copy()
+    for t in range(4):
+        goals = bench.goals_at(wl["fig"], wl["offsets"], t, N)
+        p_x0.copy_(torch.from_numpy(x0m)); p_g.copy_(torch.from_numpy(goals))
+        rm = mixed.step(p_x0, p_g) if t % 2 == 0 else mixed.step(x0m, goals)
+        rp = pure.step(x0m, goals)
+        assert np.array_equal(rm["costs"], rp["costs"]) and np.array_equal(rm["x_next"], rp["x_next"]), t
+        x0m = rp["x_next"].copy()
     fast.reset()
     p_x0.copy_(torch.from_numpy(wl["x0"])); p_g.copy_(torch.from_numpy(bench.goals_at(wl["fig"], wl["offsets"], 0, N)))
     again = fast.step(p_x0, p_g, index_offset=3)           # after reset: the cold first tick again
