@@ -35,6 +35,15 @@ def test_config_struct_layout_matches_header():
     assert (cfg.N, cfg.batch, cfg.dtype, cfg.max_qp, cfg.regularize) == (32, 1, 0, 2, 1)
     assert (cfg.dt, cfg.dQ_cost, cfg.R_cost, cfg.QN_cost, cfg.eps, cfg.mu, cfg.step_tol) == (0.01, 0.01, 1e-5, 100.0, 1.0, 10.0, 1e-3)
     assert cfg.model.gravity[2] == -9.81
+    # round-2 fields: QP mode and OSQP's default settings (src/osqp_solver.py:39-41 relies on them), limits off and unbounded
+    assert (cfg.qp_mode, cfg.limits, cfg.admm_max_iter, cfg.admm_check) == (_lib.I7_QP_EXACT, 0, 4000, 25)
+    assert (cfg.admm_rho, cfg.admm_rho_u, cfg.admm_sigma, cfg.admm_alpha, cfg.admm_eps_abs, cfg.admm_eps_rel) == (0.1, 1e-3, 1e-6, 1.6, 1e-3, 1e-3)
+    assert cfg.model.q_min[0] == -1e30 and cfg.model.u_max[5] == 1e30
+    # the model fills the limits of description/indy7.urdf:203-238 in
+    from indy7_mpc_b200 import build_model_from_urdf
+    m = build_model_from_urdf().to_c()
+    assert abs(m.q_max[0] - 3.0543261909900767) < 1e-15 and abs(m.q_min[5] + 3.7524578917878086) < 1e-15
+    assert abs(m.v_max[3] - 3.141592653589793) < 1e-15 and m.u_max[2] == 197.23
 
 
 def test_product_urdf_loader_agrees_with_oracle_loader(oracle_model):
