@@ -49,11 +49,24 @@ struct AdmmParams {
 };
 
 constexpr int ADMM_NT = 128;     // two CTAs per SM (registers: the in-register 18 x 18 factorisation), three where shared memory allows
+// per knot: L^-1 (18 x 18 row-major, zeros above the diagonal), M (18 x 18) and F (18 x 12) in planes of column PAIRS:
+// element (i, c) at ((c / 2) * 18 + i) * 2 + c % 2, so that lane i of the serial chains reads its row as 16-byte vectors
+// (one warp's instruction count bounds a stage) AND the 18 lanes of a load touch 288 contiguous bytes (coalesced)
 constexpr int FAC_LINV = 0, FAC_MT = 324, FAC_FT = 648, FAC_STRIDE = 864;
 // shared memory: the vectors (156 N), the stage scratch of the factorisation, and — while it fits — the QP blocks
 // (QB_STRIDE N), which every iteration reads twice (A x~ and A' t)
-__host__ __device__ inline int admm_smem_len(int N, bool blocks) { return 156 * N + 2 * 324 + 2 * 216 + 108 + 16 + 64 + (blocks ? QB_STRIDE * N : 0); }
+// serial chains: the stage matrices are staged through shared memory in groups of ADMM_CG stages, double-buffered: while
+// warp 0 works through group g the other warps (idle during the chain) copy group g + 1 from the L2 workspace.  Measured
+// alternatives: rows prefetched from L2 into registers two stages ahead (warp 0 waits for them: 285 k / 216 k cycles per
+// QP for the forward / backward chain against 238 k / 209 k), a three-slot ring of three stages filled two groups ahead with
+// cp.async (286 k / 228 k: the larger shared-memory footprint costs more than the deeper prefetch gains).
+constexpr int ADMM_CG = 4, ADMM_SLOTS = 2;
+// shared memory: the vectors (156 N), the stage scratch of the factorisation, the ring of the chains and — while it fits —
+// the QP blocks (QB_STRIDE N), which every iteration reads twice (A x~ and A' t)
 constexpr int ADMM_BLOCKS_IN_SMEM_MAX_N = 64;
+__host__ __device__ inline int admm_smem_len(int N, bool blocks) {
+    return 156 * N + 2 * 324 + 2 * 216 + 108 + 16 + 64 + ADMM_SLOTS * ADMM_CG * 324 + (blocks ? QB_STRIDE * N : 0);
+}
 
 // element (r, c) of G^ = [Gq Gv Hm] (6 x 18) in a QB block
 template <typename T> I7_DEV T ghat(const T* blk, int r, int c) {
@@ -63,6 +76,7 @@ template <typename T> I7_DEV T ghat(const T* blk, int r, int c) {
 template <typename T>
 __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant__ AdmmParams<T> P) {
     constexpr int NT = ADMM_NT;
+    static_assert(sizeof(T) == 8, "the ADMM kernel is fp64 only (16-byte vector loads of pairs of doubles)");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* sm = reinterpret_cast<T*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, N = P.N;
@@ -87,7 +101,8 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
     T* s_Gh = s_Gn + 216;        // 108  G^_k (6 x 18)
     T* s_ck = s_Gh + 108;        // 16   cost terms of the knot
     T* s_red = s_ck + 16;        // 64   reduction scratch
-    T* s_blk = s_red + 64;       // QB_STRIDE N  the QP blocks (short horizons only)
+    T* s_ring = s_red + 64;      // ADMM_SLOTS x ADMM_CG x 324  stage matrices of the serial chains, double-buffered by group
+    T* s_blk = s_ring + ADMM_SLOTS * ADMM_CG * 324;   // QB_STRIDE N  the QP blocks (short horizons only)
     const bool blk_smem = N <= ADMM_BLOCKS_IN_SMEM_MAX_N;
     __shared__ int s_stop;
 
@@ -197,7 +212,7 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
                     T acc = T(0);
 #pragma unroll
                     for (int c = 0; c < 12; ++c) acc += s_X[18 * i + c] * s_G[12 * j + c];
-                    fk[FAC_MT + 18 * j + i] = acc;
+                    fk[FAC_MT + ((j >> 1) * 18 + i) * 2 + (j & 1)] = acc;
                 }
             }
             __syncthreads();
@@ -207,7 +222,7 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
                     const int i = e / 12, j = e - 12 * i;
                     T acc = T(0);
                     for (int r = i; r < 18; ++r) acc += s_X[18 * r + i] * s_Gn[12 * r + j];
-                    fk[FAC_FT + 18 * j + i] = acc;
+                    fk[FAC_FT + ((j >> 1) * 18 + i) * 2 + (j & 1)] = acc;
                 }
                 for (int e = tid; e < 216; e += NT) s_G[e] = s_Gn[e];   // nobody reads G_{k-1} any more
             }
@@ -307,37 +322,59 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
             }
             __syncthreads();
             I7_ACC(4);
-            // (4) forward chain  w_k = a_k - M_k w_{k-1}   (warp 0; lane i = component i).  The stage matrices are held
-            //     in three register buffers used in rotation (static renaming, no moves): the one consumed two stages from
-            //     now is being fetched while the current one is applied (an L2 round trip is ~2.5 stages of this chain)
-            if (warp == 0) {
-                const int li = lane < 18 ? lane : 0;
-                T mA[18], mB[18], mC[18];
-                T w = s_b2[li];
-                auto load = [&](T (&m)[18], int k) {
-                    const T* Mk = fac + (size_t)(k < N ? k : N - 1) * FAC_STRIDE + FAC_MT + li;
+            // (4) forward chain  w_k = a_k - M_k w_{k-1}   (warp 0; lane i = component i).  One warp's instruction count
+            //     bounds a stage: a lane reads its row of M_k and w_{k-1} as 16-byte vectors from SHARED memory.  The
+            //     matrices get there in groups of ADMM_CG stages: while warp 0 works through group g, the other warps copy
+            //     group g + 1 into the other half of the ring — every load of a filler thread issued before its first store
+            //     (one L2 round trip per group, not one per element)
+            {
+                const int nst = N - 1, ngrp = (nst + ADMM_CG - 1) / ADMM_CG;
+                auto fill = [&](int g, int t0, int nthr) {
+                    const int k0 = 1 + g * ADMM_CG;
+                    const int ns = N - k0 < ADMM_CG ? N - k0 : ADMM_CG;
+                    double2* dst = reinterpret_cast<double2*>(s_ring + (g & 1) * ADMM_CG * 324);
+                    constexpr int R = (ADMM_CG * 162 + (NT - 32) - 1) / (NT - 32);
+                    double2 v[R];
 #pragma unroll
-                    for (int j = 0; j < 18; ++j) m[j] = Mk[18 * j];
-                };
-                auto stage = [&](const T (&m)[18], int k) {
-                    __syncwarp();
-                    T a0 = s_b2[18 * k + li], a1 = T(0), a2 = T(0);
-#pragma unroll
-                    for (int j = 0; j < 18; j += 3) {
-                        a0 -= m[j] * __shfl_sync(0xffffffffu, w, j);
-                        a1 -= m[j + 1] * __shfl_sync(0xffffffffu, w, j + 1);
-                        a2 -= m[j + 2] * __shfl_sync(0xffffffffu, w, j + 2);
+                    for (int r = 0; r < R; ++r) {
+                        const int e = (tid - t0) + r * nthr;
+                        if (e < ns * 162) {
+                            const int st = e / 162, q = e - 162 * st;
+                            v[r] = reinterpret_cast<const double2*>(fac + (size_t)(k0 + st) * FAC_STRIDE + FAC_MT)[q];
+                        }
                     }
-                    w = a0 + (a1 + a2);
-                    if (lane < 18) s_b2[18 * k + lane] = w;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const int e = (tid - t0) + r * nthr;
+                        if (e < ns * 162) dst[e] = v[r];
+                    }
                 };
-                load(mA, 1); load(mB, 2);
-                for (int k = 1; k < N; k += 3) {
-                    load(mC, k + 2); stage(mA, k);
-                    if (k + 1 >= N) break;
-                    load(mA, k + 3); stage(mB, k + 1);
-                    if (k + 2 >= N) break;
-                    load(mB, k + 4); stage(mC, k + 2);
+                fill(0, 0, NT);
+                __syncthreads();
+                for (int g = 0; g < ngrp; ++g) {
+                    if (warp == 0) {
+                        const int li = lane < 18 ? lane : 0;
+                        const int k0 = 1 + g * ADMM_CG;
+                        for (int st = 0; st < ADMM_CG && k0 + st < N; ++st) {
+                            const int k = k0 + st;
+                            const double2* Mr = reinterpret_cast<const double2*>(s_ring + (g & 1) * ADMM_CG * 324 + 324 * st) + li;
+                            __syncwarp();                         // w_{k-1} written by the lanes below is visible
+                            const double2* wp = reinterpret_cast<const double2*>(s_b2 + 18 * (k - 1));
+                            T a0 = s_b2[18 * k + li], a1 = T(0), a2 = T(0);
+#pragma unroll
+                            for (int j = 0; j < 9; j += 3) {
+                                const double2 m0 = Mr[18 * j], m1 = Mr[18 * (j + 1)], m2 = Mr[18 * (j + 2)];
+                                const double2 w0 = wp[j], w1 = wp[j + 1], w2 = wp[j + 2];
+                                a0 -= m0.x * w0.x; a0 -= m0.y * w0.y;
+                                a1 -= m1.x * w1.x; a1 -= m1.y * w1.y;
+                                a2 -= m2.x * w2.x; a2 -= m2.y * w2.y;
+                            }
+                            if (lane < 18) s_b2[18 * k + lane] = a0 + (a1 + a2);
+                        }
+                    } else if (g + 1 < ngrp) {
+                        fill(g + 1, 32, NT - 32);
+                    }
+                    __syncthreads();
                 }
             }
             __syncthreads();
@@ -357,35 +394,55 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
             }
             __syncthreads();
             I7_ACC(6);
-            // (6) backward chain  x_k = c_k - F_k x_{k+1}[:12]   (warp 0), same rotation of three register buffers
-            if (warp == 0) {
-                const int li = lane < 18 ? lane : 0;
-                T fA[12], fB[12], fC[12];
-                T xv = s_b1[18 * (N - 1) + li];
-                auto load = [&](T (&f)[12], int k) {
-                    const T* Fk = fac + (size_t)(k > 0 ? k : 0) * FAC_STRIDE + FAC_FT + li;
+            // (6) backward chain  x_k = c_k - F_k x_{k+1}[:12]   (warp 0), same scheme: groups of stages from the top
+            {
+                const int nst = N - 1, ngrp = (nst + ADMM_CG - 1) / ADMM_CG;
+                auto fill = [&](int g, int t0, int nthr) {
+                    const int k0 = N - 2 - g * ADMM_CG;             // stages k0, k0 - 1, ...
+                    const int ns = k0 + 1 < ADMM_CG ? k0 + 1 : ADMM_CG;
+                    double2* dst = reinterpret_cast<double2*>(s_ring + (g & 1) * ADMM_CG * 324);
+                    constexpr int R = (ADMM_CG * 108 + (NT - 32) - 1) / (NT - 32);
+                    double2 v[R];
 #pragma unroll
-                    for (int j = 0; j < 12; ++j) f[j] = Fk[18 * j];
-                };
-                auto stage = [&](const T (&f)[12], int k) {
-                    __syncwarp();
-                    T a0 = s_b1[18 * k + li], a1 = T(0), a2 = T(0);
-#pragma unroll
-                    for (int j = 0; j < 12; j += 3) {
-                        a0 -= f[j] * __shfl_sync(0xffffffffu, xv, j);
-                        a1 -= f[j + 1] * __shfl_sync(0xffffffffu, xv, j + 1);
-                        a2 -= f[j + 2] * __shfl_sync(0xffffffffu, xv, j + 2);
+                    for (int r = 0; r < R; ++r) {
+                        const int e = (tid - t0) + r * nthr;
+                        if (e < ns * 108) {
+                            const int st = e / 108, q = e - 108 * st;
+                            v[r] = reinterpret_cast<const double2*>(fac + (size_t)(k0 - st) * FAC_STRIDE + FAC_FT)[q];
+                        }
                     }
-                    xv = a0 + (a1 + a2);
-                    if (lane < 18) s_b1[18 * k + lane] = xv;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const int e = (tid - t0) + r * nthr;
+                        if (e < ns * 108) dst[e] = v[r];
+                    }
                 };
-                load(fA, N - 2); load(fB, N - 3);
-                for (int k = N - 2; k >= 0; k -= 3) {
-                    load(fC, k - 2); stage(fA, k);
-                    if (k - 1 < 0) break;
-                    load(fA, k - 3); stage(fB, k - 1);
-                    if (k - 2 < 0) break;
-                    load(fB, k - 4); stage(fC, k - 2);
+                fill(0, 0, NT);
+                __syncthreads();
+                for (int g = 0; g < ngrp; ++g) {
+                    if (warp == 0) {
+                        const int li = lane < 18 ? lane : 0;
+                        const int k0 = N - 2 - g * ADMM_CG;
+                        for (int st = 0; st < ADMM_CG && k0 - st >= 0; ++st) {
+                            const int k = k0 - st;
+                            const double2* Fr = reinterpret_cast<const double2*>(s_ring + (g & 1) * ADMM_CG * 324 + 216 * st) + li;
+                            __syncwarp();
+                            const double2* xp = reinterpret_cast<const double2*>(s_b1 + 18 * (k + 1));
+                            T a0 = s_b1[18 * k + li], a1 = T(0), a2 = T(0);
+#pragma unroll
+                            for (int j = 0; j < 6; j += 3) {
+                                const double2 f0 = Fr[18 * j], f1 = Fr[18 * (j + 1)], f2 = Fr[18 * (j + 2)];
+                                const double2 x0 = xp[j], x1 = xp[j + 1], x2 = xp[j + 2];
+                                a0 -= f0.x * x0.x; a0 -= f0.y * x0.y;
+                                a1 -= f1.x * x1.x; a1 -= f1.y * x1.y;
+                                a2 -= f2.x * x2.x; a2 -= f2.y * x2.y;
+                            }
+                            if (lane < 18) s_b1[18 * k + lane] = a0 + (a1 + a2);
+                        }
+                    } else if (g + 1 < ngrp) {
+                        fill(g + 1, 32, NT - 32);
+                    }
+                    __syncthreads();
                 }
             }
             __syncthreads();
