@@ -52,7 +52,9 @@ constexpr int ADMM_NT = 128;     // two CTAs per SM (registers: the in-register 
 // per knot: L^-1 (18 x 18 row-major, zeros above the diagonal), M (18 x 18) and F (18 x 12) in planes of column PAIRS:
 // element (i, c) at ((c / 2) * 18 + i) * 2 + c % 2, so that lane i of the serial chains reads its row as 16-byte vectors
 // (one warp's instruction count bounds a stage) AND the 18 lanes of a load touch 288 contiguous bytes (coalesced)
-constexpr int FAC_LINV = 0, FAC_MT = 324, FAC_FT = 648, FAC_STRIDE = 864;
+// L^-1 is kept twice, as planes of COLUMN pairs (FAC_LA: (i, c) at ((c / 2) * 18 + i) * 2 + c % 2, read by a = L^-1 r) and of
+// ROW pairs (FAC_LB: (r, i) at ((r / 2) * 18 + i) * 2 + r % 2, read by c = L^-T w): either product is nine coalesced 16-byte loads
+constexpr int FAC_LA = 0, FAC_LB = 324, FAC_MT = 648, FAC_FT = 972, FAC_STRIDE = 1188;
 // shared memory: the vectors (156 N), the stage scratch of the factorisation, and — while it fits — the QP blocks
 // (QB_STRIDE N), which every iteration reads twice (A x~ and A' t)
 // serial chains: the stage matrices are staged through shared memory in groups of ADMM_CG stages, double-buffered: while
@@ -194,7 +196,11 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
             __syncthreads();
             // G_k = X E_k with E_k = -rho [A_k B_k]' ; M_k = X[:, :12] G_{k-1}' ; L^-1 to the workspace
             T* fk = fac + (size_t)k * FAC_STRIDE;
-            for (int e = tid; e < 324; e += NT) fk[FAC_LINV + e] = s_X[e];
+            for (int e = tid; e < 324; e += NT) {
+                const int i = e / 18, c = e - 18 * i;               // s_X[e] = L^-1 (i, c)
+                fk[FAC_LA + ((c >> 1) * 18 + i) * 2 + (c & 1)] = s_X[e];
+                fk[FAC_LB + ((i >> 1) * 18 + c) * 2 + (i & 1)] = s_X[e];
+            }
             if (k < N - 1) {
                 for (int e = tid; e < 216; e += NT) {
                     const int i = e / 12, c = e - 12 * i;
@@ -310,14 +316,19 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
                 const int k = i / 18, e = i - 18 * k;
                 // full 18-term rows (the stored factor has explicit zeros above the diagonal): 18 independent loads in
                 // flight instead of a dependent load-FMA chain of data-dependent length
-                const T* Li = fac + (size_t)k * FAC_STRIDE + FAC_LINV + 18 * e;
-                const T* rk = s_b1 + 18 * k;
-                T lv[18];
+                const double2* Li = reinterpret_cast<const double2*>(fac + (size_t)k * FAC_STRIDE + FAC_LA) + e;
+                const double2* rk = reinterpret_cast<const double2*>(s_b1 + 18 * k);
+                double2 lv[9];
 #pragma unroll
-                for (int c = 0; c < 18; ++c) lv[c] = Li[c];
+                for (int c = 0; c < 9; ++c) lv[c] = Li[18 * c];
                 T a0 = T(0), a1 = T(0), a2 = T(0);
 #pragma unroll
-                for (int c = 0; c < 18; c += 3) { a0 += lv[c] * rk[c]; a1 += lv[c + 1] * rk[c + 1]; a2 += lv[c + 2] * rk[c + 2]; }
+                for (int c = 0; c < 9; c += 3) {
+                    const double2 r0 = rk[c], r1 = rk[c + 1], r2 = rk[c + 2];
+                    a0 += lv[c].x * r0.x; a0 += lv[c].y * r0.y;
+                    a1 += lv[c + 1].x * r1.x; a1 += lv[c + 1].y * r1.y;
+                    a2 += lv[c + 2].x * r2.x; a2 += lv[c + 2].y * r2.y;
+                }
                 s_b2[i] = a0 + (a1 + a2);
             }
             __syncthreads();
@@ -382,14 +393,19 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
             // (5) c = L^-T w
             for (int i = tid; i < nv; i += NT) {
                 const int k = i / 18, e = i - 18 * k;
-                const T* Lk = fac + (size_t)k * FAC_STRIDE + FAC_LINV + e;
-                const T* wk = s_b2 + 18 * k;
-                T lv[18];
+                const double2* Lk = reinterpret_cast<const double2*>(fac + (size_t)k * FAC_STRIDE + FAC_LB) + e;
+                const double2* wk = reinterpret_cast<const double2*>(s_b2 + 18 * k);
+                double2 lv[9];
 #pragma unroll
-                for (int r = 0; r < 18; ++r) lv[r] = Lk[18 * r];
+                for (int r = 0; r < 9; ++r) lv[r] = Lk[18 * r];
                 T a0 = T(0), a1 = T(0), a2 = T(0);
 #pragma unroll
-                for (int r = 0; r < 18; r += 3) { a0 += lv[r] * wk[r]; a1 += lv[r + 1] * wk[r + 1]; a2 += lv[r + 2] * wk[r + 2]; }
+                for (int r = 0; r < 9; r += 3) {
+                    const double2 w0 = wk[r], w1 = wk[r + 1], w2 = wk[r + 2];
+                    a0 += lv[r].x * w0.x; a0 += lv[r].y * w0.y;
+                    a1 += lv[r + 1].x * w1.x; a1 += lv[r + 1].y * w1.y;
+                    a2 += lv[r + 2].x * w2.x; a2 += lv[r + 2].y * w2.y;
+                }
                 s_b1[i] = a0 + (a1 + a2);
             }
             __syncthreads();
