@@ -107,6 +107,12 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
     T* s_blk = s_ring + ADMM_SLOTS * ADMM_CG * 324;   // QB_STRIDE N  the QP blocks (short horizons only)
     const bool blk_smem = N <= ADMM_BLOCKS_IN_SMEM_MAX_N;
     __shared__ int s_stop;
+    __shared__ unsigned short s_tri[171];       // (row << 8 | column) of the lower-triangular entries of an 18 x 18 block
+    for (int e = tid; e < 324; e += NT) {
+        const int a = e / 18, c = e - 18 * a;
+        if (c <= a) s_tri[(a * (a + 1)) / 2 + c] = (unsigned short)((a << 8) | c);
+    }
+    __syncthreads();
 
     for (int b = blockIdx.x; b < P.batch; b += gridDim.x) {
         if (P.done && P.done[b]) continue;
@@ -124,19 +130,21 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
         auto hi_of = [&](int e) { return e < 6 ? T(S.qmax[e]) : (e < 12 ? T(S.vmax[e - 6]) : T(S.umax[e - 12])); };
 
         long long* prof = P.prof ? P.prof + (size_t)b * 32 : nullptr;
-        long long pacc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, ptt = prof ? clock64() : 0;
+        long long pacc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, ptt = prof ? clock64() : 0, pt2 = 0;
+#define I7_SUB(i) do { if (prof) { const long long n_ = clock64(); pacc[i] += n_ - pt2; pt2 = n_; } } while (0)
 // every thread keeps the counters (a branch on tid == 0 here would leave warp 0 diverged in front of its shuffle chains)
 #define I7_ACC(i) do { if (prof) { const long long n_ = clock64(); pacc[i] += n_ - ptt; ptt = n_; } } while (0)
         // ---------------------------------------------------------------- factorisation ----------------
         for (int k = 0; k < N; ++k) {
             const T* bk = blk + (size_t)k * QB_STRIDE;
+            if (prof) pt2 = clock64();
             if (tid < 108) s_Gh[tid] = k < N - 1 ? ghat<T>(bk, tid / 18, tid % 18) : T(0);
             if (tid >= 112 && tid < 112 + 9) s_ck[tid - 112] = bk[QB_COST + tid - 112];
             __syncthreads();
             // pivot block D = H_kk - G_{k-1}' G_{k-1} (x x part), lower triangle
-            for (int e = tid; e < 324; e += NT) {
-                const int a = e / 18, c = e - 18 * a;
-                if (c > a) continue;
+            for (int e0 = tid; e0 < 171; e0 += NT) {
+                const int a = s_tri[e0] >> 8, c = s_tri[e0] & 255;         // lower triangle only: 171 tasks, not 324
+                const int e = 18 * a + c;
                 T v = T(0);
                 if (k < N - 1) {
                     T acc = T(0);
@@ -159,6 +167,7 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
                 s_D[e] = v;
             }
             __syncthreads();
+            I7_SUB(12);
             // Cholesky D = L L' and X = L^-1 by warp 0, in registers: lane i owns row i of L and column i of X
             if (warp == 0) {
                 __syncwarp();
@@ -194,6 +203,7 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
                 }
             }
             __syncthreads();
+            I7_SUB(13);
             // G_k = X E_k with E_k = -rho [A_k B_k]' ; M_k = X[:, :12] G_{k-1}' ; L^-1 to the workspace
             T* fk = fac + (size_t)k * FAC_STRIDE;
             for (int e = tid; e < 324; e += NT) {
@@ -204,10 +214,19 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
             if (k < N - 1) {
                 for (int e = tid; e < 216; e += NT) {
                     const int i = e / 12, c = e - 12 * i;
-                    T acc = T(0);
-                    for (int a = 0; a <= i; ++a) {
-                        const T eac = c < 6 ? (a == c ? T(1) : (a == c + 6 ? dt : T(0))) : s_Gh[18 * (c - 6) + a];
-                        acc += s_X[18 * i + a] * eac;
+                    // rows c < 6 of [A_k B_k] are [I, dt I, 0]; the others are G^; L^-1 carries explicit zeros above its
+                    // diagonal, so the dot products run over all 18 terms with every load independent of the others
+                    T acc;
+                    if (c < 6) acc = s_X[18 * i + c] + dt * s_X[18 * i + c + 6];
+                    else {
+                        T a0 = T(0), a1 = T(0), a2 = T(0);
+#pragma unroll
+                        for (int a = 0; a < 18; a += 3) {
+                            a0 += s_X[18 * i + a] * s_Gh[18 * (c - 6) + a];
+                            a1 += s_X[18 * i + a + 1] * s_Gh[18 * (c - 6) + a + 1];
+                            a2 += s_X[18 * i + a + 2] * s_Gh[18 * (c - 6) + a + 2];
+                        }
+                        acc = a0 + (a1 + a2);
                     }
                     s_Gn[e] = -rho * acc;
                 }
@@ -222,17 +241,25 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
                 }
             }
             __syncthreads();
+            I7_SUB(14);
             // F_k = X' G_k
             if (k < N - 1) {
                 for (int e = tid; e < 216; e += NT) {
                     const int i = e / 12, j = e - 12 * i;
-                    T acc = T(0);
-                    for (int r = i; r < 18; ++r) acc += s_X[18 * r + i] * s_Gn[12 * r + j];
+                    T b0 = T(0), b1 = T(0), b2 = T(0);
+#pragma unroll
+                    for (int r = 0; r < 18; r += 3) {
+                        b0 += s_X[18 * r + i] * s_Gn[12 * r + j];
+                        b1 += s_X[18 * (r + 1) + i] * s_Gn[12 * (r + 1) + j];
+                        b2 += s_X[18 * (r + 2) + i] * s_Gn[12 * (r + 2) + j];
+                    }
+                    const T acc = b0 + (b1 + b2);
                     fk[FAC_FT + ((j >> 1) * 18 + i) * 2 + (j & 1)] = acc;
                 }
                 for (int e = tid; e < 216; e += NT) s_G[e] = s_Gn[e];   // nobody reads G_{k-1} any more
             }
             __syncthreads();
+            I7_SUB(15);
         }
 
         I7_ACC(0);
@@ -537,8 +564,9 @@ __global__ void __launch_bounds__(ADMM_NT, 2) admm_kernel(const __grid_constant_
                 if (stop) { status = 0; break; }
             }
         }
-        if (prof && tid == 0) for (int i = 0; i < 12; ++i) prof[i] = pacc[i];
+        if (prof && tid == 0) for (int i = 0; i < 16; ++i) prof[i] = pacc[i];
 #undef I7_ACC
+#undef I7_SUB
         // ---------------------------------------------------------------- results ----------------------
         for (int i = tid; i < nv; i += NT) {
             P.wx[(size_t)b * nv + i] = s_x[i];

@@ -25,3 +25,5 @@ print(f"B={B} N={N}: ADMM iterations (median) {np.median(info[:, 0]):.0f}; cycle
 for i, n in enumerate(names):
     print(f"  {n:22s} {np.median(c[:, i]):10.0f}")
 print(f"  total                  {np.median(c[:, :10].sum(axis=1)):10.0f}")
+print("  inside the factorisation: load + pivot block %.0f, Cholesky + triangular inverse (one warp) %.0f, G / M products + stores %.0f, F product %.0f"
+      % tuple(np.median(c[:, 12 + i]) for i in range(4)))
