@@ -1194,8 +1194,18 @@ __global__ void __launch_bounds__(NT, NT == 256 ? 2 : ((NT == 128 && sizeof(T) =
 
     for (int b = blockIdx.x; b < P.batch; b += gridDim.x) {
         if (P.done && P.done[b]) continue;                           // multi-launch SQP loop: this problem has converged
-        // ---- load inputs ----
-        for (int t = tid; t < nz; t += NT) M.xu[t] = P.xu_in[(size_t)b * nz + t];
+        // ---- load inputs (every global load issued before the first store: one memory round trip, not one per
+        //      pass of a load-store loop; the inputs may sit in mapped HOST memory, zero-copy path) ----
+        {
+            const T* xin = P.xu_in + (size_t)b * nz;
+            for (int base = 0; base < nz; base += 6 * NT) {
+                T r[6];
+#pragma unroll
+                for (int q = 0; q < 6; ++q) { const int t = base + q * NT + tid; r[q] = t < nz ? xin[t] : T(0); }
+#pragma unroll
+                for (int q = 0; q < 6; ++q) { const int t = base + q * NT + tid; if (t < nz) M.xu[t] = r[q]; }
+            }
+        }
         if (tid < 6) M.xu[nz + tid] = T(0);                          // padded u_{N-1}
         for (int t = tid; t < 3 * N; t += NT) {
             const int k = t / 3, a = t - 3 * k;
