@@ -209,6 +209,21 @@ i7_status i7_goal_window(i7_handle* h, int32_t batch, const void* traj, int32_t 
 i7_status i7_find_best_idx(i7_handle* h, int32_t batch, const void* x_last, const void* u_last, const void* xs, double dt,
                            int32_t tie_last, void* x_next, void* errors, void* result, void* stream);
 
+/* i7_find_best_idx for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arguments, same kernel and same results as i7_find_best_idx, but the scratch memory of the selection (ticket counter
+ * + one error per lane, which i7_find_best_idx keeps in buffers it allocates on first use) is a file-scope
+ * `static __device__` array of the library: 256 + 8 * I7_STATIC_MAX_BATCH bytes (32.25 KB), held by every GPU that
+ * loads the library until the process exits.  The call performs no cudaMalloc / cudaFree and calls no allocating
+ * routine (host buffers travel through the staging arenas the handle sized at i7_create).  batch >
+ * I7_STATIC_MAX_BATCH is rejected with I7_ERR_INVALID (text in i7_last_error).  ALL calls on a device — from any
+ * handle and any stream — share the one array, which keeps the last call's contents: the call zeroes the ticket
+ * counter on `stream` before its launch (every error is rewritten before it is read), and two calls that overlap on
+ * the GPU (different streams, or different handles without ordering between them) RACE on it — order them. */
+#define I7_STATIC_MAX_BATCH 4096
+i7_status i7_find_best_idx_static(i7_handle* h, int32_t batch, const void* x_last, const void* u_last, const void* xs,
+                                  double dt, int32_t tie_last, void* x_next, void* errors, void* result, void* stream);
+
 /* Best-trajectory selection over a batch (north_star: "a single NCCL gather of per-problem costs and best
  * trajectory"; reference analogue gato_controller.py:105-118 argmin over hypotheses).  Writes, on the device,
  * packed = [cost_0 .. cost_{batch-1} | best_cost, best_index (as a number), XU_best (18N-6)] where cost_b =

@@ -5,6 +5,7 @@
 #include "i7_aux.cuh"
 #include "i7_admm.cuh"
 
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -1330,6 +1331,86 @@ i7_status i7_sim_forward(i7_handle* h, int32_t batch, const void* x, const void*
     cudaStream_t s = (cudaStream_t)stream;
     return h->cfg.dtype == I7_F64 ? sim_forward_t<double>(h, batch, x, u, dt, bcast, x_next, s)
                                   : sim_forward_t<float>(h, batch, x, u, dt, bcast, x_next, s);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// i7_find_best_idx_static: the hypothesis selection of i7_find_best_idx with its scratch (ticket counter + one error per
+// lane) in a file-scope device array instead of the lazily cudaMalloc'ed buffers of the handle — for callers that must
+// not allocate (CUDA graph capture, tight serving loops).  No counterpart in the reference.
+// Every GPU that loads the library holds the 256 + 8 * I7_STATIC_MAX_BATCH bytes until exit.
+// In host code the name of the array is a host-side stand-in, NOT a device address: the address handed to the kernel
+// comes from cudaGetSymbolAddress, taken once per device with that device current.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int kStaticScratchHeader = 256;       // the ticket counter lives in the first 4 bytes
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchHeader + 8 * I7_STATIC_MAX_BATCH];
+
+constexpr int kMaxDevices = 64;
+std::atomic<void*> g_static_scratch_addr[kMaxDevices];
+
+// device address of g_static_scratch on `device` (which must be current)
+i7_status static_scratch_ptr(i7_handle* h, int device, unsigned char** out) {
+    if (device < 0 || device >= kMaxDevices) { h->err = "device ordinal beyond the static scratch table"; return I7_ERR_INVALID; }
+    void* p = g_static_scratch_addr[device].load(std::memory_order_acquire);
+    if (!p) {
+        I7_CUDA(h, cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) { h->err = "cudaGetSymbolAddress returned a null address for the static scratch"; return I7_ERR_CUDA; }
+        g_static_scratch_addr[device].store(p, std::memory_order_release);     // same value from every thread
+    }
+    *out = (unsigned char*)p;
+    return I7_OK;
+}
+
+template <typename T>
+i7_status find_best_idx_static_t(i7_handle* h, int batch, const void* x_last, const void* u_last, const void* xs, double dt,
+                                 int tie_last, void* x_next, void* errors, void* result, cudaStream_t s) {
+    const size_t es = sizeof(T);
+    unsigned char* scratch = nullptr;
+    i7_status rc;
+    if ((rc = static_scratch_ptr(h, h->cfg.device, &scratch))) return rc;
+    unsigned* counter = (unsigned*)scratch;
+    T* errs_scratch = (T*)(scratch + kStaticScratchHeader);
+    // the array keeps the previous call's contents: the ticket counter must start at zero (a launch that did not run
+    // to its end would leave it elsewhere); the errors are all rewritten before they are read
+    I7_CUDA(h, cudaMemsetAsync(counter, 0, kStaticScratchHeader, s));
+    Stage st(h);                                // staging arenas of the handle, sized at i7_create: nothing is allocated
+    const T* dx = (const T*)st.in(x_last, 12 * es);
+    const T* du = (const T*)st.in(u_last, 6 * es);
+    const T* dxs = (const T*)st.in(xs, 12 * es);
+    T* o = x_next ? (T*)st.out(x_next, (size_t)batch * 12 * es) : nullptr;
+    T* dr = (T*)st.out(result, 2 * es);
+    if ((rc = st.flush_in(s))) return rc;
+    i7::sim_forward_warp_kernel<T><<<batch, 32, 0, s>>>(get_rob<T>(h), batch, dx, du, 1,
+                                                       h->has_fext ? (const T*)h->d_fext : nullptr, T(dt), o,
+                                                       i7::SelectArgs<T>{dxs, errs_scratch, dr, counter, tie_last});
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    if (errors)                                 // optional copy of the per-lane errors out of the scratch (host or device)
+        I7_CUDA(h, cudaMemcpyAsync(errors, errs_scratch, (size_t)batch * es, cudaMemcpyDefault, s));
+    if ((rc = st.flush_out(s))) return rc;
+    if (errors && ptr_kind(errors) != 1) I7_CUDA(h, cudaStreamSynchronize(s));
+    return I7_OK;
+}
+}  // namespace
+
+extern "C" {
+
+i7_status i7_find_best_idx_static(i7_handle* h, int32_t batch, const void* x_last, const void* u_last, const void* xs,
+                                  double dt, int32_t tie_last, void* x_next, void* errors, void* result, void* stream) {
+    if (!h || !x_last || !u_last || !xs || !result) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    if (batch > I7_STATIC_MAX_BATCH) {
+        h->err = "i7_find_best_idx_static: batch " + std::to_string(batch) + " exceeds the static scratch (I7_STATIC_MAX_BATCH = " +
+                 std::to_string(I7_STATIC_MAX_BATCH) + " lanes); use i7_find_best_idx";
+        return I7_ERR_INVALID;
+    }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64
+               ? find_best_idx_static_t<double>(h, batch, x_last, u_last, xs, dt, tie_last, x_next, errors, result, s)
+               : find_best_idx_static_t<float>(h, batch, x_last, u_last, xs, dt, tie_last, x_next, errors, result, s);
 }
 
 }  // extern "C"

@@ -322,6 +322,21 @@ class Engine:
         idx = None if idx < 0 else idx
         return (idx, errs) if return_errors else idx
 
+    def find_best_idx_static(self, x_last, u_last, xs, dt, batch=None, tie_last=True, return_errors=False):
+        """find_best_idx without allocations inside the library call (i7_find_best_idx_static: scratch in a static
+        device array of at most _lib.I7_STATIC_MAX_BATCH lanes, shared by every call on the device — overlapping calls
+        race).  No counterpart in the reference.  Same results as find_best_idx."""
+        B = int(batch) if batch is not None else self.batch
+        keep = []
+        px, pu, ps = self._in(x_last, (1, 12), keep), self._in(u_last, (1, 6), keep), self._in(xs, (1, 12), keep)
+        res, pr = self._out((2,), x_last, keep)
+        errs, pe = self._out((B,), x_last, keep) if return_errors else (None, None)
+        self._check(self.lib.i7_find_best_idx_static(self._h, B, px, pu, ps, float(dt), 1 if tie_last else 0, None, pe, pr,
+                                                     self._stream(x_last)))
+        idx = int(res[0])
+        idx = None if idx < 0 else idx
+        return (idx, errs) if return_errors else idx
+
     def pack_best(self, stats, xu, index_offset=0):
         """[costs | best_cost, best_index, XU_best] on the device the inputs live on (i7_pack_best)."""
         B = self._batch_of(xu)
