@@ -16,8 +16,8 @@
 //            reference form on these problems, cond ~ 4e9 — where explicit inverses of the pivot blocks lose 1e-6)
 //   iterate  right-hand side and z~ = A x~ in parallel over rows; the solve is two parallel triangular products
 //            (a = L^-1 r, c = L^-T w) around two serial chains of ONE small matrix-vector product per stage
-//            (w_k = a_k - M_k w_{k-1} forward, x_k = c_k - F_k x_{k+1} backward) run by one warp with the stage matrices
-//            prefetched into registers one stage ahead.
+//            (w_k = a_k - M_k w_{k-1} forward, x_k = c_k - F_k x_{k+1} backward) run by one warp, the stage matrices
+//            staged through a shared-memory ring by the other warps (see ADMM_CG below).
 #pragma once
 #include "i7_sqp.cuh"
 
@@ -48,15 +48,13 @@ struct AdmmParams {
     AdmmSettings S;
 };
 
-constexpr int ADMM_NT = 128;     // two CTAs per SM (registers: the in-register 18 x 18 factorisation), three where shared memory allows
-// per knot: L^-1 (18 x 18 row-major, zeros above the diagonal), M (18 x 18) and F (18 x 12) in planes of column PAIRS:
-// element (i, c) at ((c / 2) * 18 + i) * 2 + c % 2, so that lane i of the serial chains reads its row as 16-byte vectors
-// (one warp's instruction count bounds a stage) AND the 18 lanes of a load touch 288 contiguous bytes (coalesced)
-// L^-1 is kept twice, as planes of COLUMN pairs (FAC_LA: (i, c) at ((c / 2) * 18 + i) * 2 + c % 2, read by a = L^-1 r) and of
-// ROW pairs (FAC_LB: (r, i) at ((r / 2) * 18 + i) * 2 + r % 2, read by c = L^-T w): either product is nine coalesced 16-byte loads
+constexpr int ADMM_NT = 128;     // two CTAs per SM (registers: the in-register 18 x 18 factorisation; a cap for three spills, measured 1.9x slower)
+// factor workspace per knot: M (18 x 18, FAC_MT) and F (18 x 12, FAC_FT) in planes of column PAIRS — element (i, c) at
+// ((c / 2) * 18 + i) * 2 + c % 2 — so that lane i of the serial chains reads its row as 16-byte vectors (one warp's
+// instruction count bounds a stage) AND the 18 lanes of a load touch 288 contiguous bytes (coalesced).  L^-1 is kept
+// twice, as planes of COLUMN pairs (FAC_LA, same formula, read by a = L^-1 r) and of ROW pairs (FAC_LB: (r, i) at
+// ((r / 2) * 18 + i) * 2 + r % 2, read by c = L^-T w): either product is nine coalesced 16-byte loads
 constexpr int FAC_LA = 0, FAC_LB = 324, FAC_MT = 648, FAC_FT = 972, FAC_STRIDE = 1188;
-// shared memory: the vectors (156 N), the stage scratch of the factorisation, and — while it fits — the QP blocks
-// (QB_STRIDE N), which every iteration reads twice (A x~ and A' t)
 // serial chains: the stage matrices are staged through shared memory in groups of ADMM_CG stages, double-buffered: while
 // warp 0 works through group g the other warps (idle during the chain) copy group g + 1 from the L2 workspace.  Measured
 // alternatives: rows prefetched from L2 into registers two stages ahead (warp 0 waits for them: 285 k / 216 k cycles per
