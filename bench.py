@@ -589,6 +589,18 @@ def run_b200(args):
                 "frac": bytes_launch / kern_avg_s / 1e9 / hbm_peak, "peak_source": peak_src,
                 "algorithmic_bytes_per_solve": algorithmic_bytes(N, esize)},
     }
+    try:        # shared-memory pipe (SURVEY.md section 8d asks for it beside the FMA pipe): wavefronts counted by ncu, time live
+        wf = tj.get(f"sqp_kernel_B{B}_N{N}_{args.dtype}_smem_wavefronts")
+        if wf:
+            props = torch.cuda.get_device_properties(dev)
+            sm_hz = props.clock_rate * 1e3 if hasattr(props, "clock_rate") else 1.965e9
+            per_clk = wf / (kern_avg_s * sm_hz * props.multi_processor_count)
+            roofline["smem"] = {"achieved": per_clk, "peak": 1.0, "unit": "wavefronts (128 B) per cycle per SM", "frac": per_clk,
+                                "wavefronts_per_launch": wf, "bank_conflict_share": tj.get(f"sqp_kernel_B{B}_N{N}_{args.dtype}_smem_conflicts", 0) / wf,
+                                "source": "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum of the ncu capture named in profiles/traffic.json; "
+                                          "duration measured in this run, SM clock = the device's maximum"}
+    except Exception:
+        pass
 
     cpu = None
     if not args.no_cpu_baseline:

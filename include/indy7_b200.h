@@ -224,6 +224,26 @@ i7_status i7_find_best_idx(i7_handle* h, int32_t batch, const void* x_last, cons
 i7_status i7_find_best_idx_static(i7_handle* h, int32_t batch, const void* x_last, const void* u_last, const void* xs,
                                   double dt, int32_t tie_last, void* x_next, void* errors, void* result, void* stream);
 
+/* resample_f_ext_batch (gato_controller.py:120-129) on the device, and its two variants in the drivers (notebook
+ * run_mpc_fig8; src/gato_mpc_batch_sample.py:286-298): around the selected lane `best`,
+ *     f[b] = f[best] + noise[b];  f[keep] = f[best];  f[:, 3:] = 0;  f[0] = 0;  f *= decay
+ * in exactly that order in double precision (bit-identical to the numpy statements).  `noise` (batch x 6) are the
+ * caller's normal draws: the reference seeds np.random on the host (gato_controller.py:15) and its stream is what parity
+ * means here, so the draws stay with the caller.  best_idx >= 0: the lane; best_idx < 0: the lane is read from
+ * `best_result` (the 2-number result of i7_find_best_idx, host or device, handle dtype) — with device buffers the two
+ * calls chain on a stream without a host round trip; a result of -1 (no lane qualified) leaves the batch unchanged.
+ * keep_lane: a lane index (the notebook keeps lane 1), I7_KEEP_BEST (gato_controller.py:125) or I7_KEEP_NONE.
+ * flags: I7_RESAMPLE_KEEP_TORQUE — the kept lane is restored AFTER the torque part is cleared (notebook order);
+ * I7_RESAMPLE_APPLY — the new batch also becomes the handle's wrench batch, as by i7_set_external_wrench.
+ * f_ext / noise / f_ext_out: batch x 6 doubles [linear; angular], host or device; f_ext_out may equal f_ext. */
+#define I7_KEEP_BEST (-1)
+#define I7_KEEP_NONE (-2)
+#define I7_RESAMPLE_KEEP_TORQUE 1
+#define I7_RESAMPLE_APPLY 2
+i7_status i7_resample_wrench(i7_handle* h, int32_t batch, int32_t best_idx, const void* best_result, const double* f_ext,
+                             const double* noise, int32_t keep_lane, int32_t flags, double decay, double* f_ext_out,
+                             void* stream);
+
 /* Best-trajectory selection over a batch (north_star: "a single NCCL gather of per-problem costs and best
  * trajectory"; reference analogue gato_controller.py:105-118 argmin over hypotheses).  Writes, on the device,
  * packed = [cost_0 .. cost_{batch-1} | best_cost, best_index (as a number), XU_best (18N-6)] where cost_b =

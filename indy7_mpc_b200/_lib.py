@@ -10,6 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libindy7_b200.so")
 
 I7_NJ, I7_STATS_LEN = 6, 12
+I7_KEEP_BEST, I7_KEEP_NONE, I7_RESAMPLE_KEEP_TORQUE, I7_RESAMPLE_APPLY = -1, -2, 1, 2
 I7_STATIC_MAX_BATCH = 4096     # lanes of the static scratch of i7_find_best_idx_static
 I7_F64, I7_F32 = 0, 1
 I7_QP_EXACT, I7_QP_OSQP = 0, 1
@@ -68,6 +69,7 @@ SYMBOLS = {
     "i7_goal_window": (_i32, [_vp, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp]),
     "i7_find_best_idx": (_i32, [_vp, _i32, _vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp]),
     "i7_find_best_idx_static": (_i32, [_vp, _i32, _vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp]),
+    "i7_resample_wrench": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _dbl, _vp, _vp]),
     "i7_qp_state": (_i32, [_vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "i7_solve_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "i7_dump_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),

@@ -103,6 +103,16 @@ class _SQPSolverBase:
                                  tie_last=tie_last)
 
 
+    def resample_f_ext_batch(self, best_idx, noise, keep_lane=-1, keep_torque=False, decay=1.0):
+        """Extension of the reference binding: ``BatchGATO.resample_f_ext_batch`` (gato_controller.py:120-129) on the
+        device (i7_resample_wrench): the batch set by set_external_wrench_batch is re-centred on lane `best_idx` with the
+        caller's normal draws `noise` (B x 6), becomes the solver's wrench batch and is returned."""
+        eng = self._engine or self._ensure(self._N or 32, self._dt or 0.01)
+        self._f_ext = eng.resample_wrench(self._f_ext, noise, int(best_idx), keep_lane=keep_lane, keep_torque=keep_torque,
+                                          decay=decay, apply=True)
+        return self._f_ext.copy()
+
+
 def _make(B):
     return type(f"SQPSolverfloat_{B}", (_SQPSolverBase,), {"BATCH": B, "__doc__": f"batch of {B} SQP problems"})
 

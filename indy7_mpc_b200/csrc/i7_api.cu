@@ -1414,3 +1414,52 @@ i7_status i7_find_best_idx_static(i7_handle* h, int32_t batch, const void* x_las
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// i7_resample_wrench: gato_controller.py:120-129 resample_f_ext_batch (and the notebook / batch-sample variants) on the
+// device, chained to i7_find_best_idx without a host round trip (best index read from its device result).
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+template <typename T>
+i7_status resample_wrench_t(i7_handle* h, int batch, int best_idx, const void* best_result, const double* f_ext,
+                            const double* noise, int keep_lane, int flags, double decay, double* f_ext_out, cudaStream_t s) {
+    Stage st(h);
+    const T* d_res = best_idx < 0 ? (const T*)st.in(best_result, 2 * sizeof(T)) : nullptr;
+    const double* d_f = (const double*)st.in(f_ext, (size_t)batch * 6 * sizeof(double));
+    const double* d_n = (const double*)st.in(noise, (size_t)batch * 6 * sizeof(double));
+    // in place on device memory: the kernel reads the selected lane before it writes any (one CTA)
+    double* d_o = (f_ext_out == f_ext && ptr_kind(f_ext) == 1) ? const_cast<double*>(d_f)
+                                                               : (double*)st.out(f_ext_out, (size_t)batch * 6 * sizeof(double));
+    i7_status rc;
+    if ((rc = st.flush_in(s))) return rc;
+    const bool apply = (flags & I7_RESAMPLE_APPLY) != 0;
+    i7::resample_wrench_kernel<T><<<1, 256, 0, s>>>(batch, best_idx, d_res, d_f, d_n, keep_lane,
+                                                    (flags & I7_RESAMPLE_KEEP_TORQUE) ? 1 : 0, decay, d_o,
+                                                    apply ? (T*)h->d_fext : nullptr);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    if (apply) h->has_fext = true;
+    return st.flush_out(s);
+}
+}  // namespace
+
+extern "C" {
+
+i7_status i7_resample_wrench(i7_handle* h, int32_t batch, int32_t best_idx, const void* best_result, const double* f_ext,
+                             const double* noise, int32_t keep_lane, int32_t flags, double decay, double* f_ext_out,
+                             void* stream) {
+    if (!h || !f_ext || !noise || !f_ext_out) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    if (best_idx >= batch || (best_idx < 0 && !best_result)) {
+        h->err = "best_idx must be a lane of the batch, or negative with best_result = the result of i7_find_best_idx";
+        return I7_ERR_INVALID;
+    }
+    if (keep_lane < I7_KEEP_NONE) { h->err = "keep_lane: a lane index, I7_KEEP_BEST or I7_KEEP_NONE"; return I7_ERR_INVALID; }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64
+               ? resample_wrench_t<double>(h, batch, best_idx, best_result, f_ext, noise, keep_lane, flags, decay, f_ext_out, s)
+               : resample_wrench_t<float>(h, batch, best_idx, best_result, f_ext, noise, keep_lane, flags, decay, f_ext_out, s);
+}
+
+}  // extern "C"

@@ -351,6 +351,42 @@ __global__ void goal_window_kernel(int batch, int N, const T* __restrict__ traj,
     }
 }
 
+// Wrench-hypothesis resampling around the selected lane (gato_controller.py:120-129 resample_f_ext_batch; notebook
+// variant gato_mpc_batch_sample run_mpc_fig8): f[b] = f[best] + noise[b]; the kept lane = f[best]; torque part 0; lane 0
+// = 0; everything x decay.  The normal draws come from the caller (the reference seeds np.random on the host,
+// gato_controller.py:15: its stream is the parity).  Arithmetic in double whatever the handle dtype (the reference keeps
+// f_ext_batch in float64); ONE CTA, so the update may run in place: every thread holds f[best] before the barrier, lanes
+// are written after it.  `fext` (optional): the handle's wrench batch, [angular; linear] in the handle dtype.
+template <typename T>
+__global__ void __launch_bounds__(256) resample_wrench_kernel(int batch, int best_idx, const T* __restrict__ best_result,
+                                                              const double* f_in, const double* __restrict__ noise,
+                                                              int keep_lane, int keep_torque, double decay, double* f_out,
+                                                              T* __restrict__ fext) {
+    int best = best_idx;
+    if (best < 0 && best_result) best = (int)best_result[0];
+    const bool valid = best >= 0 && best < batch;          // no lane qualified: the batch is left as it is
+    double fb[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) fb[a] = valid ? f_in[6 * best + a] : 0.0;
+    __syncthreads();
+    const int keep = keep_lane == -1 ? best : keep_lane;
+    for (int e = threadIdx.x; e < 6 * batch; e += blockDim.x) {
+        const int b = e / 6, a = e - 6 * b;
+        double v;
+        if (!valid) v = f_in[e];
+        else {
+            v = fb[a] + noise[e];
+            if (b == keep && !keep_torque) v = fb[a];
+            if (a >= 3) v = 0.0;
+            if (b == keep && keep_torque) v = fb[a];
+            if (b == 0) v = 0.0;
+            v *= decay;
+        }
+        f_out[e] = v;
+        if (fext) fext[6 * b + (a < 3 ? a + 3 : a - 3)] = T(v);
+    }
+}
+
 // FMA-pipe peak: 8 independent chains per thread, 2 flop per FMA
 template <typename T>
 __global__ void fma_peak_kernel(int iters, T seed, T* sink) {

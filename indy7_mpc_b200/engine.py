@@ -337,6 +337,67 @@ class Engine:
         idx = None if idx < 0 else idx
         return (idx, errs) if return_errors else idx
 
+    def find_best_idx_async(self, x_last, u_last, xs, dt, batch=None, tie_last=True):
+        """find_best_idx without the read-back: returns the 2-number result [index (-1: no lane qualified), error] in the
+        memory of the inputs (a device tensor for device inputs — nothing waits for the GPU), to be chained into
+        `resample_wrench(best=...)`."""
+        B = int(batch) if batch is not None else self.batch
+        keep = []
+        px, pu, ps = self._in(x_last, (1, 12), keep), self._in(u_last, (1, 6), keep), self._in(xs, (1, 12), keep)
+        res, pr = self._out((2,), x_last, keep)
+        self._check(self.lib.i7_find_best_idx(self._h, B, px, pu, ps, float(dt), 1 if tie_last else 0, None, None, pr,
+                                              self._stream(x_last)))
+        return res
+
+    def resample_wrench(self, f_ext, noise, best, keep_lane=_lib.I7_KEEP_BEST, keep_torque=False, decay=1.0, apply=True,
+                        inplace=False):
+        """resample_f_ext_batch (gato_controller.py:120-129) on the device (i7_resample_wrench): f = f[best] + noise,
+        kept lane = f[best], torque part 0, lane 0 = 0, x decay — bit-identical to the numpy statements.  f_ext, noise:
+        (B, 6) float64, numpy or torch (host or device); `noise` are the caller's np.random draws.  best: a lane index, or
+        the result of `find_best_idx_async` (read on the device).  keep_lane: lane index, I7_KEEP_BEST, I7_KEEP_NONE
+        (None).  apply: the new batch also becomes the engine's wrench batch.  Returns the new batch (same kind of
+        array as f_ext; the same tensor with inplace=True)."""
+        keep = []
+
+        def f64(x):
+            if _is_torch(x):
+                t = x.detach().reshape(-1, 6)
+                if t.dtype != torch.float64 or not t.is_contiguous():
+                    if inplace and x is f_ext:
+                        raise ValueError("inplace needs a contiguous float64 tensor")
+                    t = t.to(torch.float64).contiguous()
+                keep.append(t)
+                return t, t.data_ptr()
+            a = np.ascontiguousarray(np.asarray(x, dtype=np.float64).reshape(-1, 6))
+            keep.append(a)
+            return a, _addr(a)
+        f, pf = f64(f_ext)
+        n, pn = f64(noise)
+        B = f.shape[0]
+        if tuple(n.shape) != (B, 6):
+            raise ValueError(f"noise must be ({B}, 6)")
+        if B > self.batch:
+            raise ValueError(f"batch {B} exceeds the engine's maximum batch {self.batch}")
+        if isinstance(best, (int, np.integer)):
+            bi, pb = int(best), None
+            if not 0 <= bi < B:
+                raise ValueError(f"best lane {bi} outside the batch of {B}")
+        else:
+            bi, pb = -1, self._in(best, (1, 2), keep)
+        if inplace:
+            out, po = f, pf
+        elif _is_torch(f):
+            out = torch.empty_like(f)
+            po = out.data_ptr()
+        else:
+            out = np.empty_like(f)
+            po = _addr(out)
+        kl = _lib.I7_KEEP_NONE if keep_lane is None else int(keep_lane)
+        flags = (_lib.I7_RESAMPLE_KEEP_TORQUE if keep_torque else 0) | (_lib.I7_RESAMPLE_APPLY if apply else 0)
+        like = f if (_is_torch(f) and f.is_cuda) else None
+        self._check(self.lib.i7_resample_wrench(self._h, B, bi, pb, pf, pn, kl, flags, float(decay), po, self._stream(like)))
+        return out
+
     def pack_best(self, stats, xu, index_offset=0):
         """[costs | best_cost, best_index, XU_best] on the device the inputs live on (i7_pack_best)."""
         B = self._batch_of(xu)

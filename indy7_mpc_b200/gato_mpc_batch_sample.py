@@ -217,14 +217,10 @@ class MPC_GATO_Batch_Sample:
         S.solver.set_external_wrench_batch(S.f_ext_batch)
         best_id = S.solver.find_best_idx(x_last, u_last, xcur, float(dt), tie_last=True)   # one launch, `<=` argmin
         if self.resample_f_ext and self.f_ext_resample_std != 0:
-            f_best = S.f_ext_batch[best_id].copy()
-            S.f_ext_batch = np.tile(f_best, (S.batch_size, 1)) + np.random.normal(0, self.f_ext_resample_std,
-                                                                                   S.f_ext_batch.shape)
-            S.f_ext_batch[:, 3:] = 0.0
-            if S.batch_size > 1:
-                S.f_ext_batch[1] = f_best
-            S.f_ext_batch[0] = 0.0
-            S.solver.set_external_wrench_batch(S.f_ext_batch)
+            # f = f[best] + noise; torque part 0; lane 1 = f[best]; lane 0 = 0 — on the device (i7_resample_wrench); the
+            # normal draws stay np.random's (the reference's stream, seeded on the host)
+            noise = np.random.normal(0, self.f_ext_resample_std, S.f_ext_batch.shape)
+            S.f_ext_batch = S.solver.resample_f_ext_batch(best_id, noise, keep_lane=1, keep_torque=True)
         return best_id
 
     def find_best_trajectory_id(self, x_last, u_last, xcur, dt):

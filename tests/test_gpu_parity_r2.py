@@ -323,3 +323,73 @@ def test_indy7sqp_step_bound_path_equals_generic(pkg):
     cold = pkg.Indy7SQP(N=N, batch=B, cluster=1); cold.set_external_wrench(wl["f_ext"])
     ref = cold.step(wl["x0"], bench.goals_at(wl["fig"], wl["offsets"], 0, N), index_offset=3)
     assert np.array_equal(again["costs"], ref["costs"])
+
+
+@pytest.mark.parametrize("dtype", ["fp64", "fp32"])
+def test_resample_wrench_equals_numpy_statements(pkg, dtype):
+    """i7_resample_wrench against the reference's numpy statements, bit for bit: gato_controller.py:120-129 (kept lane =
+    best, x 0.97), the notebook variant (lane 1 keeps the best wrench, restored after the torque part is cleared) and
+    src/gato_mpc_batch_sample.py:286-298 (no kept lane); host and device buffers, in place, chained to the device result
+    of the selection; the handle's wrench batch follows (checked through sim_forward)."""
+    import torch
+    from indy7_mpc_b200 import _lib
+    B = 37
+    rng = np.random.default_rng(99)
+    e = pkg.Engine(N=8, batch=B, dtype=dtype)
+    f0 = rng.normal(0, 5, (B, 6))
+
+    def controller(f, best, noise, std_decay=0.97):            # gato_controller.py:120-129, statement by statement
+        f = f.copy()
+        fb = f[best, :].copy()
+        f[:, :] = fb
+        f += noise
+        f[best, :] = fb
+        f[:, 3:] = 0.0
+        f[0] = np.array([0.0, 0.0, 0.0, 0.0, 0.0, 0.0])
+        f *= std_decay
+        return f
+
+    def notebook(f, best, noise):
+        fb = f[best].copy()
+        g = np.tile(fb, (B, 1)) + noise
+        g[:, 3:] = 0.0
+        g[1] = fb
+        g[0] = 0.0
+        return g
+
+    def batch_sample(f, best, noise):                          # src/gato_mpc_batch_sample.py:286-298
+        g = f[best].copy() + noise
+        g[:, 3:] = 0.0
+        g[0] = 0.0
+        return g
+    f = f0.copy()
+    for it, best in enumerate([5, 0, B - 1, 1]):
+        noise = rng.normal(0, 2.0, (B, 6))
+        ref = controller(f, best, noise)
+        out = e.resample_wrench(f, noise, best, keep_lane=_lib.I7_KEEP_BEST, decay=0.97)
+        assert isinstance(out, np.ndarray) and np.array_equal(out, ref), it
+        assert np.array_equal(e.resample_wrench(f, noise, best, keep_lane=1, keep_torque=True, apply=False), notebook(f, best, noise))
+        assert np.array_equal(e.resample_wrench(f, noise, best, keep_lane=None, apply=False), batch_sample(f, best, noise))
+        f = ref                                                # the recursion of the controller, tick after tick
+    # the handle's wrench batch is the applied one: same plant step as after set_external_wrench
+    x, u = rng.uniform(-1, 1, 12), rng.uniform(-5, 5, 6)
+    xn_applied = np.asarray(e.sim_forward(x, u, 0.002, batch=B))
+    e.set_external_wrench(f)
+    assert np.array_equal(xn_applied, np.asarray(e.sim_forward(x, u, 0.002, batch=B)))
+    # device buffers, in place, lane taken from the device result of the selection (no host round trip)
+    d = lambda a, dt=torch.float64: torch.tensor(a, device="cuda", dtype=dt)
+    xs = xn_applied[7].astype(float)
+    res = e.find_best_idx_async(d(x, e._torch_dtype()), d(u, e._torch_dtype()), d(xs, e._torch_dtype()), 0.002, batch=B)
+    assert res.is_cuda
+    noise = rng.normal(0, 2.0, (B, 6))
+    fd = d(f)
+    out = e.resample_wrench(fd, d(noise), res, decay=0.97, inplace=True)
+    assert out.data_ptr() == fd.data_ptr() and int(res[0]) == 7
+    assert np.array_equal(fd.cpu().numpy(), controller(f, 7, noise))
+    # no lane qualified (-1): the batch stays as it is
+    res_nan = e.find_best_idx_async(d(x, e._torch_dtype()), d(u, e._torch_dtype()), d(np.full(12, np.nan), e._torch_dtype()), 0.002, batch=B)
+    before = fd.clone()
+    e.resample_wrench(fd, d(noise), res_nan, inplace=True)
+    assert int(res_nan[0]) == -1 and torch.equal(fd, before)
+    with pytest.raises(ValueError):
+        e.resample_wrench(f, noise, B)
