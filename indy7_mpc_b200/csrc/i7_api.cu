@@ -126,7 +126,6 @@ int ptr_kind(const void* p) {
     if (at.type == cudaMemoryTypeHost) return 2;
     return 0;
 }
-bool is_device_ptr(const void* p) { return ptr_kind(p) == 1; }
 
 i7_status arena_reserve(i7_handle* h, Arena& a, size_t bytes) {
     if (bytes <= a.bytes) return I7_OK;
