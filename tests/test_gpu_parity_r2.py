@@ -382,6 +382,10 @@ def test_resample_wrench_equals_numpy_statements(pkg, dtype):
     res = e.find_best_idx_async(d(x, e._torch_dtype()), d(u, e._torch_dtype()), d(xs, e._torch_dtype()), 0.002, batch=B)
     assert res.is_cuda
     noise = rng.normal(0, 2.0, (B, 6))
+    # the same chain with host buffers (result of the selection in a numpy array)
+    res_h = e.find_best_idx_async(x, u, xs, 0.002, batch=B)
+    assert isinstance(res_h, np.ndarray) and int(res_h[0]) == 7
+    assert np.array_equal(e.resample_wrench(f, noise, res_h, decay=0.97, apply=False), controller(f, 7, noise))
     fd = d(f)
     out = e.resample_wrench(fd, d(noise), res, decay=0.97, inplace=True)
     assert out.data_ptr() == fd.data_ptr() and int(res[0]) == 7
