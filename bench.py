@@ -332,6 +332,31 @@ def fp_roofline(eng, st_host, N, B, kern_ms, dtype, fma_peak):
             "algorithmic_flops_per_solve": flops}
 
 
+def controller_tick_latency(eng, wl, B, N, ticks):
+    """The reference controller's own tick on configs[2] (GATO_Controller.joint_callback, gato_controller.py:201-256: all
+    lanes share state and reference, selection by one-step prediction error, resampling around the selected lane, its
+    trajectory handed to every lane): wall clock per `ControllerTick.tick` call — host buffers in, control out."""
+    import time
+    from indy7_mpc_b200 import ControllerTick
+    np.random.seed(42)                                   # gato_controller.py:308
+    ref = np.zeros((wl["fig"].shape[0], 6))
+    ref[:, :3] = wl["fig"][:, :3]
+    ct = ControllerTick(eng, ref.reshape(-1), B, f_ext_std=2.0 if B >= 32 else 20.0, f_ext_resample_std=0.2 if B >= 32 else 1.0)
+    x = np.asarray(wl["x0"][0], float).copy()
+    t_us = []
+    for t in range(ticks + 10):
+        t0 = time.perf_counter()
+        u, best = ct.tick(x, 0.01)
+        t_us.append((time.perf_counter() - t0) * 1e6)
+        x = ct.XU_best[18:30].copy()                     # plant = the selected lane's own prediction (timing run)
+    t_us = np.array(t_us[10:])
+    eng.set_external_wrench(wl["f_ext"])
+    return {"host_wall_us": {"p50": float(np.percentile(t_us, 50)), "p99": float(np.percentile(t_us, 99)), "mean": float(t_us.mean())},
+            "ticks": int(ticks), "launches_per_tick": 5, "finite": bool(np.all(np.isfinite(ct.XU_best))),
+            "what": "ControllerTick.tick: goal window, solve, selection by prediction error, wrench resampling, hand-over "
+                    "of the best trajectory; measured state / elapsed time / normal draws from the host, control back on the host"}
+
+
 def extra_configs(args, local, fma_peaks):
     """BASELINE.json configs[2] (batch 16/32/64, N=32) and configs[4] (N=128, batch 512, fp64 vs fp32) on one GPU:
     device-resident closed-loop ticks, L2 flushed, with the FMA-pipe fraction and the CPU figure of the same lanes."""
@@ -371,6 +396,8 @@ def extra_configs(args, local, fma_peaks):
             first[dtype] = o.double().cpu().numpy()
             if "fp64" in first and dtype == "fp32":
                 rec["fp32_vs_fp64_rel"] = float(np.abs(first["fp32"] - first["fp64"]).max() / np.abs(first["fp64"]).max())
+        if name == "configs[2]":
+            rec["controller_tick"] = controller_tick_latency(eng, wl, B, N, max(args.config_ticks, 20) * 5)
         if not args.no_cpu_baseline:
             key = (B, N, limits)
             if key not in cpu_cache:

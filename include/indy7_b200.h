@@ -244,6 +244,15 @@ i7_status i7_resample_wrench(i7_handle* h, int32_t batch, int32_t best_idx, cons
                              const double* noise, int32_t keep_lane, int32_t flags, double decay, double* f_ext_out,
                              void* stream);
 
+/* Hand-over at the end of a controller tick (gato_controller.py:226,249): XU_best = XU_new[best] -> best_out (18N-6
+ * numbers), and XU_batch[:, :] = XU_best -> xu_out (batch x (18N-6); may equal xu_new; NULL to skip).  best_idx >= 0: the
+ * lane; < 0: read from `best_result`, the result of i7_find_best_idx (host or device, handle dtype); a result of -1 (no
+ * lane qualified — the reference would index with None) takes lane 0, the zero-wrench hypothesis.  Pointers host or
+ * device.  With i7_goal_window, i7_solve, i7_find_best_idx and i7_resample_wrench this makes the whole
+ * GATO_Controller.joint_callback tick (gato_controller.py:201-256) a chain of launches on one stream. */
+i7_status i7_broadcast_best(i7_handle* h, int32_t batch, const void* xu_new, int32_t best_idx, const void* best_result,
+                            void* xu_out, void* best_out, void* stream);
+
 /* Best-trajectory selection over a batch (north_star: "a single NCCL gather of per-problem costs and best
  * trajectory"; reference analogue gato_controller.py:105-118 argmin over hypotheses).  Writes, on the device,
  * packed = [cost_0 .. cost_{batch-1} | best_cost, best_index (as a number), XU_best (18N-6)] where cost_b =

@@ -8,6 +8,6 @@ from .osqp_solver import OSQPSolver                                         # no
 from .osqp_sqp import SQP_OSQP                                              # noqa: F401
 from .osqp_mpc import MPC_OSQP                                              # noqa: F401
 from .api import Indy7SQP                                                   # noqa: F401
-from .tick import DeviceTick                                                # noqa: F401
+from .tick import DeviceTick, ControllerTick                                # noqa: F401
 
 __version__ = "0.1.0"

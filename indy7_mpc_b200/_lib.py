@@ -70,6 +70,7 @@ SYMBOLS = {
     "i7_find_best_idx": (_i32, [_vp, _i32, _vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp]),
     "i7_find_best_idx_static": (_i32, [_vp, _i32, _vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp]),
     "i7_resample_wrench": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _dbl, _vp, _vp]),
+    "i7_broadcast_best": (_i32, [_vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp]),
     "i7_qp_state": (_i32, [_vp, _i32, _vp, _vp, _vp, _vp, _vp]),
     "i7_solve_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "i7_dump_qp": (_i32, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),

@@ -1212,6 +1212,7 @@ i7_status find_best_idx_t(i7_handle* h, int batch, const void* x_last, const voi
         I7_CUDA(h, cudaMalloc(&h->d_sel_errs, (size_t)h->cfg.batch * es));
     }
     Stage st(h);
+    st.zero_copy = h->zero_copy != 0;       // page-locked buffers (30 numbers in, 2 out) are read and written in place
     const T* dx = (const T*)st.in(x_last, 12 * es);
     const T* du = (const T*)st.in(u_last, 6 * es);
     const T* dxs = (const T*)st.in(xs, 12 * es);
@@ -1423,6 +1424,7 @@ template <typename T>
 i7_status resample_wrench_t(i7_handle* h, int batch, int best_idx, const void* best_result, const double* f_ext,
                             const double* noise, int keep_lane, int flags, double decay, double* f_ext_out, cudaStream_t s) {
     Stage st(h);
+    st.zero_copy = h->zero_copy != 0;       // page-locked draws are read in place
     const T* d_res = best_idx < 0 ? (const T*)st.in(best_result, 2 * sizeof(T)) : nullptr;
     const double* d_f = (const double*)st.in(f_ext, (size_t)batch * 6 * sizeof(double));
     const double* d_n = (const double*)st.in(noise, (size_t)batch * 6 * sizeof(double));
@@ -1459,6 +1461,49 @@ i7_status i7_resample_wrench(i7_handle* h, int32_t batch, int32_t best_idx, cons
     return h->cfg.dtype == I7_F64
                ? resample_wrench_t<double>(h, batch, best_idx, best_result, f_ext, noise, keep_lane, flags, decay, f_ext_out, s)
                : resample_wrench_t<float>(h, batch, best_idx, best_result, f_ext, noise, keep_lane, flags, decay, f_ext_out, s);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// i7_broadcast_best: the hand-over at the end of a controller tick (gato_controller.py:226,249).
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+template <typename T>
+i7_status broadcast_best_t(i7_handle* h, int batch, const void* xu_new, int best_idx, const void* best_result, void* xu_out,
+                           void* best_out, cudaStream_t s) {
+    const size_t es = sizeof(T), nz = h->nz;
+    Stage st(h);
+    const T* d_new = (const T*)st.in(xu_new, (size_t)batch * nz * es);
+    const T* d_res = best_idx < 0 ? (const T*)st.in(best_result, 2 * es) : nullptr;
+    T* d_out = !xu_out ? nullptr
+                       : ((xu_out == xu_new && ptr_kind(xu_new) == 1) ? const_cast<T*>(d_new) : (T*)st.out(xu_out, (size_t)batch * nz * es));
+    T* d_best = (T*)st.out(best_out, nz * es);
+    i7_status rc;
+    if ((rc = st.flush_in(s))) return rc;
+    const size_t total = (size_t)batch * nz;
+    const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
+    i7::broadcast_best_kernel<T><<<blocks, 256, 0, s>>>(batch, (int)nz, d_new, best_idx, d_res, d_out, d_best);
+    ++h->launches;
+    I7_CUDA(h, cudaGetLastError());
+    return st.flush_out(s);
+}
+}  // namespace
+
+extern "C" {
+
+i7_status i7_broadcast_best(i7_handle* h, int32_t batch, const void* xu_new, int32_t best_idx, const void* best_result,
+                            void* xu_out, void* best_out, void* stream) {
+    if (!h || !xu_new || (!xu_out && !best_out)) { if (h) h->err = "null argument"; return I7_ERR_INVALID; }
+    if (batch < 1 || batch > h->cfg.batch) { h->err = "batch out of range for this handle"; return I7_ERR_INVALID; }
+    if (best_idx >= batch || (best_idx < 0 && !best_result)) {
+        h->err = "best_idx must be a lane of the batch, or negative with best_result = the result of i7_find_best_idx";
+        return I7_ERR_INVALID;
+    }
+    I7_CUDA(h, cudaSetDevice(h->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    return h->cfg.dtype == I7_F64 ? broadcast_best_t<double>(h, batch, xu_new, best_idx, best_result, xu_out, best_out, s)
+                                  : broadcast_best_t<float>(h, batch, xu_new, best_idx, best_result, xu_out, best_out, s);
 }
 
 }  // extern "C"

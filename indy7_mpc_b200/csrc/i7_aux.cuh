@@ -387,6 +387,26 @@ __global__ void __launch_bounds__(256) resample_wrench_kernel(int batch, int bes
     }
 }
 
+// The controller's hand-over of a tick (gato_controller.py:226,249): XU_best = XU_new[best]; XU_batch[:, :] = XU_best —
+// every lane starts the next solve from the best lane's trajectory.  The lane comes from the caller or from the device
+// result of the selection (-1, no lane qualified: lane 0, the zero-wrench hypothesis).  In place is allowed: lane `best`
+// is only read.
+template <typename T>
+__global__ void broadcast_best_kernel(int batch, int nz, const T* xu_new, int best_idx, const T* __restrict__ best_result,
+                                      T* xu_out, T* __restrict__ best_out) {
+    int best = best_idx;
+    if (best < 0 && best_result) best = (int)best_result[0];
+    if (best < 0 || best >= batch) best = 0;
+    const T* src = xu_new + (size_t)best * nz;
+    const size_t total = (size_t)batch * nz;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int b = (int)(e / nz), r = (int)(e - (size_t)b * nz);
+        const T v = src[r];
+        if (xu_out && !(xu_out == xu_new && b == best)) xu_out[e] = v;
+        if (best_out && b == 0) best_out[r] = v;
+    }
+}
+
 // FMA-pipe peak: 8 independent chains per thread, 2 flop per FMA
 template <typename T>
 __global__ void fma_peak_kernel(int iters, T seed, T* sink) {

@@ -61,7 +61,7 @@ class Engine:
             raise ValueError("qp_mode must be 'exact' or 'osqp'")
         self.qp_mode, self.limits = qp_mode, bool(limits)
         self.model = model
-        self.N, self.batch, self.dtype = int(N), int(batch), dtype
+        self.N, self.batch, self.dtype, self.dt = int(N), int(batch), dtype, float(dt)
         self.np_dtype = np.float64 if dtype == "fp64" else np.float32
         self.nz = 18 * self.N - 6
         if isinstance(device, str):
@@ -397,6 +397,28 @@ class Engine:
         like = f if (_is_torch(f) and f.is_cuda) else None
         self._check(self.lib.i7_resample_wrench(self._h, B, bi, pb, pf, pn, kl, flags, float(decay), po, self._stream(like)))
         return out
+
+    def broadcast_best(self, xu_new, best, inplace=False):
+        """XU_best = xu_new[best]; every lane of the returned batch = XU_best (gato_controller.py:226,249;
+        i7_broadcast_best).  best: a lane index or the result of `find_best_idx_async`.  Returns (xu_batch, xu_best)."""
+        B = self._batch_of(xu_new)
+        keep = []
+        p_new = self._in(xu_new, (B, self.nz), keep)
+        if isinstance(best, (int, np.integer)):
+            bi, pb = int(best), None
+            if not 0 <= bi < B:
+                raise ValueError(f"best lane {bi} outside the batch of {B}")
+        else:
+            bi, pb = -1, self._in(best, (1, 2), keep)
+        if inplace:
+            if not (_is_torch(xu_new) and xu_new.is_cuda and keep[0].data_ptr() == xu_new.data_ptr()):
+                raise ValueError("inplace needs a contiguous device tensor of the engine dtype")
+            out, p_out = xu_new, p_new
+        else:
+            out, p_out = self._out((B, self.nz), xu_new, keep, "bcast")
+        bo, p_bo = self._out((self.nz,), xu_new, keep, "bcast_best")
+        self._check(self.lib.i7_broadcast_best(self._h, B, p_new, bi, pb, p_out, p_bo, self._stream(xu_new)))
+        return out, bo
 
     def pack_best(self, stats, xu, index_offset=0):
         """[costs | best_cost, best_index, XU_best] on the device the inputs live on (i7_pack_best)."""

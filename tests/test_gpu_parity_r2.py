@@ -397,3 +397,78 @@ def test_resample_wrench_equals_numpy_statements(pkg, dtype):
     assert int(res_nan[0]) == -1 and torch.equal(fd, before)
     with pytest.raises(ValueError):
         e.resample_wrench(f, noise, B)
+
+
+@pytest.mark.parametrize("qp_mode", ["exact", "osqp"])
+def test_controller_tick_equals_joint_callback_statements(pkg, oracle_model, qp_mode):
+    """ControllerTick (five launches per tick, buffers bound once, the selected lane never leaves the device between
+    selection, resampling and hand-over) against GATO_Controller.joint_callback (gato_controller.py:201-256) restated
+    statement by statement over host arrays and the generic calls (each of which has its own test against the CPU
+    restatement): same np.random stream -> same lane, same control, same wrench batch at every tick of a closed loop."""
+    from oracle import rbd
+    from tests.cases import HOME
+    from indy7_mpc_b200 import ControllerTick
+    from indy7_mpc_b200.reference_traj import figure8
+    B, N, dt = 16, 32, 0.01
+    ref_traj = figure8(A_x=0.5, A_z=0.55, offset=[0.0, 0.4, 0.45], period=10, dt=dt, cycles=2)
+    ref_traj = np.concatenate([np.tile(ref_traj[0:6], 20), ref_traj])            # gato_controller.py:322-323 (shorter padding)
+    f_actual = np.array([-6.0, 2.0, -4.0, 0.0, 0.0, 0.0])
+    x_start = np.concatenate([HOME, np.zeros(6)])
+    elapsed = [0.01, 0.012, 0.009, 0.02, 0.01, 0.011, 0.01, 0.013]
+    plant = lambda x, u, h: np.hstack(rbd.rk4(oracle_model, x[:6], x[6:], u, h, f_actual))
+
+    def statements():
+        np.random.seed(11)
+        e = pkg.Engine(N=N, dt=dt, batch=B, dtype="fp64", qp_mode=qp_mode)
+        f_ext_batch = np.random.normal(0, 20.0, (B, 6))                        # :77-80
+        f_ext_batch[:, 3:] = 0.0
+        f_ext_batch[0] = 0.0
+        e.set_external_wrench(f_ext_batch)
+        XU_batch, xs_batch, goals = np.zeros((B, 18 * N - 6)), np.zeros((B, 12)), np.zeros((B, 6 * N))
+        x_last = u_last = None
+        off, x_curr, log = 0.0, x_start.copy(), []
+        for el in elapsed:
+            if x_last is None:
+                x_last, u_last = x_curr, np.zeros(6)
+            off += el / dt
+            offset = int(off)
+            goals[:, :] = ref_traj[6 * offset:6 * (offset + N)]
+            xs_batch[:, :] = x_curr
+            XU_batch[:, 0:12] = x_curr
+            e.reset(); e.reset_rho(); e.reset_lambda()
+            XU_new, _ = e.solve(XU_batch, xs_batch, goals)
+            XU_new = np.asarray(XU_new, float)
+            best = e.find_best_idx(x_last, u_last, x_curr, el, batch=B, tie_last=True)
+            fb = f_ext_batch[best, :].copy()                                       # :120-129
+            f_ext_batch[:, :] = fb
+            f_ext_batch += np.random.normal(0, 1.0, f_ext_batch.shape)
+            f_ext_batch[best, :] = fb
+            f_ext_batch[:, 3:] = 0.0
+            f_ext_batch[0] = 0.0
+            f_ext_batch *= 0.97
+            e.set_external_wrench(f_ext_batch)
+            XU_best = XU_new[best]
+            u_curr = XU_best[12:18].copy()
+            XU_batch[:, :] = XU_best
+            log.append((best, u_curr, f_ext_batch.copy(), XU_best.copy()))
+            x_last, u_last = x_curr, u_curr
+            x_curr = plant(x_curr, u_curr, el)
+        return log
+
+    ref = statements()
+    np.random.seed(11)
+    e = pkg.Engine(N=N, dt=dt, batch=B, dtype="fp64", qp_mode=qp_mode)
+    ct = ControllerTick(e, ref_traj, B, f_ext_std=20.0, f_ext_resample_std=1.0)
+    x_curr = x_start.copy()
+    picks = []
+    for t, el in enumerate(elapsed):
+        u, best = ct.tick(x_curr, el)
+        b_ref, u_ref, f_ref, xu_ref = ref[t]
+        assert best == b_ref, (t, best, b_ref)
+        assert np.array_equal(u, u_ref), (t, np.abs(u - u_ref).max())
+        assert np.array_equal(ct.f_ext_batch, f_ref)
+        assert np.array_equal(ct.XU_best, xu_ref)
+        assert np.array_equal(ct.xu.cpu().numpy(), np.tile(xu_ref, (B, 1)))      # XU_batch[:, :] = XU_best
+        picks.append(best)
+        x_curr = plant(x_curr, u, el)
+    assert len(set(picks)) > 1                                                    # the selection is not a constant
