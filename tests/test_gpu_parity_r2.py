@@ -399,8 +399,8 @@ def test_resample_wrench_equals_numpy_statements(pkg, dtype):
         e.resample_wrench(f, noise, B)
 
 
-@pytest.mark.parametrize("qp_mode", ["exact", "osqp"])
-def test_controller_tick_equals_joint_callback_statements(pkg, oracle_model, qp_mode):
+@pytest.mark.parametrize("qp_mode,dtype", [("exact", "fp64"), ("osqp", "fp64"), ("exact", "fp32")])
+def test_controller_tick_equals_joint_callback_statements(pkg, oracle_model, qp_mode, dtype):
     """ControllerTick (five launches per tick, buffers bound once, the selected lane never leaves the device between
     selection, resampling and hand-over) against GATO_Controller.joint_callback (gato_controller.py:201-256) restated
     statement by statement over host arrays and the generic calls (each of which has its own test against the CPU
@@ -419,7 +419,7 @@ def test_controller_tick_equals_joint_callback_statements(pkg, oracle_model, qp_
 
     def statements():
         np.random.seed(11)
-        e = pkg.Engine(N=N, dt=dt, batch=B, dtype="fp64", qp_mode=qp_mode)
+        e = pkg.Engine(N=N, dt=dt, batch=B, dtype=dtype, qp_mode=qp_mode)
         f_ext_batch = np.random.normal(0, 20.0, (B, 6))                        # :77-80
         f_ext_batch[:, 3:] = 0.0
         f_ext_batch[0] = 0.0
@@ -457,7 +457,7 @@ def test_controller_tick_equals_joint_callback_statements(pkg, oracle_model, qp_
 
     ref = statements()
     np.random.seed(11)
-    e = pkg.Engine(N=N, dt=dt, batch=B, dtype="fp64", qp_mode=qp_mode)
+    e = pkg.Engine(N=N, dt=dt, batch=B, dtype=dtype, qp_mode=qp_mode)
     ct = ControllerTick(e, ref_traj, B, f_ext_std=20.0, f_ext_resample_std=1.0)
     x_curr = x_start.copy()
     picks = []
