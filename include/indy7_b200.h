@@ -32,6 +32,10 @@
  *     length 18N-6.  Goals: N knots of `goal_stride` numbers (3 = [x y z]; 6 = GATO format [x y z 0 0 0],
  *     src/gato_mpc_batch.py:80-88), only the first three of each knot are read.
  *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ *   - CUDA graphs: with device pointers only, i7_solve (exact QP mode), i7_pack_best, i7_shift, i7_goal_window,
+ *     i7_sim_forward and i7_broadcast_best issue nothing but kernel launches and device-to-device copies on `stream` and
+ *     may be recorded under stream capture after one ordinary call of the same kind on the handle (first-use set-up);
+ *     the replayed graph is bit-identical to the eager calls (tests/test_gpu_parity_r2.py::test_device_tick_under_cuda_graph).
  */
 #ifndef INDY7_B200_H
 #define INDY7_B200_H

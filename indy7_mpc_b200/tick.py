@@ -80,6 +80,32 @@ class DeviceTick:
         self.select()
         self.shift()
 
+    def capture(self):
+        """solve + select + shift recorded ONCE into a CUDA graph on torch's current stream (the library's calls on
+        device buffers are capturable: launches and device-to-device copies only).  Returns `replay(tick)`: the goal
+        window of the tick (its tick number is a launch argument, so it stays an ordinary launch) followed by one graph
+        launch — bit-identical to `run(tick)`, a few microseconds less host time per tick.  Run at least one eager tick
+        first (first-use set-up of a kernel must not fall inside the capture)."""
+        stream = torch.cuda.current_stream(self._dev)
+        stream.synchronize()
+        keep = tuple(t.clone() for t in (self.xu, self.x0, self.out, self.stats, self.packed))
+        best_keep = self.best.clone()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            self.solve()
+            self.select()
+            self.shift()
+        # capturing executes nothing, but keep the state exactly as it was in case a driver version replays while instantiating
+        for dst, src in zip((self.xu, self.x0, self.out, self.stats, self.packed), keep):
+            dst.copy_(src)
+        self.best.copy_(best_keep)
+        self._graph = graph
+
+        def replay(tick):
+            self.goal(tick)
+            graph.replay()
+        return replay
+
 
 class ControllerTick:
     """`GATO_Controller.joint_callback` (gato_controller.py:201-256) without the ROS plumbing: B wrench hypotheses solve

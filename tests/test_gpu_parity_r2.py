@@ -472,3 +472,30 @@ def test_controller_tick_equals_joint_callback_statements(pkg, oracle_model, qp_
         picks.append(best)
         x_curr = plant(x_curr, u, el)
     assert len(set(picks)) > 1                                                    # the selection is not a constant
+
+
+def test_device_tick_under_cuda_graph(pkg):
+    """The tick's solve + selection + shift captured into a CUDA graph (DeviceTick.capture) and replayed: bit-identical
+    to the eager tick over a closed loop, for the CTA form and a latency (cluster) form."""
+    import torch
+    for B in (16, 300):
+        wl = bench.make_workload(B, 32)
+        ticks = []
+        for _ in range(2):
+            e = pkg.Engine(N=32, batch=B, dtype="fp64")
+            e.set_external_wrench(wl["f_ext"])
+            ticks.append(pkg.DeviceTick(e, wl["fig"], wl["offsets"], wl["xu"], wl["x0"], mode="local"))
+        eager, graphed = ticks
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            for t in range(2):
+                eager.run(t)
+                graphed.run(t)
+            replay = graphed.capture()
+            for t in range(2, 8):
+                eager.run(t)
+                replay(t)
+                s.synchronize()
+                assert torch.equal(eager.out, graphed.out) and torch.equal(eager.stats, graphed.stats), (B, t)
+                assert torch.equal(eager.packed, graphed.packed) and torch.equal(eager.xu, graphed.xu), (B, t)
+        assert torch.isfinite(graphed.out).all()
